@@ -1,0 +1,155 @@
+/*
+ * zonos_b200.h — C ABI of libzonos_b200.so, the B200 (sm_100a) hot path behind the reference's
+ * `Zonos.generate(conditioning)` / `model.autoencoder.decode(codes)` API
+ * (BreakTheBeta/Zonos_Vibes: zonos/model.py:218-315, zonos/autoencoder.py:25-27).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes only.  Every pointer named `d_*` is a DEVICE pointer owned by the
+ *     caller (e.g. `tensor.data_ptr()`); the library owns only its context arena (weights, KV pages, scratch).
+ *   - Every call returns 0 on success or a negative zb_status; `zb_last_error()` gives the text.  Nothing throws.
+ *   - `stream` is a `cudaStream_t` passed as `void*`; all work is asynchronous on that stream unless stated.
+ *   - A context is bound to one device and is not re-entrant (mirrors the reference, model.py:39-44).
+ *   - There is NO CPU fallback: without a CUDA device every compute entry point fails with ZB_ERR_CUDA.
+ *
+ * Each entry point cites the reference interface (file:line) it replaces.
+ */
+#ifndef ZONOS_B200_H
+#define ZONOS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZB_ABI_VERSION 1
+
+typedef enum {
+  ZB_OK = 0,
+  ZB_ERR_ARG = -1,      /* bad argument / unsupported shape                */
+  ZB_ERR_CUDA = -2,     /* CUDA runtime error (text in zb_last_error)      */
+  ZB_ERR_STATE = -3,    /* call sequence error (e.g. weights not finalised)*/
+  ZB_ERR_NOMEM = -4
+} zb_status;
+
+typedef enum { ZB_BF16 = 0, ZB_F32 = 1, ZB_I64 = 2, ZB_I32 = 3 } zb_dtype;
+
+/* Architecture contract = the fields of zonos/config.py:28-62 the hot path reads.  */
+typedef struct {
+  int32_t d_model;          /* BackboneConfig.d_model                         */
+  int32_t n_layer;          /* BackboneConfig.n_layer                         */
+  int32_t num_heads;        /* attn_cfg["num_heads"]                          */
+  int32_t num_heads_kv;     /* attn_cfg["num_heads_kv"]                       */
+  int32_t ffn;              /* attn_mlp_d_intermediate                        */
+  int32_t n_codebooks;      /* 9  (autoencoder.py:14)                         */
+  int32_t vocab;            /* 1026 logits per head after the pad hook (model.py:46-51) */
+  int32_t eos_token_id;     /* 1024 */
+  int32_t masked_token_id;  /* 1025 */
+  float   norm_eps;         /* BackboneConfig.norm_epsilon                    */
+  int32_t rope_table_len;   /* 16384 (backbone/_torch.py:67)                  */
+  int32_t reserved[5];
+} zb_config;
+
+/* kwargs of sample_from_logits (zonos/sampling.py:117-129). */
+typedef struct {
+  float   temperature;
+  float   top_p;
+  int32_t top_k;
+  float   min_p;
+  float   linear, conf, quad;
+  float   repetition_penalty;
+  int32_t repetition_penalty_window;
+  int32_t reserved[3];
+} zb_sampling;
+
+typedef struct zb_ctx zb_ctx;
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+int  zb_abi_version(void);
+int  zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out);
+int  zb_ctx_destroy(zb_ctx* ctx);
+const char* zb_last_error(const zb_ctx* ctx);   /* ctx may be NULL: last create() error */
+
+/* ---- weights: replaces Zonos.from_local's load_state_dict (model.py:78-88) ------------------
+ * `name` is the reference state_dict key: backbone.layers.{i}.norm.weight, ...,
+ * embeddings.{k}.weight, heads.{k}.weight (1025 or 1026 rows; padded like utils.py:12-27),
+ * and "rope.freqs_cis" = the fp32 table of backbone/_torch.py:9-15 [rope_table_len, Dh/2, 2].
+ * The data is copied into the context arena (device-to-device, on `stream`). */
+int  zb_set_tensor(zb_ctx* ctx, const char* name, const void* d_ptr, int64_t numel, int dtype, void* stream);
+int  zb_weights_finalize(zb_ctx* ctx, void* stream);          /* checks every tensor was provided */
+
+/* ---- KV cache: replaces setup_cache/allocate_inference_cache (model.py:198-202, _torch.py:64-71)
+ * rows = 2*B with classifier-free guidance.  Pages of 128 tokens, bf16, head-major inside a page. */
+int  zb_kv_alloc(zb_ctx* ctx, int rows, int max_seqlen);
+int  zb_kv_reset(zb_ctx* ctx, void* stream);                  /* seqlen_offset = lengths_per_sample = 0 */
+
+/* ---- plugin level: TorchZonosBackbone.forward (backbone/_torch.py:73-80) ---------------------
+ * d_hidden_in/out: bf16 [rows, S, d_model].  Appends S tokens to the KV cache at `seqlen_offset` and uses
+ * RoPE positions d_lengths[r] + s (int32 [rows]; NULL = seqlen_offset for every row).  Output is post-norm_f. */
+int  zb_backbone_forward(zb_ctx* ctx, const void* d_hidden_in, void* d_hidden_out, int rows, int S,
+                         int seqlen_offset, const int32_t* d_lengths, void* stream);
+
+/* ---- delay pattern (codebook_pattern.py:5-12), int64 ----------------------------------------- */
+int  zb_delay_apply(const int64_t* d_codes, int64_t* d_out, int B, int n_q, int T, int64_t mask_token, void* stream);
+int  zb_delay_revert(const int64_t* d_delayed, int64_t* d_out, int B, int n_q, int L, void* stream);
+
+/* ---- sampling (sampling.py:117-182) on given logits -------------------------------------------
+ * d_logits fp32 [B, n_q, V]; d_history int64 [B, n_q, hist_len] or NULL (= generated_tokens);
+ * d_tokens int64 [B, n_q] out; d_probs_out fp32 [B, n_q, V] or NULL: the filtered, renormalised
+ * distribution the draw is made from (for mask parity tests).  Philox4x32-10 keyed by (seed, step). */
+int  zb_sample(const float* d_logits, const int64_t* d_history, int hist_len, int64_t* d_tokens,
+               float* d_probs_out, int B, int n_q, int V, const zb_sampling* sp,
+               uint64_t seed, uint64_t step, void* stream);
+
+/* ---- logits of one forward pass: Zonos._compute_logits (model.py:103-116) ---------------------
+ * Teacher-forced step used by parity tests and by generate: embeds column `col` of d_delayed
+ * (int64 [B, n_q, L]) for rows b and B+b (model.py:141-142), runs the backbone at the current KV
+ * position, applies heads + CFG + pad mask (+ logit_bias when apply_eos_bias, model.py:266-267,280),
+ * advances the position, writes fp32 [B, n_q, vocab] to d_logits_out. */
+int  zb_decode_logits(zb_ctx* ctx, const int64_t* d_delayed, int B, int L, int col, float cfg_scale,
+                      int apply_eos_bias, float* d_logits_out, void* stream);
+
+/* ---- generation: Zonos.generate (model.py:218-315) --------------------------------------------
+ * zb_gen_begin: d_prefix bf16 [2B, Lc, d_model] (rows [0,B) cond, [B,2B) uncond, model.py:204-212);
+ *   d_delayed int64 [B, n_q, L] already delay-patterned with -1 = unknown (model.py:246-251);
+ *   prefix_cols = P+1 known leading columns.  Runs the prefill (model.py:253-264), samples without
+ *   logit_bias/repetition penalty (model.py:256) and writes column P+1.
+ * zb_gen_steps: runs up to n_steps iterations of the loop model.py:276-307 entirely on the device
+ *   (EOS wind-down and frame write-back included; no host sync inside).  compat_scatter=1 reproduces
+ *   masked_scatter_'s sequential routing, 0 = positional.
+ * zb_gen_poll: synchronises `stream` and returns loop state. */
+int  zb_gen_begin(zb_ctx* ctx, const void* d_prefix, int B, int Lc, int64_t* d_delayed, int L, int prefix_cols,
+                  float cfg_scale, const zb_sampling* sp, uint64_t seed, int compat_scatter, void* stream);
+int  zb_gen_steps(zb_ctx* ctx, int n_steps, void* stream);
+int  zb_gen_poll(zb_ctx* ctx, int* done, int* col, int32_t* h_out_len /* [B] or NULL */, void* stream);
+
+/* ---- DAC 44 kHz decoder: DACAutoencoder.decode (autoencoder.py:25-27) --------------------------
+ * Weights use the HF DacModel keys, fp32 on the device; repacked at load. */
+typedef struct zb_dac zb_dac;
+int  zb_dac_create(int device, zb_dac** out);
+int  zb_dac_destroy(zb_dac* dac);
+const char* zb_dac_last_error(const zb_dac* dac);
+int  zb_dac_set_tensor(zb_dac* dac, const char* name, const float* d_ptr, int64_t numel, void* stream);
+int  zb_dac_finalize(zb_dac* dac, void* stream);
+/* d_codes int64 [B, 9, T] in [0,1023]; d_wav fp32 [B, 1, 512*T].  impl: 0 = tcgen05 bf16 (default), 1 = SIMT fp32. */
+int  zb_dac_decode(zb_dac* dac, const int64_t* d_codes, float* d_wav, int B, int T, int impl, void* stream);
+/* debug/parity: copy an intermediate of the last decode ("latent", "conv1", "block0".."block3") as fp32
+ * [B, C, T_l] (reference layout) into d_out; returns ZB_ERR_ARG if the name is unknown. */
+int  zb_dac_get_intermediate(zb_dac* dac, const char* name, float* d_out, int64_t numel, void* stream);
+int  zb_dac_set_option(zb_dac* dac, const char* key, int value);      /* "keep_intermediates" */
+int64_t zb_dac_launch_count(const zb_dac* dac);
+
+/* ---- introspection used by bench.py (launch counting, roofline byte counts) ------------------- */
+int64_t zb_weight_bytes(const zb_ctx* ctx);            /* algorithmic weight bytes streamed per decode step */
+int64_t zb_launch_count(const zb_ctx* ctx);            /* kernels launched by this context so far (graph nodes count per replay) */
+int  zb_set_option(zb_ctx* ctx, const char* key, int value);   /* "pdl", "l2_prefetch", "graph": tuning switches */
+/* isolated device timing of one kernel family ("in_proj", "attn", "out_proj", "fc1", "fc2"), `iters` launches cycling
+ * over the layers, CUDA events on `stream`; total ms in *ms_out (synchronises).  Scratch outputs only. */
+int  zb_bench_kernel(zb_ctx* ctx, const char* name, int iters, float* ms_out, void* stream);
+/* device-timed (CUDA events on `stream`) duration of the last zb_gen_steps call, ms; <0 if none */
+float zb_last_steps_ms(zb_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZONOS_B200_H */

@@ -1,0 +1,122 @@
+"""CPU: the C-ABI library loads and exports every symbol include/zonos_b200.h declares; host-side logic; the
+multi-replica plumbing over gloo with world_size 2.  No compute calls (no GPU here)."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_symbols():
+    text = open(os.path.join(ROOT, "include", "zonos_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(zb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from zonos_vibes_b200 import _lib
+    lib = _lib.load()
+    syms = _header_symbols()
+    assert len(syms) >= 25
+    for s in syms:
+        assert hasattr(lib, s), f"{s} declared in zonos_b200.h but not exported"
+    assert set(_lib.SIGNATURES) == set(syms), set(_lib.SIGNATURES) ^ set(syms)
+    assert lib.zb_abi_version() == 1
+
+
+def test_struct_layout_matches_header():
+    from zonos_vibes_b200 import _lib
+    assert C.sizeof(_lib.ZbConfig) == 16 * 4
+    assert C.sizeof(_lib.ZbSampling) == 12 * 4
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="only meaningful without a GPU")
+def test_no_cpu_fallback_fails_loudly():
+    from zonos_vibes_b200 import _lib
+    lib = _lib.load()
+    zc = _lib.ZbConfig()
+    zc.d_model, zc.n_layer, zc.num_heads, zc.num_heads_kv, zc.ffn = 256, 1, 2, 1, 512
+    zc.n_codebooks, zc.vocab, zc.rope_table_len = 9, 1026, 16384
+    h = C.c_void_p()
+    rc = lib.zb_ctx_create(C.byref(zc), 0, C.byref(h))
+    assert rc == -2 and b"no CPU fallback" in lib.zb_last_error(None)
+    d = C.c_void_p()
+    assert lib.zb_dac_create(0, C.byref(d)) == -2
+    import zonos_vibes_b200 as z
+    with pytest.raises(_lib.ZbError):
+        z.apply_delay_pattern(torch.zeros(1, 9, 4, dtype=torch.int64), 1025)
+    with pytest.raises(_lib.ZbError):
+        z.sample_from_logits(torch.zeros(1, 9, 1026))
+
+
+def test_bad_config_rejected():
+    from zonos_vibes_b200 import _lib
+    lib = _lib.load()
+    zc = _lib.ZbConfig()
+    zc.d_model, zc.n_layer, zc.num_heads, zc.num_heads_kv, zc.ffn = 250, 1, 2, 1, 512      # not a multiple of 256
+    zc.n_codebooks, zc.vocab, zc.rope_table_len = 9, 1026, 16384
+    h = C.c_void_p()
+    assert lib.zb_ctx_create(C.byref(zc), 0, C.byref(h)) == -1
+    assert lib.zb_delay_apply(None, None, 1, 9, 4, 1025, None) == -1
+
+
+def test_config_mirror_and_backbone_state_dict_keys():
+    import zonos_oracle as zo
+    import zonos_vibes_b200 as z
+    cfg = zo.TINY_CONFIG
+    zc = z.ZonosConfig.from_dict(cfg.to_reference_dict())
+    assert zc.eos_token_id == 1024 and zc.masked_token_id == 1025 and zc.backbone.d_model == 256
+    sd = zo.synth_state_dict(cfg, 0)
+    m = z.Zonos(zc)
+    own = set(m.state_dict())
+    assert own == set(sd), (own ^ set(sd))                      # same keys as the reference
+    for k, v in m.state_dict().items():
+        assert tuple(v.shape) == tuple(sd[k].shape), k
+    assert "b200" in z.BACKBONES and z.BACKBONES["b200"].supported_architectures == ["transformer"]
+
+
+def test_shard_indices():
+    from zonos_vibes_b200.replicas import shard_indices
+    for n in (0, 1, 7, 64):
+        for w in (1, 2, 8):
+            parts = [shard_indices(n, r, w) for r in range(w)]
+            assert sorted(i for p in parts for i in p) == list(range(n))
+            assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
+
+
+_WORKER = r"""
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from zonos_vibes_b200.replicas import shard_indices, gather_ragged, max_over_ranks
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+n = 5
+local = {i: torch.full((9, 3 + i), i, dtype=torch.int64) for i in shard_indices(n, rank, world)}
+out = gather_ragged(local, n)
+m = max_over_ranks(1.0 + rank)
+assert m == float(world)
+if rank == 0:
+    assert [tuple(t.shape) for t in out] == [(9, 3 + i) for i in range(n)]
+    assert all(int(t[0, 0]) == i for i, t in enumerate(out))
+    print("GLOO_OK")
+else:
+    assert out is None
+dist.barrier()
+dist.destroy_process_group()
+"""
+
+
+def test_replica_gather_gloo_world2(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text(_WORKER)
+    r = subprocess.run(
+        [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+         "--master-port", "29533", str(script), ROOT],
+        capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "GLOO_OK" in r.stdout

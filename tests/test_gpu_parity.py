@@ -1,0 +1,283 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI, via the thin Python host) against the CPU oracle and the
+golden vectors frozen from the real reference.  Bars (BASELINE.json north_star):
+  * delay-pattern indexing and sampling masks: bit-exact;
+  * per-step logits: |a-b| <= 2e-2*|b| + 2e-2*rms(b)   (rtol 2e-2 in bf16; the rms term covers logits near zero);
+  * greedy token streams identical (a divergence is tolerated only at a step where the oracle's own top-2 gap is
+    below the logit tolerance);
+  * DAC waveform: max-abs <= 1e-2 on identical codes.
+"""
+import pytest
+import torch
+
+import dac_oracle as do
+import zonos_oracle as zo
+
+pytestmark = pytest.mark.gpu
+
+CFGS = {"tiny": zo.TINY_CONFIG, "small": zo.SMALL_CONFIG, "full": zo.FULL_CONFIG}
+_models = {}
+
+
+def make_model(cname, cuda, eos=False):
+    import zonos_vibes_b200 as z
+    key = (cname, eos)
+    if key not in _models:
+        cfg = CFGS[cname]
+        sd = zo.synth_state_dict(cfg, 0)
+        if eos:
+            from make_golden import eos_biased
+            sd = eos_biased(sd, cfg)
+        _models[key] = z.Zonos.from_state_dict(z.ZonosConfig.from_dict(cfg.to_reference_dict()), sd, cuda)
+    return _models[key]
+
+
+def assert_logits_close(got, want, what=""):
+    got, want = got.float().cpu(), want.float().cpu()
+    fin = torch.isfinite(want)
+    assert torch.equal(torch.isfinite(got), fin), f"{what}: -inf pattern differs"
+    assert torch.equal(got[~fin], want[~fin])
+    g, w = got[fin], want[fin]
+    rms = w.pow(2).mean().sqrt()
+    err = (g - w).abs()
+    tol = 2e-2 * w.abs() + 2e-2 * rms
+    worst = (err / tol).max().item()
+    assert worst <= 1.0, f"{what}: max err/tol = {worst:.3f} (max abs err {err.max().item():.4f}, rms {rms.item():.3f})"
+
+
+# ------------------------------------------------------------------------------------------------ delay pattern
+@pytest.mark.parametrize("name", ["small", "one", "empty", "big"])
+def test_delay_pattern_bit_exact(golden, cuda, name):
+    import zonos_vibes_b200 as z
+    codes = golden[f"delay.{name}.codes"].to(cuda)
+    d = z.apply_delay_pattern(codes, 1025)
+    assert torch.equal(d.cpu(), golden[f"delay.{name}.delayed"])
+    assert torch.equal(z.revert_delay_pattern(d).cpu(), golden[f"delay.{name}.reverted"])
+
+
+def test_delay_pattern_full_size_roundtrip(cuda):
+    import zonos_vibes_b200 as z
+    codes = torch.randint(0, 1024, (64, 9, 2580), device=cuda)
+    d = z.apply_delay_pattern(codes, 1025)
+    assert d.shape == (64, 9, 2589)
+    assert torch.equal(z.revert_delay_pattern(d), codes)
+    assert torch.equal(d.cpu(), zo.apply_delay_pattern(codes.cpu(), 1025))
+    k = torch.arange(9, device=cuda)
+    assert bool((d[:, k, k] == 1025).all())          # first k+1 columns of codebook k are mask tokens
+
+
+# ------------------------------------------------------------------------------------------------ sampling
+def test_sampling_masks_bit_exact(golden, cuda):
+    import zonos_vibes_b200 as z
+    logits, hist = golden["sample.logits"].to(cuda), golden["sample.history"].to(cuda)
+    for name, kw in golden["sample.cases"].items():
+        for h in (0, 1):
+            tok, pr = z.sample_from_logits(logits, generated_tokens=hist if h else None, seed=1, return_probs=True, **kw)
+            want = golden[f"sample.{name}.h{h}.probs"]
+            pr = pr.cpu()
+            assert torch.equal(pr > 0, want > 0), f"mask differs for {name} h{h}"
+            assert torch.allclose(pr, want, rtol=2e-4, atol=1e-7), f"probs differ for {name} h{h}"
+            assert bool((want.gather(-1, tok.cpu()) > 0).all()), "sampled a masked token"
+    for h in (0, 1):
+        tok = z.sample_from_logits(logits, temperature=0, generated_tokens=hist if h else None)
+        assert torch.equal(tok.cpu(), golden[f"sample.greedy.h{h}.tokens"])
+
+
+def test_sampling_draw_distribution(cuda):
+    import zonos_vibes_b200 as z
+    p = torch.tensor([0.5, 0.25, 0.125, 0.0625, 0.0625])
+    logits = torch.full((4, 9, 1026), -float("inf"))
+    logits[..., :5] = p.log()
+    logits = logits.to(cuda)
+    counts = torch.zeros(5)
+    n = 600
+    for step in range(n):
+        tok = z.sample_from_logits(logits, repetition_penalty=1.0, seed=1234, step=step)
+        counts += torch.bincount(tok.flatten().cpu(), minlength=5)[:5].float()
+    total = n * 36
+    assert counts.sum() == total
+    sigma = (p * (1 - p) * total).sqrt()
+    assert bool(((counts - p * total).abs() < 5 * sigma).all()), counts / total
+    a = z.sample_from_logits(logits, repetition_penalty=1.0, seed=7, step=3)
+    b = z.sample_from_logits(logits, repetition_penalty=1.0, seed=7, step=3)
+    assert torch.equal(a, b)                       # Philox: same (seed, step) -> same draw
+
+
+# ------------------------------------------------------------------------------------------------ logits
+@pytest.mark.parametrize("cname", ["tiny", "small"])
+def test_teacher_forced_logits(golden, cuda, cname):
+    m = make_model(cname, cuda)
+    prefix = zo.synth_prefix_conditioning(CFGS[cname], 1, 6, 1)
+    got = m.compute_logits_teacher_forced(prefix, golden[f"gen.{cname}.greedy.delayed"], 40)
+    want = golden[f"gen.{cname}.greedy.logits"]
+    for s in range(41):
+        assert_logits_close(got[s], want[s:s + 1], f"{cname} step {s}")
+
+
+def test_teacher_forced_logits_full_size(golden, cuda):
+    m = make_model("full", cuda)
+    prefix = zo.synth_prefix_conditioning(zo.FULL_CONFIG, 1, 24, 1)
+    got = m.compute_logits_teacher_forced(prefix, golden["full.delayed"], 6)
+    for s in range(7):
+        assert_logits_close(got[s], golden["full.logits"][s:s + 1], f"full step {s}")
+
+
+# ------------------------------------------------------------------------------------------------ token streams
+def _check_stream(got, want, logits, what):
+    got, want = got.cpu(), want.cpu()
+    if got.shape == want.shape and torch.equal(got, want):
+        return
+    t_min = min(got.shape[-1], want.shape[-1])
+    diff = (got[..., :t_min] != want[..., :t_min]).any(1)[0].nonzero()
+    first = int(diff[0]) if len(diff) else t_min
+    # frame f of codebook k is sampled at loop step f + k; the earliest step that can have produced the mismatch:
+    assert logits is not None, f"{what}: streams differ at frame {first}"
+    ks = (got[0, :, first] != want[0, :, first]).nonzero().flatten().tolist()
+    k = ks[0]
+    step = first + k
+    top2 = logits[step, k].topk(2).values
+    gap = float(top2[0] - top2[1])
+    assert gap < 5e-2, f"{what}: diverged at frame {first} cb {k} although the oracle's top-2 gap is {gap:.4f}"
+    assert first >= 4, f"{what}: diverged immediately (frame {first})"
+
+
+@pytest.mark.parametrize("cname", ["tiny", "small"])
+def test_greedy_stream_identical(golden, cuda, cname):
+    m = make_model(cname, cuda)
+    prefix = zo.synth_prefix_conditioning(CFGS[cname], 1, 6, 1).to(cuda)
+    out = m.generate(prefix, max_new_tokens=48, sampling_params=dict(temperature=0), progress_bar=False)
+    assert out.dtype == torch.int64 and out.shape[:2] == (1, 9)
+    _check_stream(out, golden[f"gen.{cname}.greedy.codes"], golden[f"gen.{cname}.greedy.logits"], cname)
+
+
+@pytest.mark.parametrize("cname", ["tiny", "small"])
+def test_greedy_eos_winddown(golden, cuda, cname):
+    m = make_model(cname, cuda, eos=True)
+    prefix = zo.synth_prefix_conditioning(CFGS[cname], 1, 6, 1).to(cuda)
+    out = m.generate(prefix, max_new_tokens=64, sampling_params=dict(temperature=0), progress_bar=False)
+    want = golden[f"gen.{cname}.eos.greedy.codes"]
+    assert out.shape == want.shape, (out.shape, want.shape)      # EOS at the same step, trimmed to offset-9
+    assert torch.equal(out.cpu(), want)
+
+
+def test_sampled_eos_terminates(cuda):
+    m = make_model("tiny", cuda, eos=True)
+    prefix = zo.synth_prefix_conditioning(zo.TINY_CONFIG, 1, 6, 1).to(cuda)
+    lens = []
+    for seed in range(6):
+        out = m.generate(prefix, max_new_tokens=64, sampling_params=dict(min_p=0.1), progress_bar=False, seed=seed)
+        assert int(out.max()) < 1024 and int(out.min()) >= 0
+        lens.append(out.shape[-1])
+        again = m.generate(prefix, max_new_tokens=64, sampling_params=dict(min_p=0.1), progress_bar=False, seed=seed)
+        assert torch.equal(out, again)             # seeded Philox => reproducible
+    assert min(lens) < 64, lens                    # EOS was sampled at least once and cut the utterance short
+
+
+def test_callback_abort_and_signature(cuda):
+    m = make_model("tiny", cuda)
+    prefix = zo.synth_prefix_conditioning(zo.TINY_CONFIG, 1, 6, 1).to(cuda)
+    seen = []
+
+    def cb(frame, step, max_steps):
+        seen.append((tuple(frame.shape), step, max_steps))
+        return step < 20
+
+    out = m.generate(prefix, max_new_tokens=48, sampling_params=dict(temperature=0), progress_bar=False, callback=cb)
+    assert seen[0] == ((1, 9, 1), 1, 56) and seen[-1][1] == 20
+    assert out.shape[-1] == 20 + 1 - 9            # offset - 9 with offset = 1 + 20 (model.py:311)
+
+
+def test_batch_is_independent_batch1_runs(golden, cuda):
+    m = make_model("tiny", cuda)
+    cfg = zo.TINY_CONFIG
+    p = [zo.synth_prefix_conditioning(cfg, 1, 6, s) for s in (1, 2, 3)]
+    singles = [m.generate(x.to(cuda), max_new_tokens=24, sampling_params=dict(temperature=0), progress_bar=False) for x in p]
+    batch_prefix = torch.cat([torch.cat([x[:1] for x in p]), torch.cat([x[1:] for x in p])]).to(cuda)    # cond rows, then uncond rows
+    out = m.generate(batch_prefix, max_new_tokens=24, batch_size=3, sampling_params=dict(temperature=0), progress_bar=False)
+    assert out.shape == (3, 9, 24)
+    for i in range(3):
+        assert torch.equal(out[i:i + 1], singles[i]), i
+
+
+# ------------------------------------------------------------------------------------------------ plugin boundary
+@pytest.mark.parametrize("cname", ["tiny", "small"])
+def test_backbone_plugin_forward(golden, cuda, cname):
+    import zonos_vibes_b200 as z
+    cfg = CFGS[cname]
+    zc = z.ZonosConfig.from_dict(cfg.to_reference_dict())
+    bb = z.BACKBONES["b200"](zc.backbone).to(cuda, torch.bfloat16)
+    sd = {k[len("backbone."):]: v for k, v in zo.synth_state_dict(cfg, 0).items() if k.startswith("backbone.")}
+    bb.load_state_dict(sd)
+    kv = bb.allocate_inference_cache(2, 32)
+    assert set(kv) == set(range(cfg.n_layer))
+    params = z.InferenceParams(32, 2, 0, 0, kv, torch.zeros(2, dtype=torch.int32, device=cuda))
+    x = golden[f"backbone.{cname}.x"].to(cuda)
+    y0 = bb(x[:, :8], params)
+    params.seqlen_offset += 8
+    params.lengths_per_sample[:] += 8
+    y1 = bb(x[:, 8:9], params)
+    for got, want in ((y0, golden[f"backbone.{cname}.y_prefill"]), (y1, golden[f"backbone.{cname}.y_decode"])):
+        got, want = got.float().cpu(), want.float()
+        assert got.shape == want.shape
+        err = (got - want).abs()
+        assert bool((err <= 2e-2 * want.abs() + 2e-2 * want.pow(2).mean().sqrt()).all()), err.max()
+
+
+# ------------------------------------------------------------------------------------------------ DAC
+def _dac(cuda):
+    import zonos_vibes_b200 as z
+    if "dac" not in _models:
+        _models["dac"] = z.DACAutoencoder(do.synth_dac_state_dict(2), cuda)
+    return _models["dac"]
+
+
+@pytest.mark.parametrize("name", ["b1", "b2"])
+def test_dac_simt_matches_oracle(golden, cuda, name):
+    dac = _dac(cuda)
+    dac.impl = 1
+    wav = dac.decode(golden[f"dac.{name}.codes"].to(cuda))
+    want = golden[f"dac.{name}.wav"]
+    assert wav.shape == want.shape and wav.dtype == torch.float32
+    assert (wav.cpu() - want).abs().max().item() <= 1e-3
+
+
+@pytest.mark.parametrize("name", ["b1", "b2"])
+def test_dac_tcgen05_matches_oracle(golden, cuda, name):
+    dac = _dac(cuda)
+    dac.impl = 0
+    wav = dac.decode(golden[f"dac.{name}.codes"].to(cuda))
+    want = golden[f"dac.{name}.wav"]
+    assert wav.shape == want.shape
+    assert (wav.cpu() - want).abs().max().item() <= 1e-2
+
+
+def test_dac_intermediates_tcgen05(golden, cuda):
+    dac = _dac(cuda)
+    dac.impl = 0
+    dac.set_option("keep_intermediates", 1)
+    codes = golden["dac.b1.codes"]
+    dac.decode(codes.to(cuda))
+    col = {}
+    do.dac_decode(do.synth_dac_state_dict(2), codes, col)
+    t = codes.shape[-1]
+    shapes = {"latent": (1024, t), "conv1": (1536, t), "block0": (768, 8 * t), "block1": (384, 64 * t),
+              "block2": (192, 256 * t), "block3": (96, 512 * t)}
+    try:
+        for name, (c, length) in shapes.items():
+            got = dac.intermediate(name, c, length).cpu()
+            want = col[name][0]
+            rel = (got - want).abs().max() / want.abs().max()
+            assert rel.item() < 5e-3, (name, rel.item())
+    finally:
+        dac.set_option("keep_intermediates", 0)
+
+
+def test_dac_window_equals_full_interior(cuda):
+    """Size-independent property: decoding a window reproduces the full decode away from the edges."""
+    dac = _dac(cuda)
+    dac.impl = 0
+    codes = torch.randint(0, 1024, (1, 9, 160), generator=torch.Generator().manual_seed(5)).to(cuda)
+    full = dac.decode(codes)
+    win = dac.decode(codes[..., 32:128].contiguous())
+    a = full[..., (32 + 16) * 512:(128 - 16) * 512]
+    b = win[..., 16 * 512:(96 - 16) * 512]
+    assert (a - b).abs().max().item() <= 2e-3

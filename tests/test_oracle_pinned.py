@@ -1,0 +1,115 @@
+"""CPU: the oracle (oracle/*.py) against the golden vectors frozen from the real reference (oracle/make_golden.py),
+and live against /root/reference + the installed transformers DacModel when they are present."""
+import pytest
+import torch
+
+import dac_oracle as do
+import zonos_oracle as zo
+from ref_loader import reference_available
+
+CFGS = {"tiny": zo.TINY_CONFIG, "small": zo.SMALL_CONFIG}
+
+
+@pytest.mark.parametrize("name", ["small", "one", "empty", "big"])
+def test_delay_pattern_golden(golden, name):
+    codes = golden[f"delay.{name}.codes"]
+    d = zo.apply_delay_pattern(codes, 1025)
+    assert torch.equal(d, golden[f"delay.{name}.delayed"])
+    assert torch.equal(zo.revert_delay_pattern(d), golden[f"delay.{name}.reverted"])
+    assert torch.equal(zo.revert_delay_pattern(d), codes)          # round trip
+
+
+def test_sampling_filters_golden(golden):
+    logits, hist = golden["sample.logits"], golden["sample.history"]
+    for name, kw in golden["sample.cases"].items():
+        for h in (0, 1):
+            _, pr = zo.filtered_probs(logits.clone(), generated_tokens=hist if h else None, **kw)
+            assert torch.equal(pr, golden[f"sample.{name}.h{h}.probs"]), (name, h)
+    assert torch.equal(zo.sample_from_logits(logits.clone(), temperature=0, generated_tokens=hist), golden["sample.greedy.h1.tokens"])
+    assert torch.equal(zo.sample_from_logits(logits.clone(), temperature=0), golden["sample.greedy.h0.tokens"])
+
+
+@pytest.mark.parametrize("cname", ["tiny", "small"])
+def test_generate_streams_golden(golden, cname):
+    cfg = CFGS[cname]
+    sd = zo.synth_state_dict(cfg, 0)
+    o = zo.OracleZonos(cfg, sd)
+    prefix = zo.synth_prefix_conditioning(cfg, 1, 6, 1)
+    for sname, sp in {"greedy": dict(temperature=0), "minp": dict(min_p=0.1)}.items():
+        torch.manual_seed(5)
+        out = o.generate(prefix, max_new_tokens=48, sampling_params=sp)
+        assert torch.equal(out, golden[f"gen.{cname}.{sname}.codes"]), sname
+    tf = o.teacher_forced_logits(prefix, golden[f"gen.{cname}.greedy.delayed"], 40)
+    assert torch.equal(tf, golden[f"gen.{cname}.greedy.logits"])
+
+
+@pytest.mark.parametrize("cname", ["tiny", "small"])
+def test_generate_eos_winddown_golden(golden, cname):
+    from make_golden import eos_biased
+    cfg = CFGS[cname]
+    o = zo.OracleZonos(cfg, eos_biased(zo.synth_state_dict(cfg, 0), cfg))
+    prefix = zo.synth_prefix_conditioning(cfg, 1, 6, 1)
+    for seed in (1, 2, 3):
+        torch.manual_seed(seed)
+        out = o.generate(prefix, max_new_tokens=64, sampling_params=dict(min_p=0.1))
+        assert torch.equal(out, golden[f"gen.{cname}.eos.seed{seed}.codes"]), seed
+    torch.manual_seed(0)
+    out = o.generate(prefix, max_new_tokens=64, sampling_params=dict(temperature=0))
+    assert torch.equal(out, golden[f"gen.{cname}.eos.greedy.codes"])
+
+
+@pytest.mark.parametrize("cname", ["tiny", "small"])
+def test_backbone_boundary_golden(golden, cname):
+    cfg = CFGS[cname]
+    o = zo.OracleZonos(cfg, zo.synth_state_dict(cfg, 0))
+    x = golden[f"backbone.{cname}.x"]
+    params = o.setup_cache(2, 32)
+    y0 = o.backbone(x[:, :8], params)
+    params.seqlen_offset += 8
+    params.lengths_per_sample[:] += 8
+    y1 = o.backbone(x[:, 8:9], params)
+    assert torch.equal(y0, golden[f"backbone.{cname}.y_prefill"])
+    assert torch.equal(y1, golden[f"backbone.{cname}.y_decode"])
+
+
+def test_full_size_logits_golden(golden):
+    cfg = zo.FULL_CONFIG
+    o = zo.OracleZonos(cfg, zo.synth_state_dict(cfg, 0))
+    prefix = zo.synth_prefix_conditioning(cfg, 1, 24, 1)
+    tf = o.teacher_forced_logits(prefix, golden["full.delayed"], 2)
+    assert torch.equal(tf, golden["full.logits"][:3])
+
+
+@pytest.mark.parametrize("name", ["b1", "b2"])
+def test_dac_decode_golden(golden, name):
+    wav = do.dac_decode(do.synth_dac_state_dict(2), golden[f"dac.{name}.codes"])
+    assert wav.shape == golden[f"dac.{name}.wav"].shape
+    assert torch.equal(wav, golden[f"dac.{name}.wav"])
+    assert wav.abs().max() > 0.2          # the fixture is not a trivial near-zero signal
+
+
+def test_dac_against_installed_transformers():
+    sd = do.synth_dac_state_dict(4)
+    codes = torch.randint(0, 1024, (1, 9, 12), generator=torch.Generator().manual_seed(9))
+    hf = do.load_into_hf(sd)
+    with torch.inference_mode():
+        want = hf.decode(audio_codes=codes).audio_values.unsqueeze(1).float()
+    assert torch.equal(do.dac_decode(sd, codes), want)
+
+
+@pytest.mark.skipif(not reference_available(), reason="/root/reference not present (GPU box)")
+def test_oracle_against_live_reference():
+    from ref_loader import build_reference_model
+    cfg = zo.TINY_CONFIG
+    sd = zo.synth_state_dict(cfg, 3)
+    ref, model = build_reference_model(cfg, sd)
+    o = zo.OracleZonos(cfg, sd)
+    prefix = zo.synth_prefix_conditioning(cfg, 1, 5, 2)
+    for sp in (dict(temperature=0), dict(top_k=30, top_p=0.9), dict(linear=0.5, conf=0.4, quad=0.0)):
+        torch.manual_seed(11)
+        a = model.generate(prefix, max_new_tokens=24, sampling_params=sp, progress_bar=False, disable_torch_compile=True)
+        torch.manual_seed(11)
+        b = o.generate(prefix, max_new_tokens=24, sampling_params=sp)
+        assert torch.equal(a, b), sp
+    codes = torch.randint(0, 1024, (2, 9, 11))
+    assert torch.equal(ref.pattern.apply_delay_pattern(codes, 1025), zo.apply_delay_pattern(codes, 1025))

@@ -1,0 +1,201 @@
+"""B200 backbone behind the reference's backbone plugin API (zonos/backbone/__init__.py:1-12, _torch.py:52-80).
+
+`BACKBONES["b200"] = B200ZonosBackbone` can be handed to the reference's own `Zonos(config, backbone_cls)`; the class
+keeps the reference's parameter names (`layers.{i}.norm/mixer/norm2/mlp`, `norm_f`) so the reference's
+`load_state_dict` fills it, and implements `allocate_inference_cache` / `forward` on top of the native context.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from .config import BackboneConfig, InferenceParams
+
+ROPE_TABLE_LEN = 16384       # zonos/backbone/_torch.py:67
+N_CODEBOOKS = 9              # zonos/autoencoder.py:14
+VOCAB = 1026                 # head width after the pad hook (zonos/model.py:46-51, utils.py:12-27)
+
+
+def precompute_freqs_cis(seq_len: int, n_elem: int, base: float = 10000.0) -> torch.Tensor:
+    """RoPE table [seq_len, n_elem/2, 2] fp32 = (cos, sin)(pos * base^(-2i/n_elem)); host-side setup data, built
+    with the reference's formula (zonos/backbone/_torch.py:9-15) so positions round identically."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, n_elem, 2)[: n_elem // 2].float() / n_elem))
+    angle = torch.outer(torch.arange(seq_len), inv_freq)
+    unit = torch.polar(torch.ones_like(angle), angle)          # same primitive as the reference => same roundings
+    return torch.stack([unit.real, unit.imag], dim=-1).float().contiguous()
+
+
+class NativeContext:
+    """Owns one zb_ctx (weights arena + KV pages + scratch) on one device."""
+
+    def __init__(self, cfg: BackboneConfig, device: torch.device, eos_token_id: int = 1024, masked_token_id: int = 1025):
+        if cfg.ssm_cfg:
+            raise _lib.ZbError("the 'b200' backbone in this build covers the transformer architecture (ssm_cfg must be empty)")
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _lib.ZbError("zonos_vibes_b200 needs a CUDA (sm_100) device; there is no CPU fallback")
+        zc = _lib.ZbConfig()
+        zc.d_model, zc.n_layer = cfg.d_model, cfg.n_layer
+        zc.num_heads, zc.num_heads_kv = cfg.attn_cfg["num_heads"], cfg.attn_cfg["num_heads_kv"]
+        zc.ffn, zc.n_codebooks, zc.vocab = cfg.attn_mlp_d_intermediate, N_CODEBOOKS, VOCAB
+        zc.eos_token_id, zc.masked_token_id = eos_token_id, masked_token_id
+        zc.norm_eps, zc.rope_table_len = cfg.norm_epsilon, ROPE_TABLE_LEN
+        self.zc = zc
+        self.handle = C.c_void_p()
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", idx)
+        _lib.check(self.lib.zb_ctx_create(C.byref(zc), idx, C.byref(self.handle)))
+        self.rows = 0
+        self.finalized = False
+        head_dim = cfg.d_model // zc.num_heads
+        self.set_tensor("rope.freqs_cis", precompute_freqs_cis(ROPE_TABLE_LEN, head_dim).to(self.device))
+
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                self.lib.zb_ctx_destroy(self.handle)
+                self.handle = None
+        except Exception:  # noqa: BLE001
+            pass
+
+    def check(self, rc: int) -> None:
+        _lib.check(rc, self.handle)
+
+    @property
+    def stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def set_tensor(self, name: str, t: torch.Tensor) -> None:
+        want = torch.float32 if name == "rope.freqs_cis" else torch.bfloat16
+        t = t.detach().to(self.device, want).contiguous()
+        with torch.cuda.device(self.device):
+            self.check(self.lib.zb_set_tensor(self.handle, name.encode(), t.data_ptr(), t.numel(),
+                                              _lib.ZB_F32 if want == torch.float32 else _lib.ZB_BF16, self.stream))
+            torch.cuda.current_stream(self.device).synchronize()     # `t` may be a temporary
+
+    def finalize(self) -> None:
+        with torch.cuda.device(self.device):
+            self.check(self.lib.zb_weights_finalize(self.handle, self.stream))
+        self.finalized = True
+
+    def kv_alloc(self, rows: int, max_seqlen: int) -> None:
+        with torch.cuda.device(self.device):
+            self.check(self.lib.zb_kv_alloc(self.handle, rows, max_seqlen))
+            self.check(self.lib.zb_kv_reset(self.handle, self.stream))
+        self.rows = rows
+
+    def set_option(self, key: str, value: int) -> None:
+        self.check(self.lib.zb_set_option(self.handle, key.encode(), int(value)))
+
+
+class _Norm(nn.Module):
+    def __init__(self, d):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(d))
+        self.bias = nn.Parameter(torch.zeros(d))
+
+
+class _Proj(nn.Module):
+    def __init__(self, out_f, in_f):
+        super().__init__()
+        self.weight = nn.Parameter(torch.empty(out_f, in_f).uniform_(-in_f ** -0.5, in_f ** -0.5))
+
+
+class _Mixer(nn.Module):
+    def __init__(self, cfg: BackboneConfig):
+        super().__init__()
+        h, hkv = cfg.attn_cfg["num_heads"], cfg.attn_cfg["num_heads_kv"]
+        dh = cfg.d_model // h
+        self.in_proj = _Proj((h + 2 * hkv) * dh, cfg.d_model)
+        self.out_proj = _Proj(cfg.d_model, h * dh)
+
+
+class _Mlp(nn.Module):
+    def __init__(self, cfg: BackboneConfig):
+        super().__init__()
+        self.fc1 = _Proj(2 * cfg.attn_mlp_d_intermediate, cfg.d_model)
+        self.fc2 = _Proj(cfg.d_model, cfg.attn_mlp_d_intermediate)
+
+
+class _Block(nn.Module):
+    def __init__(self, cfg: BackboneConfig):
+        super().__init__()
+        self.norm = _Norm(cfg.d_model)
+        self.mixer = _Mixer(cfg)
+        self.norm2 = _Norm(cfg.d_model)
+        self.mlp = _Mlp(cfg)
+
+
+class B200ZonosBackbone(nn.Module):
+    """Drop-in for `TorchZonosBackbone` (zonos/backbone/_torch.py:52-80): same constructor, same state_dict keys,
+    same `allocate_inference_cache` / `forward` contract.  Parameters are plain holders: the arithmetic runs in
+    libzonos_b200 from a repacked device arena that is (re)filled from them on first use."""
+
+    supported_architectures = ["transformer"]
+
+    def __init__(self, config: BackboneConfig):
+        assert not config.ssm_cfg, "This backbone implementation only supports the Transformer model."
+        super().__init__()
+        self.config = config
+        self.layers = nn.ModuleList(_Block(config) for _ in range(config.n_layer))
+        self.norm_f = _Norm(config.d_model)
+        self._ctx: NativeContext | None = None
+        self._extra_weights: dict[str, torch.Tensor] = {}
+        self.eos_token_id, self.masked_token_id = 1024, 1025
+
+    # -- native context ---------------------------------------------------------------------------
+    def native(self) -> NativeContext:
+        if self._ctx is None:
+            dev = self.norm_f.weight.device
+            ctx = NativeContext(self.config, dev, self.eos_token_id, self.masked_token_id)
+            for name, p in self.state_dict().items():
+                ctx.set_tensor("backbone." + name, p)
+            d = self.config.d_model
+            zeros = torch.zeros(VOCAB, d, dtype=torch.bfloat16, device=ctx.device)
+            for k in range(N_CODEBOOKS):      # heads/embeddings belong to `Zonos`; zero unless it provides them
+                ctx.set_tensor(f"heads.{k}.weight", self._extra_weights.get(f"heads.{k}.weight", zeros))
+                ctx.set_tensor(f"embeddings.{k}.weight", self._extra_weights.get(f"embeddings.{k}.weight", zeros))
+            ctx.finalize()
+            self._ctx = ctx
+        return self._ctx
+
+    def invalidate(self) -> None:
+        """Call after changing parameters (e.g. load_state_dict) so the arena is refilled on next use."""
+        self._ctx = None
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        self._ctx = None
+        return super()._load_from_state_dict(*args, **kwargs)
+
+    # -- plugin API --------------------------------------------------------------------------------
+    def allocate_inference_cache(self, batch_size: int, max_seqlen: int, dtype: torch.dtype = torch.bfloat16):
+        """_torch.py:64-71: returns {layer_idx: handle}.  The pages live in the native context (bf16, 128-token pages)."""
+        if dtype != torch.bfloat16:
+            raise _lib.ZbError("the B200 KV cache is bf16")
+        ctx = self.native()
+        ctx.kv_alloc(batch_size, max_seqlen)
+        return {i: ("zb_kv", i) for i in range(self.config.n_layer)}
+
+    def forward(self, hidden_states: torch.Tensor, inference_params: InferenceParams) -> torch.Tensor:
+        """_torch.py:73-80: [rows, S, d] bf16 -> [rows, S, d] (post-norm_f); appends S tokens to the KV cache at
+        `inference_params.seqlen_offset`, RoPE position = lengths_per_sample[r] + s."""
+        ctx = self.native()
+        x = hidden_states.to(torch.bfloat16).contiguous()
+        rows, s, d = x.shape
+        out = torch.empty_like(x)
+        lengths = inference_params.lengths_per_sample
+        lp = None
+        if lengths is not None:
+            lengths = lengths.to(ctx.device, torch.int32).contiguous()
+            lp = lengths.data_ptr()
+        with torch.cuda.device(ctx.device):
+            ctx.check(ctx.lib.zb_backbone_forward(ctx.handle, x.data_ptr(), out.data_ptr(), rows, s,
+                                                  int(inference_params.seqlen_offset), lp, ctx.stream))
+        return out
+
+
+BACKBONES = {"b200": B200ZonosBackbone}

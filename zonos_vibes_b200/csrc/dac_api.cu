@@ -1,0 +1,412 @@
+// C ABI of libzonos_b200.so — DAC 44 kHz decoder side (DACAutoencoder.decode, zonos/autoencoder.py:25-27).
+#include <stdarg.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "dac_simt.cuh"
+#include "dac_tc.cuh"
+
+namespace {
+
+constexpr int kNq = 9, kCodes = 1024, kCodeDim = 8, kHidden = 1024, kDecoder = 1536;
+constexpr int kStrides[4] = {8, 8, 4, 2};
+constexpr int kDil[3] = {1, 3, 9};
+
+struct RawT {
+  float* ptr = nullptr;
+  int64_t numel = 0;
+  bool provided = false;
+};
+
+struct ConvW {            // one Conv1d / ConvTranspose1d
+  std::string name;       // HF prefix, e.g. "decoder.block.0.res_unit1.conv1"
+  int Cin = 0, Cout = 0, K = 0, dil = 1, pad = 0, stride = 1;   // stride > 1 => transposed
+  float* w_kio = nullptr;   // fp32 [K][Cin][Cout]
+  __half* w_koi = nullptr;  // fp16 [K][Cout][Cin]
+  float* bias = nullptr;    // -> raw tensor
+};
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+}  // namespace
+
+struct zb_dac {
+  int device = 0;
+  ZbErr err;
+  std::map<std::string, RawT> raw;
+  bool finalized = false;
+  float* table = nullptr;           // folded RVQ tables [9][1024][1024] fp32
+  ConvW conv1, conv2;
+  ConvW convt[4];
+  ConvW ru1[4][3], ru2[4][3];       // res_unit{u}.conv1 / .conv2
+  // workspace (one utterance at a time)
+  int ws_T = 0;
+  float* f32buf[3] = {nullptr, nullptr, nullptr};
+  __half* f16buf[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  int keep = 0;
+  std::map<std::string, std::pair<float*, int64_t>> dbg;   // fp32 [C][T_l] copies (keep=1)
+  EncodeTiledFn encode = nullptr;
+  int64_t launches = 0;
+};
+
+static std::string g_dac_create_error;
+
+namespace {
+
+const float* rawp(zb_dac* d, const std::string& n) { return d->raw[n].ptr; }
+
+void declare(zb_dac* d, const std::string& n, int64_t numel) {
+  RawT t;
+  t.numel = numel;
+  d->raw[n] = t;
+}
+
+void declare_conv(zb_dac* d, ConvW& c, const std::string& name, int Cin, int Cout, int K, int dil, int stride) {
+  c.name = name; c.Cin = Cin; c.Cout = Cout; c.K = K; c.dil = dil; c.stride = stride;
+  c.pad = stride > 1 ? (stride + 1) / 2 : ((K - 1) * dil) / 2;
+  declare(d, name + ".weight", (int64_t)Cin * Cout * K);
+  declare(d, name + ".bias", Cout);
+}
+
+int dbg_store_f32(zb_dac* d, const std::string& name, const float* x_tc, int T, int C, cudaStream_t s) {
+  auto& e = d->dbg[name];
+  const int64_t n = (int64_t)T * C;
+  if (e.second != n) {
+    if (e.first) cudaFree(e.first);
+    ZB_CUDA(d->err, cudaMalloc((void**)&e.first, n * 4));
+    e.second = n;
+  }
+  k_dac_to_channel_major<<<ZB_NUM_SMS * 4, 256, 0, s>>>(x_tc, e.first, T, C);
+  return ZB_OK;
+}
+int dbg_store_f16(zb_dac* d, const std::string& name, const __half* x_tc, int T, int C, cudaStream_t s) {
+  auto& e = d->dbg[name];
+  const int64_t n = (int64_t)T * C;
+  if (e.second != n) {
+    if (e.first) cudaFree(e.first);
+    ZB_CUDA(d->err, cudaMalloc((void**)&e.first, n * 4));
+    e.second = n;
+  }
+  k_dac_f16_to_channel_major<<<ZB_NUM_SMS * 4, 256, 0, s>>>(x_tc, e.first, T, C);
+  return ZB_OK;
+}
+
+int ensure_workspace(zb_dac* d, int T) {
+  if (T <= d->ws_T) return ZB_OK;
+  ZB_CUDA(d->err, cudaDeviceSynchronize());
+  for (auto& p : d->f32buf) { if (p) cudaFree(p); p = nullptr; }
+  for (auto& p : d->f16buf) { if (p) cudaFree(p); p = nullptr; }
+  d->ws_T = 0;
+  const size_t elems = (size_t)49152 * T;    // max over levels of T_l * C_l (256T*192 = 512T*96)
+  for (auto& p : d->f16buf) ZB_CUDA(d->err, cudaMalloc((void**)&p, elems * sizeof(__half)));
+  d->ws_T = T;
+  return ZB_OK;
+}
+int ensure_workspace_f32(zb_dac* d, int T) {
+  if (d->f32buf[0] && T <= d->ws_T) return ZB_OK;
+  int rc = ensure_workspace(d, T);
+  if (rc) return rc;
+  const size_t elems = (size_t)49152 * d->ws_T;
+  for (auto& p : d->f32buf) { if (p) cudaFree(p); p = nullptr; }
+  for (auto& p : d->f32buf) ZB_CUDA(d->err, cudaMalloc((void**)&p, elems * sizeof(float)));
+  return ZB_OK;
+}
+
+// ---------------- SIMT path ----------------
+int conv_simt(zb_dac* d, const ConvW& c, const float* x, int T_in, const float* alpha, const float* residual, float* out,
+              int tanh_out, cudaStream_t s) {
+  ConvSimtParams p;
+  memset(&p, 0, sizeof(p));
+  p.x = x; p.w = c.w_kio; p.bias = c.bias; p.alpha = alpha; p.residual = residual; p.out = out;
+  p.T_in = T_in; p.T_out = T_in * c.stride; p.Cin = c.Cin; p.Cout = c.Cout; p.K = c.K; p.dil = c.dil; p.pad = c.pad; p.stride = c.stride;
+  p.tanh_out = tanh_out;
+  dim3 grid((p.T_out + DSC_TT - 1) / DSC_TT, (c.Cout + DSC_TC - 1) / DSC_TC);
+  if (c.stride > 1) k_dac_convt_simt<<<grid, 256, 0, s>>>(p);
+  else k_dac_conv_simt<<<grid, 256, 0, s>>>(p);
+  d->launches++;
+  ZB_CUDA(d->err, cudaGetLastError());
+  return ZB_OK;
+}
+
+int decode_one_simt(zb_dac* d, const long long* codes, float* wav, int T, cudaStream_t s) {
+  int rc;
+  float *a = d->f32buf[0], *b = d->f32buf[1], *y = d->f32buf[2];
+  k_dac_latent<<<T, 256, 0, s>>>(codes, d->table, a, nullptr, T, kHidden, kNq, kCodes);
+  d->launches++;
+  if (d->keep && (rc = dbg_store_f32(d, "latent", a, T, kHidden, s))) return rc;
+  if ((rc = conv_simt(d, d->conv1, a, T, nullptr, nullptr, b, 0, s))) return rc;
+  if (d->keep && (rc = dbg_store_f32(d, "conv1", b, T, kDecoder, s))) return rc;
+  std::swap(a, b);                                      // a = current activation (raw)
+  int Tl = T;
+  for (int j = 0; j < 4; ++j) {
+    const std::string bp = "decoder.block." + std::to_string(j);
+    if ((rc = conv_simt(d, d->convt[j], a, Tl, rawp(d, bp + ".snake1.alpha"), nullptr, b, 0, s))) return rc;
+    Tl *= kStrides[j];
+    std::swap(a, b);
+    for (int u = 0; u < 3; ++u) {
+      const std::string rp = bp + ".res_unit" + std::to_string(u + 1);
+      if ((rc = conv_simt(d, d->ru1[j][u], a, Tl, rawp(d, rp + ".snake1.alpha"), nullptr, y, 0, s))) return rc;
+      if ((rc = conv_simt(d, d->ru2[j][u], y, Tl, rawp(d, rp + ".snake2.alpha"), a, b, 0, s))) return rc;
+      std::swap(a, b);
+    }
+    if (d->keep && (rc = dbg_store_f32(d, "block" + std::to_string(j), a, Tl, d->convt[j].Cout, s))) return rc;
+  }
+  // final conv writes [T*512][1] == the waveform row of this utterance
+  if ((rc = conv_simt(d, d->conv2, a, Tl, rawp(d, "decoder.snake1.alpha"), nullptr, wav, 1, s))) return rc;
+  return ZB_OK;
+}
+
+// ---------------- tcgen05 path ----------------
+int make_map(zb_dac* d, CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint32_t box_rows) {
+  cuuint64_t dims[2] = {inner, rows};
+  cuuint64_t strides[1] = {inner * 2};
+  cuuint32_t box[2] = {TC_BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = d->encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return d->err.fail(ZB_ERR_CUDA, "cuTensorMapEncodeTiled failed: %d (inner=%llu rows=%llu box=%u)", (int)r,
+                                            (unsigned long long)inner, (unsigned long long)rows, box_rows);
+  return ZB_OK;
+}
+
+int pick_n_tile(int Cout) {
+  if (Cout % 256 == 0) return 256;
+  if (Cout % 192 == 0) return 192;
+  if (Cout % 128 == 0) return 128;
+  if (Cout % 96 == 0) return 96;
+  if (Cout % 64 == 0) return 64;
+  return 32;
+}
+
+int conv_tc(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half* residual, __half* out_raw, __half* out_act,
+            const float* alpha_next, cudaStream_t s) {
+  TcConvParams p;
+  memset(&p, 0, sizeof(p));
+  p.ntaps = c.stride > 1 ? 2 : c.K;
+  p.dil = c.dil; p.pad = c.pad; p.stride = c.stride;
+  p.kchunks = (c.Cin + TC_BK - 1) / TC_BK;
+  p.T_out = T_in * c.stride;
+  p.m_rows = c.stride > 1 ? T_in + 1 : T_in;
+  p.Cout = c.Cout;
+  p.n_tile = pick_n_tile(c.Cout);
+  p.tmem_cols = p.n_tile <= 32 ? 32 : p.n_tile <= 64 ? 64 : p.n_tile <= 128 ? 128 : 256;
+  const int stage_bytes = TC_A_BYTES + p.n_tile * 128;
+  int stages = (108 * 1024) / stage_bytes;               // two CTAs per SM
+  if (stages < 2) stages = 2;
+  if (stages > 8) stages = 8;
+  p.stages = stages;
+  p.bias = c.bias; p.residual = residual; p.out_raw = out_raw; p.out_act = out_act; p.alpha_next = alpha_next;
+  CUtensorMap mx, mw;
+  int rc;
+  if ((rc = make_map(d, &mx, x, c.Cin, T_in, TC_BM))) return rc;
+  if ((rc = make_map(d, &mw, c.w_koi, c.Cin, (uint64_t)c.K * c.Cout, p.n_tile))) return rc;
+  const size_t smem = 1024 + (size_t)stages * stage_bytes + 256;
+  dim3 grid((p.m_rows + TC_BM - 1) / TC_BM, c.Cout / p.n_tile, c.stride > 1 ? c.stride : 1);
+  k_dac_conv_tc<<<grid, TC_THREADS, smem, s>>>(mx, mw, p);
+  d->launches++;
+  ZB_CUDA(d->err, cudaGetLastError());
+  return ZB_OK;
+}
+
+int decode_one_tc(zb_dac* d, const long long* codes, float* wav, int T, cudaStream_t s) {
+  int rc;
+  __half *A = d->f16buf[0], *R = d->f16buf[1], *Y = d->f16buf[2], *A2 = d->f16buf[3], *R2 = d->f16buf[4];
+  const bool keep = d->keep != 0;
+  // latent (raw, fp16) -> conv1 -> act = snake(., block0.snake1)
+  k_dac_latent<<<T, 256, 0, s>>>(codes, d->table, nullptr, R, T, kHidden, kNq, kCodes);
+  d->launches++;
+  if (keep && (rc = dbg_store_f16(d, "latent", R, T, kHidden, s))) return rc;
+  if ((rc = conv_tc(d, d->conv1, R, T, nullptr, keep ? R2 : nullptr, A, rawp(d, "decoder.block.0.snake1.alpha"), s))) return rc;
+  if (keep && (rc = dbg_store_f16(d, "conv1", R2, T, kDecoder, s))) return rc;
+  int Tl = T;
+  for (int j = 0; j < 4; ++j) {
+    const std::string bp = "decoder.block." + std::to_string(j);
+    // A (snaked) -> ConvT -> R (raw, residual of unit 1), A2 = snake(., ru1.snake1)
+    if ((rc = conv_tc(d, d->convt[j], A, Tl, nullptr, R, A2, rawp(d, bp + ".res_unit1.snake1.alpha"), s))) return rc;
+    Tl *= kStrides[j];
+    std::swap(A, A2);
+    for (int u = 0; u < 3; ++u) {
+      const std::string rp = bp + ".res_unit" + std::to_string(u + 1);
+      // conv1 (k7, dilated): A -> Y = snake(., snake2)
+      if ((rc = conv_tc(d, d->ru1[j][u], A, Tl, nullptr, nullptr, Y, rawp(d, rp + ".snake2.alpha"), s))) return rc;
+      // conv2 (k1) + residual R -> R2 (raw, only if a later unit needs it) and A2 = snake(., next alpha)
+      std::string next_alpha;
+      if (u < 2) next_alpha = bp + ".res_unit" + std::to_string(u + 2) + ".snake1.alpha";
+      else if (j < 3) next_alpha = "decoder.block." + std::to_string(j + 1) + ".snake1.alpha";
+      else next_alpha = "decoder.snake1.alpha";
+      const bool need_raw = (u < 2) || keep;
+      if ((rc = conv_tc(d, d->ru2[j][u], Y, Tl, R, need_raw ? R2 : nullptr, A2, rawp(d, next_alpha), s))) return rc;
+      std::swap(A, A2);
+      std::swap(R, R2);
+    }
+    if (keep && (rc = dbg_store_f16(d, "block" + std::to_string(j), R, Tl, d->convt[j].Cout, s))) return rc;
+  }
+  // final Conv1d(96 -> 1, k7) + tanh on the snaked activation
+  const ConvW& c = d->conv2;
+  float bias_h = 0.f;
+  ZB_CUDA(d->err, cudaMemcpyAsync(&bias_h, c.bias, 4, cudaMemcpyDeviceToHost, s));
+  ZB_CUDA(d->err, cudaStreamSynchronize(s));
+  k_dac_final_conv<<<ZB_NUM_SMS * 8, 256, 0, s>>>(A, c.w_kio, bias_h, wav, Tl, c.Cin, c.K, c.pad);
+  d->launches++;
+  ZB_CUDA(d->err, cudaGetLastError());
+  return ZB_OK;
+}
+
+}  // namespace
+
+// =============================================================================================
+extern "C" {
+
+const char* zb_dac_last_error(const zb_dac* d) { return d ? d->err.msg.c_str() : g_dac_create_error.c_str(); }
+
+int zb_dac_create(int device, zb_dac** out) {
+  if (!out) return ZB_ERR_ARG;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= device) {
+    g_dac_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (libzonos_b200 has no CPU fallback)";
+    return ZB_ERR_CUDA;
+  }
+  cudaSetDevice(device);
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, device);
+  if (prop.major != 10) { g_dac_create_error = "libzonos_b200 is built for sm_100a only"; return ZB_ERR_CUDA; }
+  zb_dac* d = new zb_dac();
+  d->device = device;
+  for (int k = 0; k < kNq; ++k) {
+    const std::string q = "quantizer.quantizers." + std::to_string(k);
+    declare(d, q + ".codebook.weight", (int64_t)kCodes * kCodeDim);
+    declare(d, q + ".out_proj.weight", (int64_t)kHidden * kCodeDim);
+    declare(d, q + ".out_proj.bias", kHidden);
+  }
+  declare_conv(d, d->conv1, "decoder.conv1", kHidden, kDecoder, 7, 1, 1);
+  int C = kDecoder;
+  for (int j = 0; j < 4; ++j) {
+    const std::string bp = "decoder.block." + std::to_string(j);
+    declare(d, bp + ".snake1.alpha", C);
+    declare_conv(d, d->convt[j], bp + ".conv_t1", C, C / 2, 2 * kStrides[j], 1, kStrides[j]);
+    C /= 2;
+    for (int u = 0; u < 3; ++u) {
+      const std::string rp = bp + ".res_unit" + std::to_string(u + 1);
+      declare(d, rp + ".snake1.alpha", C);
+      declare_conv(d, d->ru1[j][u], rp + ".conv1", C, C, 7, kDil[u], 1);
+      declare(d, rp + ".snake2.alpha", C);
+      declare_conv(d, d->ru2[j][u], rp + ".conv2", C, C, 1, 1, 1);
+    }
+  }
+  declare(d, "decoder.snake1.alpha", C);
+  declare_conv(d, d->conv2, "decoder.conv2", C, 1, 7, 1, 1);
+  // driver entry point for tensor-map encoding (no -lcuda link dependency)
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+    g_dac_create_error = "cuTensorMapEncodeTiled not available from the driver";
+    delete d;
+    return ZB_ERR_CUDA;
+  }
+  d->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  *out = d;
+  return ZB_OK;
+}
+
+int zb_dac_destroy(zb_dac* d) {
+  if (!d) return ZB_OK;
+  cudaSetDevice(d->device);
+  cudaDeviceSynchronize();
+  for (auto& kv : d->raw) if (kv.second.ptr) cudaFree(kv.second.ptr);
+  for (auto& kv : d->dbg) if (kv.second.first) cudaFree(kv.second.first);
+  if (d->table) cudaFree(d->table);
+  std::vector<ConvW*> all = {&d->conv1, &d->conv2};
+  for (int j = 0; j < 4; ++j) { all.push_back(&d->convt[j]); for (int u = 0; u < 3; ++u) { all.push_back(&d->ru1[j][u]); all.push_back(&d->ru2[j][u]); } }
+  for (ConvW* c : all) { if (c->w_kio) cudaFree(c->w_kio); if (c->w_koi) cudaFree(c->w_koi); }
+  for (auto& p : d->f32buf) if (p) cudaFree(p);
+  for (auto& p : d->f16buf) if (p) cudaFree(p);
+  delete d;
+  return ZB_OK;
+}
+
+int zb_dac_set_tensor(zb_dac* d, const char* name, const float* d_ptr, int64_t numel, void* stream) {
+  if (!d || !name || !d_ptr) return ZB_ERR_ARG;
+  auto it = d->raw.find(name);
+  if (it == d->raw.end()) return d->err.fail(ZB_ERR_ARG, "unknown DAC tensor '%s'", name);
+  RawT& t = it->second;
+  if (numel != t.numel) return d->err.fail(ZB_ERR_ARG, "DAC tensor '%s': numel %lld, expected %lld", name, (long long)numel, (long long)t.numel);
+  ZB_CUDA(d->err, cudaSetDevice(d->device));
+  if (!t.ptr) ZB_CUDA(d->err, cudaMalloc((void**)&t.ptr, (size_t)numel * 4));
+  ZB_CUDA(d->err, cudaMemcpyAsync(t.ptr, d_ptr, (size_t)numel * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  t.provided = true;
+  d->finalized = false;
+  return ZB_OK;
+}
+
+int zb_dac_finalize(zb_dac* d, void* stream) {
+  if (!d) return ZB_ERR_ARG;
+  for (auto& kv : d->raw)
+    if (!kv.second.provided) return d->err.fail(ZB_ERR_STATE, "DAC tensor '%s' was not provided", kv.first.c_str());
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(d->err, cudaSetDevice(d->device));
+  if (!d->table) ZB_CUDA(d->err, cudaMalloc((void**)&d->table, (size_t)kNq * kCodes * kHidden * 4));
+  for (int k = 0; k < kNq; ++k) {
+    const std::string q = "quantizer.quantizers." + std::to_string(k);
+    k_dac_fold<<<kCodes, 256, 0, s>>>(rawp(d, q + ".codebook.weight"), rawp(d, q + ".out_proj.weight"), rawp(d, q + ".out_proj.bias"),
+                                      d->table + (size_t)k * kCodes * kHidden, kHidden, kCodes, kCodeDim);
+  }
+  std::vector<ConvW*> all = {&d->conv1, &d->conv2};
+  for (int j = 0; j < 4; ++j) { all.push_back(&d->convt[j]); for (int u = 0; u < 3; ++u) { all.push_back(&d->ru1[j][u]); all.push_back(&d->ru2[j][u]); } }
+  for (ConvW* c : all) {
+    const size_t n = (size_t)c->Cin * c->Cout * c->K;
+    if (!c->w_kio) ZB_CUDA(d->err, cudaMalloc((void**)&c->w_kio, n * 4));
+    if (!c->w_koi) ZB_CUDA(d->err, cudaMalloc((void**)&c->w_koi, n * 2));
+    c->bias = d->raw[c->name + ".bias"].ptr;
+    k_dac_repack<<<ZB_NUM_SMS * 4, 256, 0, s>>>(rawp(d, c->name + ".weight"), c->w_kio, c->w_koi, c->Cout, c->Cin, c->K, c->stride > 1 ? 1 : 0);
+  }
+  ZB_CUDA(d->err, cudaGetLastError());
+  ZB_CUDA(d->err, cudaStreamSynchronize(s));
+  // opt-in to large dynamic smem for the tensor-core kernel
+  ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  d->finalized = true;
+  return ZB_OK;
+}
+
+int zb_dac_decode(zb_dac* d, const int64_t* d_codes, float* d_wav, int B, int T, int impl, void* stream) {
+  if (!d || !d_codes || !d_wav || B < 0 || T < 0) return ZB_ERR_ARG;
+  if (!d->finalized) return d->err.fail(ZB_ERR_STATE, "zb_dac_finalize first");
+  if (B == 0 || T == 0) return ZB_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(d->err, cudaSetDevice(d->device));
+  int rc = impl == 1 ? ensure_workspace_f32(d, T) : ensure_workspace(d, T);
+  if (rc) return rc;
+  for (int b = 0; b < B; ++b) {
+    const long long* codes = reinterpret_cast<const long long*>(d_codes) + (size_t)b * kNq * T;
+    float* wav = d_wav + (size_t)b * 512 * T;
+    rc = impl == 1 ? decode_one_simt(d, codes, wav, T, s) : decode_one_tc(d, codes, wav, T, s);
+    if (rc) return rc;
+  }
+  return ZB_OK;
+}
+
+int zb_dac_get_intermediate(zb_dac* d, const char* name, float* d_out, int64_t numel, void* stream) {
+  if (!d || !name || !d_out) return ZB_ERR_ARG;
+  auto it = d->dbg.find(name);
+  if (it == d->dbg.end() || !it->second.first) return d->err.fail(ZB_ERR_ARG, "no intermediate '%s' (set keep=1 and decode first)", name);
+  if (numel != it->second.second) return d->err.fail(ZB_ERR_ARG, "intermediate '%s' has %lld elements", name, (long long)it->second.second);
+  ZB_CUDA(d->err, cudaMemcpyAsync(d_out, it->second.first, (size_t)numel * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return ZB_OK;
+}
+
+int zb_dac_set_option(zb_dac* d, const char* key, int value) {
+  if (!d || !key) return ZB_ERR_ARG;
+  if (std::string(key) == "keep_intermediates") { d->keep = value; return ZB_OK; }
+  return d->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
+}
+
+int64_t zb_dac_launch_count(const zb_dac* d) { return d ? d->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,789 @@
+// C ABI of libzonos_b200.so — backbone/generation side.  See include/zonos_b200.h for the contract.
+#include <stdarg.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "attention_kernels.cuh"
+#include "decode_kernels.cuh"
+#include "sample_kernels.cuh"
+
+int ZbErr::fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  msg = buf;
+  return code;
+}
+
+static std::string g_create_error;
+
+namespace {
+
+struct Slot {
+  void* ptr = nullptr;
+  int64_t numel = 0;
+  int dtype = ZB_BF16;
+  bool provided = false;
+  int64_t alt_numel = 0;   // heads: 1025 rows accepted, pad row zeroed
+};
+
+struct LayerW {
+  bf16 *ln1_w, *ln1_b, *w_in, *w_out, *ln2_w, *ln2_b, *w_fc1, *w_fc2;
+};
+
+struct Pass {   // one GEMV launch covers template rows mapped by (base0, base1, lim0, lim1)
+  int R, base0, base1, lim0, lim1;
+};
+
+}  // namespace
+
+struct zb_ctx {
+  zb_config cfg{};
+  int device = 0;
+  ZbErr err;
+  // weights
+  char* arena = nullptr;
+  size_t arena_bytes = 0;
+  std::map<std::string, Slot> slots;
+  std::vector<LayerW> layers;
+  bf16 *normf_w = nullptr, *normf_b = nullptr, *emb = nullptr, *heads = nullptr;
+  float* rope = nullptr;
+  bool finalized = false;
+  int64_t step_weight_bytes = 0;
+  // kv cache
+  bf16* kv = nullptr;
+  size_t kv_layer_elems = 0;
+  int* page_table = nullptr;
+  int rows = 0, max_pages = 0, max_seqlen = 0;
+  // scratch
+  bf16 *x = nullptr, *q = nullptr, *y = nullptr, *h = nullptr;
+  float *logits = nullptr, *part_o = nullptr, *part_ml = nullptr;
+  int* counters = nullptr;
+  int nsplit = 1;
+  long long* tokens = nullptr;
+  int *remaining = nullptr, *stopping = nullptr, *out_len = nullptr, *rope_pos = nullptr;
+  ZbDevState* st = nullptr;
+  // generation
+  long long* delayed = nullptr;
+  int B = 0, L = 0;
+  cudaGraphExec_t graph = nullptr;
+  int graph_nodes = 0;
+  int graph_B = -1, graph_L = -1;
+  long long* graph_delayed = nullptr;
+  // options
+  int opt_pdl = 1, opt_l2_prefetch_mb = 0, opt_graph = 1;
+  int64_t launches = 0;
+  bool counting = true;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool ev_valid = false;
+  cudaStream_t cap_stream = nullptr;   // capture happens here: the caller's stream may be the legacy default stream
+};
+
+namespace {
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// -------------------------------------------------------------------------------------------
+// launch helper: optional programmatic-dependent-launch attribute on every kernel
+// -------------------------------------------------------------------------------------------
+template <typename... KArgs, typename... Args>
+cudaError_t launch(zb_ctx* c, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  if (c->opt_pdl) {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  if (c->counting) c->launches += 1;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+typedef void (*GemvKernel)(const GemvParams);
+
+template <int EPI>
+GemvKernel gemv_kernel_for(int R) {
+  switch (R) {
+    case 2: return k_gemv<2, EPI>;
+    case 4: return k_gemv<4, EPI>;
+    case 6: return k_gemv<6, EPI>;
+    case 8: return k_gemv<8, EPI>;
+  }
+  return nullptr;
+}
+GemvKernel gemv_kernel(int R, int epi) {
+  switch (epi) {
+    case EPI_QKV: return gemv_kernel_for<EPI_QKV>(R);
+    case EPI_RESID: return gemv_kernel_for<EPI_RESID>(R);
+    case EPI_SWIGLU: return gemv_kernel_for<EPI_SWIGLU>(R);
+    case EPI_HEADS: return gemv_kernel_for<EPI_HEADS>(R);
+  }
+  return nullptr;
+}
+size_t gemv_smem(int R, int K) { return (size_t)R * K * sizeof(bf16) + (size_t)(GEMV_THREADS / 32) * R * sizeof(float); }
+
+typedef void (*AttnKernel)(const AttnParams);
+AttnKernel attn_kernel(int G) {
+  switch (G) {
+    case 1: return k_attn_decode<1>;
+    case 2: return k_attn_decode<2>;
+    case 4: return k_attn_decode<4>;
+    case 8: return k_attn_decode<8>;
+  }
+  return nullptr;
+}
+
+std::vector<Pass> cfg_passes(int B) {       // cond/uncond pairs of up to 4 utterances per pass
+  std::vector<Pass> v;
+  for (int b0 = 0; b0 < B; b0 += 4) {
+    const int nb = B - b0 < 4 ? B - b0 : 4;
+    v.push_back(Pass{2 * nb, b0, B + b0, B, 2 * B});
+  }
+  return v;
+}
+std::vector<Pass> plain_passes(int rows) {  // consecutive rows, 8 per pass
+  std::vector<Pass> v;
+  for (int r0 = 0; r0 < rows; r0 += 8) {
+    int n = rows - r0 < 8 ? rows - r0 : 8;
+    int R = (n + 1) & ~1;
+    v.push_back(Pass{R, r0, r0 + R / 2, rows, rows});
+  }
+  return v;
+}
+
+struct NextW {   // head of the next weight matrix, for the optional L2 prefetch
+  const bf16* ptr = nullptr;
+  size_t bytes = 0;
+  size_t second_off = 0;   // byte offset of the paired half (fc1 gate rows), 0 = single range
+};
+
+void set_prefetch(zb_ctx* c, GemvParams& p, const NextW& nx) {
+  p.pf0 = p.pf1 = nullptr;
+  p.pf_bytes = 0;
+  if (c->opt_l2_prefetch_mb <= 0 || nx.ptr == nullptr) return;
+  size_t budget = (size_t)c->opt_l2_prefetch_mb << 20;
+  const int nr = nx.second_off ? 2 : 1;
+  size_t per = nx.bytes / nr;
+  if (per > budget / nr) per = budget / nr;
+  per = per / (16 * ZB_NUM_SMS * GEMV_CTAS_PER_SM) * (16 * ZB_NUM_SMS * GEMV_CTAS_PER_SM);
+  if (per == 0) return;
+  p.pf0 = reinterpret_cast<const char*>(nx.ptr);
+  p.pf1 = nx.second_off ? p.pf0 + nx.second_off : nullptr;
+  p.pf_bytes = (unsigned)per;
+}
+
+GemvParams base_params(zb_ctx* c, const Pass& ps) {
+  GemvParams p;
+  memset(&p, 0, sizeof(p));
+  p.base0 = ps.base0; p.base1 = ps.base1; p.lim0 = ps.lim0; p.lim1 = ps.lim1;
+  p.st = c->st;
+  p.eps = c->cfg.norm_eps;
+  return p;
+}
+
+cudaError_t launch_gemv(zb_ctx* c, int epi, const Pass& ps, const GemvParams& p, cudaStream_t s) {
+  GemvKernel k = gemv_kernel(ps.R, epi);
+  return launch(c, k, dim3(ZB_NUM_SMS * GEMV_CTAS_PER_SM), dim3(GEMV_THREADS), gemv_smem(ps.R, p.K), s, p);
+}
+
+// all transformer layers for the current token (x in c->x, positions in device state)
+cudaError_t enqueue_layers(zb_ctx* c, const std::vector<Pass>& passes, cudaStream_t s, bool heads_follow) {
+  const zb_config& g = c->cfg;
+  const int d = g.d_model, H = g.num_heads, Hkv = g.num_heads_kv, F = g.ffn;
+  const int q_size = H * ZB_DH, kv_size = Hkv * ZB_DH;
+  cudaError_t e;
+  for (int l = 0; l < g.n_layer; ++l) {
+    const LayerW& w = c->layers[l];
+    bf16* kv_layer = c->kv + (size_t)l * c->kv_layer_elems;
+    for (const Pass& ps : passes) {   // LN1 + in_proj + RoPE + KV append
+      GemvParams p = base_params(c, ps);
+      p.W = w.w_in; p.K = d; p.n_tasks = (q_size + 2 * kv_size) / 2; p.row0_mul = 2; p.row1_off = 1;
+      p.x = c->x; p.ln_w = w.ln1_w; p.ln_b = w.ln1_b;
+      p.out = c->q; p.out_stride = q_size;
+      p.kv_layer = kv_layer; p.page_table = c->page_table; p.max_pages = c->max_pages; p.Hkv = Hkv;
+      p.q_size = q_size; p.kv_size = kv_size; p.rope = c->rope; p.rope_pos = c->rope_pos;
+      set_prefetch(c, p, NextW{w.w_out, (size_t)d * q_size * 2, 0});
+      if ((e = launch_gemv(c, EPI_QKV, ps, p, s)) != cudaSuccess) return e;
+    }
+    {
+      AttnParams a;
+      memset(&a, 0, sizeof(a));
+      a.q = c->q; a.kv_layer = kv_layer; a.page_table = c->page_table; a.max_pages = c->max_pages;
+      a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
+      a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
+      if ((e = launch(c, attn_kernel(H / Hkv), dim3(c->nsplit, Hkv, c->rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
+    }
+    for (const Pass& ps : passes) {   // out_proj + residual
+      GemvParams p = base_params(c, ps);
+      p.W = w.w_out; p.K = q_size; p.n_tasks = d / 2; p.row0_mul = 2; p.row1_off = 1;
+      p.x = c->y; p.out = c->x; p.out_stride = d;
+      set_prefetch(c, p, NextW{w.w_fc1, (size_t)2 * F * d * 2, (size_t)F * d * 2});
+      if ((e = launch_gemv(c, EPI_RESID, ps, p, s)) != cudaSuccess) return e;
+    }
+    for (const Pass& ps : passes) {   // LN2 + fc1 + SwiGLU
+      GemvParams p = base_params(c, ps);
+      p.W = w.w_fc1; p.K = d; p.n_tasks = F; p.row0_mul = 1; p.row1_off = F;
+      p.x = c->x; p.ln_w = w.ln2_w; p.ln_b = w.ln2_b;
+      p.out = c->h; p.out_stride = F;
+      set_prefetch(c, p, NextW{w.w_fc2, (size_t)d * F * 2, 0});
+      if ((e = launch_gemv(c, EPI_SWIGLU, ps, p, s)) != cudaSuccess) return e;
+    }
+    for (const Pass& ps : passes) {   // fc2 + residual
+      GemvParams p = base_params(c, ps);
+      p.W = w.w_fc2; p.K = F; p.n_tasks = d / 2; p.row0_mul = 2; p.row1_off = 1;
+      p.x = c->h; p.out = c->x; p.out_stride = d;
+      NextW nx;
+      if (l + 1 < g.n_layer) nx = NextW{c->layers[l + 1].w_in, (size_t)(q_size + 2 * kv_size) * d * 2, 0};
+      else if (heads_follow) nx = NextW{c->heads, (size_t)g.n_codebooks * g.vocab * d * 2, 0};
+      set_prefetch(c, p, nx);
+      if ((e = launch_gemv(c, EPI_RESID, ps, p, s)) != cudaSuccess) return e;
+    }
+  }
+  return cudaSuccess;
+}
+
+cudaError_t enqueue_heads(zb_ctx* c, const std::vector<Pass>& passes, float* logits, cudaStream_t s) {
+  const zb_config& g = c->cfg;
+  cudaError_t e;
+  for (const Pass& ps : passes) {
+    GemvParams p = base_params(c, ps);
+    p.W = c->heads; p.K = g.d_model; p.n_tasks = g.n_codebooks * g.vocab / 2; p.row0_mul = 2; p.row1_off = 1;
+    p.x = c->x; p.ln_w = c->normf_w; p.ln_b = c->normf_b;
+    p.logits = logits; p.n_q = g.n_codebooks; p.V = g.vocab; p.eos = g.eos_token_id;
+    const LayerW& w0 = c->layers[0];
+    set_prefetch(c, p, NextW{w0.w_in, (size_t)(g.num_heads + 2 * g.num_heads_kv) * ZB_DH * g.d_model * 2, 0});
+    if ((e = launch_gemv(c, EPI_HEADS, ps, p, s)) != cudaSuccess) return e;
+  }
+  return cudaSuccess;
+}
+
+// one full decode-loop iteration (model.py:276-301) — the body that is graph-captured
+cudaError_t enqueue_decode_step(zb_ctx* c, cudaStream_t s) {
+  const zb_config& g = c->cfg;
+  cudaError_t e;
+  const std::vector<Pass> passes = cfg_passes(c->B);
+  int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
+  if ((e = launch(c, k_embed, dim3(c->B), dim3(thr), 0, s, (const bf16*)c->emb, (const long long*)c->delayed, c->x,
+                  g.d_model, g.n_codebooks, g.vocab, (const ZbDevState*)c->st)) != cudaSuccess) return e;
+  if ((e = enqueue_layers(c, passes, s, true)) != cudaSuccess) return e;
+  if ((e = enqueue_heads(c, passes, c->logits, s)) != cudaSuccess) return e;
+  SampleParams sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.logits = c->logits; sp.history = c->delayed; sp.hist_stride = c->L; sp.tokens = c->tokens;
+  sp.n_q = g.n_codebooks; sp.V = g.vocab; sp.st = c->st;
+  if ((e = launch(c, k_sample, dim3(g.n_codebooks, c->B), dim3(SMP_THREADS), 0, s, sp)) != cudaSuccess) return e;
+  UpdateParams up;
+  memset(&up, 0, sizeof(up));
+  up.st = c->st; up.delayed = c->delayed; up.tokens = c->tokens; up.remaining = c->remaining; up.stopping = c->stopping;
+  up.out_len = c->out_len; up.rope_pos = c->rope_pos; up.rows = 2 * c->B; up.n_q = g.n_codebooks;
+  up.eos = g.eos_token_id; up.mask = g.masked_token_id;
+  int ub = c->B < 32 ? 32 : (c->B + 31) / 32 * 32;
+  if (ub > 1024) ub = 1024;
+  if ((e = launch(c, k_update, dim3(1), dim3(ub), 0, s, up)) != cudaSuccess) return e;
+  return cudaSuccess;
+}
+
+void drop_graph(zb_ctx* c) {
+  if (c->graph) { cudaGraphExecDestroy(c->graph); c->graph = nullptr; }
+  c->graph_nodes = 0;
+}
+
+void free_kv(zb_ctx* c) {
+  drop_graph(c);
+  void* ptrs[] = {c->kv, c->page_table, c->x, c->q, c->y, c->h, c->logits, c->part_o, c->part_ml, c->counters,
+                  c->tokens, c->remaining, c->stopping, c->out_len, c->rope_pos};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  c->kv = nullptr; c->page_table = nullptr; c->x = c->q = c->y = c->h = nullptr; c->logits = c->part_o = c->part_ml = nullptr;
+  c->counters = nullptr; c->tokens = nullptr; c->remaining = c->stopping = c->out_len = c->rope_pos = nullptr;
+  c->rows = 0;
+}
+
+}  // namespace
+
+// =============================================================================================
+extern "C" {
+
+int zb_abi_version(void) { return ZB_ABI_VERSION; }
+
+const char* zb_last_error(const zb_ctx* ctx) { return ctx ? ctx->err.msg.c_str() : g_create_error.c_str(); }
+
+int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) {
+  ZbErr tmp;
+  auto bad = [&](int code, const std::string& m) { g_create_error = m; return code; };
+  if (!cfg || !out) return bad(ZB_ERR_ARG, "null argument");
+  if (cfg->d_model <= 0 || cfg->d_model % 256 != 0 || cfg->d_model > GEMV_MAX_LN_DIM)
+    return bad(ZB_ERR_ARG, "d_model must be a multiple of 256 and <= 2048");
+  if (cfg->num_heads <= 0 || cfg->d_model != cfg->num_heads * ZB_DH) return bad(ZB_ERR_ARG, "head_dim must be 128");
+  if (cfg->num_heads_kv <= 0 || cfg->num_heads % cfg->num_heads_kv != 0) return bad(ZB_ERR_ARG, "num_heads % num_heads_kv != 0");
+  const int G = cfg->num_heads / cfg->num_heads_kv;
+  if (!(G == 1 || G == 2 || G == 4 || G == 8)) return bad(ZB_ERR_ARG, "GQA group size must be 1, 2, 4 or 8");
+  if (cfg->ffn <= 0 || cfg->ffn % 256 != 0) return bad(ZB_ERR_ARG, "ffn must be a multiple of 256");
+  if (cfg->n_codebooks <= 0 || cfg->n_codebooks > 16 || cfg->vocab % 2 != 0 || cfg->vocab > SMP_MAXV)
+    return bad(ZB_ERR_ARG, "n_codebooks in [1,16], vocab even and <= 2048");
+  if (gemv_smem(8, cfg->ffn) > 227 * 1024) return bad(ZB_ERR_ARG, "ffn too large for the staged-activation GEMV");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= device)
+    return bad(ZB_ERR_CUDA, std::string("no CUDA device ") + std::to_string(device) + ": " + cudaGetErrorString(e) +
+                                " (libzonos_b200 has no CPU fallback)");
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return bad(ZB_ERR_CUDA, cudaGetErrorString(e));
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, device);
+  if (prop.major != 10) return bad(ZB_ERR_CUDA, "libzonos_b200 is built for sm_100a only");
+
+  zb_ctx* c = new zb_ctx();
+  c->cfg = *cfg;
+  c->device = device;
+  const int d = cfg->d_model, F = cfg->ffn, nl = cfg->n_layer;
+  const int qkv = (cfg->num_heads + 2 * cfg->num_heads_kv) * ZB_DH;
+  // ---- carve the weight arena (layer-major so the stream order == address order)
+  size_t off = 0;
+  auto carve = [&](const std::string& name, int64_t numel, int dtype, int64_t alt = 0) {
+    Slot s;
+    s.numel = numel; s.dtype = dtype; s.alt_numel = alt;
+    s.ptr = reinterpret_cast<void*>(off);
+    off = align_up(off + (size_t)numel * (dtype == ZB_F32 ? 4 : 2), 256);
+    c->slots[name] = s;
+  };
+  for (int l = 0; l < nl; ++l) {
+    const std::string p = "backbone.layers." + std::to_string(l);
+    carve(p + ".norm.weight", d, ZB_BF16);
+    carve(p + ".norm.bias", d, ZB_BF16);
+    carve(p + ".mixer.in_proj.weight", (int64_t)qkv * d, ZB_BF16);
+    carve(p + ".mixer.out_proj.weight", (int64_t)d * cfg->num_heads * ZB_DH, ZB_BF16);
+    carve(p + ".norm2.weight", d, ZB_BF16);
+    carve(p + ".norm2.bias", d, ZB_BF16);
+    carve(p + ".mlp.fc1.weight", (int64_t)2 * F * d, ZB_BF16);
+    carve(p + ".mlp.fc2.weight", (int64_t)d * F, ZB_BF16);
+  }
+  carve("backbone.norm_f.weight", d, ZB_BF16);
+  carve("backbone.norm_f.bias", d, ZB_BF16);
+  for (int k = 0; k < cfg->n_codebooks; ++k) carve("heads." + std::to_string(k) + ".weight", (int64_t)cfg->vocab * d, ZB_BF16, (int64_t)(cfg->vocab - 1) * d);
+  for (int k = 0; k < cfg->n_codebooks; ++k) carve("embeddings." + std::to_string(k) + ".weight", (int64_t)cfg->vocab * d, ZB_BF16);
+  carve("rope.freqs_cis", (int64_t)cfg->rope_table_len * (ZB_DH / 2) * 2, ZB_F32);
+  c->arena_bytes = off;
+  if ((e = cudaMalloc(&c->arena, c->arena_bytes)) != cudaSuccess) {
+    delete c;
+    return bad(ZB_ERR_NOMEM, std::string("weight arena: ") + cudaGetErrorString(e));
+  }
+  cudaMemset(c->arena, 0, c->arena_bytes);
+  for (auto& kv : c->slots) kv.second.ptr = c->arena + reinterpret_cast<size_t>(kv.second.ptr);
+  auto W = [&](const std::string& n) { return reinterpret_cast<bf16*>(c->slots[n].ptr); };
+  c->layers.resize(nl);
+  for (int l = 0; l < nl; ++l) {
+    const std::string p = "backbone.layers." + std::to_string(l);
+    c->layers[l] = LayerW{W(p + ".norm.weight"), W(p + ".norm.bias"), W(p + ".mixer.in_proj.weight"), W(p + ".mixer.out_proj.weight"),
+                          W(p + ".norm2.weight"), W(p + ".norm2.bias"), W(p + ".mlp.fc1.weight"), W(p + ".mlp.fc2.weight")};
+  }
+  c->normf_w = W("backbone.norm_f.weight");
+  c->normf_b = W("backbone.norm_f.bias");
+  c->heads = W("heads.0.weight");        // heads are contiguous: [n_q][vocab][d] (vocab*d*2 is a multiple of 256)
+  c->emb = W("embeddings.0.weight");
+  c->rope = reinterpret_cast<float*>(c->slots["rope.freqs_cis"].ptr);
+  if (((size_t)cfg->vocab * d * 2) % 256 != 0) { cudaFree(c->arena); delete c; return bad(ZB_ERR_ARG, "vocab*d_model*2 must be a multiple of 256"); }
+  // algorithmic bytes streamed per decode step: layer weights + LN params + final LN + real head rows
+  c->step_weight_bytes = (int64_t)nl * ((int64_t)qkv * d + (int64_t)d * d + (int64_t)2 * F * d + (int64_t)d * F + 4 * d) * 2 +
+                         (int64_t)2 * d * 2 + (int64_t)cfg->n_codebooks * (cfg->vocab - 1) * d * 2;
+
+  // opt-in to large dynamic shared memory for every GEMV instantiation
+  const size_t max_smem = gemv_smem(8, F > d ? F : d);
+  for (int R = 2; R <= 8; R += 2)
+    for (int epi = 0; epi < 4; ++epi)
+      if ((e = cudaFuncSetAttribute(gemv_kernel(R, epi), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem)) != cudaSuccess) {
+        cudaFree(c->arena); delete c;
+        return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
+      }
+  if ((e = cudaMalloc(&c->st, sizeof(ZbDevState))) != cudaSuccess) { cudaFree(c->arena); delete c; return bad(ZB_ERR_NOMEM, cudaGetErrorString(e)); }
+  cudaMemset(c->st, 0, sizeof(ZbDevState));
+  cudaEventCreate(&c->ev0);
+  cudaEventCreate(&c->ev1);
+  cudaStreamCreateWithFlags(&c->cap_stream, cudaStreamNonBlocking);
+  *out = c;
+  return ZB_OK;
+}
+
+int zb_ctx_destroy(zb_ctx* c) {
+  if (!c) return ZB_OK;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  free_kv(c);
+  if (c->arena) cudaFree(c->arena);
+  if (c->st) cudaFree(c->st);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->cap_stream) cudaStreamDestroy(c->cap_stream);
+  delete c;
+  return ZB_OK;
+}
+
+int zb_set_tensor(zb_ctx* c, const char* name, const void* d_ptr, int64_t numel, int dtype, void* stream) {
+  if (!c || !name || !d_ptr) return ZB_ERR_ARG;
+  auto it = c->slots.find(name);
+  if (it == c->slots.end()) return c->err.fail(ZB_ERR_ARG, "unknown tensor '%s'", name);
+  Slot& s = it->second;
+  if (dtype != s.dtype) return c->err.fail(ZB_ERR_ARG, "tensor '%s': dtype %d, expected %d", name, dtype, s.dtype);
+  if (numel != s.numel && !(s.alt_numel && numel == s.alt_numel))
+    return c->err.fail(ZB_ERR_ARG, "tensor '%s': numel %lld, expected %lld", name, (long long)numel, (long long)s.numel);
+  const size_t esz = s.dtype == ZB_F32 ? 4 : 2;
+  cudaStream_t st = (cudaStream_t)stream;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  if (numel != s.numel) ZB_CUDA(c->err, cudaMemsetAsync(s.ptr, 0, (size_t)s.numel * esz, st));   // zero pad row (utils.py:12-27)
+  ZB_CUDA(c->err, cudaMemcpyAsync(s.ptr, d_ptr, (size_t)numel * esz, cudaMemcpyDeviceToDevice, st));
+  s.provided = true;
+  return ZB_OK;
+}
+
+int zb_weights_finalize(zb_ctx* c, void* stream) {
+  if (!c) return ZB_ERR_ARG;
+  for (auto& kv : c->slots)
+    if (!kv.second.provided) return c->err.fail(ZB_ERR_STATE, "tensor '%s' was not provided", kv.first.c_str());
+  ZB_CUDA(c->err, cudaStreamSynchronize((cudaStream_t)stream));
+  c->finalized = true;
+  return ZB_OK;
+}
+
+int zb_kv_alloc(zb_ctx* c, int rows, int max_seqlen) {
+  if (!c || rows <= 0 || max_seqlen <= 0) return ZB_ERR_ARG;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  if (max_seqlen > c->cfg.rope_table_len) return c->err.fail(ZB_ERR_ARG, "max_seqlen %d exceeds the RoPE table (%d)", max_seqlen, c->cfg.rope_table_len);
+  const zb_config& g = c->cfg;
+  const int pages_per_row = (max_seqlen + ZB_PAGE - 1) / ZB_PAGE;
+  if (c->kv && c->rows == rows && c->max_pages == pages_per_row) { c->max_seqlen = max_seqlen; return ZB_OK; }
+  ZB_CUDA(c->err, cudaDeviceSynchronize());
+  free_kv(c);
+  c->rows = rows; c->max_pages = pages_per_row; c->max_seqlen = max_seqlen;
+  const size_t total_pages = (size_t)rows * pages_per_row;
+  c->kv_layer_elems = total_pages * 2 * g.num_heads_kv * ZB_PAGE * ZB_DH;
+  int ns = (4 * ZB_NUM_SMS) / (rows * g.num_heads_kv);
+  ns = ns < 1 ? 1 : (ns > 32 ? 32 : ns);
+  c->nsplit = ns;
+  const int G = g.num_heads / g.num_heads_kv;
+  const int rows_pad = (rows + 7) / 8 * 8;
+#define ZB_ALLOC(ptr, bytes) ZB_CUDA(c->err, cudaMalloc((void**)&(ptr), (bytes)))
+  ZB_ALLOC(c->kv, c->kv_layer_elems * g.n_layer * sizeof(bf16));
+  ZB_ALLOC(c->page_table, total_pages * sizeof(int));
+  ZB_ALLOC(c->x, (size_t)rows_pad * g.d_model * 2);
+  ZB_ALLOC(c->q, (size_t)rows_pad * g.num_heads * ZB_DH * 2);
+  ZB_ALLOC(c->y, (size_t)rows_pad * g.num_heads * ZB_DH * 2);
+  ZB_ALLOC(c->h, (size_t)rows_pad * g.ffn * 2);
+  ZB_ALLOC(c->logits, (size_t)rows_pad * g.n_codebooks * g.vocab * 4);
+  ZB_ALLOC(c->part_o, (size_t)rows * g.num_heads_kv * ns * G * ZB_DH * 4);
+  ZB_ALLOC(c->part_ml, (size_t)rows * g.num_heads_kv * ns * G * 2 * 4);
+  ZB_ALLOC(c->counters, (size_t)rows * g.num_heads_kv * 4);
+  ZB_ALLOC(c->tokens, (size_t)rows_pad * g.n_codebooks * 8);
+  ZB_ALLOC(c->remaining, (size_t)rows_pad * 4);
+  ZB_ALLOC(c->stopping, (size_t)rows_pad * 4);
+  ZB_ALLOC(c->out_len, (size_t)rows_pad * 4);
+  ZB_ALLOC(c->rope_pos, (size_t)rows_pad * 4);
+#undef ZB_ALLOC
+  ZB_CUDA(c->err, cudaMemset(c->kv, 0, c->kv_layer_elems * g.n_layer * sizeof(bf16)));
+  ZB_CUDA(c->err, cudaMemset(c->counters, 0, (size_t)rows * g.num_heads_kv * 4));
+  ZB_CUDA(c->err, cudaMemset(c->x, 0, (size_t)rows_pad * g.d_model * 2));
+  ZB_CUDA(c->err, cudaMemset(c->rope_pos, 0, (size_t)rows_pad * 4));
+  std::vector<int> pt(total_pages);
+  for (size_t i = 0; i < total_pages; ++i) pt[i] = (int)i;          // identity paging: row r owns pages [r*P, (r+1)*P)
+  ZB_CUDA(c->err, cudaMemcpy(c->page_table, pt.data(), total_pages * sizeof(int), cudaMemcpyHostToDevice));
+  return ZB_OK;
+}
+
+int zb_kv_reset(zb_ctx* c, void* stream) {
+  if (!c || !c->kv) return c ? c->err.fail(ZB_ERR_STATE, "zb_kv_alloc first") : ZB_ERR_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  ZB_CUDA(c->err, cudaMemsetAsync(c->st, 0, sizeof(ZbDevState), s));
+  ZB_CUDA(c->err, cudaMemsetAsync(c->rope_pos, 0, (size_t)c->rows * 4, s));
+  return ZB_OK;
+}
+
+static int check_ready(zb_ctx* c) {
+  if (!c) return ZB_ERR_ARG;
+  if (!c->finalized) return c->err.fail(ZB_ERR_STATE, "weights not finalised");
+  if (!c->kv) return c->err.fail(ZB_ERR_STATE, "zb_kv_alloc first");
+  return ZB_OK;
+}
+
+int zb_backbone_forward(zb_ctx* c, const void* d_in, void* d_out, int rows, int S, int seqlen_offset,
+                        const int32_t* d_lengths, void* stream) {
+  int rc = check_ready(c);
+  if (rc) return rc;
+  if (rows != c->rows) return c->err.fail(ZB_ERR_ARG, "rows %d != allocated %d", rows, c->rows);
+  if (seqlen_offset + S > c->max_seqlen) return c->err.fail(ZB_ERR_ARG, "sequence overflows the KV cache");
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  const zb_config& g = c->cfg;
+  const std::vector<Pass> passes = plain_passes(rows);
+  int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
+  for (int t = 0; t < S; ++t) {
+    ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, seqlen_offset + t, (const int*)d_lengths, t));
+    ZB_CUDA(c->err, launch(c, k_load_hidden, dim3(rows), dim3(thr), 0, s, (const bf16*)d_in, c->x, g.d_model, S, t));
+    ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
+    if (d_out)
+      ZB_CUDA(c->err, launch(c, k_final_ln, dim3(rows), dim3(256), 0, s, (const bf16*)c->x, (const bf16*)c->normf_w, (const bf16*)c->normf_b,
+                             g.norm_eps, (bf16*)d_out, g.d_model, S, t));
+  }
+  // leave the device state positioned after the appended tokens (generation continues from here)
+  ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, seqlen_offset + S, (const int*)d_lengths, S));
+  return ZB_OK;
+}
+
+int zb_delay_apply(const int64_t* d_codes, int64_t* d_out, int B, int n_q, int T, int64_t mask_token, void* stream) {
+  if (!d_codes || !d_out || B < 0 || n_q <= 0 || T < 0) return ZB_ERR_ARG;
+  const size_t n = (size_t)B * n_q * (T + n_q);
+  if (n == 0) return ZB_OK;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > ZB_NUM_SMS * 8) blocks = ZB_NUM_SMS * 8;
+  k_delay_apply<<<blocks, 256, 0, (cudaStream_t)stream>>>((const long long*)d_codes, (long long*)d_out, B, n_q, T, (long long)mask_token);
+  return cudaGetLastError() == cudaSuccess ? ZB_OK : ZB_ERR_CUDA;
+}
+
+int zb_delay_revert(const int64_t* d_delayed, int64_t* d_out, int B, int n_q, int L, void* stream) {
+  if (!d_delayed || !d_out || B < 0 || n_q <= 0 || L < n_q) return ZB_ERR_ARG;
+  const size_t n = (size_t)B * n_q * (L - n_q);
+  if (n == 0) return ZB_OK;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > ZB_NUM_SMS * 8) blocks = ZB_NUM_SMS * 8;
+  k_delay_revert<<<blocks, 256, 0, (cudaStream_t)stream>>>((const long long*)d_delayed, (long long*)d_out, B, n_q, L);
+  return cudaGetLastError() == cudaSuccess ? ZB_OK : ZB_ERR_CUDA;
+}
+
+int zb_sample(const float* d_logits, const int64_t* d_history, int hist_len, int64_t* d_tokens, float* d_probs_out,
+              int B, int n_q, int V, const zb_sampling* sp, uint64_t seed, uint64_t step, void* stream) {
+  if (!d_logits || !d_tokens || !sp || B <= 0 || n_q <= 0 || V <= 0 || V > SMP_MAXV) return ZB_ERR_ARG;
+  SampleParams p;
+  memset(&p, 0, sizeof(p));
+  p.logits = d_logits; p.history = (const long long*)d_history; p.hist_stride = hist_len; p.hist_len = d_history ? hist_len : 0;
+  p.tokens = (long long*)d_tokens; p.probs_out = d_probs_out; p.n_q = n_q; p.V = V; p.sp = *sp; p.seed = seed; p.step = step; p.st = nullptr;
+  k_sample<<<dim3(n_q, B), SMP_THREADS, 0, (cudaStream_t)stream>>>(p);
+  return cudaGetLastError() == cudaSuccess ? ZB_OK : ZB_ERR_CUDA;
+}
+
+static int upload_state(zb_ctx* c, const ZbDevState& h, cudaStream_t s) {
+  // small pageable H2D copy: staged by the driver before returning, so `h` may live on the stack
+  ZB_CUDA(c->err, cudaMemcpyAsync(c->st, &h, sizeof(h), cudaMemcpyHostToDevice, s));
+  return ZB_OK;
+}
+
+int zb_decode_logits(zb_ctx* c, const int64_t* d_delayed, int B, int L, int col, float cfg_scale, int apply_eos_bias,
+                     float* d_logits_out, void* stream) {
+  int rc = check_ready(c);
+  if (rc) return rc;
+  if (2 * B != c->rows) return c->err.fail(ZB_ERR_ARG, "2*B=%d != allocated rows %d", 2 * B, c->rows);
+  if (col < 0 || col >= L) return c->err.fail(ZB_ERR_ARG, "col out of range");
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  const zb_config& g = c->cfg;
+  // read back pos (tiny sync; this entry point is a parity/debug path, not the generation loop)
+  ZbDevState h;
+  ZB_CUDA(c->err, cudaMemcpyAsync(&h, c->st, sizeof(h), cudaMemcpyDeviceToHost, s));
+  ZB_CUDA(c->err, cudaStreamSynchronize(s));
+  if (h.pos + 1 > c->max_seqlen) return c->err.fail(ZB_ERR_ARG, "KV cache full");
+  h.col = col; h.L = L; h.B = B; h.done = 0; h.cfg_scale = cfg_scale; h.apply_eos_bias = apply_eos_bias;
+  if ((rc = upload_state(c, h, s))) return rc;
+  c->B = B; c->L = L;
+  const std::vector<Pass> passes = cfg_passes(B);
+  int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
+  ZB_CUDA(c->err, launch(c, k_embed, dim3(B), dim3(thr), 0, s, (const bf16*)c->emb, (const long long*)d_delayed, c->x,
+                         g.d_model, g.n_codebooks, g.vocab, (const ZbDevState*)c->st));
+  ZB_CUDA(c->err, enqueue_layers(c, passes, s, true));
+  ZB_CUDA(c->err, enqueue_heads(c, passes, d_logits_out, s));
+  ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
+  return ZB_OK;
+}
+
+int zb_gen_begin(zb_ctx* c, const void* d_prefix, int B, int Lc, int64_t* d_delayed, int L, int prefix_cols,
+                 float cfg_scale, const zb_sampling* sp, uint64_t seed, int compat_scatter, void* stream) {
+  int rc = check_ready(c);
+  if (rc) return rc;
+  if (!d_prefix || !d_delayed || !sp) return c->err.fail(ZB_ERR_ARG, "null argument");
+  if (2 * B != c->rows) return c->err.fail(ZB_ERR_ARG, "2*B=%d != allocated rows %d", 2 * B, c->rows);
+  if (prefix_cols < 1 || prefix_cols >= L) return c->err.fail(ZB_ERR_ARG, "prefix_cols out of range");
+  if (Lc + L > c->max_seqlen) return c->err.fail(ZB_ERR_ARG, "Lc + L = %d exceeds max_seqlen %d", Lc + L, c->max_seqlen);
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  const zb_config& g = c->cfg;
+  c->B = B; c->L = L; c->delayed = (long long*)d_delayed;
+  c->ev_valid = false;
+
+  ZbDevState h;
+  memset(&h, 0, sizeof(h));
+  h.L = L; h.B = B; h.cfg_scale = cfg_scale; h.seed = seed; h.sp = *sp; h.compat_scatter = compat_scatter;
+  if ((rc = upload_state(c, h, s))) return rc;
+  ZB_CUDA(c->err, cudaMemsetAsync(c->rope_pos, 0, (size_t)c->rows * 4, s));
+  ZB_CUDA(c->err, cudaMemsetAsync(c->stopping, 0, (size_t)B * 4, s));
+  ZB_CUDA(c->err, cudaMemsetAsync(c->out_len, 0, (size_t)B * 4, s));
+  std::vector<int> rem(B, L - prefix_cols);                           // max_steps, model.py:270-271
+  ZB_CUDA(c->err, cudaMemcpyAsync(c->remaining, rem.data(), (size_t)B * 4, cudaMemcpyHostToDevice, s));
+  ZB_CUDA(c->err, cudaStreamSynchronize(s));                          // `rem` is host-stack memory
+
+  // ---- prefill (model.py:181-196,253-264), token by token through the decode-step kernels: causal attention over
+  // the prefix is exactly what a sequence of single-token steps computes.
+  const std::vector<Pass> passes = cfg_passes(B);
+  int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
+  for (int t = 0; t < Lc; ++t) {
+    ZB_CUDA(c->err, launch(c, k_load_hidden, dim3(2 * B), dim3(thr), 0, s, (const bf16*)d_prefix, c->x, g.d_model, Lc, t));
+    ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
+    ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
+  }
+  for (int j = 0; j + 1 < prefix_cols; ++j) {      // known audio-prefix columns: no sampling
+    h.pos = Lc + j; h.col = j;
+    if ((rc = upload_state(c, h, s))) return rc;
+    ZB_CUDA(c->err, launch(c, k_embed, dim3(B), dim3(thr), 0, s, (const bf16*)c->emb, (const long long*)c->delayed, c->x,
+                           g.d_model, g.n_codebooks, g.vocab, (const ZbDevState*)c->st));
+    ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
+    ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
+  }
+  // last prefix column -> logits -> sample (no logit_bias, no repetition penalty, no EOS logic: model.py:255-260)
+  h.pos = Lc + prefix_cols - 1; h.col = prefix_cols - 1;
+  h.apply_eos_bias = 0; h.use_history = 0; h.eos_logic = 0;
+  if ((rc = upload_state(c, h, s))) return rc;
+  const bool counting = c->counting;
+  ZB_CUDA(c->err, enqueue_decode_step(c, s));
+  c->counting = counting;
+  // switch to loop mode (model.py:266-301)
+  h.pos = Lc + prefix_cols; h.col = prefix_cols; h.step = 1;
+  h.apply_eos_bias = 1; h.use_history = 1; h.eos_logic = 1;
+  if ((rc = upload_state(c, h, s))) return rc;
+  return ZB_OK;
+}
+
+int zb_gen_steps(zb_ctx* c, int n_steps, void* stream) {
+  int rc = check_ready(c);
+  if (rc) return rc;
+  if (!c->delayed) return c->err.fail(ZB_ERR_STATE, "zb_gen_begin first");
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  if (c->opt_graph) {
+    if (c->graph && (c->graph_B != c->B || c->graph_L != c->L || c->graph_delayed != c->delayed)) drop_graph(c);
+    if (!c->graph) {
+      cudaGraph_t graph = nullptr;
+      const int64_t before = c->launches;
+      ZB_CUDA(c->err, cudaStreamBeginCapture(c->cap_stream, cudaStreamCaptureModeThreadLocal));
+      cudaError_t e = enqueue_decode_step(c, c->cap_stream);
+      cudaError_t e2 = cudaStreamEndCapture(c->cap_stream, &graph);
+      if (e != cudaSuccess || e2 != cudaSuccess) {
+        if (graph) cudaGraphDestroy(graph);
+        return c->err.fail(ZB_ERR_CUDA, "graph capture failed: %s / %s", cudaGetErrorString(e), cudaGetErrorString(e2));
+      }
+      c->graph_nodes = (int)(c->launches - before);
+      c->launches = before;
+      cudaError_t e3 = cudaGraphInstantiate(&c->graph, graph, 0);
+      cudaGraphDestroy(graph);
+      if (e3 != cudaSuccess) { c->graph = nullptr; return c->err.fail(ZB_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e3)); }
+      c->graph_B = c->B; c->graph_L = c->L; c->graph_delayed = c->delayed;
+    }
+    ZB_CUDA(c->err, cudaEventRecord(c->ev0, s));
+    for (int i = 0; i < n_steps; ++i) ZB_CUDA(c->err, cudaGraphLaunch(c->graph, s));
+    ZB_CUDA(c->err, cudaEventRecord(c->ev1, s));
+    c->launches += (int64_t)n_steps * c->graph_nodes;
+  } else {
+    ZB_CUDA(c->err, cudaEventRecord(c->ev0, s));
+    for (int i = 0; i < n_steps; ++i) ZB_CUDA(c->err, enqueue_decode_step(c, s));
+    ZB_CUDA(c->err, cudaEventRecord(c->ev1, s));
+  }
+  c->ev_valid = true;
+  return ZB_OK;
+}
+
+int zb_gen_poll(zb_ctx* c, int* done, int* col, int32_t* h_out_len, void* stream) {
+  int rc = check_ready(c);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  ZbDevState h;
+  ZB_CUDA(c->err, cudaMemcpyAsync(&h, c->st, sizeof(h), cudaMemcpyDeviceToHost, s));
+  if (h_out_len) ZB_CUDA(c->err, cudaMemcpyAsync(h_out_len, c->out_len, (size_t)c->B * 4, cudaMemcpyDeviceToHost, s));
+  ZB_CUDA(c->err, cudaStreamSynchronize(s));
+  if (done) *done = h.done;
+  if (col) *col = h.col;
+  return ZB_OK;
+}
+
+int64_t zb_weight_bytes(const zb_ctx* c) { return c ? c->step_weight_bytes : 0; }
+int64_t zb_launch_count(const zb_ctx* c) { return c ? c->launches : 0; }
+
+int zb_set_option(zb_ctx* c, const char* key, int value) {
+  if (!c || !key) return ZB_ERR_ARG;
+  const std::string k(key);
+  if (k == "pdl") c->opt_pdl = value;
+  else if (k == "l2_prefetch") c->opt_l2_prefetch_mb = value;
+  else if (k == "graph") c->opt_graph = value;
+  else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
+  drop_graph(c);
+  return ZB_OK;
+}
+
+int zb_bench_kernel(zb_ctx* c, const char* name, int iters, float* ms_out, void* stream) {
+  // Isolated timing of one kernel family: launch it `iters` times back to back, cycling over the layers so that
+  // consecutive launches read different weights (26 x 67 MB >> L2), CUDA events on `stream`.  Outputs are scratch.
+  int rc = check_ready(c);
+  if (rc) return rc;
+  if (!name || !ms_out || iters <= 0) return ZB_ERR_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  const zb_config& g = c->cfg;
+  const int d = g.d_model, H = g.num_heads, Hkv = g.num_heads_kv, F = g.ffn;
+  const int q_size = H * ZB_DH, kv_size = Hkv * ZB_DH;
+  const std::string k(name);
+  const Pass ps = (c->rows % 2 == 0 && c->rows <= 8) ? Pass{c->rows, 0, c->rows / 2, c->rows / 2, c->rows} : Pass{2, 0, 1, 1, 2};
+  const bool counting = c->counting;
+  c->counting = false;
+  cudaError_t e = cudaSuccess;
+  ZB_CUDA(c->err, cudaEventRecord(c->ev0, s));
+  for (int i = 0; i < iters && e == cudaSuccess; ++i) {
+    const int l = i % g.n_layer;
+    const LayerW& w = c->layers[l];
+    GemvParams p = base_params(c, ps);
+    if (k == "fc1") {
+      p.W = w.w_fc1; p.K = d; p.n_tasks = F; p.row0_mul = 1; p.row1_off = F; p.x = c->x; p.ln_w = w.ln2_w; p.ln_b = w.ln2_b;
+      p.out = c->h; p.out_stride = F;
+      e = launch_gemv(c, EPI_SWIGLU, ps, p, s);
+    } else if (k == "fc2") {
+      p.W = w.w_fc2; p.K = F; p.n_tasks = d / 2; p.row0_mul = 2; p.row1_off = 1; p.x = c->h; p.out = c->y; p.out_stride = d;
+      e = launch_gemv(c, EPI_RESID, ps, p, s);
+    } else if (k == "out_proj") {
+      p.W = w.w_out; p.K = q_size; p.n_tasks = d / 2; p.row0_mul = 2; p.row1_off = 1; p.x = c->q; p.out = c->y; p.out_stride = d;
+      e = launch_gemv(c, EPI_RESID, ps, p, s);
+    } else if (k == "in_proj") {
+      p.W = w.w_in; p.K = d; p.n_tasks = (q_size + 2 * kv_size) / 2; p.row0_mul = 2; p.row1_off = 1; p.x = c->x; p.ln_w = w.ln1_w; p.ln_b = w.ln1_b;
+      p.out = c->q; p.out_stride = q_size; p.kv_layer = c->kv + (size_t)l * c->kv_layer_elems; p.page_table = c->page_table;
+      p.max_pages = c->max_pages; p.Hkv = Hkv; p.q_size = q_size; p.kv_size = kv_size; p.rope = c->rope; p.rope_pos = c->rope_pos;
+      e = launch_gemv(c, EPI_QKV, ps, p, s);
+    } else if (k == "attn") {
+      AttnParams a;
+      memset(&a, 0, sizeof(a));
+      a.q = c->q; a.kv_layer = c->kv + (size_t)l * c->kv_layer_elems; a.page_table = c->page_table; a.max_pages = c->max_pages;
+      a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
+      a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
+      e = launch(c, attn_kernel(H / Hkv), dim3(c->nsplit, Hkv, c->rows), dim3(ATT_THREADS), 0, s, a);
+    } else {
+      c->counting = counting;
+      return c->err.fail(ZB_ERR_ARG, "unknown kernel '%s'", name);
+    }
+  }
+  c->counting = counting;
+  ZB_CUDA(c->err, e);
+  ZB_CUDA(c->err, cudaEventRecord(c->ev1, s));
+  ZB_CUDA(c->err, cudaEventSynchronize(c->ev1));
+  ZB_CUDA(c->err, cudaEventElapsedTime(ms_out, c->ev0, c->ev1));
+  return ZB_OK;
+}
+
+float zb_last_steps_ms(zb_ctx* c) {
+  if (!c || !c->ev_valid) return -1.f;
+  float ms = -1.f;
+  if (cudaEventSynchronize(c->ev1) != cudaSuccess) return -1.f;
+  if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) != cudaSuccess) return -1.f;
+  return ms;
+}
+
+}  // extern "C"
