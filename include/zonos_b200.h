@@ -123,6 +123,12 @@ int  zb_gen_begin(zb_ctx* ctx, const void* d_prefix, int B, int Lc, int64_t* d_d
 int  zb_gen_steps(zb_ctx* ctx, int n_steps, void* stream);
 int  zb_gen_poll(zb_ctx* ctx, int* done, int* col, int32_t* h_out_len /* [B] or NULL */, void* stream);
 
+/* One application of the device-side frame write-back + EOS wind-down (model.py:283-301) on caller-owned state:
+ * d_tokens int64 [B, n_q] = the sampled next_token, d_remaining / d_stopping / d_out_len int32 [B]; writes column
+ * col+1 of d_delayed.  Exposed for exact-integer parity tests of the loop state machine. */
+int  zb_update_frame(zb_ctx* ctx, int64_t* d_delayed, int B, int L, int col, const int64_t* d_tokens, int32_t* d_remaining,
+                     int32_t* d_stopping, int32_t* d_out_len, int eos_logic, int compat_scatter, void* stream);
+
 /* ---- DAC 44 kHz decoder: DACAutoencoder.decode (autoencoder.py:25-27) --------------------------
  * Weights use the HF DacModel keys, fp32 on the device; repacked at load. */
 typedef struct zb_dac zb_dac;

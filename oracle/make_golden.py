@@ -125,6 +125,11 @@ def main():
         torch.manual_seed(0)
         g[f"gen.{cname}.eos.greedy.codes"] = model_e.generate(prefix, max_new_tokens=64, sampling_params=dict(temperature=0),
                                                               progress_bar=False, disable_torch_compile=True)
+        tr = {}
+        out_e = zo.OracleZonos(cfg, sd_e).generate(prefix, max_new_tokens=64, sampling_params=dict(temperature=0), trace=tr)
+        assert torch.equal(out_e, g[f"gen.{cname}.eos.greedy.codes"])
+        g[f"gen.{cname}.eos.greedy.delayed"] = tr["delayed"]
+        g[f"gen.{cname}.eos.greedy.logits"] = torch.cat(tr["logits"], 0)
         # backbone plugin boundary: forward() on a [2, S, d] block, prefill then one decode token
         params = model.setup_cache(2, 32)
         x = zo.synth_prefix_conditioning(cfg, 1, 9, 3)
@@ -143,7 +148,27 @@ def main():
     delayed = ref.pattern.apply_delay_pattern(codes, 1025)
     g["full.delayed"] = delayed
     g["full.logits"] = ref_teacher_forced(ref, model, prefix, delayed, 6)
-    del model, sd
+    # greedy stream of the first 256 frames from the real reference + the oracle's per-step top-2 (after the repetition
+    # penalty) so that GPU tests can tell a genuine mismatch from a bf16 coin flip
+    torch.manual_seed(0)
+    codes256 = model.generate(prefix, max_new_tokens=256, sampling_params=dict(temperature=0), progress_bar=False,
+                              disable_torch_compile=True)
+    tr = {}
+    o_full = zo.OracleZonos(cfg, sd)
+    assert torch.equal(o_full.generate(prefix, max_new_tokens=256, sampling_params=dict(temperature=0), trace=tr), codes256)
+    g["full.greedy.codes"] = codes256
+    g["full.greedy.delayed"] = tr["delayed"]
+    top_v, top_i = [], []
+    for s, lg in enumerate(tr["logits"]):
+        if s > 0:
+            lg = zo.repetition_penalty(lg, tr["delayed"][..., : s + 1], 3.0, 2)
+        v, i = lg[0].topk(2, dim=-1)
+        top_v.append(v)
+        top_i.append(i)
+    g["full.greedy.top2_values"] = torch.stack(top_v)          # [steps, 9, 2]
+    g["full.greedy.top2_indices"] = torch.stack(top_i)
+    g["full.greedy.logit_rms"] = torch.stack([lg[torch.isfinite(lg)].pow(2).mean().sqrt() for lg in tr["logits"]])
+    del model, sd, o_full
 
     # ---- DAC decode through the reference's DACAutoencoder (transformers DacModel, fp32 on CPU)
     dsd = do.synth_dac_state_dict(2)

@@ -63,6 +63,7 @@ def test_bad_config_rejected():
     h = C.c_void_p()
     assert lib.zb_ctx_create(C.byref(zc), 0, C.byref(h)) == -1
     assert lib.zb_delay_apply(None, None, 1, 9, 4, 1025, None) == -1
+    assert lib.zb_delay_apply(None, None, 0, 9, 4, 1025, None) == 0          # empty batch: nothing to do
 
 
 def test_config_mirror_and_backbone_state_dict_keys():

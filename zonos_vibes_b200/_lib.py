@@ -50,6 +50,7 @@ SIGNATURES = {
     "zb_gen_begin": (_I, [_P, _P, _I, _I, _P, _I, _I, _F, C.POINTER(ZbSampling), _U64, _I, _P]),
     "zb_gen_steps": (_I, [_P, _I, _P]),
     "zb_gen_poll": (_I, [_P, C.POINTER(_I), C.POINTER(_I), _P, _P]),
+    "zb_update_frame": (_I, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _I, _I, _P]),
     "zb_dac_create": (_I, [_I, C.POINTER(_P)]),
     "zb_dac_destroy": (_I, [_P]),
     "zb_dac_last_error": (C.c_char_p, [_P]),

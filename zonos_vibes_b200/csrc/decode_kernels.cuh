@@ -52,6 +52,7 @@ struct GemvParams {
   int n_q;
   int V;
   int eos;                       // logit_bias index (model.py:266-267)
+  int n_rows;                    // total weight rows (MMA kernel: guards the ragged last 8-row task)
   // optional L2 prefetch of (the head of) the next kernel's weights: up to two byte ranges
   const char* pf0;
   const char* pf1;
@@ -66,7 +67,7 @@ __device__ __forceinline__ int gemv_row(const GemvParams& p, int r, bool& valid)
 }
 
 template <int R>
-__device__ __forceinline__ void gemv_stage_activations(const GemvParams& p, bf16* xs, float* red) {
+__device__ __forceinline__ void gemv_stage_activations(const GemvParams& p, bf16* xs, float* red, int ld) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
   const int K = p.K;
   if (p.ln_w == nullptr) {
@@ -75,7 +76,7 @@ __device__ __forceinline__ void gemv_stage_activations(const GemvParams& p, bf16
       bool ok;
       const int a = gemv_row<R>(p, r, ok);
       for (int e = tid * 8; e < K; e += blockDim.x * 8)
-        *reinterpret_cast<uint4*>(xs + (size_t)r * K + e) =
+        *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) =
             ok ? *reinterpret_cast<const uint4*>(p.x + (size_t)a * K + e) : make_uint4(0, 0, 0, 0);
     }
     return;
@@ -143,7 +144,7 @@ __device__ __forceinline__ void gemv_stage_activations(const GemvParams& p, bf16
         float a1 = (v[r][2 * j + 1] - mean[r]) * rstd * g[2 * j + 1] + b[2 * j + 1];
         o[j] = __floats2bfloat162_rn(a0, a1);
       }
-      *reinterpret_cast<uint4*>(xs + (size_t)r * K + e) = *reinterpret_cast<uint4*>(o);
+      *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) = *reinterpret_cast<uint4*>(o);
     }
   }
 }
@@ -283,7 +284,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, GEMV_CTAS_PER_SM) k_gemv(const G
   pdl_wait_prior_grid();
   if (p.st->done) return;
 
-  gemv_stage_activations<R>(p, xs, red);
+  gemv_stage_activations<R>(p, xs, red, K);
   __syncthreads();
 
   float acc0[R], acc1[R];

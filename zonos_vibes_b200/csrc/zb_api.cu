@@ -8,6 +8,7 @@
 
 #include "attention_kernels.cuh"
 #include "decode_kernels.cuh"
+#include "gemv_mma.cuh"
 #include "sample_kernels.cuh"
 
 int ZbErr::fail(int code, const char* fmt, ...) {
@@ -76,7 +77,7 @@ struct zb_ctx {
   int graph_B = -1, graph_L = -1;
   long long* graph_delayed = nullptr;
   // options
-  int opt_pdl = 1, opt_l2_prefetch_mb = 0, opt_graph = 1;
+  int opt_pdl = 1, opt_l2_prefetch_mb = 0, opt_graph = 1, opt_gemv = 1;
   int64_t launches = 0;
   bool counting = true;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -129,6 +130,29 @@ GemvKernel gemv_kernel(int R, int epi) {
     case EPI_HEADS: return gemv_kernel_for<EPI_HEADS>(R);
   }
   return nullptr;
+}
+template <int EPI>
+GemvKernel gemv_mma_kernel_for(int R) {
+  switch (R) {
+    case 2: return k_gemv_mma<2, EPI>;
+    case 4: return k_gemv_mma<4, EPI>;
+    case 6: return k_gemv_mma<6, EPI>;
+    case 8: return k_gemv_mma<8, EPI>;
+  }
+  return nullptr;
+}
+GemvKernel gemv_mma_kernel(int R, int epi) {
+  switch (epi) {
+    case EPI_QKV: return gemv_mma_kernel_for<EPI_QKV>(R);
+    case EPI_RESID: return gemv_mma_kernel_for<EPI_RESID>(R);
+    case EPI_SWIGLU: return gemv_mma_kernel_for<EPI_SWIGLU>(R);
+    case EPI_HEADS: return gemv_mma_kernel_for<EPI_HEADS>(R);
+  }
+  return nullptr;
+}
+size_t gemv_mma_smem(int R, int K, int epi) {
+  const int NT = epi == EPI_SWIGLU ? 2 : 1;
+  return (size_t)R * (K + GM_XPAD) * sizeof(bf16) + (size_t)2 * NT * GM_WARPS * 64 * sizeof(float) + (size_t)GM_WARPS * R * sizeof(float);
 }
 size_t gemv_smem(int R, int K) { return (size_t)R * K * sizeof(bf16) + (size_t)(GEMV_THREADS / 32) * R * sizeof(float); }
 
@@ -191,9 +215,15 @@ GemvParams base_params(zb_ctx* c, const Pass& ps) {
   return p;
 }
 
-cudaError_t launch_gemv(zb_ctx* c, int epi, const Pass& ps, const GemvParams& p, cudaStream_t s) {
-  GemvKernel k = gemv_kernel(ps.R, epi);
-  return launch(c, k, dim3(ZB_NUM_SMS * GEMV_CTAS_PER_SM), dim3(GEMV_THREADS), gemv_smem(ps.R, p.K), s, p);
+cudaError_t launch_gemv(zb_ctx* c, int epi, const Pass& ps, const GemvParams& pin, cudaStream_t s) {
+  GemvParams p = pin;
+  // rows that produce outputs: SwiGLU pairs value row i with gate row i+F (n_tasks == F); the others use adjacent pairs
+  p.n_rows = epi == EPI_SWIGLU ? pin.n_tasks : pin.n_tasks * 2;
+  if (c->opt_gemv == 0) {     // SIMT cross-check path
+    return launch(c, gemv_kernel(ps.R, epi), dim3(ZB_NUM_SMS * GEMV_CTAS_PER_SM), dim3(GEMV_THREADS), gemv_smem(ps.R, p.K), s, p);
+  }
+  p.n_tasks = (p.n_rows + GM_ROWS - 1) / GM_ROWS;
+  return launch(c, gemv_mma_kernel(ps.R, epi), dim3(ZB_NUM_SMS * 2), dim3(GM_THREADS), gemv_mma_smem(ps.R, p.K, epi), s, p);
 }
 
 // all transformer layers for the current token (x in c->x, positions in device state)
@@ -403,6 +433,13 @@ int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) {
         cudaFree(c->arena); delete c;
         return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
       }
+  for (int R = 2; R <= 8; R += 2)
+    for (int epi = 0; epi < 4; ++epi)
+      if ((e = cudaFuncSetAttribute(gemv_mma_kernel(R, epi), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)gemv_mma_smem(8, F > d ? F : d, EPI_SWIGLU))) != cudaSuccess) {
+        cudaFree(c->arena); delete c;
+        return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute(mma): ") + cudaGetErrorString(e));
+      }
   if ((e = cudaMalloc(&c->st, sizeof(ZbDevState))) != cudaSuccess) { cudaFree(c->arena); delete c; return bad(ZB_ERR_NOMEM, cudaGetErrorString(e)); }
   cudaMemset(c->st, 0, sizeof(ZbDevState));
   cudaEventCreate(&c->ev0);
@@ -537,9 +574,10 @@ int zb_backbone_forward(zb_ctx* c, const void* d_in, void* d_out, int rows, int 
 }
 
 int zb_delay_apply(const int64_t* d_codes, int64_t* d_out, int B, int n_q, int T, int64_t mask_token, void* stream) {
-  if (!d_codes || !d_out || B < 0 || n_q <= 0 || T < 0) return ZB_ERR_ARG;
+  if (B < 0 || n_q <= 0 || T < 0) return ZB_ERR_ARG;
   const size_t n = (size_t)B * n_q * (T + n_q);
   if (n == 0) return ZB_OK;
+  if (!d_out || (!d_codes && T > 0)) return ZB_ERR_ARG;
   int blocks = (int)((n + 255) / 256);
   if (blocks > ZB_NUM_SMS * 8) blocks = ZB_NUM_SMS * 8;
   k_delay_apply<<<blocks, 256, 0, (cudaStream_t)stream>>>((const long long*)d_codes, (long long*)d_out, B, n_q, T, (long long)mask_token);
@@ -547,9 +585,10 @@ int zb_delay_apply(const int64_t* d_codes, int64_t* d_out, int B, int n_q, int T
 }
 
 int zb_delay_revert(const int64_t* d_delayed, int64_t* d_out, int B, int n_q, int L, void* stream) {
-  if (!d_delayed || !d_out || B < 0 || n_q <= 0 || L < n_q) return ZB_ERR_ARG;
+  if (B < 0 || n_q <= 0 || L < n_q) return ZB_ERR_ARG;
   const size_t n = (size_t)B * n_q * (L - n_q);
   if (n == 0) return ZB_OK;
+  if (!d_delayed || !d_out) return ZB_ERR_ARG;
   int blocks = (int)((n + 255) / 256);
   if (blocks > ZB_NUM_SMS * 8) blocks = ZB_NUM_SMS * 8;
   k_delay_revert<<<blocks, 256, 0, (cudaStream_t)stream>>>((const long long*)d_delayed, (long long*)d_out, B, n_q, L);
@@ -708,6 +747,30 @@ int zb_gen_poll(zb_ctx* c, int* done, int* col, int32_t* h_out_len, void* stream
   return ZB_OK;
 }
 
+int zb_update_frame(zb_ctx* c, int64_t* d_delayed, int B, int L, int col, const int64_t* d_tokens, int32_t* d_remaining,
+                    int32_t* d_stopping, int32_t* d_out_len, int eos_logic, int compat_scatter, void* stream) {
+  // One application of the frame write-back / EOS wind-down kernel on caller-owned state (exact-integer parity tests
+  // against model.py:283-301 without any model numerics in the way).
+  if (!c || !d_delayed || !d_tokens || !d_remaining || !d_stopping || !d_out_len || B <= 0 || col < 0) return ZB_ERR_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(c->err, cudaSetDevice(c->device));
+  ZbDevState h;
+  memset(&h, 0, sizeof(h));
+  h.col = col; h.L = L; h.B = B; h.eos_logic = eos_logic; h.compat_scatter = compat_scatter;
+  int rc = upload_state(c, h, s);
+  if (rc) return rc;
+  UpdateParams up;
+  memset(&up, 0, sizeof(up));
+  up.st = c->st; up.delayed = (long long*)d_delayed; up.tokens = (const long long*)d_tokens; up.remaining = d_remaining;
+  up.stopping = d_stopping; up.out_len = d_out_len; up.rope_pos = nullptr; up.rows = 0; up.n_q = c->cfg.n_codebooks;
+  up.eos = c->cfg.eos_token_id; up.mask = c->cfg.masked_token_id;
+  int ub = B < 32 ? 32 : (B + 31) / 32 * 32;
+  if (ub > 1024) ub = 1024;
+  k_update<<<1, ub, 0, s>>>(up);
+  ZB_CUDA(c->err, cudaGetLastError());
+  return ZB_OK;
+}
+
 int64_t zb_weight_bytes(const zb_ctx* c) { return c ? c->step_weight_bytes : 0; }
 int64_t zb_launch_count(const zb_ctx* c) { return c ? c->launches : 0; }
 
@@ -717,6 +780,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   if (k == "pdl") c->opt_pdl = value;
   else if (k == "l2_prefetch") c->opt_l2_prefetch_mb = value;
   else if (k == "graph") c->opt_graph = value;
+  else if (k == "gemv") c->opt_gemv = value;          // 1 = mma.sync weight streaming (default), 0 = SIMT cross-check
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
   drop_graph(c);
   return ZB_OK;
@@ -738,6 +802,14 @@ int zb_bench_kernel(zb_ctx* c, const char* name, int iters, float* ms_out, void*
   const bool counting = c->counting;
   c->counting = false;
   cudaError_t e = cudaSuccess;
+  {
+    ZbDevState h;
+    ZB_CUDA(c->err, cudaMemcpyAsync(&h, c->st, sizeof(h), cudaMemcpyDeviceToHost, s));
+    ZB_CUDA(c->err, cudaStreamSynchronize(s));
+    h.done = 0;
+    if (h.pos >= c->max_seqlen) h.pos = c->max_seqlen - 1;
+    if ((rc = upload_state(c, h, s))) return rc;
+  }
   ZB_CUDA(c->err, cudaEventRecord(c->ev0, s));
   for (int i = 0; i < iters && e == cudaSuccess; ++i) {
     const int l = i % g.n_layer;

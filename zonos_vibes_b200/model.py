@@ -45,6 +45,7 @@ class Zonos(nn.Module):
         self._heads_synced = False
         self.last_lengths: list[int] | None = None
         self.last_step_ms: float | None = None
+        self.last_delayed_codes: torch.Tensor | None = None
 
     # ---- construction ---------------------------------------------------------------------------
     @property
@@ -220,6 +221,7 @@ class Zonos(nn.Module):
         if progress is not None:
             progress.close()
         self.last_step_ms = total_ms / max(step, 1)
+        self.last_delayed_codes = delayed_codes          # debug / parity: the raw delayed buffer of this run
 
         out_codes = revert_delay_pattern(delayed_codes)
         out_codes.masked_fill_(out_codes >= 1024, 0)
