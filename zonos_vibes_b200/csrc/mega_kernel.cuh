@@ -1,0 +1,1067 @@
+// Persistent decode kernel: the WHOLE generation step (embedding gather-sum, n_layer x [LN+QKV+RoPE+KV-append, split-KV
+// GQA attention, out_proj+residual, LN+fc1+SwiGLU, fc2+residual], final LN + 9 heads + CFG, sampling, EOS wind-down and
+// frame write-back) — and any number of consecutive steps — in ONE cooperative launch of one CTA per SM.
+// Reference arithmetic: zonos/model.py:97-116,276-301, zonos/backbone/_torch.py:83-152, zonos/sampling.py:117-182.
+//
+// Why: at batch 1 the step is a chain of 113 GEMVs that together stream 3.2 GB of weights.  As separate
+// kernels each GEMV pays launch + ramp-up + tail (measured r01: 5.8-19.5 us per launch where the bytes alone need
+// 1.3-10 us; the step ran at 32 % of HBM peak).  Nothing that is streamed depends on the activations, so here the
+// stream NEVER stops:
+//   * warp 8 of every CTA is a TMA producer.  It walks the fixed, activation-independent schedule of everything this
+//     CTA will need from HBM — its 8-row weight tiles (one 4 KB `cp.async.bulk` per row into a padded,
+//     bank-conflict-free shared-memory stage; 2 KB copies ran at only 4.0 TB/s, 4 KB copies at 7.0 TB/s:
+//     profiles/r01_ring_bench.md), the LayerNorm parameters, the RoPE rows and its slice of the KV cache — through a
+//     ring of 33 KB stages with full/empty mbarriers, running ahead of the math across phase, layer and step
+//     boundaries.  With the HBM queues kept full by that stream, a cold demand load costs 5-10 us
+//     (profiles/r01_mega_trace_v1.md), so NO consumer ever touches HBM-cold data directly;
+//   * warps 0..7 are consumers: per phase they stage the (tiny, L2-resident) activations in shared memory (LayerNorm
+//     fused), then eat stages with `mma.sync.m16n8k16` (activations = A rows 0..R-1, 8 weight rows = B columns; K is
+//     split over the 8 warps and reduced through shared memory), run store-only fused epilogues (the CTA keeps its own
+//     slice of the residual stream in shared memory), and meet the other CTAs at a grid barrier;
+//   * rows are dealt to CTAs in contiguous, balanced ranges (<= 1 unit difference), whole rows per CTA, so there is
+//     no cross-CTA split-K and the fp32 summation order — hence every token — is reproducible.
+// tcgen05 is deliberately not used here: with M = 2..8 activation rows the contraction is a GEMV, ~100x below the
+// tensor roofline and bound by the HBM stream; `mma.sync` from shared memory costs ~0.4 issue slots per weight element.
+#pragma once
+#include "attention_kernels.cuh"
+#include "decode_kernels.cuh"
+#include "gemv_mma.cuh"
+#include "sample_kernels.cuh"
+
+#define MG_CONSUMERS 256
+#define MG_THREADS 288               // 8 consumer warps + 1 producer warp
+#define MG_WARPS 8
+#define MG_KC 2048                   // weight columns per ring stage (4 KB per row copy)
+#define MG_ROW_BYTES (MG_KC * 2 + 64)   // stage row stride: +64 B => 8 rows x 16 B quarter-warp reads hit 32 distinct banks
+#define MG_STAGE_BYTES (8 * MG_ROW_BYTES)
+#define MG_MAX_STAGES 8
+#define MG_XPAD 32                   // bf16 elements of padding per staged activation row
+#define MG_KV_TOK 64                 // tokens per KV stage: K rows at [0, 16 KB), V rows at [16 KB, 32 KB)
+#define MG_MAX_SPLIT 8              // KV splits per (row, kv head): the merge stages all partials in the s_o scratch ([8][G][128])
+#define MG_OWN 16                    // residual-stream columns a CTA can own (2 * ceil(d/2 / grid) <= 16)
+#define MG_ROPE_BYTES (ZB_DH / 2 * 2 * 4)   // one RoPE table row: 64 x (cos, sin) fp32
+
+enum { MG_MODE_HIDDEN = 0, MG_MODE_FORCED = 1, MG_MODE_LOGITS = 2, MG_MODE_DECODE = 3 };
+
+struct MegaLayer {
+  const bf16 *ln1_w, *ln1_b, *w_in, *w_out, *ln2_w, *ln2_b, *w_fc1, *w_fc2;
+};
+
+struct MegaParams {
+  MegaLayer l0;                // layer 0; layer l = l0 + l * layer_stride bytes (the arena is layer-major with a constant
+  long long layer_stride;      // stride), so no role ever loads a weight POINTER from memory: under a saturated HBM stream
+                               // even an L1 miss on a pointer table costs microseconds
+  int n_layer, d, q_size, kv_size, F, H, Hkv;
+  const bf16 *normf_w, *normf_b, *heads, *emb;
+  const float* rope;           // [table_len][Dh/2][2]
+  int n_q, V, eos, mask_tok;
+  float eps, scale_log2;
+  // activations: global scratch, L2 resident, read with ld.cg (they are written by other CTAs of this launch)
+  bf16 *x, *q, *y, *h;         // [R][d], [R][q_size], [R][q_size], [R][F]
+  float* logits;               // [B][n_q][V]
+  bf16* kv;                    // [n_layer][page][2][Hkv][ZB_PAGE][ZB_DH]
+  size_t kv_layer_elems;
+  const int* page_table;       // [R][max_pages]
+  int max_pages;
+  float *part_o, *part_ml;     // split-KV partials [R][Hkv][nsplit][G][Dh], [...][2]
+  int* att_counters;           // [R][Hkv] tickets (zero between launches)
+  int nsplit;
+  int R, B;                    // activation rows (= 2B in the CFG modes) and utterances
+  ZbDevState* st;
+  int* rope_pos;               // [R]
+  long long* delayed;          // [B][n_q][L]
+  long long* tokens;           // [B][n_q]
+  int *remaining, *stopping, *out_len;
+  unsigned* bar_counter;       // grid barrier (zero at launch)
+  int mode, n_steps;
+  const bf16* hidden_in;       // MG_MODE_HIDDEN: x <- hidden_in[r, t0 + i, :], row stride hidden_S tokens
+  bf16* hidden_out;            // optional: post-norm_f hidden states, same indexing
+  int hidden_S, hidden_t0;
+  int n_stages;                // ring stages
+  int scratch_bytes;           // activation staging / attention / sampling scratch
+  unsigned long long* dbg;     // optional trace: [grid][MG_TRACE_SLOTS] globaltimer stamps of step dbg_step (thread 0)
+  int dbg_step;
+};
+#define MG_TRACE_SLOTS 64
+__device__ __forceinline__ unsigned long long mg_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define MG_STAMP()                                                                                         \
+  do {                                                                                                     \
+    if (trace && threadIdx.x == 0 && trace_n < MG_TRACE_SLOTS) p.dbg[(size_t)blockIdx.x * MG_TRACE_SLOTS + trace_n++] = mg_globaltimer(); \
+  } while (0)
+
+// ---- PTX helpers ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t mg_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mg_mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mg_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mg_mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mg_mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mg_mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mg_mbar_try_wait(bar, parity)) {}
+}
+// 1-D bulk copy global -> shared, completion counted on an mbarrier (TMA engine, no tensor map needed)
+__device__ __forceinline__ void mg_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ uint4 mg_ldcg16(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ int mg_ld_volatile(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
+
+// ---- grid barrier over the consumer threads of all CTAs -----------------------------------------------------------
+__device__ __forceinline__ void mg_grid_sync(unsigned* counter, unsigned& target) {
+  SyncConsumers::sync();
+  if (threadIdx.x == 0) {
+    target += gridDim.x;
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(counter) : "memory");
+    unsigned v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+    } while (v < target);
+  }
+  SyncConsumers::sync();
+}
+
+// ---- per-CTA context ----------------------------------------------------------------------------------------------
+struct MgCtx {
+  unsigned char* ring;       // n_stages x MG_STAGE_BYTES
+  unsigned char* scratch;    // activation staging etc.
+  float* part;               // [2][2][8 warps][8 r][8 n]
+  float* red;                // [64]
+  float* s_rope;             // [8][128]: (cos, sin) rows of this step's positions
+  float* s_xown;             // [8][MG_OWN]: this CTA's columns of the residual stream
+  int* s_page;               // [8]: KV page of the current position per row
+  uint32_t full0, empty0;    // smem addresses of the barrier arrays
+  int n_stages;
+  int stage, parity;         // ring cursor of this role
+  int tile_flip;             // partial-buffer parity (consumers)
+  bool prof;                 // debug profile on
+  long long t_full;          // clock64 ticks thread 0 spent waiting on full barriers (prof)
+};
+
+__device__ __forceinline__ void mg_advance(MgCtx& cx) {
+  if (++cx.stage == cx.n_stages) { cx.stage = 0; cx.parity ^= 1; }
+}
+
+// Balanced contiguous split of `n_units` over the grid.
+__device__ __forceinline__ void mg_range(int n_units, int& lo, int& hi) {
+  lo = (int)(((long long)n_units * blockIdx.x) / gridDim.x);
+  hi = (int)(((long long)n_units * (blockIdx.x + 1)) / gridDim.x);
+}
+
+// The attention work item of this CTA for context length pos+1: (row, kv head, split) and its token range.
+struct MgAttItem {
+  bool mine;
+  int row, kvh, split, t0, t1, chunk;
+};
+__device__ __forceinline__ MgAttItem mg_att_item(const MegaParams& p, int pos) {
+  MgAttItem it;
+  const int nsplit = p.nsplit;
+  it.mine = (int)blockIdx.x < p.R * p.Hkv * nsplit;
+  it.split = blockIdx.x % nsplit;
+  const int pair = blockIdx.x / nsplit;
+  it.kvh = pair % p.Hkv;
+  it.row = pair / p.Hkv;
+  const int ctx = pos + 1;
+  int chunk = (ctx + nsplit - 1) / nsplit;
+  chunk = (chunk + 7) & ~7;
+  it.chunk = chunk;
+  it.t0 = it.split * chunk;
+  it.t1 = min(ctx, it.t0 + chunk);
+  return it;
+}
+
+// =================================================================================================================
+// producer side: the activation-independent schedule of everything this CTA reads from HBM, as an iterator that
+// yields one ring stage per call (cp.async.bulk into the ring, gated by the empty barriers).  The consumers enumerate
+// the same order with plain nested loops (mg_gemv_phase / mg_stage_ln / mg_attention / the RoPE stage).  (An L2-prefetch
+// cursor running ahead of the load cursor was measured at 0/4/10/20 stages and made no difference: removed.)
+// =================================================================================================================
+
+enum { MG_PH_ROPE = 0, MG_PH_LN1, MG_PH_QKV, MG_PH_KV, MG_PH_OUT, MG_PH_LN2, MG_PH_FC1, MG_PH_FC2, MG_PH_LNF, MG_PH_HEADS, MG_PH_END };
+
+struct MgDesc {              // per-lane view of one stage
+  const void* src;           // nullptr: this lane issues nothing
+  uint32_t bytes;
+  uint32_t dst_off;          // offset inside the stage
+  uint32_t total;            // bytes of the whole stage (warp-uniform)
+};
+
+struct MgSched {
+  int step, l, ph;
+  int n0, nt, kc0, ts;       // cursors inside the current phase
+  bool fresh;                // phase cursors not yet initialised
+  int lo, hi;                // row range of the current tile phase
+  int pos0, rope0;           // KV position at launch; (lane < R) RoPE position of row `lane` at launch
+  bool with_heads, final_ln;
+};
+
+__device__ __forceinline__ void mg_sched_init(MgSched& s, const MegaParams& p, int pos0, int rope0, bool with_heads, bool final_ln) {
+  s.step = 0; s.l = 0; s.ph = MG_PH_ROPE; s.fresh = true;
+  s.n0 = s.nt = s.kc0 = s.ts = 0; s.lo = s.hi = 0;
+  s.pos0 = pos0; s.rope0 = rope0; s.with_heads = with_heads; s.final_ln = final_ln;
+}
+
+__device__ __forceinline__ const bf16* mg_lw(const bf16* base0, long long stride, int l) {
+  return reinterpret_cast<const bf16*>(reinterpret_cast<const char*>(base0) + (long long)l * stride);
+}
+
+// tile-phase parameters
+__device__ __forceinline__ void mg_phase_weights(const MegaParams& p, int l, int ph, const bf16*& W, int& K, int& n_units, int& gate_off,
+                                                 int& NT, int& UNIT) {
+  gate_off = 0; NT = 1; UNIT = 2;
+  switch (ph) {
+    case MG_PH_QKV: W = mg_lw(p.l0.w_in, p.layer_stride, l); K = p.d; n_units = (p.q_size + 2 * p.kv_size) / 2; break;
+    case MG_PH_OUT: W = mg_lw(p.l0.w_out, p.layer_stride, l); K = p.q_size; n_units = p.d / 2; break;
+    case MG_PH_FC1: W = mg_lw(p.l0.w_fc1, p.layer_stride, l); K = p.d; n_units = p.F; gate_off = p.F; NT = 2; UNIT = 1; break;
+    case MG_PH_FC2: W = mg_lw(p.l0.w_fc2, p.layer_stride, l); K = p.F; n_units = p.d / 2; break;
+    default: W = p.heads; K = p.d; n_units = p.n_q * p.V / 2; break;      // MG_PH_HEADS
+  }
+}
+
+// Advance to the next stage of the schedule.  Warp-uniform control flow; returns false at the end of the launch.
+__device__ __forceinline__ bool mg_sched_next(MgSched& s, const MegaParams& p, MgDesc& d) {
+  const int lane = threadIdx.x & 31;
+  d.src = nullptr; d.bytes = 0; d.dst_off = 0; d.total = 0;
+  for (;;) {
+    if (s.step >= p.n_steps) return false;
+    switch (s.ph) {
+      case MG_PH_ROPE: {
+        if (lane < p.R) {
+          d.src = p.rope + (size_t)(s.rope0 + s.step) * (ZB_DH / 2) * 2;
+          d.bytes = MG_ROPE_BYTES; d.dst_off = lane * MG_ROW_BYTES;
+        }
+        d.total = p.R * MG_ROPE_BYTES;
+        s.ph = MG_PH_LN1; s.l = 0;
+        return true;
+      }
+      case MG_PH_LN1: case MG_PH_LN2: case MG_PH_LNF: {
+        const bf16* w = s.ph == MG_PH_LN1 ? mg_lw(p.l0.ln1_w, p.layer_stride, s.l) : s.ph == MG_PH_LN2 ? mg_lw(p.l0.ln2_w, p.layer_stride, s.l) : p.normf_w;
+        const bf16* b = s.ph == MG_PH_LN1 ? mg_lw(p.l0.ln1_b, p.layer_stride, s.l) : s.ph == MG_PH_LN2 ? mg_lw(p.l0.ln2_b, p.layer_stride, s.l) : p.normf_b;
+        if (s.ph == MG_PH_LNF && !(s.with_heads || s.final_ln)) { s.ph = MG_PH_END; break; }
+        if (lane < 2) { d.src = lane == 0 ? w : b; d.bytes = p.d * 2; d.dst_off = lane * MG_ROW_BYTES; }
+        d.total = 2 * p.d * 2;
+        s.ph = s.ph == MG_PH_LNF ? (s.with_heads ? MG_PH_HEADS : MG_PH_END) : s.ph + 1;
+        s.fresh = true;
+        return true;
+      }
+      case MG_PH_KV: {
+        const int pos = s.pos0 + s.step;
+        const MgAttItem it = mg_att_item(p, pos);
+        const int tp = min(it.t1, pos);
+        if (s.fresh) { s.ts = it.t0; s.fresh = false; }
+        if (!it.mine || s.ts >= tp) { s.ph = MG_PH_OUT; s.fresh = true; break; }
+        const int ts = s.ts;
+        const int n = min(MG_KV_TOK, tp - ts);
+        const int n1 = min(n, ZB_PAGE - ts % ZB_PAGE);         // tokens before the page boundary
+        if (lane < 4) {
+          const int run = lane >> 1, isv = lane & 1;
+          const int tb = run == 0 ? ts : ts + n1;
+          const int nn = run == 0 ? n1 : n - n1;
+          if (nn > 0) {
+            const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
+            const size_t kv_stride = (size_t)p.Hkv * head_stride;
+            const int page = p.page_table[(size_t)it.row * p.max_pages + tb / ZB_PAGE];
+            d.src = p.kv + (size_t)s.l * p.kv_layer_elems + (size_t)page * 2 * kv_stride + (size_t)it.kvh * head_stride +
+                    (size_t)(tb % ZB_PAGE) * ZB_DH + (isv ? kv_stride : 0);
+            d.bytes = nn * ZB_DH * 2;
+            d.dst_off = isv * (MG_KV_TOK * ZB_DH * 2) + (tb - ts) * ZB_DH * 2;
+          }
+        }
+        d.total = n * ZB_DH * 2 * 2;
+        s.ts += MG_KV_TOK;
+        return true;
+      }
+      case MG_PH_QKV: case MG_PH_OUT: case MG_PH_FC1: case MG_PH_FC2: case MG_PH_HEADS: {
+        const bf16* W; int K, n_units, gate_off, NT, UNIT;
+        mg_phase_weights(p, s.l, s.ph, W, K, n_units, gate_off, NT, UNIT);
+        if (s.fresh) {
+          mg_range(n_units, s.lo, s.hi);
+          s.lo *= UNIT; s.hi *= UNIT;
+          s.n0 = s.lo; s.nt = 0; s.kc0 = 0; s.fresh = false;
+        }
+        if (s.n0 >= s.hi) {
+          if (s.ph == MG_PH_FC2) {
+            if (++s.l < p.n_layer) s.ph = MG_PH_LN1; else { s.l = p.n_layer - 1; s.ph = MG_PH_LNF; }
+          } else if (s.ph == MG_PH_HEADS) s.ph = MG_PH_END;
+          else s.ph = s.ph + 1;
+          s.fresh = true;
+          break;
+        }
+        const int cnt = min(8, s.hi - s.n0);
+        const int kcs = min(MG_KC, K - s.kc0);
+        if (lane < cnt) {
+          d.src = W + (size_t)(s.n0 + s.nt * gate_off + lane) * K + s.kc0;
+          d.bytes = kcs * 2; d.dst_off = lane * MG_ROW_BYTES;
+        }
+        d.total = cnt * kcs * 2;
+        s.kc0 += MG_KC;
+        if (s.kc0 >= K) { s.kc0 = 0; if (++s.nt == NT) { s.nt = 0; s.n0 += 8; } }
+        return true;
+      }
+      default: {   // MG_PH_END
+        ++s.step; s.l = 0; s.ph = MG_PH_ROPE; s.fresh = true;
+        break;
+      }
+    }
+  }
+}
+
+// =================================================================================================================
+// consumers: ring access
+// =================================================================================================================
+__device__ __forceinline__ const unsigned char* mg_cons_wait(MgCtx& cx) {
+  if (cx.prof && threadIdx.x == 0) {
+    const long long c0 = clock64();
+    mg_mbar_wait(cx.full0 + 8u * cx.stage, cx.parity);
+    cx.t_full += clock64() - c0;
+  } else {
+    mg_mbar_wait(cx.full0 + 8u * cx.stage, cx.parity);
+  }
+  return cx.ring + (size_t)cx.stage * MG_STAGE_BYTES;
+}
+__device__ __forceinline__ void mg_cons_release(MgCtx& cx) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mg_mbar_arrive(cx.empty0 + 8u * cx.stage);
+  mg_advance(cx);
+}
+
+// =================================================================================================================
+// consumers: activation staging
+// =================================================================================================================
+// xs[r][0..K) <- bf16 row r of src (plain copy), rows r < R
+__device__ __forceinline__ void mg_stage_copy(bf16* xs, int ld, const bf16* src, int K, int R) {
+  const int tid = threadIdx.x;
+  for (int r = 0; r < R; ++r)
+    for (int e = tid * 8; e < K; e += MG_CONSUMERS * 8)
+      *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) = mg_ldcg16(src + (size_t)r * K + e);
+  SyncConsumers::sync();
+}
+
+__device__ __forceinline__ void mg_unpack8(const uint4& raw, float (&v)[8]) {
+  v[0] = bf16lo(raw.x); v[1] = bf16hi(raw.x); v[2] = bf16lo(raw.y); v[3] = bf16hi(raw.y);
+  v[4] = bf16lo(raw.z); v[5] = bf16hi(raw.z); v[6] = bf16lo(raw.w); v[7] = bf16hi(raw.w);
+}
+
+// LayerNorm (F.layer_norm: biased variance, eps inside the sqrt, fp32 statistics, bf16 result) of rows r < R of src
+// into xs.  The affine parameters arrive through the ring (stage rows 0 / 1).  K <= 2048 (one uint4 per thread per row).
+// Deliberately NOT unrolled over rows and not inlined: the persistent kernel's per-layer code must stay inside the
+// instruction cache — instruction fetches that miss compete with the saturated weight stream (the first version,
+// 360 KB of SASS, spent ~7 us per LayerNorm waiting on instruction fetch: profiles/r01_mega_trace_v1.md).
+__device__ __noinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const bf16* src, int K, int R, float eps) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int e = tid * 8;
+  const bool active = e < K;
+  float* red = cx.red;              // [64] per-warp partials, [64..72) mean, [72..80) rstd
+  // pass 1: raw rows -> xs, row sums
+  for (int r = 0; r < R; ++r) {
+    uint4 raw = make_uint4(0, 0, 0, 0);
+    if (active) {
+      raw = mg_ldcg16(src + (size_t)r * K + e);
+      *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) = raw;
+    }
+    float v[8];
+    mg_unpack8(raw, v);
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t += v[j];
+    t = warp_sum(t);
+    if (lane == 0) red[warp * 8 + r] = t;
+  }
+  // affine parameters from the ring
+  const unsigned char* sp = mg_cons_wait(cx);
+  uint4 wr = make_uint4(0, 0, 0, 0), br = make_uint4(0, 0, 0, 0);
+  if (active) {
+    wr = *reinterpret_cast<const uint4*>(sp + e * 2);
+    br = *reinterpret_cast<const uint4*>(sp + MG_ROW_BYTES + e * 2);
+  }
+  mg_cons_release(cx);
+  SyncConsumers::sync();
+  if (tid < R) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < MG_WARPS; ++w) t += red[w * 8 + tid];
+    red[64 + tid] = t / (float)K;
+  }
+  SyncConsumers::sync();
+  // pass 2: variance (each thread re-reads its own 16 B from xs)
+  for (int r = 0; r < R; ++r) {
+    const float mean = red[64 + r];
+    float t = 0.f;
+    if (active) {
+      float v[8];
+      mg_unpack8(*reinterpret_cast<const uint4*>(xs + (size_t)r * ld + e), v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const float dlt = v[j] - mean; t += dlt * dlt; }
+    }
+    t = warp_sum(t);
+    if (lane == 0) red[warp * 8 + r] = t;
+  }
+  SyncConsumers::sync();
+  if (tid < R) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < MG_WARPS; ++w) t += red[w * 8 + tid];
+    red[72 + tid] = rsqrtf(t / (float)K + eps);
+  }
+  SyncConsumers::sync();
+  if (active) {
+    float g[8], bb[8];
+    mg_unpack8(wr, g);
+    mg_unpack8(br, bb);
+    for (int r = 0; r < R; ++r) {
+      const float mean = red[64 + r], rstd = red[72 + r];
+      float v[8];
+      mg_unpack8(*reinterpret_cast<const uint4*>(xs + (size_t)r * ld + e), v);
+      __nv_bfloat162 o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float a0 = (v[2 * j] - mean) * rstd * g[2 * j] + bb[2 * j];
+        const float a1 = (v[2 * j + 1] - mean) * rstd * g[2 * j + 1] + bb[2 * j + 1];
+        o[j] = __floats2bfloat162_rn(a0, a1);
+      }
+      *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) = *reinterpret_cast<uint4*>(o);
+    }
+  }
+  SyncConsumers::sync();
+}
+
+// =================================================================================================================
+// consumers: epilogues (same arithmetic as gm_epilogue_* in gemv_mma.cuh).  Store-only: nothing here waits on memory.
+// =================================================================================================================
+struct MgEpi {
+  bf16* out;             // RESID: x; SWIGLU: h; QKV: q
+  int out_stride;
+  bf16* kv_layer;
+  int pos;
+  int own_lo;            // RESID: first residual column owned by this CTA
+  float cfg_scale;
+  int eos_bias;
+  float* logits;
+};
+
+__device__ __forceinline__ void mg_epi_resid(const MgCtx& cx, const MgEpi& e, int a, int n0, float s0, float s1) {
+  // x <- bf16(x + bf16(W a))   (_torch.py:100-101, bf16 residual stream); the old value lives in shared memory
+  float* xo = cx.s_xown + a * MG_OWN + (n0 - e.own_lo);
+  const __nv_bfloat162 o = __floats2bfloat162_rn(xo[0] + bf16_round(s0), xo[1] + bf16_round(s1));
+  *reinterpret_cast<__nv_bfloat162*>(e.out + (size_t)a * e.out_stride + n0) = o;
+  const float2 f = __bfloat1622float2(o);
+  xo[0] = f.x; xo[1] = f.y;
+}
+
+__device__ __forceinline__ void mg_epi_qkv(const MegaParams& p, const MgCtx& cx, const MgEpi& e, int a, int n0, float s0, float s1) {
+  const float v0 = bf16_round(s0), v1 = bf16_round(s1);
+  const int pos = e.pos;
+  if (n0 < p.q_size + p.kv_size) {
+    const int i = (n0 % ZB_DH) >> 1;
+    const float2 cs = *reinterpret_cast<const float2*>(cx.s_rope + a * (ZB_DH) + i * 2);
+    const float o0 = __fsub_rn(__fmul_rn(v0, cs.x), __fmul_rn(v1, cs.y));
+    const float o1 = __fadd_rn(__fmul_rn(v1, cs.x), __fmul_rn(v0, cs.y));
+    const __nv_bfloat162 o = __floats2bfloat162_rn(o0, o1);
+    if (n0 < p.q_size) {
+      *reinterpret_cast<__nv_bfloat162*>(e.out + (size_t)a * e.out_stride + n0) = o;
+    } else {
+      const int m = n0 - p.q_size;
+      const int page = cx.s_page[a];
+      bf16* dst = e.kv_layer + ((((size_t)page * 2 + 0) * p.Hkv + m / ZB_DH) * ZB_PAGE + pos % ZB_PAGE) * ZB_DH + m % ZB_DH;
+      *reinterpret_cast<__nv_bfloat162*>(dst) = o;
+    }
+  } else {
+    const int m = n0 - p.q_size - p.kv_size;
+    const int page = cx.s_page[a];
+    bf16* dst = e.kv_layer + ((((size_t)page * 2 + 1) * p.Hkv + m / ZB_DH) * ZB_PAGE + pos % ZB_PAGE) * ZB_DH + m % ZB_DH;
+    *reinterpret_cast<__nv_bfloat162*>(dst) = __floats2bfloat162_rn(v0, v1);
+  }
+}
+
+__device__ __forceinline__ void mg_epi_heads(const MegaParams& p, const MgEpi& e, int b, int n0, float c0, float c1, float u0, float u1) {
+  const int k = n0 / p.V, n = n0 % p.V;
+  float out[2];
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const float c = bf16_round(j == 0 ? c0 : c1);
+    const float u = bf16_round(j == 0 ? u0 : u1);
+    float l = __fadd_rn(u, __fmul_rn(__fsub_rn(c, u), e.cfg_scale));
+    const int nn = n + j;
+    if (nn >= 1025) l = -INFINITY;
+    if (e.eos_bias && k >= 1 && nn == p.eos) l = -INFINITY;
+    out[j] = l;
+  }
+  *reinterpret_cast<float2*>(e.logits + ((size_t)b * p.n_q + k) * p.V + n) = make_float2(out[0], out[1]);
+}
+
+// =================================================================================================================
+// consumers: one GEMV phase over this CTA's row range.  xs must be staged (and synced) before the call.  ONE copy of
+// this code serves all five weight matrices (runtime epilogue switch): code size matters more than a few branches.
+// =================================================================================================================
+__device__ __noinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, const bf16* xs, int ld, int K, int n_units, int gate_off,
+                                           int kind, const MgEpi& epi) {
+  const int NT = kind == EPI_SWIGLU ? 2 : 1;
+  const int UNIT = kind == EPI_SWIGLU ? 1 : 2;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int R = p.R;
+  int lo, hi;
+  mg_range(n_units, lo, hi);
+  lo *= UNIT; hi *= UNIT;
+  for (int n0 = lo; n0 < hi; n0 += 8) {
+    const int cnt = min(8, hi - n0);
+    float acc[2][4];
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) { acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f; }
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      if (nt < NT) {
+        for (int kc0 = 0; kc0 < K; kc0 += MG_KC) {
+          const int kcs = min(MG_KC, K - kc0);
+          const int slice = kcs >> 3;                  // this warp's columns of the chunk (multiple of 32)
+          const int nkb = slice >> 5;
+          const unsigned char* wp = mg_cons_wait(cx) + g * MG_ROW_BYTES + (warp * slice + t * 8) * 2;
+          const bf16* xp = xs + (size_t)g * ld + kc0 + warp * slice + t * 8;
+#pragma unroll 4
+          for (int j = 0; j < nkb; ++j) {
+            const uint4 wv = *reinterpret_cast<const uint4*>(wp + j * 64);
+            uint4 xv = make_uint4(0, 0, 0, 0);
+            if (g < R) xv = *reinterpret_cast<const uint4*>(xp + j * 32);
+            mma_bf16_16816(acc[nt], xv.x, xv.y, wv.x, wv.y);
+            mma_bf16_16816(acc[nt], xv.z, xv.w, wv.z, wv.w);
+          }
+          mg_cons_release(cx);
+        }
+      }
+    }
+    // ---- reduce the K-slices of the 8 warps, run the epilogue
+    float* pb = cx.part + (size_t)(cx.tile_flip & 1) * 2 * MG_WARPS * 64;
+    cx.tile_flip ^= 1;
+    *reinterpret_cast<float2*>(pb + ((0 * MG_WARPS + warp) * 8 + g) * 8 + 2 * t) = make_float2(acc[0][0], acc[0][1]);
+    if (NT == 2) *reinterpret_cast<float2*>(pb + ((1 * MG_WARPS + warp) * 8 + g) * 8 + 2 * t) = make_float2(acc[1][0], acc[1][1]);
+    SyncConsumers::sync();
+    if (kind == EPI_SWIGLU) {
+      if (tid < R * 8) {
+        const int r = tid >> 3, n = tid & 7;
+        float yv = 0.f, gt = 0.f;
+#pragma unroll
+        for (int w = 0; w < MG_WARPS; ++w) { yv += pb[((0 * MG_WARPS + w) * 8 + r) * 8 + n]; gt += pb[((1 * MG_WARPS + w) * 8 + r) * 8 + n]; }
+        if (n < cnt) {
+          yv = bf16_round(yv);
+          gt = bf16_round(gt);
+          const float sg = bf16_round(gt / (1.0f + expf(-gt)));
+          epi.out[(size_t)r * epi.out_stride + n0 + n] = __float2bfloat16_rn(yv * sg);
+        }
+      }
+    } else if (kind == EPI_HEADS) {
+      const int B = R >> 1;
+      if (tid < B * 4) {
+        const int b = tid >> 2, j = tid & 3;
+        float c0 = 0.f, c1 = 0.f, u0 = 0.f, u1 = 0.f;
+#pragma unroll
+        for (int w = 0; w < MG_WARPS; ++w) {
+          c0 += pb[(w * 8 + b) * 8 + 2 * j]; c1 += pb[(w * 8 + b) * 8 + 2 * j + 1];
+          u0 += pb[(w * 8 + b + B) * 8 + 2 * j]; u1 += pb[(w * 8 + b + B) * 8 + 2 * j + 1];
+        }
+        if (2 * j < cnt) mg_epi_heads(p, epi, b, n0 + 2 * j, c0, c1, u0, u1);
+      }
+    } else {
+      if (tid < R * 4) {
+        const int r = tid >> 2, j = tid & 3;
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int w = 0; w < MG_WARPS; ++w) { s0 += pb[(w * 8 + r) * 8 + 2 * j]; s1 += pb[(w * 8 + r) * 8 + 2 * j + 1]; }
+        if (2 * j < cnt) {
+          if (kind == EPI_QKV) mg_epi_qkv(p, cx, epi, r, n0 + 2 * j, s0, s1);
+          else mg_epi_resid(cx, epi, r, n0 + 2 * j, s0, s1);
+        }
+      }
+    }
+    // no second barrier: the next tile writes the other half of `part`; this half is rewritten only after the NEXT
+    // tile's barrier, which every epilogue thread reaches after finishing its reads.
+  }
+}
+
+// =================================================================================================================
+// consumers: split-KV GQA decode attention for this CTA's (row, kv head, split) item; same arithmetic as
+// k_attn_decode.  K/V of earlier steps arrive through the ring; the row appended in this step is read from L2.
+// =================================================================================================================
+template <int G>
+__device__ __forceinline__ void mg_att_token(const uint4& kraw, const uint4& vraw, bool valid, const float (&q)[G][8], float (&m)[G], float (&l)[G],
+                                             float (&acc)[G][8], float scale_log2) {
+  float kf[8], vf[8];
+  mg_unpack8(kraw, kf);
+  mg_unpack8(vraw, vf);
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s = fmaf(q[g][j], kf[j], s);
+    s += __shfl_xor_sync(0xffffffffu, s, 8);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    if (valid) {
+      s *= scale_log2;
+      const float mn = fmaxf(m[g], s);
+      const float corr = exp2f(m[g] - mn);       // m = -inf on the first token -> 0
+      const float pr = exp2f(s - mn);
+      l[g] = l[g] * corr + pr;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[g][j] = fmaf(pr, vf[j], acc[g][j] * corr);
+      m[g] = mn;
+    }
+  }
+}
+
+template <int G>
+__device__ __noinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const bf16* kv_layer, int pos) {
+  const MgAttItem it = mg_att_item(p, pos);
+  if (!it.mine) return;                               // CTA-uniform
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int half = lane >> 4, l16 = lane & 15;
+  const int nsplit = p.nsplit, row = it.row, kvh = it.kvh, split = it.split;
+  const int ctx = pos + 1;
+
+  float q[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g) mg_unpack8(mg_ldcg16(p.q + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + l16 * 8), q[g]);
+  float m[G], l[G], acc[G][8];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    m[g] = -INFINITY; l[g] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[g][j] = 0.f;
+  }
+  // ---- tokens of earlier steps: MG_KV_TOK per ring stage, a half-warp per token; then ONE extra pass for the row
+  // appended in this step (written by other CTAs in phase 1, read from L2 by warp 0).  A single copy of the token
+  // arithmetic serves both (code size).
+  const int tp = min(it.t1, pos);
+  const bool has_new = it.t0 <= pos && pos < it.t1;
+  const int n_kv_stages = tp > it.t0 ? (tp - it.t0 + MG_KV_TOK - 1) / MG_KV_TOK : 0;
+  for (int si = 0; si < n_kv_stages + (has_new ? 1 : 0); ++si) {
+    const bool fresh = si == n_kv_stages;              // the extra pass
+    const int ts = it.t0 + si * MG_KV_TOK;
+    const int n = fresh ? 1 : min(MG_KV_TOK, tp - ts);
+    const unsigned char* sp = nullptr;
+    if (!fresh) sp = mg_cons_wait(cx);
+    const int i_end = fresh ? (warp == 0 ? 2 : 0) : MG_KV_TOK;
+    for (int i = 2 * warp + half; i < i_end; i += 2 * MG_WARPS) {
+      const bool valid = i < n;
+      uint4 kraw = make_uint4(0, 0, 0, 0), vraw = make_uint4(0, 0, 0, 0);
+      if (valid) {
+        if (fresh) {
+          const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
+          const size_t kv_stride = (size_t)p.Hkv * head_stride;
+          const bf16* kp = kv_layer + (size_t)cx.s_page[row] * 2 * kv_stride + (size_t)kvh * head_stride + (size_t)(pos % ZB_PAGE) * ZB_DH + l16 * 8;
+          kraw = mg_ldcg16(kp);
+          vraw = mg_ldcg16(kp + kv_stride);
+        } else {
+          kraw = *reinterpret_cast<const uint4*>(sp + i * (ZB_DH * 2) + l16 * 16);
+          vraw = *reinterpret_cast<const uint4*>(sp + MG_KV_TOK * ZB_DH * 2 + i * (ZB_DH * 2) + l16 * 16);
+        }
+      }
+      if (__any_sync(0xffffffffu, valid)) mg_att_token<G>(kraw, vraw, valid, q, m, l, acc, p.scale_log2);
+    }
+    if (!fresh) mg_cons_release(cx);
+  }
+  // merge the two half-warps
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const float mo = __shfl_xor_sync(0xffffffffu, m[g], 16);
+    const float lo = __shfl_xor_sync(0xffffffffu, l[g], 16);
+    const float mn = fmaxf(m[g], mo);
+    const float cs = (m[g] == -INFINITY) ? 0.f : exp2f(m[g] - mn);
+    const float co = (mo == -INFINITY) ? 0.f : exp2f(mo - mn);
+    l[g] = l[g] * cs + lo * co;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float ao = __shfl_xor_sync(0xffffffffu, acc[g][j], 16);
+      acc[g][j] = acc[g][j] * cs + ao * co;
+    }
+    m[g] = mn;
+  }
+  // merge the 8 warps through shared memory
+  float* s_o = reinterpret_cast<float*>(cx.scratch);              // [8][G][128]
+  float* s_m = s_o + MG_WARPS * G * ZB_DH;                        // [8][G]
+  float* s_l = s_m + MG_WARPS * G;                                // [8][G]
+  float* s_ml = s_l + MG_WARPS * G;                               // [32 * 8 * 2]
+  int* s_last = reinterpret_cast<int*>(s_ml + 32 * 8 * 2);
+  if (half == 0) {
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s_o[(warp * G + g) * ZB_DH + l16 * 8 + j] = acc[g][j];
+      if (l16 == 0) { s_m[warp * G + g] = m[g]; s_l[warp * G + g] = l[g]; }
+    }
+  }
+  SyncConsumers::sync();
+  const size_t pbase = (((size_t)row * p.Hkv + kvh) * nsplit + split) * G;
+#pragma unroll 1
+  for (int oi = tid; oi < G * ZB_DH; oi += MG_CONSUMERS) {
+    const int g = oi >> 7, dim = oi & (ZB_DH - 1);
+    float mn = -INFINITY;
+#pragma unroll 1
+    for (int w = 0; w < MG_WARPS; ++w) mn = fmaxf(mn, s_m[w * G + g]);
+    float lt = 0.f, ot = 0.f;
+#pragma unroll 1
+    for (int w = 0; w < MG_WARPS; ++w) {
+      const float c = (s_m[w * G + g] == -INFINITY) ? 0.f : exp2f(s_m[w * G + g] - mn);
+      lt += s_l[w * G + g] * c;
+      ot += s_o[(w * G + g) * ZB_DH + dim] * c;
+    }
+    p.part_o[(pbase + g) * ZB_DH + dim] = ot;
+    if (dim == 0) { p.part_ml[(pbase + g) * 2 + 0] = mn; p.part_ml[(pbase + g) * 2 + 1] = lt; }
+  }
+  __threadfence();
+  SyncConsumers::sync();
+  if (tid == 0) {
+    const int ticket = atomicAdd(&p.att_counters[row * p.Hkv + kvh], 1);
+    *s_last = (ticket == nsplit - 1);
+  }
+  SyncConsumers::sync();
+  if (!*s_last) return;                                           // CTA-uniform
+  __threadfence();
+  // ---- the last CTA of this (row, kv head) merges the split partials: ONE cooperative, coalesced L2 read of all of
+  // them into shared memory (a single round trip), then small runtime loops (compact code, see mg_stage_ln).
+  const int nact = min(nsplit, (ctx + it.chunk - 1) / it.chunk);
+  const size_t rbase = ((size_t)row * p.Hkv + kvh) * nsplit * G;
+  float* s_po = s_o;                                              // [nact][G][128]  (<= 16 x G x 128 floats, reuses s_o)
+  float* s_pml = s_ml;                                            // [nact][G][2]
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(p.part_o + rbase * ZB_DH);
+    const int n16 = nact * G * ZB_DH / 4;
+#pragma unroll 4
+    for (int i = tid; i < n16; i += MG_CONSUMERS) reinterpret_cast<uint4*>(s_po)[i] = __ldcg(src + i);
+#pragma unroll 1
+    for (int i = tid; i < nact * G * 2; i += MG_CONSUMERS) s_pml[i] = __ldcg(&p.part_ml[rbase * 2 + i]);
+  }
+  SyncConsumers::sync();
+#pragma unroll 1
+  for (int oi = tid; oi < G * ZB_DH; oi += MG_CONSUMERS) {
+    const int g = oi >> 7, dim = oi & (ZB_DH - 1);
+    float mn = -INFINITY;
+#pragma unroll 1
+    for (int s2 = 0; s2 < nact; ++s2) mn = fmaxf(mn, s_pml[(s2 * G + g) * 2]);
+    float lt = 0.f, ot = 0.f;
+#pragma unroll 1
+    for (int s2 = 0; s2 < nact; ++s2) {
+      const float ms = s_pml[(s2 * G + g) * 2];
+      const float c = (ms == -INFINITY) ? 0.f : exp2f(ms - mn);
+      lt += s_pml[(s2 * G + g) * 2 + 1] * c;
+      ot += s_po[(s2 * G + g) * ZB_DH + dim] * c;
+    }
+    p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + dim] = __float2bfloat16_rn(ot / lt);
+  }
+  if (tid == 0) p.att_counters[row * p.Hkv + kvh] = 0;
+}
+
+// =================================================================================================================
+// consumers: step input
+// =================================================================================================================
+__device__ __noinline__ void mg_embed_row(const MegaParams& p, int b, int col, int L) {
+  // model.py:97-98,141-142: x[b] = x[B+b] = ((E0[c0] + E1[c1]) + ...), sequential bf16 adds.  All table rows are
+  // requested before the first one is used (they are HBM-cold and the memory queues are full of the weight stream).
+  const int d = p.d;
+  for (int e = threadIdx.x * 8; e < d; e += MG_CONSUMERS * 8) {
+    uint4 raw[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      raw[k] = make_uint4(0, 0, 0, 0);
+      if (k < p.n_q) {
+        long long id = __ldcg(p.delayed + ((size_t)b * p.n_q + k) * L + col);
+        id = id < 0 ? 0 : (id >= p.V ? p.V - 1 : id);
+        raw[k] = *reinterpret_cast<const uint4*>(p.emb + ((size_t)k * p.V + id) * d + e);
+      }
+    }
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      if (k < p.n_q) {
+        float v[8];
+        mg_unpack8(raw[k], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = k == 0 ? v[j] : bf16_round(acc[j] + v[j]);
+      }
+    }
+    __nv_bfloat162 o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+    *reinterpret_cast<uint4*>(p.x + (size_t)b * d + e) = *reinterpret_cast<uint4*>(o);
+    *reinterpret_cast<uint4*>(p.x + (size_t)(b + p.B) * d + e) = *reinterpret_cast<uint4*>(o);
+  }
+}
+
+// Once-per-step code kept out of line so that it does not inflate the per-layer instruction footprint.
+__device__ __noinline__ void mg_sample(const SampleParams& sp, int k, int b, unsigned char* scratch) {
+  sample_body<SyncConsumers>(sp, k, b, sample_smem_carve(scratch));
+}
+__device__ __noinline__ void mg_update(const UpdateParams& up, int* s_alive) { update_body<SyncConsumers>(up, s_alive, MG_CONSUMERS); }
+
+// =================================================================================================================
+// the kernel
+// =================================================================================================================
+template <int G>
+__global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_constant__ MegaParams p) {
+  extern __shared__ __align__(128) unsigned char mg_smem[];
+  MgCtx cx;
+  cx.n_stages = p.n_stages;
+  cx.ring = mg_smem;
+  cx.scratch = cx.ring + (size_t)p.n_stages * MG_STAGE_BYTES;
+  cx.part = reinterpret_cast<float*>(cx.scratch + p.scratch_bytes);
+  cx.red = cx.part + 2 * 2 * MG_WARPS * 64;
+  cx.s_rope = cx.red + 96;
+  cx.s_xown = cx.s_rope + 8 * ZB_DH;
+  cx.s_page = reinterpret_cast<int*>(cx.s_xown + 8 * MG_OWN);
+  unsigned char* bars = reinterpret_cast<unsigned char*>(cx.s_page + 16);
+  cx.full0 = mg_smem_u32(bars);
+  cx.empty0 = cx.full0 + 8u * MG_MAX_STAGES;
+  volatile int* s_flags = reinterpret_cast<volatile int*>(bars + 16 * MG_MAX_STAGES);   // [0] stop, [1] consumer cursor, [2] misc
+  cx.stage = 0; cx.parity = 0; cx.tile_flip = 0;
+  cx.prof = p.dbg != nullptr; cx.t_full = 0;
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  if (tid == 0) {
+    for (int s = 0; s < p.n_stages; ++s) { mg_mbar_init(cx.full0 + 8u * s, 1); mg_mbar_init(cx.empty0 + 8u * s, MG_WARPS); }
+    s_flags[0] = 0; s_flags[1] = 0; s_flags[2] = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  const bool with_heads = p.mode == MG_MODE_LOGITS || p.mode == MG_MODE_DECODE;
+  const bool final_ln = p.mode == MG_MODE_HIDDEN && p.hidden_out != nullptr && (int)blockIdx.x < p.R;
+  const int qkv_rows = p.q_size + 2 * p.kv_size;
+  ZbDevState* st = p.st;
+
+  if (warp == MG_WARPS) {
+    // ================================================ producer warp ================================================
+    const int lane = tid & 31;
+    const int pos0 = mg_ld_volatile(&st->pos);
+    const int rope0 = lane < p.R ? p.rope_pos[lane] : 0;
+    if (!mg_ld_volatile(&st->done)) {
+      MgSched ld;
+      mg_sched_init(ld, p, pos0, rope0, with_heads, final_ln);
+      MgDesc d;
+      // optional profile of this warp (clock64 ticks): [0] schedule arithmetic, [1] waiting for a free slot, [2] issue, [3] stages
+      long long t_sched = 0, t_wait = 0, t_issue = 0, n_ld = 0;
+      const bool prof = p.dbg != nullptr;
+      for (;;) {
+        const long long c0 = prof ? clock64() : 0;
+        if (!mg_sched_next(ld, p, d)) break;
+        const long long c1 = prof ? clock64() : 0;
+        // wait for a free ring slot
+        int go = 1;
+        if (lane == 0) {
+          while (!mg_mbar_try_wait(cx.empty0 + 8u * cx.stage, cx.parity ^ 1)) {
+            if (*s_flags) { go = 0; break; }
+          }
+          if (go) mg_mbar_expect_tx(cx.full0 + 8u * cx.stage, d.total);
+        }
+        if (!__shfl_sync(0xffffffffu, go, 0)) break;
+        const long long c2 = prof ? clock64() : 0;
+        if (d.src != nullptr)
+          mg_bulk_g2s(mg_smem_u32(cx.ring + (size_t)cx.stage * MG_STAGE_BYTES + d.dst_off), d.src, d.bytes, cx.full0 + 8u * cx.stage);
+        mg_advance(cx);
+        if (prof) { const long long c3 = clock64(); t_sched += c1 - c0; t_wait += c2 - c1; t_issue += c3 - c2; ++n_ld; }
+      }
+      if (prof && lane == 0) {
+        unsigned long long* o = p.dbg + (size_t)gridDim.x * MG_TRACE_SLOTS + (size_t)blockIdx.x * 8;
+        o[0] = t_sched; o[1] = t_wait; o[2] = t_issue; o[3] = n_ld;
+      }
+    }
+    // ---- drain: wait until the consumers are done, then until every copy this warp issued has landed
+    if (lane == 0) {
+      while (!s_flags[0]) {}
+      __threadfence_block();
+      // stages [consumer cursor, producer cursor) were issued but never consumed
+      int cs = s_flags[1] & 0xffff, cp = (s_flags[1] >> 16) & 1;
+      while (cs != cx.stage || cp != cx.parity) {
+        mg_mbar_wait(cx.full0 + 8u * cs, cp);
+        if (++cs == cx.n_stages) { cs = 0; cp ^= 1; }
+      }
+    }
+    return;
+  }
+
+  // ================================================== consumer warps ==================================================
+  unsigned bar_target = 0;
+  const long long t_kernel0 = clock64();
+  bf16* xs = reinterpret_cast<bf16*>(cx.scratch);
+  const int ld_d = p.d + MG_XPAD, ld_q = p.q_size + MG_XPAD, ld_f = p.F + MG_XPAD;
+  int own_lo, own_hi;                                 // residual-stream columns owned by this CTA (out_proj / fc2 rows)
+  mg_range(p.d / 2, own_lo, own_hi);
+  own_lo *= 2; own_hi *= 2;
+
+  const bool embed_ahead = p.mode == MG_MODE_DECODE || p.mode == MG_MODE_FORCED;
+  for (int step = 0; step < p.n_steps; ++step) {
+    if (mg_ld_volatile(&st->done)) break;
+    const bool trace = p.dbg != nullptr && step == p.dbg_step;
+    int trace_n = 0;
+    MG_STAMP();                                                   // 0: step start
+    const int pos = mg_ld_volatile(&st->pos), col = mg_ld_volatile(&st->col), Lbuf = mg_ld_volatile(&st->L);
+
+    // ---- step input.  In the embedding modes only the first step of a launch embeds here: later steps get x from
+    // CTA 0 at the end of the previous step (right after the frame write-back), which saves a grid barrier per step.
+    const bool input_here = p.mode == MG_MODE_HIDDEN || step == 0 || !embed_ahead;
+    if (p.mode == MG_MODE_HIDDEN) {
+      if ((int)blockIdx.x < p.R) {
+        const int r = blockIdx.x;
+        const bf16* src = p.hidden_in + ((size_t)r * p.hidden_S + p.hidden_t0 + step) * p.d;
+        for (int e = tid * 8; e < p.d; e += MG_CONSUMERS * 8)
+          *reinterpret_cast<uint4*>(p.x + (size_t)r * p.d + e) = *reinterpret_cast<const uint4*>(src + e);
+      }
+    } else if (input_here && (int)blockIdx.x < p.B) {
+      mg_embed_row(p, blockIdx.x, col, Lbuf);
+    }
+    // RoPE rows of this step (ring) and the KV page of the current position
+    {
+      const unsigned char* sp = mg_cons_wait(cx);
+      if (tid < p.R * (MG_ROPE_BYTES / 16)) {
+        const int r = tid / (MG_ROPE_BYTES / 16), c = tid % (MG_ROPE_BYTES / 16);
+        *reinterpret_cast<uint4*>(cx.s_rope + r * ZB_DH + c * 4) = *reinterpret_cast<const uint4*>(sp + r * MG_ROW_BYTES + c * 16);
+      }
+      if (tid < p.R) cx.s_page[tid] = p.page_table[tid * p.max_pages + pos / ZB_PAGE];
+      mg_cons_release(cx);
+    }
+    if (input_here) mg_grid_sync(p.bar_counter, bar_target);
+    MG_STAMP();                                                   // 1: input written + barrier
+    // this CTA's columns of the residual stream (kept in shared memory for the whole step)
+    if (tid < p.R * MG_OWN) {
+      const int r = tid / MG_OWN, i = tid % MG_OWN;
+      if (own_lo + i < own_hi) cx.s_xown[r * MG_OWN + i] = __bfloat162float(__ldcg(p.x + (size_t)r * p.d + own_lo + i));
+    }
+
+    MgEpi epi;
+    epi.pos = pos; epi.own_lo = own_lo;
+    epi.cfg_scale = 0.f; epi.eos_bias = 0; epi.logits = p.logits;
+    for (int l = 0; l < p.n_layer; ++l) {
+      bf16* kv_layer = p.kv + (size_t)l * p.kv_layer_elems;
+      // P1: LN1 + in_proj + RoPE + KV append
+      mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
+      MG_STAMP();                                                 // per layer +0: LN1 staged
+      epi.out = p.q; epi.out_stride = p.q_size; epi.kv_layer = kv_layer;
+      mg_gemv_phase(p, cx, xs, ld_d, p.d, qkv_rows / 2, 0, EPI_QKV, epi);
+      MG_STAMP();                                                 // +1: in_proj done
+      mg_grid_sync(p.bar_counter, bar_target);
+      MG_STAMP();                                                 // +2: barrier
+      // P2: attention
+      mg_attention<G>(p, cx, kv_layer, pos);
+      MG_STAMP();                                                 // +3: attention done
+      mg_grid_sync(p.bar_counter, bar_target);
+      MG_STAMP();                                                 // +4: barrier
+      // P3: out_proj + residual
+      mg_stage_copy(xs, ld_q, p.y, p.q_size, p.R);
+      epi.out = p.x; epi.out_stride = p.d;
+      mg_gemv_phase(p, cx, xs, ld_q, p.q_size, p.d / 2, 0, EPI_RESID, epi);
+      MG_STAMP();                                                 // +5: out_proj done
+      mg_grid_sync(p.bar_counter, bar_target);
+      MG_STAMP();                                                 // +6: barrier
+      // P4: LN2 + fc1 + SwiGLU
+      mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
+      MG_STAMP();                                                 // +7: LN2 staged
+      epi.out = p.h; epi.out_stride = p.F;
+      mg_gemv_phase(p, cx, xs, ld_d, p.d, p.F, p.F, EPI_SWIGLU, epi);
+      MG_STAMP();                                                 // +8: fc1 done
+      mg_grid_sync(p.bar_counter, bar_target);
+      MG_STAMP();                                                 // +9: barrier
+      // P5: fc2 + residual
+      mg_stage_copy(xs, ld_f, p.h, p.F, p.R);
+      MG_STAMP();                                                 // +10: h staged
+      epi.out = p.x; epi.out_stride = p.d;
+      mg_gemv_phase(p, cx, xs, ld_f, p.F, p.d / 2, 0, EPI_RESID, epi);
+      MG_STAMP();                                                 // +11: fc2 done
+      mg_grid_sync(p.bar_counter, bar_target);
+      MG_STAMP();                                                 // +12: barrier
+    }
+
+    if (with_heads) {
+      // final LN + 9 heads + CFG + pad mask (+ logit bias)   (model.py:100-116,266-267,280)
+      mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
+      epi.cfg_scale = *reinterpret_cast<const volatile float*>(&st->cfg_scale);
+      epi.eos_bias = mg_ld_volatile(&st->apply_eos_bias);
+      mg_gemv_phase(p, cx, xs, ld_d, p.d, p.n_q * p.V / 2, 0, EPI_HEADS, epi);
+      mg_grid_sync(p.bar_counter, bar_target);
+      if (p.mode == MG_MODE_DECODE) {
+        if ((int)blockIdx.x < p.n_q * p.B) {
+          SampleParams sp;
+          sp.logits = p.logits; sp.history = p.delayed; sp.hist_stride = Lbuf;
+          sp.hist_len = mg_ld_volatile(&st->use_history) ? col + 1 : 0;
+          sp.tokens = p.tokens; sp.probs_out = nullptr; sp.n_q = p.n_q; sp.V = p.V;
+          const volatile zb_sampling* vs = &st->sp;
+          sp.sp.temperature = vs->temperature; sp.sp.top_p = vs->top_p; sp.sp.top_k = vs->top_k; sp.sp.min_p = vs->min_p;
+          sp.sp.linear = vs->linear; sp.sp.conf = vs->conf; sp.sp.quad = vs->quad;
+          sp.sp.repetition_penalty = vs->repetition_penalty; sp.sp.repetition_penalty_window = vs->repetition_penalty_window;
+          sp.seed = *reinterpret_cast<const volatile unsigned long long*>(&st->seed);
+          sp.step = (unsigned long long)mg_ld_volatile(&st->step);
+          sp.st = nullptr;
+          mg_sample(sp, blockIdx.x % p.n_q, blockIdx.x / p.n_q, cx.scratch);
+          if (tid == 0) {
+            // hint: pull the embedding row of the sampled token into L2 now; CTA 0 gathers it after the write-back
+            long long id = p.tokens[blockIdx.x];
+            id = id < 0 ? 0 : (id >= p.V ? p.V - 1 : id);
+            const bf16* rowp = p.emb + ((size_t)(blockIdx.x % p.n_q) * p.V + id) * p.d;
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(rowp), "r"(p.d * 2) : "memory");
+          }
+        }
+        mg_grid_sync(p.bar_counter, bar_target);
+      }
+    } else if (final_ln) {
+      // plugin-level forward: norm_f of the residual stream (backbone/_torch.py:80)
+      const int r = blockIdx.x;
+      mg_stage_ln(cx, xs, ld_d, p.x + (size_t)r * p.d, p.d, 1, p.eps);
+      bf16* dst = p.hidden_out + ((size_t)r * p.hidden_S + p.hidden_t0 + step) * p.d;
+      for (int e = tid * 8; e < p.d; e += MG_CONSUMERS * 8) *reinterpret_cast<uint4*>(dst + e) = *reinterpret_cast<const uint4*>(xs + e);
+    }
+
+    // ---- advance the device state (CTA 0), then make it visible to everyone
+    if (blockIdx.x == 0) {
+      if (p.mode == MG_MODE_DECODE) {
+        UpdateParams up;
+        up.st = st; up.delayed = p.delayed; up.tokens = p.tokens; up.remaining = p.remaining; up.stopping = p.stopping;
+        up.out_len = p.out_len; up.rope_pos = p.rope_pos; up.rows = p.R; up.n_q = p.n_q; up.eos = p.eos; up.mask = p.mask_tok;
+        mg_update(up, const_cast<int*>(&s_flags[2]));
+      } else {
+        if (tid == 0) {
+          st->pos = pos + 1;
+          if (p.mode == MG_MODE_FORCED) st->col = col + 1;
+        }
+        for (int r = tid; r < p.R; r += MG_CONSUMERS) p.rope_pos[r] += 1;
+      }
+      if (embed_ahead && step + 1 < p.n_steps) {
+        SyncConsumers::sync();                                    // the frame write-back above is visible CTA-wide
+        if (!mg_ld_volatile(&st->done))
+          for (int b = 0; b < p.B; ++b) mg_embed_row(p, b, col + 1, Lbuf);
+      }
+    }
+    mg_grid_sync(p.bar_counter, bar_target);
+  }
+
+  // ---- tell the producer where the consumers stopped
+  SyncConsumers::sync();
+  if (cx.prof && tid == 0) {
+    unsigned long long* o = p.dbg + (size_t)gridDim.x * MG_TRACE_SLOTS + (size_t)blockIdx.x * 8;
+    o[4] = cx.t_full; o[5] = clock64() - t_kernel0;
+  }
+  if (tid == 0) {
+    s_flags[1] = cx.stage | (cx.parity << 16);
+    __threadfence_block();
+    s_flags[0] = 1;
+  }
+}

@@ -24,27 +24,30 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
 // uniform in (0, 1]
 __device__ __forceinline__ float u01(uint32_t r) { return ((float)(r >> 8) + 1.0f) * (1.0f / 16777216.0f); }
 
+template <class Sync>
 __device__ __forceinline__ float block_reduce_sum(float v, float* red) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   v = warp_sum(v);
-  __syncthreads();
+  Sync::sync();
   if (lane == 0) red[warp] = v;
-  __syncthreads();
+  Sync::sync();
   float t = 0.f;
   for (int w = 0; w < SMP_THREADS / 32; ++w) t += red[w];
   return t;
 }
+template <class Sync>
 __device__ __forceinline__ float block_reduce_max(float v, float* red) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   v = warp_max(v);
-  __syncthreads();
+  Sync::sync();
   if (lane == 0) red[warp] = v;
-  __syncthreads();
+  Sync::sync();
   float t = -INFINITY;
   for (int w = 0; w < SMP_THREADS / 32; ++w) t = fmaxf(t, red[w]);
   return t;
 }
 // argmax with first-index tie break (torch.argmax)
+template <class Sync>
 __device__ __forceinline__ int block_argmax(float v, int idx, float* red, int* redi) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -53,9 +56,9 @@ __device__ __forceinline__ int block_argmax(float v, int idx, float* red, int* r
     const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
     if (ov > v || (ov == v && oi < idx)) { v = ov; idx = oi; }
   }
-  __syncthreads();
+  Sync::sync();
   if (lane == 0) { red[warp] = v; redi[warp] = idx; }
-  __syncthreads();
+  Sync::sync();
   float bv = red[0]; int bi = redi[0];
   for (int w = 1; w < SMP_THREADS / 32; ++w)
     if (red[w] > bv || (red[w] == bv && redi[w] < bi)) { bv = red[w]; bi = redi[w]; }
@@ -75,16 +78,36 @@ struct SampleParams {
   const ZbDevState* st;         // non-NULL: sampling params / history bounds / seed / step come from device state
 };
 
-// grid = (n_q, B), block = SMP_THREADS
-__global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
-  pdl_launch_dependents();
-  pdl_wait_prior_grid();
-  __shared__ float s_p[SMP_MAXV];
-  __shared__ float s_key[SMP_MAXV];
-  __shared__ int s_idx[SMP_MAXV];
-  __shared__ float red[SMP_THREADS / 32];
-  __shared__ int redi[SMP_THREADS / 32];
-  __shared__ float s_kth;
+// Shared-memory scratch of one sampling block (SMP_THREADS threads): 3 * SMP_MAXV * 4 + 80 bytes.
+struct SampleSmem {
+  float* s_p;      // [SMP_MAXV]
+  float* s_key;    // [SMP_MAXV]
+  int* s_idx;      // [SMP_MAXV]
+  float* red;      // [SMP_THREADS / 32]
+  int* redi;       // [SMP_THREADS / 32]
+  float* s_kth;    // [1]
+};
+#define SMP_SMEM_BYTES (3 * SMP_MAXV * 4 + 2 * (SMP_THREADS / 32) * 4 + 16)
+__device__ __forceinline__ SampleSmem sample_smem_carve(unsigned char* base) {
+  SampleSmem m;
+  m.s_p = reinterpret_cast<float*>(base);
+  m.s_key = m.s_p + SMP_MAXV;
+  m.s_idx = reinterpret_cast<int*>(m.s_key + SMP_MAXV);
+  m.red = reinterpret_cast<float*>(m.s_idx + SMP_MAXV);
+  m.redi = reinterpret_cast<int*>(m.red + SMP_THREADS / 32);
+  m.s_kth = reinterpret_cast<float*>(m.redi + SMP_THREADS / 32);
+  return m;
+}
+
+// One sampling block = threads 0..SMP_THREADS-1 of the CTA, all of which must call this (block-uniform control flow);
+// Sync::sync() is the barrier over exactly those threads.  (k, b) = (codebook, utterance).
+template <class Sync>
+__device__ void sample_body(const SampleParams& p, const int k, const int b, const SampleSmem& sm) {
+  float* const s_p = sm.s_p;
+  float* const s_key = sm.s_key;
+  int* const s_idx = sm.s_idx;
+  float* const red = sm.red;
+  int* const redi = sm.redi;
 
   zb_sampling sp = p.sp;
   unsigned long long seed = p.seed, step = p.step;
@@ -94,7 +117,7 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
     sp = p.st->sp; seed = p.st->seed; step = (unsigned long long)p.st->step;
     hist_len = p.st->use_history ? p.st->col + 1 : 0;      // generated_tokens = delayed[..., :offset], offset = col+1
   }
-  const int k = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, V = p.V;
+  const int tid = threadIdx.x, V = p.V;
   const float* lg = p.logits + ((size_t)b * p.n_q + k) * V;
 
   // ---- repetition penalty (sampling.py:99-114): factor = penalty^(#occurrences in the window), ids clamped to V-1
@@ -102,7 +125,7 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
 #pragma unroll
   for (int j = 0; j < SMP_PER; ++j) {
     const int i = tid + j * SMP_THREADS;
-    x[j] = i < V ? lg[i] : -INFINITY;
+    x[j] = i < V ? __ldcg(lg + i) : -INFINITY;
   }
   // factor = penalty^count by repeated multiplication, exactly like scatter_reduce(prod) over ones.
   if (sp.repetition_penalty != 1.0f && p.history != nullptr && hist_len > 0) {
@@ -114,11 +137,11 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
       if (i < V) {
         float f = 1.0f;
         for (int w = 0; w < win; ++w) {
-          long long tok = h[hist_len - win + w];
+          long long tok = __ldcg(h + hist_len - win + w);
           if (tok > V - 1) tok = V - 1;
           if ((long long)i == tok) f *= sp.repetition_penalty;
         }
-        const float raw = lg[i];
+        const float raw = __ldcg(lg + i);
         x[j] = raw <= 0.f ? raw * f : raw / f;
       }
     }
@@ -130,11 +153,11 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
     float mx = -INFINITY;
 #pragma unroll
     for (int j = 0; j < SMP_PER; ++j) { x[j] = x[j] / sp.temperature; mx = fmaxf(mx, x[j]); }
-    mx = block_reduce_max(mx, red);
+    mx = block_reduce_max<Sync>(mx, red);
     float sum = 0.f;
 #pragma unroll
     for (int j = 0; j < SMP_PER; ++j) { x[j] = (tid + j * SMP_THREADS < V) ? expf(x[j] - mx) : 0.f; sum += x[j]; }
-    sum = block_reduce_sum(sum, red);
+    sum = block_reduce_sum<Sync>(sum, red);
 #pragma unroll
     for (int j = 0; j < SMP_PER; ++j) x[j] = x[j] / sum;
 
@@ -147,7 +170,7 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
         lp[j] = logf(fmaxf(x[j], 1e-20f));
         if (tid + j * SMP_THREADS < V) ent += x[j] * lp[j];
       }
-      ent = -block_reduce_sum(ent, red);
+      ent = -block_reduce_sum<Sync>(ent, red);
       float mx2 = -INFINITY;
 #pragma unroll
       for (int j = 0; j < SMP_PER; ++j) {
@@ -155,11 +178,11 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
         x[j] = (tid + j * SMP_THREADS < V) ? raw : -INFINITY;
         mx2 = fmaxf(mx2, x[j]);
       }
-      mx2 = block_reduce_max(mx2, red);
+      mx2 = block_reduce_max<Sync>(mx2, red);
       float sum2 = 0.f;
 #pragma unroll
       for (int j = 0; j < SMP_PER; ++j) { x[j] = (tid + j * SMP_THREADS < V) ? expf(x[j] - mx2) : 0.f; sum2 += x[j]; }
-      sum2 = block_reduce_sum(sum2, red);
+      sum2 = block_reduce_sum<Sync>(sum2, red);
 #pragma unroll
       for (int j = 0; j < SMP_PER; ++j) x[j] = x[j] / sum2;
     }
@@ -173,7 +196,7 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
         s_idx[i] = i;
         s_p[i] = i < V ? x[j] : 0.f;
       }
-      __syncthreads();
+      Sync::sync();
       for (int size = 2; size <= SMP_MAXV; size <<= 1) {
         for (int strd = size >> 1; strd > 0; strd >>= 1) {
           for (int t = tid; t < SMP_MAXV / 2; t += SMP_THREADS) {
@@ -186,7 +209,7 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
             const bool a_first = (a > c) || (a == c && ia < ic);
             if (a_first != desc) { s_key[lo] = c; s_key[hi] = a; s_idx[lo] = ic; s_idx[hi] = ia; }
           }
-          __syncthreads();
+          Sync::sync();
         }
       }
       if (sp.top_p > 0.f) {
@@ -201,24 +224,24 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
             if (drop) s_p[s_idx[r]] = 0.f;
           }
         }
-        __syncthreads();
+        Sync::sync();
         float sum3 = 0.f;
 #pragma unroll
         for (int j = 0; j < SMP_PER; ++j) { const int i = tid + j * SMP_THREADS; x[j] = i < V ? s_p[i] : 0.f; sum3 += x[j]; }
-        sum3 = block_reduce_sum(sum3, red);
+        sum3 = block_reduce_sum<Sync>(sum3, red);
 #pragma unroll
         for (int j = 0; j < SMP_PER; ++j) { x[j] = x[j] / sum3; const int i = tid + j * SMP_THREADS; if (i < V) s_p[i] = x[j]; }
-        __syncthreads();
+        Sync::sync();
       }
       if (sp.top_k > 0) {
         // pivot = k-th largest CURRENT probability; order is unchanged by the monotone steps above
-        if (tid == 0) s_kth = s_p[s_idx[min(sp.top_k, V) - 1]];
-        __syncthreads();
-        const float kth = s_kth;
+        if (tid == 0) *sm.s_kth = s_p[s_idx[min(sp.top_k, V) - 1]];
+        Sync::sync();
+        const float kth = *sm.s_kth;
         float sum4 = 0.f;
 #pragma unroll
         for (int j = 0; j < SMP_PER; ++j) { if (x[j] < kth) x[j] = 0.f; sum4 += x[j]; }
-        sum4 = block_reduce_sum(sum4, red);
+        sum4 = block_reduce_sum<Sync>(sum4, red);
 #pragma unroll
         for (int j = 0; j < SMP_PER; ++j) x[j] = x[j] / sum4;
       }
@@ -228,12 +251,12 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
       float top = 0.f;
 #pragma unroll
       for (int j = 0; j < SMP_PER; ++j) top = fmaxf(top, x[j]);
-      top = block_reduce_max(top, red);
+      top = block_reduce_max<Sync>(top, red);
       const float thr = sp.min_p * top;
       float sum5 = 0.f;
 #pragma unroll
       for (int j = 0; j < SMP_PER; ++j) { if (x[j] < thr) x[j] = 0.f; sum5 += x[j]; }
-      sum5 = block_reduce_sum(sum5, red);
+      sum5 = block_reduce_sum<Sync>(sum5, red);
 #pragma unroll
       for (int j = 0; j < SMP_PER; ++j) x[j] = x[j] / sum5;
     }
@@ -258,7 +281,7 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
         if (sc > best || (sc == best && i < besti)) { best = sc; besti = i; }
       }
     }
-    token = block_argmax(best, besti, red, redi);
+    token = block_argmax<Sync>(best, besti, red, redi);
   } else {
     // greedy: argmax of the (penalised) logits, first index on ties (sampling.py:180)
     float best = -INFINITY; int besti = 0x7fffffff;
@@ -267,7 +290,7 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
       const int i = tid + j * SMP_THREADS;
       if (i < V && (x[j] > best || (x[j] == best && i < besti) || besti == 0x7fffffff)) { best = x[j]; besti = i; }
     }
-    token = block_argmax(best, besti, red, redi);
+    token = block_argmax<Sync>(best, besti, red, redi);
     if (p.probs_out) {
 #pragma unroll
       for (int j = 0; j < SMP_PER; ++j) {
@@ -277,6 +300,14 @@ __global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
     }
   }
   if (tid == 0) p.tokens[(size_t)b * p.n_q + k] = token;
+}
+
+// grid = (n_q, B), block = SMP_THREADS
+__global__ void __launch_bounds__(SMP_THREADS) k_sample(const SampleParams p) {
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+  __shared__ __align__(16) unsigned char s_raw[SMP_SMEM_BYTES];
+  sample_body<SyncCta>(p, blockIdx.x, blockIdx.y, sample_smem_carve(s_raw));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -296,20 +327,20 @@ struct UpdateParams {
   int eos, mask;
 };
 
-__global__ void k_update(const UpdateParams p) {
-  pdl_launch_dependents();
-  pdl_wait_prior_grid();
+// One block; threads 0..nthreads-1 all call it.  `s_alive` is one int of shared memory.
+template <class Sync>
+__device__ void update_body(const UpdateParams& p, int* s_alive_p, const int nthreads) {
   ZbDevState* st = p.st;
   if (st->done) return;
-  __shared__ int s_alive;
+  int& s_alive = *s_alive_p;
   if (threadIdx.x == 0) s_alive = 0;
-  __syncthreads();
+  Sync::sync();
   const int B = st->B, L = st->L, col = st->col, wcol = col + 1, nq = p.n_q;
-  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+  for (int b = threadIdx.x; b < B; b += nthreads) {
     int rem = p.remaining[b];
     if (rem > 0) {                                    // finished utterances are frozen (independent batch-1 runs)
       long long tok[16];
-      for (int k = 0; k < nq; ++k) tok[k] = p.tokens[(size_t)b * nq + k];
+      for (int k = 0; k < nq; ++k) tok[k] = __ldcg(p.tokens + (size_t)b * nq + k);
       if (st->eos_logic) {
         if (tok[0] == p.eos) { rem = min(rem, nq); p.stopping[b] = 1; }
         if (p.stopping[b]) {
@@ -333,14 +364,21 @@ __global__ void k_update(const UpdateParams p) {
       if (rem > 0) atomicOr(&s_alive, 1);
     }
   }
-  __syncthreads();
+  Sync::sync();
   if (threadIdx.x == 0) {
     st->col = wcol;
     st->pos += 1;
     st->step += 1;
     if (st->eos_logic && !s_alive) st->done = 1;
   }
-  for (int r = threadIdx.x; r < p.rows; r += blockDim.x) p.rope_pos[r] += 1;
+  for (int r = threadIdx.x; r < p.rows; r += nthreads) p.rope_pos[r] += 1;
+}
+
+__global__ void k_update(const UpdateParams p) {
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+  __shared__ int s_alive;
+  update_body<SyncCta>(p, &s_alive, (int)blockDim.x);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -9,6 +9,7 @@
 #include "attention_kernels.cuh"
 #include "decode_kernels.cuh"
 #include "gemv_mma.cuh"
+#include "mega_kernel.cuh"
 #include "sample_kernels.cuh"
 
 int ZbErr::fail(int code, const char* fmt, ...) {
@@ -83,6 +84,16 @@ struct zb_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool ev_valid = false;
   cudaStream_t cap_stream = nullptr;   // capture happens here: the caller's stream may be the legacy default stream
+  // persistent decode kernel (mega_kernel.cuh)
+  MegaLayer mega_l0{};
+  long long mega_layer_stride = 0;
+  bool mega_ok = false;
+  unsigned* bar_counter = nullptr;
+  int n_sms = ZB_NUM_SMS;
+  int smem_optin = 0;
+  int opt_mega = 1;
+  int opt_trace = 0;                   // debug: print a per-phase timeline of one step of every persistent launch
+  unsigned long long* dbg = nullptr;
 };
 
 namespace {
@@ -323,6 +334,108 @@ cudaError_t enqueue_decode_step(zb_ctx* c, cudaStream_t s) {
   return cudaSuccess;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// persistent decode kernel
+// ---------------------------------------------------------------------------------------------------------------
+typedef void (*MegaKernel)(const MegaParams);
+MegaKernel mega_kernel(int G) {
+  switch (G) {
+    case 1: return k_decode_mega<1>;
+    case 2: return k_decode_mega<2>;
+    case 4: return k_decode_mega<4>;
+    case 8: return k_decode_mega<8>;
+  }
+  return nullptr;
+}
+
+bool use_mega(const zb_ctx* c, int rows) {
+  const int own = 2 * ((c->cfg.d_model / 2 + c->n_sms - 1) / c->n_sms);     // residual columns per CTA kept in shared memory
+  return c->opt_mega && rows >= 1 && rows <= 8 && c->mega_ok && own <= MG_OWN;
+}
+
+// mode: MG_MODE_*.  R activation rows (= 2B in the CFG modes).  One cooperative launch runs `n_steps` steps.
+cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* logits, const void* hidden_in, void* hidden_out,
+                        int hidden_S, int hidden_t0, cudaStream_t s) {
+  const zb_config& g = c->cfg;
+  const int G = g.num_heads / g.num_heads_kv;
+  MegaParams p;
+  memset(&p, 0, sizeof(p));
+  p.l0 = c->mega_l0; p.layer_stride = c->mega_layer_stride; p.n_layer = g.n_layer; p.d = g.d_model; p.q_size = g.num_heads * ZB_DH; p.kv_size = g.num_heads_kv * ZB_DH;
+  p.F = g.ffn; p.H = g.num_heads; p.Hkv = g.num_heads_kv;
+  p.normf_w = c->normf_w; p.normf_b = c->normf_b; p.heads = c->heads; p.emb = c->emb; p.rope = c->rope;
+  p.n_q = g.n_codebooks; p.V = g.vocab; p.eos = g.eos_token_id; p.mask_tok = g.masked_token_id;
+  p.eps = g.norm_eps; p.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
+  p.x = c->x; p.q = c->q; p.y = c->y; p.h = c->h; p.logits = logits ? logits : c->logits;
+  p.kv = c->kv; p.kv_layer_elems = c->kv_layer_elems; p.page_table = c->page_table; p.max_pages = c->max_pages;
+  p.part_o = c->part_o; p.part_ml = c->part_ml; p.att_counters = c->counters;
+  int ns = c->n_sms / (R * g.num_heads_kv);
+  ns = ns < 1 ? 1 : (ns > c->nsplit ? c->nsplit : ns);
+  if (ns > MG_MAX_SPLIT) ns = MG_MAX_SPLIT;
+  p.nsplit = ns;
+  p.R = R; p.B = B; p.st = c->st; p.rope_pos = c->rope_pos; p.delayed = c->delayed; p.tokens = c->tokens;
+  p.remaining = c->remaining; p.stopping = c->stopping; p.out_len = c->out_len; p.bar_counter = c->bar_counter;
+  p.mode = mode; p.n_steps = n_steps;
+  p.hidden_in = (const bf16*)hidden_in; p.hidden_out = (bf16*)hidden_out; p.hidden_S = hidden_S; p.hidden_t0 = hidden_t0;
+  // shared memory plan: [ring][scratch][partials 8 KB][red 256 B][barriers][flags]
+  int maxK = g.d_model > p.q_size ? g.d_model : p.q_size;
+  if (g.ffn > maxK) maxK = g.ffn;
+  size_t scratch = (size_t)R * (maxK + MG_XPAD) * 2;
+  const size_t att = ((size_t)MG_WARPS * G * ZB_DH + 2 * MG_WARPS * G + 32 * 8 * 2) * 4 + 16;
+  if (att > scratch) scratch = att;
+  if ((size_t)SMP_SMEM_BYTES > scratch) scratch = SMP_SMEM_BYTES;
+  scratch = align_up(scratch, 128);
+  const size_t fixed = 2 * 2 * MG_WARPS * 64 * 4 + 96 * 4 + 8 * ZB_DH * 4 + 8 * MG_OWN * 4 + 64 + 16 * MG_MAX_STAGES + 64;
+  int stages = (int)(((size_t)c->smem_optin - scratch - fixed) / MG_STAGE_BYTES);
+  if (stages > MG_MAX_STAGES) stages = MG_MAX_STAGES;
+  if (stages < 2) return cudaErrorInvalidConfiguration;
+  p.n_stages = stages; p.scratch_bytes = (int)scratch;
+  const size_t smem = (size_t)stages * MG_STAGE_BYTES + scratch + fixed;
+
+  cudaError_t e = cudaMemsetAsync(c->bar_counter, 0, sizeof(unsigned), s);
+  if (e != cudaSuccess) return e;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(c->n_sms);
+  cfg.blockDim = dim3(MG_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;       // all CTAs co-resident: they meet at grid barriers
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (c->counting) c->launches += 1;
+  if (c->opt_trace) {
+    const size_t nb = (size_t)c->n_sms * (MG_TRACE_SLOTS + 8) * sizeof(unsigned long long);
+    if (!c->dbg && (e = cudaMalloc(&c->dbg, nb)) != cudaSuccess) return e;
+    cudaMemsetAsync(c->dbg, 0, nb, s);
+    p.dbg = c->dbg; p.dbg_step = n_steps / 2;
+    e = cudaLaunchKernelEx(&cfg, mega_kernel(G), p);
+    if (e != cudaSuccess) return e;
+    std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8));
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
+    cudaMemcpy(hbuf.data(), c->dbg, nb, cudaMemcpyDeviceToHost);
+    const int ctas[3] = {0, c->n_sms / 2, c->n_sms - 1};
+    fprintf(stderr, "[mega trace] mode %d steps %d step %d: ns since step start (cta %d / %d / %d)\n", mode, n_steps, p.dbg_step, ctas[0], ctas[1], ctas[2]);
+    for (int i = 0; i < MG_TRACE_SLOTS; ++i) {
+      if (!hbuf[i]) break;
+      fprintf(stderr, "  slot %2d:", i);
+      for (int j = 0; j < 3; ++j) {
+        const unsigned long long* row = hbuf.data() + (size_t)ctas[j] * MG_TRACE_SLOTS;
+        fprintf(stderr, " %9lld (+%6lld)", (long long)(row[i] - hbuf[0]), i ? (long long)(row[i] - row[i - 1]) : 0LL);
+      }
+      fprintf(stderr, "\n");
+    }
+    // whole-launch profile of the producer warp / consumer thread 0 (clock64 ticks)
+    for (int j = 0; j < 3; ++j) {
+      const unsigned long long* o = hbuf.data() + (size_t)c->n_sms * MG_TRACE_SLOTS + (size_t)ctas[j] * 8;
+      fprintf(stderr, "  [prof cta %3d] producer: sched %llu wait_empty %llu issue %llu ticks over %llu stages | consumer: wait_full %llu of %llu ticks\n",
+              ctas[j], o[0], o[1], o[2], o[3], o[4], o[5]);
+    }
+    return cudaSuccess;
+  }
+  return cudaLaunchKernelEx(&cfg, mega_kernel(G), p);
+}
+
 void drop_graph(zb_ctx* c) {
   if (c->graph) { cudaGraphExecDestroy(c->graph); c->graph = nullptr; }
   c->graph_nodes = 0;
@@ -425,21 +538,43 @@ int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) {
   c->step_weight_bytes = (int64_t)nl * ((int64_t)qkv * d + (int64_t)d * d + (int64_t)2 * F * d + (int64_t)d * F + 4 * d) * 2 +
                          (int64_t)2 * d * 2 + (int64_t)cfg->n_codebooks * (cfg->vocab - 1) * d * 2;
 
-  // opt-in to large dynamic shared memory for every GEMV instantiation
-  const size_t max_smem = gemv_smem(8, F > d ? F : d);
+  // opt-in to large dynamic shared memory for every GEMV instantiation.  The attribute is per FUNCTION (shared by all
+  // contexts of the process), so it is always raised to the device maximum: a context for a small config created
+  // after a large one must not shrink it.
+  const int max_smem = (int)prop.sharedMemPerBlockOptin;
   for (int R = 2; R <= 8; R += 2)
-    for (int epi = 0; epi < 4; ++epi)
-      if ((e = cudaFuncSetAttribute(gemv_kernel(R, epi), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)max_smem)) != cudaSuccess) {
+    for (int epi = 0; epi < 4; ++epi) {
+      if ((e = cudaFuncSetAttribute(gemv_kernel(R, epi), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
+          (e = cudaFuncSetAttribute(gemv_mma_kernel(R, epi), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess) {
         cudaFree(c->arena); delete c;
         return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
       }
-  for (int R = 2; R <= 8; R += 2)
-    for (int epi = 0; epi < 4; ++epi)
-      if ((e = cudaFuncSetAttribute(gemv_mma_kernel(R, epi), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)gemv_mma_smem(8, F > d ? F : d, EPI_SWIGLU))) != cudaSuccess) {
-        cudaFree(c->arena); delete c;
-        return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute(mma): ") + cudaGetErrorString(e));
-      }
+    }
+  c->n_sms = prop.multiProcessorCount;
+  c->smem_optin = max_smem;
+  for (int G2 = 1; G2 <= 8; G2 *= 2)
+    if ((e = cudaFuncSetAttribute(mega_kernel(G2), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess) {
+      cudaFree(c->arena); delete c;
+      return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute(mega): ") + cudaGetErrorString(e));
+    }
+  {
+    // the persistent kernel addresses layer l as layer 0 + l * stride: check that the arena really is layer-periodic
+    const LayerW& w0 = c->layers[0];
+    c->mega_l0 = MegaLayer{w0.ln1_w, w0.ln1_b, w0.w_in, w0.w_out, w0.ln2_w, w0.ln2_b, w0.w_fc1, w0.w_fc2};
+    c->mega_layer_stride = nl > 1 ? (long long)((const char*)c->layers[1].ln1_w - (const char*)w0.ln1_w) : 0;
+    c->mega_ok = true;
+    for (int l = 0; l < nl; ++l) {
+      const LayerW& w = c->layers[l];
+      const bf16* a[8] = {w.ln1_w, w.ln1_b, w.w_in, w.w_out, w.ln2_w, w.ln2_b, w.w_fc1, w.w_fc2};
+      const bf16* b[8] = {w0.ln1_w, w0.ln1_b, w0.w_in, w0.w_out, w0.ln2_w, w0.ln2_b, w0.w_fc1, w0.w_fc2};
+      for (int i = 0; i < 8; ++i)
+        if ((const char*)a[i] != (const char*)b[i] + (long long)l * c->mega_layer_stride) c->mega_ok = false;
+    }
+    if ((e = cudaMalloc(&c->bar_counter, 256)) != cudaSuccess) {
+      cudaFree(c->arena); delete c;
+      return bad(ZB_ERR_NOMEM, std::string("barrier counter: ") + cudaGetErrorString(e));
+    }
+  }
   if ((e = cudaMalloc(&c->st, sizeof(ZbDevState))) != cudaSuccess) { cudaFree(c->arena); delete c; return bad(ZB_ERR_NOMEM, cudaGetErrorString(e)); }
   cudaMemset(c->st, 0, sizeof(ZbDevState));
   cudaEventCreate(&c->ev0);
@@ -456,6 +591,8 @@ int zb_ctx_destroy(zb_ctx* c) {
   free_kv(c);
   if (c->arena) cudaFree(c->arena);
   if (c->st) cudaFree(c->st);
+  if (c->bar_counter) cudaFree(c->bar_counter);
+  if (c->dbg) cudaFree(c->dbg);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
   if (c->cap_stream) cudaStreamDestroy(c->cap_stream);
@@ -558,6 +695,11 @@ int zb_backbone_forward(zb_ctx* c, const void* d_in, void* d_out, int rows, int 
   cudaStream_t s = (cudaStream_t)stream;
   ZB_CUDA(c->err, cudaSetDevice(c->device));
   const zb_config& g = c->cfg;
+  if (use_mega(c, rows)) {
+    ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, seqlen_offset, (const int*)d_lengths, 0));
+    ZB_CUDA(c->err, launch_mega(c, MG_MODE_HIDDEN, S, rows, 0, nullptr, d_in, d_out, S, 0, s));   // advances pos / rope_pos by S
+    return ZB_OK;
+  }
   const std::vector<Pass> passes = plain_passes(rows);
   int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
   for (int t = 0; t < S; ++t) {
@@ -629,6 +771,14 @@ int zb_decode_logits(zb_ctx* c, const int64_t* d_delayed, int B, int L, int col,
   h.col = col; h.L = L; h.B = B; h.done = 0; h.cfg_scale = cfg_scale; h.apply_eos_bias = apply_eos_bias;
   if ((rc = upload_state(c, h, s))) return rc;
   c->B = B; c->L = L;
+  if (use_mega(c, 2 * B)) {
+    long long* keep = c->delayed;
+    c->delayed = (long long*)d_delayed;
+    cudaError_t em = launch_mega(c, MG_MODE_LOGITS, 1, 2 * B, B, d_logits_out, nullptr, nullptr, 0, 0, s);
+    c->delayed = keep;
+    ZB_CUDA(c->err, em);
+    return ZB_OK;
+  }
   const std::vector<Pass> passes = cfg_passes(B);
   int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
   ZB_CUDA(c->err, launch(c, k_embed, dim3(B), dim3(thr), 0, s, (const bf16*)c->emb, (const long long*)d_delayed, c->x,
@@ -664,30 +814,40 @@ int zb_gen_begin(zb_ctx* c, const void* d_prefix, int B, int Lc, int64_t* d_dela
   ZB_CUDA(c->err, cudaMemcpyAsync(c->remaining, rem.data(), (size_t)B * 4, cudaMemcpyHostToDevice, s));
   ZB_CUDA(c->err, cudaStreamSynchronize(s));                          // `rem` is host-stack memory
 
+  const bool mega = use_mega(c, 2 * B);
+  if (mega) {
+    // prefill through the persistent kernel: Lc conditioning tokens, then the known audio-prefix columns
+    ZB_CUDA(c->err, launch_mega(c, MG_MODE_HIDDEN, Lc, 2 * B, B, nullptr, d_prefix, nullptr, Lc, 0, s));
+    if (prefix_cols > 1) {
+      h.pos = Lc; h.col = 0;
+      if ((rc = upload_state(c, h, s))) return rc;
+      ZB_CUDA(c->err, launch_mega(c, MG_MODE_FORCED, prefix_cols - 1, 2 * B, B, nullptr, nullptr, nullptr, 0, 0, s));
+    }
+  } else {
   // ---- prefill (model.py:181-196,253-264), token by token through the decode-step kernels: causal attention over
-  // the prefix is exactly what a sequence of single-token steps computes.
-  const std::vector<Pass> passes = cfg_passes(B);
-  int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
-  for (int t = 0; t < Lc; ++t) {
-    ZB_CUDA(c->err, launch(c, k_load_hidden, dim3(2 * B), dim3(thr), 0, s, (const bf16*)d_prefix, c->x, g.d_model, Lc, t));
-    ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
-    ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
-  }
-  for (int j = 0; j + 1 < prefix_cols; ++j) {      // known audio-prefix columns: no sampling
-    h.pos = Lc + j; h.col = j;
-    if ((rc = upload_state(c, h, s))) return rc;
-    ZB_CUDA(c->err, launch(c, k_embed, dim3(B), dim3(thr), 0, s, (const bf16*)c->emb, (const long long*)c->delayed, c->x,
-                           g.d_model, g.n_codebooks, g.vocab, (const ZbDevState*)c->st));
-    ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
-    ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
+    // the prefix is exactly what a sequence of single-token steps computes.
+    const std::vector<Pass> passes = cfg_passes(B);
+    int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
+    for (int t = 0; t < Lc; ++t) {
+      ZB_CUDA(c->err, launch(c, k_load_hidden, dim3(2 * B), dim3(thr), 0, s, (const bf16*)d_prefix, c->x, g.d_model, Lc, t));
+      ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
+      ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
+    }
+    for (int j = 0; j + 1 < prefix_cols; ++j) {      // known audio-prefix columns: no sampling
+      h.pos = Lc + j; h.col = j;
+      if ((rc = upload_state(c, h, s))) return rc;
+      ZB_CUDA(c->err, launch(c, k_embed, dim3(B), dim3(thr), 0, s, (const bf16*)c->emb, (const long long*)c->delayed, c->x,
+                             g.d_model, g.n_codebooks, g.vocab, (const ZbDevState*)c->st));
+      ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
+      ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
+    }
   }
   // last prefix column -> logits -> sample (no logit_bias, no repetition penalty, no EOS logic: model.py:255-260)
   h.pos = Lc + prefix_cols - 1; h.col = prefix_cols - 1;
   h.apply_eos_bias = 0; h.use_history = 0; h.eos_logic = 0;
   if ((rc = upload_state(c, h, s))) return rc;
-  const bool counting = c->counting;
-  ZB_CUDA(c->err, enqueue_decode_step(c, s));
-  c->counting = counting;
+  if (mega) ZB_CUDA(c->err, launch_mega(c, MG_MODE_DECODE, 1, 2 * B, B, nullptr, nullptr, nullptr, 0, 0, s));
+  else ZB_CUDA(c->err, enqueue_decode_step(c, s));
   // switch to loop mode (model.py:266-301)
   h.pos = Lc + prefix_cols; h.col = prefix_cols; h.step = 1;
   h.apply_eos_bias = 1; h.use_history = 1; h.eos_logic = 1;
@@ -701,6 +861,13 @@ int zb_gen_steps(zb_ctx* c, int n_steps, void* stream) {
   if (!c->delayed) return c->err.fail(ZB_ERR_STATE, "zb_gen_begin first");
   cudaStream_t s = (cudaStream_t)stream;
   ZB_CUDA(c->err, cudaSetDevice(c->device));
+  if (use_mega(c, 2 * c->B)) {
+    ZB_CUDA(c->err, cudaEventRecord(c->ev0, s));
+    ZB_CUDA(c->err, launch_mega(c, MG_MODE_DECODE, n_steps, 2 * c->B, c->B, nullptr, nullptr, nullptr, 0, 0, s));
+    ZB_CUDA(c->err, cudaEventRecord(c->ev1, s));
+    c->ev_valid = true;
+    return ZB_OK;
+  }
   if (c->opt_graph) {
     if (c->graph && (c->graph_B != c->B || c->graph_L != c->L || c->graph_delayed != c->delayed)) drop_graph(c);
     if (!c->graph) {
@@ -780,7 +947,9 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   if (k == "pdl") c->opt_pdl = value;
   else if (k == "l2_prefetch") c->opt_l2_prefetch_mb = value;
   else if (k == "graph") c->opt_graph = value;
-  else if (k == "gemv") c->opt_gemv = value;          // 1 = mma.sync weight streaming (default), 0 = SIMT cross-check
+  else if (k == "gemv") c->opt_gemv = value;
+  else if (k == "mega") c->opt_mega = value;
+  else if (k == "trace") c->opt_trace = value;
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
   drop_graph(c);
   return ZB_OK;

@@ -83,6 +83,15 @@ __device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) 
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
 
+// Barrier policies for code shared between stand-alone kernels (whole CTA) and the persistent decode kernel, where
+// the 256 consumer threads synchronise on named barrier 1 while the producer warp runs its own loop.
+struct SyncCta {
+  static __device__ __forceinline__ void sync() { __syncthreads(); }
+};
+struct SyncConsumers {
+  static __device__ __forceinline__ void sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+};
+
 // ---------------------------------------------------------------------------------------------
 // device-resident generation state (one per context); every step kernel reads it, k_update writes it.
 // ---------------------------------------------------------------------------------------------
