@@ -154,6 +154,17 @@ int main() {
       {"8x4KB(K=2048) st6 mode2 poll_lane0", 8, 4096, 4160, 6, 2, 0, 0, 4096},
       {"8x4KB(K=2048) st6 mode0", 8, 4096, 4160, 6, 0, 0, 0, 4096},
       {"1x16KB  st12 mode2 poll_lane0", 1, 16384, 16384, 12, 2, 0, 0, 0},
+      {"8x4KB st5 mode2 poll_lane0", 8, 4096, 4160, 5, 2, 0, 0, 4096},
+      {"8x4KB st5 mode2 poll_all", 8, 4096, 4160, 5, 2, 1, 0, 4096},
+      {"8x4KB st4 mode2 poll_lane0", 8, 4096, 4160, 4, 2, 0, 0, 4096},
+      {"8x4KB st3 mode2 poll_lane0", 8, 4096, 4160, 3, 2, 0, 0, 4096},
+      {"8x4KB st2 mode2 poll_lane0", 8, 4096, 4160, 2, 2, 0, 0, 4096},
+      {"8x4KB st5 mode0 poll_lane0", 8, 4096, 4160, 5, 0, 0, 0, 4096},
+      {"16x4KB st3 mode2 poll_lane0", 16, 4096, 4160, 3, 2, 0, 0, 4096},
+      {"16x4KB st2 mode2 poll_lane0", 16, 4096, 4160, 2, 2, 0, 0, 4096},
+      {"8x8KB(K=8192) st3 mode2 poll_lane0", 8, 8192, 8256, 3, 2, 0, 0, 16384},
+      {"8x8KB(K=8192) st2 mode2 poll_lane0", 8, 8192, 8256, 2, 2, 0, 0, 16384},
+      {"8x4KB(K=8192) st5 mode2 poll_lane0", 8, 4096, 4160, 5, 2, 0, 0, 16384},
   };
   for (const Cfg& c : cfgs) {
     P p;

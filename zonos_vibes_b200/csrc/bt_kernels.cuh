@@ -1,0 +1,332 @@
+// Batched decode step (more than 8 activation rows, i.e. B > 4 utterances with CFG): once the batch makes the
+// projections dense contractions they move to the 5th-gen tensor cores.  Reference arithmetic: the same
+// zonos/backbone/_torch.py:83-152 and zonos/model.py:100-116 as the batch-1 kernels; batch semantics = B independent
+// batch-1 runs.
+//
+//   D[m, n] = sum_k X[m, k] * W[n, k]        X = activations [rows][K] bf16 (L2 resident), W = weights [N][K] bf16 (HBM)
+//
+// k_bt_gemm: one CTA = one 128-row activation tile x one 128-row weight tile x one K split.  Warp 0 = TMA producer
+// (A box {64 k, 128 rows} of the activations, B box {64 k, 128 rows} of the weights, both SWIZZLE_128B K-major),
+// warp 1 = TMEM allocator + single-thread tcgen05.mma issuer (kind::f16, bf16 operands, fp32 accumulators in TMEM),
+// warps 2..5 = epilogue (tcgen05.ld 32x32b).  The weights are streamed ONCE per step for all rows (the per-op GEMV
+// path would re-stream them per group of 8 rows), so the step stays HBM-bound: 3.2 GB of weights + the KV cache.
+// The grid is filled by split-K (out_proj / fc2 have only 16 weight tiles): every split stores its fp32 partial tile to
+// a workspace and a small fused "finish" kernel sums the splits in a FIXED order (reproducible tokens) and applies the
+// epilogue that needs whole rows anyway (residual + next LayerNorm, RoPE + KV append, CFG mix).  fc1 needs no split
+// (128 tiles) and runs its SwiGLU epilogue straight out of TMEM: value rows and gate rows are two B boxes of one tile.
+#pragma once
+#include <cuda.h>
+
+#include "decode_kernels.cuh"
+#include "tc_common.cuh"
+
+#define BT_THREADS 192
+#define BT_BM 128
+#define BT_BN 128
+#define BT_BK 64
+#define BT_A_BYTES (BT_BM * BT_BK * 2)      // 16 KB
+#define BT_B_BYTES (BT_BN * BT_BK * 2)      // 16 KB
+#define BT_STAGE_BYTES (BT_A_BYTES + BT_B_BYTES)
+#define BT_STAGES 6
+#define BT_SMEM_BYTES (1024 + BT_STAGES * BT_STAGE_BYTES + 256)
+
+enum { BT_MODE_PARTIAL = 0, BT_MODE_SWIGLU = 1 };
+
+struct BtGemmParams {
+  int M;                 // real activation rows
+  int N;                 // weight rows (PARTIAL) or ffn size F (SWIGLU: value rows [0,F), gate rows [F,2F))
+  int num_kb;            // K / 64
+  int kb_per_split;      // k-blocks per split (grid.z splits)
+  int mode;
+  float* partial;        // PARTIAL: [splits][m_pad][N] fp32
+  int m_pad;
+  bf16* h;               // SWIGLU: [rows][F] bf16
+  const ZbDevState* st;  // done flag
+};
+
+// grid = (n_tiles, m_tiles, splits); block = 192; dyn smem = BT_SMEM_BYTES
+__global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm(const __grid_constant__ CUtensorMap map_x,
+                                                           const __grid_constant__ CUtensorMap map_w, const BtGemmParams p) {
+  extern __shared__ unsigned char bt_smem_raw[];
+  const uint32_t raw = smem_u32(bt_smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bar_base = base + BT_STAGES * BT_STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * (uint32_t)s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (uint32_t)(BT_STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (uint32_t)(2 * BT_STAGES);
+  const uint32_t tmem_slot = tmem_full_bar + 8u;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(bt_smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tile = blockIdx.x, m0 = blockIdx.y * BT_BM, split = blockIdx.z;
+  const int kb0 = split * p.kb_per_split;
+  const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+  const int nkb = kb1 - kb0;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+    for (int s = 0; s < BT_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_d = *tmem_slot_ptr;
+
+  pdl_launch_dependents();
+  const bool swiglu = p.mode == BT_MODE_SWIGLU;
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer.  The weight tiles do not depend on the previous kernel: they are requested BEFORE the
+      // grid dependency resolves (programmatic dependent launch), the activation tiles after.
+      int pre = nkb < BT_STAGES ? nkb : BT_STAGES;
+      for (int i = 0; i < pre; ++i) {
+        const uint32_t b_dst = base + (uint32_t)i * BT_STAGE_BYTES + BT_A_BYTES;
+        mbar_expect_tx(full_bar(i), BT_STAGE_BYTES);
+        if (swiglu) {
+          tma_load_2d(b_dst, &map_w, (kb0 + i) * BT_BK, n_tile * 64, full_bar(i));
+          tma_load_2d(b_dst + BT_B_BYTES / 2, &map_w, (kb0 + i) * BT_BK, p.N + n_tile * 64, full_bar(i));
+        } else {
+          tma_load_2d(b_dst, &map_w, (kb0 + i) * BT_BK, n_tile * BT_BN, full_bar(i));
+        }
+      }
+      pdl_wait_prior_grid();
+      for (int i = 0; i < pre; ++i) tma_load_2d(base + (uint32_t)i * BT_STAGE_BYTES, &map_x, (kb0 + i) * BT_BK, m0, full_bar(i));
+      for (int i = pre; i < nkb; ++i) {
+        const int s = i % BT_STAGES;
+        mbar_wait(empty_bar(s), ((i / BT_STAGES) - 1) & 1);
+        const uint32_t a_dst = base + (uint32_t)s * BT_STAGE_BYTES;
+        const uint32_t b_dst = a_dst + BT_A_BYTES;
+        mbar_expect_tx(full_bar(s), BT_STAGE_BYTES);
+        tma_load_2d(a_dst, &map_x, (kb0 + i) * BT_BK, m0, full_bar(s));
+        if (swiglu) {
+          tma_load_2d(b_dst, &map_w, (kb0 + i) * BT_BK, n_tile * 64, full_bar(s));
+          tma_load_2d(b_dst + BT_B_BYTES / 2, &map_w, (kb0 + i) * BT_BK, p.N + n_tile * 64, full_bar(s));
+        } else {
+          tma_load_2d(b_dst, &map_w, (kb0 + i) * BT_BK, n_tile * BT_BN, full_bar(s));
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_f16(BT_BN, 1u);        // bf16 x bf16 -> fp32
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % BT_STAGES;
+        mbar_wait(full_bar(s), (i / BT_STAGES) & 1);
+        tc_fence_after();
+        const uint32_t a_addr = base + (uint32_t)s * BT_STAGE_BYTES;
+        const uint64_t adesc = umma_desc_sw128(a_addr);
+        const uint64_t bdesc = umma_desc_sw128(a_addr + BT_A_BYTES);
+#pragma unroll
+        for (int k = 0; k < BT_BK / 16; ++k)
+          tc_mma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (i | k) != 0);
+        tc_commit(empty_bar(s));
+      }
+      tc_commit(tmem_full_bar);
+    }
+    __syncwarp();
+  } else {
+    // ===== epilogue: warp w owns TMEM lanes [32*(w%4), +32) = activation rows
+    const int lg = warp & 3;
+    const int m = m0 + lg * 32 + lane;
+    const bool valid = m < p.M;
+    if (nkb > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    if (swiglu) {
+      // fc1 -> y * silu(gate), all three rounded to bf16 like the reference's bf16 tensors (_torch.py:150-152)
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t vy[32], vg[32];
+        tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, vy);
+        tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)(64 + c0), vg);
+        if (valid) {
+          bf16* dst = p.h + (size_t)m * p.N + n_tile * 64 + c0;
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            __nv_bfloat162 o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float r[2];
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const float y = bf16_round(__uint_as_float(vy[q4 * 8 + 2 * j + e]));
+                const float gt = bf16_round(__uint_as_float(vg[q4 * 8 + 2 * j + e]));
+                const float sg = bf16_round(gt / (1.0f + expf(-gt)));
+                r[e] = y * sg;
+              }
+              o[j] = __floats2bfloat162_rn(r[0], r[1]);
+            }
+            if (n_tile * 64 + c0 + q4 * 8 < p.N) *reinterpret_cast<uint4*>(dst + q4 * 8) = *reinterpret_cast<uint4*>(o);
+          }
+        }
+      }
+    } else {
+      float* dst_row = p.partial + ((size_t)split * p.m_pad + m) * p.N + (size_t)n_tile * BT_BN;
+      for (int c0 = 0; c0 < BT_BN; c0 += 32) {
+        uint32_t v[32];
+        if (nkb > 0) {
+          tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        if (valid) {
+          const int nb = n_tile * BT_BN + c0;
+          if (nb + 32 <= p.N && (p.N & 3) == 0) {
+#pragma unroll
+            for (int q4 = 0; q4 < 8; ++q4) *reinterpret_cast<uint4*>(dst_row + c0 + q4 * 4) = make_uint4(v[q4 * 4], v[q4 * 4 + 1], v[q4 * 4 + 2], v[q4 * 4 + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (nb + j < p.N) dst_row[c0 + j] = __uint_as_float(v[j]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(128u) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// finish kernels: fixed-order split sums + the epilogues that need whole rows
+// ---------------------------------------------------------------------------------------------------------------
+struct BtFinishParams {
+  const float* partial;      // [splits][m_pad][N] fp32 (nullptr: no GEMM result to add, LayerNorm only)
+  int splits, m_pad, N;
+  bf16* x;                   // residual stream [rows][d]
+  bf16* xn;                  // LayerNorm output [rows][d] (A operand of the next GEMM); nullptr = none
+  const bf16 *ln_w, *ln_b;
+  float eps;
+  int d;
+  // qkv
+  bf16* q;                   // [rows][q_size]
+  bf16* kv_layer;
+  const int* page_table;
+  int max_pages, Hkv, q_size, kv_size;
+  const float* rope;
+  const int* rope_pos;
+  // heads
+  float* logits;             // [B][n_q][V]
+  int n_q, V, eos, B;
+  const ZbDevState* st;
+};
+
+__device__ __forceinline__ float bt_split_sum(const float* partial, int splits, size_t split_stride, size_t off) {
+  float s = 0.f;
+  for (int i = 0; i < splits; ++i) s += __ldcg(partial + (size_t)i * split_stride + off);
+  return s;
+}
+
+// x[row] += bf16(sum of the split partials)  (bf16 residual stream, _torch.py:100-101), then xn[row] = LayerNorm(x[row])
+// with the NEXT norm's parameters (F.layer_norm: biased variance, eps inside the sqrt, fp32 statistics).
+// grid = rows, block = 256; d <= 2048 * k handled by a strided loop with the row kept in shared memory.
+__global__ void __launch_bounds__(256) k_bt_resid_ln(const BtFinishParams p) {
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+  extern __shared__ float bt_row[];          // [d]
+  __shared__ float red[16];
+  const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const size_t split_stride = (size_t)p.m_pad * p.N;
+  float sum = 0.f;
+  for (int e = tid * 2; e < p.d; e += 512) {
+    __nv_bfloat162* px = reinterpret_cast<__nv_bfloat162*>(p.x + (size_t)row * p.d + e);
+    float2 v = __bfloat1622float2(*px);
+    if (p.partial) {
+      const float a0 = bt_split_sum(p.partial, p.splits, split_stride, (size_t)row * p.N + e);
+      const float a1 = bt_split_sum(p.partial, p.splits, split_stride, (size_t)row * p.N + e + 1);
+      const __nv_bfloat162 o = __floats2bfloat162_rn(v.x + bf16_round(a0), v.y + bf16_round(a1));
+      *px = o;
+      v = __bfloat1622float2(o);
+    }
+    bt_row[e] = v.x; bt_row[e + 1] = v.y;
+    sum += v.x + v.y;
+  }
+  if (!p.xn) return;
+  sum = warp_sum(sum);
+  if (lane == 0) red[warp] = sum;
+  __syncthreads();
+  float tot = 0.f;
+  for (int w = 0; w < 8; ++w) tot += red[w];
+  const float mean = tot / (float)p.d;
+  float var = 0.f;
+  for (int e = tid * 2; e < p.d; e += 512) { const float a = bt_row[e] - mean, b = bt_row[e + 1] - mean; var += a * a + b * b; }
+  var = warp_sum(var);
+  if (lane == 0) red[8 + warp] = var;
+  __syncthreads();
+  float vt = 0.f;
+  for (int w = 0; w < 8; ++w) vt += red[8 + w];
+  const float rstd = rsqrtf(vt / (float)p.d + p.eps);
+  for (int e = tid * 2; e < p.d; e += 512) {
+    const float2 g = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p.ln_w + e));
+    const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p.ln_b + e));
+    *reinterpret_cast<__nv_bfloat162*>(p.xn + (size_t)row * p.d + e) =
+        __floats2bfloat162_rn((bt_row[e] - mean) * rstd * g.x + b.x, (bt_row[e + 1] - mean) * rstd * g.y + b.y);
+  }
+}
+
+// in_proj finish: bf16 round, interleaved-pair RoPE in fp32 on q and k (_torch.py:18-30), q -> q buffer, k/v -> paged cache
+// at the current position (_torch.py:33-49).  grid = rows, block = 256.
+__global__ void __launch_bounds__(256) k_bt_qkv_finish(const BtFinishParams p) {
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+  if (p.st->done) return;
+  const int row = blockIdx.x;
+  const int pos = p.st->pos;
+  const size_t split_stride = (size_t)p.m_pad * p.N;
+  const int page = p.page_table[(size_t)row * p.max_pages + pos / ZB_PAGE];
+  const float* cs_row = p.rope + (size_t)p.rope_pos[row] * (ZB_DH / 2) * 2;
+  for (int n0 = threadIdx.x * 2; n0 < p.N; n0 += 512) {
+    const float v0 = bf16_round(bt_split_sum(p.partial, p.splits, split_stride, (size_t)row * p.N + n0));
+    const float v1 = bf16_round(bt_split_sum(p.partial, p.splits, split_stride, (size_t)row * p.N + n0 + 1));
+    if (n0 < p.q_size + p.kv_size) {
+      const int i = (n0 % ZB_DH) >> 1;
+      const float2 cs = *reinterpret_cast<const float2*>(cs_row + i * 2);
+      const float o0 = __fsub_rn(__fmul_rn(v0, cs.x), __fmul_rn(v1, cs.y));
+      const float o1 = __fadd_rn(__fmul_rn(v1, cs.x), __fmul_rn(v0, cs.y));
+      const __nv_bfloat162 o = __floats2bfloat162_rn(o0, o1);
+      if (n0 < p.q_size) {
+        *reinterpret_cast<__nv_bfloat162*>(p.q + (size_t)row * p.q_size + n0) = o;
+      } else {
+        const int m = n0 - p.q_size;
+        bf16* dst = p.kv_layer + ((((size_t)page * 2 + 0) * p.Hkv + m / ZB_DH) * ZB_PAGE + pos % ZB_PAGE) * ZB_DH + m % ZB_DH;
+        *reinterpret_cast<__nv_bfloat162*>(dst) = o;
+      }
+    } else {
+      const int m = n0 - p.q_size - p.kv_size;
+      bf16* dst = p.kv_layer + ((((size_t)page * 2 + 1) * p.Hkv + m / ZB_DH) * ZB_PAGE + pos % ZB_PAGE) * ZB_DH + m % ZB_DH;
+      *reinterpret_cast<__nv_bfloat162*>(dst) = __floats2bfloat162_rn(v0, v1);
+    }
+  }
+}
+
+// heads finish: bf16 round, fp32 CFG mix of rows b (cond) and B+b (uncond), pad / EOS masks (model.py:111-115,266-267,280).
+// grid = (n_q, B), block = 256.
+__global__ void __launch_bounds__(256) k_bt_heads_finish(const BtFinishParams p) {
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+  if (p.st->done) return;
+  const int k = blockIdx.x, b = blockIdx.y;
+  const float scale = p.st->cfg_scale;
+  const int eos_bias = p.st->apply_eos_bias;
+  const size_t split_stride = (size_t)p.m_pad * p.N;
+  for (int n = threadIdx.x; n < p.V; n += 256) {
+    const size_t col = (size_t)k * p.V + n;
+    const float c = bf16_round(bt_split_sum(p.partial, p.splits, split_stride, (size_t)b * p.N + col));
+    const float u = bf16_round(bt_split_sum(p.partial, p.splits, split_stride, (size_t)(b + p.B) * p.N + col));
+    float l = __fadd_rn(u, __fmul_rn(__fsub_rn(c, u), scale));
+    if (n >= 1025) l = -INFINITY;
+    if (eos_bias && k >= 1 && n == p.eos) l = -INFINITY;
+    p.logits[((size_t)b * p.n_q + k) * p.V + n] = l;
+  }
+}

@@ -27,6 +27,14 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
       : "r"(a0), "r"(z), "r"(a2), "r"(z), "r"(b0), "r"(b1));
 }
 
+// all four A registers (16 rows)
+__device__ __forceinline__ void mma_bf16_16816_full(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
 // ---- single-row epilogues (same arithmetic as gemv_epilogue in decode_kernels.cuh) ---------------------------
 template <int EPI>
 __device__ __forceinline__ void gm_epilogue_pair(const GemvParams& p, int a /*activation row*/, int n0, float s0, float s1) {
@@ -131,9 +139,13 @@ __global__ void __launch_bounds__(GM_THREADS, 2) k_gemv_mma(const GemvParams p) 
   gemv_stage_activations<R>(p, xs, red, ld);
   __syncthreads();
 
-  float acc[NT][4];
+  // four independent accumulator sets per weight tile: HMMA chains through its accumulator, and a single chain of
+  // dependent HMMAs leaves the tensor pipe idle between issues
+  float acc[NT][4][4];
 #pragma unroll
-  for (int nt = 0; nt < NT; ++nt) { acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f; }
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int a = 0; a < 4; ++a) { acc[nt][a][0] = acc[nt][a][1] = acc[nt][a][2] = acc[nt][a][3] = 0.f; }
   const bf16* xrow = xs + (size_t)g * ld + kbase;      // only dereferenced when g < R
 
   auto compute_unit = [&](const uint4(&d)[NT][U], int u) {
@@ -145,8 +157,8 @@ __global__ void __launch_bounds__(GM_THREADS, 2) k_gemv_mma(const GemvParams p) 
         if (g < R) xv = *reinterpret_cast<const uint4*>(xrow + (kb0 + j) * 32);
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
-          mma_bf16_16816(acc[nt], xv.x, xv.y, d[nt][j].x, d[nt][j].y);
-          mma_bf16_16816(acc[nt], xv.z, xv.w, d[nt][j].z, d[nt][j].w);
+          mma_bf16_16816(acc[nt][2 * (j & 1)], xv.x, xv.y, d[nt][j].x, d[nt][j].y);
+          mma_bf16_16816(acc[nt][2 * (j & 1) + 1], xv.z, xv.w, d[nt][j].z, d[nt][j].w);
         }
       }
     }
@@ -158,8 +170,11 @@ __global__ void __launch_bounds__(GM_THREADS, 2) k_gemv_mma(const GemvParams p) 
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
         // c0,c1 = D[row g][n = 2t, 2t+1]
-        *reinterpret_cast<float2*>(pb + ((nt * GM_WARPS + warp) * 8 + g) * 8 + 2 * t) = make_float2(acc[nt][0], acc[nt][1]);
-        acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+        *reinterpret_cast<float2*>(pb + ((nt * GM_WARPS + warp) * 8 + g) * 8 + 2 * t) =
+            make_float2((acc[nt][0][0] + acc[nt][1][0]) + (acc[nt][2][0] + acc[nt][3][0]),
+                        (acc[nt][0][1] + acc[nt][1][1]) + (acc[nt][2][1] + acc[nt][3][1]));
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { acc[nt][a][0] = acc[nt][a][1] = acc[nt][a][2] = acc[nt][a][3] = 0.f; }
       }
       __syncthreads();
       const int n_base = task * GM_ROWS;

@@ -78,6 +78,8 @@ struct MegaParams {
   bf16* hidden_out;            // optional: post-norm_f hidden states, same indexing
   int hidden_S, hidden_t0;
   int n_stages;                // ring stages
+  int poll_all;                // 1: all consumer threads poll the full barriers; 0: one lane per warp
+  unsigned producer_sleep_ns;  // producer back-off between polls of a full ring (0 = hot spin)
   int scratch_bytes;           // activation staging / attention / sampling scratch
   unsigned long long* dbg;     // optional trace: [grid][MG_TRACE_SLOTS] globaltimer stamps of step dbg_step (thread 0)
   int dbg_step;
@@ -90,7 +92,7 @@ __device__ __forceinline__ unsigned long long mg_globaltimer() {
 }
 #define MG_STAMP()                                                                                         \
   do {                                                                                                     \
-    if (trace && threadIdx.x == 0 && trace_n < MG_TRACE_SLOTS) p.dbg[(size_t)blockIdx.x * MG_TRACE_SLOTS + trace_n++] = mg_globaltimer(); \
+    if (cx.trace && threadIdx.x == 0 && cx.trace_n < MG_TRACE_SLOTS) cx.trace_out[cx.trace_n++] = mg_globaltimer(); \
   } while (0)
 
 // ---- PTX helpers ------------------------------------------------------------------------------------------------
@@ -126,6 +128,11 @@ __device__ __forceinline__ void mg_bulk_g2s(uint32_t dst, const void* src, uint3
                "r"(bytes), "r"(bar)
                : "memory");
 }
+__device__ __forceinline__ uint4 mg_lds128(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+  return r;
+}
 __device__ __forceinline__ uint4 mg_ldcg16(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
 __device__ __forceinline__ int mg_ld_volatile(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
 
@@ -146,6 +153,7 @@ __device__ __forceinline__ void mg_grid_sync(unsigned* counter, unsigned& target
 // ---- per-CTA context ----------------------------------------------------------------------------------------------
 struct MgCtx {
   unsigned char* ring;       // n_stages x MG_STAGE_BYTES
+  uint32_t ring_addr;        // the same, as a shared-space address
   unsigned char* scratch;    // activation staging etc.
   float* part;               // [2][2][8 warps][8 r][8 n]
   float* red;                // [64]
@@ -157,7 +165,12 @@ struct MgCtx {
   int stage, parity;         // ring cursor of this role
   int tile_flip;             // partial-buffer parity (consumers)
   bool prof;                 // debug profile on
+  bool poll_all;             // every consumer thread polls the full barriers (A/B switch)
+  bool trace;                // this step is being traced
+  int trace_n;
+  unsigned long long* trace_out;
   long long t_full;          // clock64 ticks thread 0 spent waiting on full barriers (prof)
+  long long t_fc1, t_fc1_full, t_fc1_sync;   // fc1 phases only: total / waiting on full barriers / tile reduce + epilogue
 };
 
 __device__ __forceinline__ void mg_advance(MgCtx& cx) {
@@ -173,12 +186,12 @@ __device__ __forceinline__ void mg_range(int n_units, int& lo, int& hi) {
 // The attention work item of this CTA for context length pos+1: (row, kv head, split) and its token range.
 struct MgAttItem {
   bool mine;
-  int row, kvh, split, t0, t1, chunk;
+  int row, kvh, split, t0, t1, chunk, nact;
 };
+#define MG_MIN_CHUNK 256             // tokens per split at least: short contexts use ONE split and skip the partial merge
 __device__ __forceinline__ MgAttItem mg_att_item(const MegaParams& p, int pos) {
   MgAttItem it;
   const int nsplit = p.nsplit;
-  it.mine = (int)blockIdx.x < p.R * p.Hkv * nsplit;
   it.split = blockIdx.x % nsplit;
   const int pair = blockIdx.x / nsplit;
   it.kvh = pair % p.Hkv;
@@ -186,7 +199,10 @@ __device__ __forceinline__ MgAttItem mg_att_item(const MegaParams& p, int pos) {
   const int ctx = pos + 1;
   int chunk = (ctx + nsplit - 1) / nsplit;
   chunk = (chunk + 7) & ~7;
+  if (chunk < MG_MIN_CHUNK) chunk = MG_MIN_CHUNK;
   it.chunk = chunk;
+  it.nact = (ctx + chunk - 1) / chunk;                 // splits that own tokens (<= nsplit)
+  it.mine = (int)blockIdx.x < p.R * p.Hkv * nsplit && it.split < it.nact;
   it.t0 = it.split * chunk;
   it.t1 = min(ctx, it.t0 + chunk);
   return it;
@@ -214,6 +230,8 @@ struct MgSched {
   bool fresh;                // phase cursors not yet initialised
   int lo, hi;                // row range of the current tile phase
   int pos0, rope0;           // KV position at launch; (lane < R) RoPE position of row `lane` at launch
+  int my_page;               // lane i: page-table entry i of this CTA's attention row (max_pages <= 32), else -1: the
+                             // producer never loads the page table from memory inside the loop
   bool with_heads, final_ln;
 };
 
@@ -221,6 +239,9 @@ __device__ __forceinline__ void mg_sched_init(MgSched& s, const MegaParams& p, i
   s.step = 0; s.l = 0; s.ph = MG_PH_ROPE; s.fresh = true;
   s.n0 = s.nt = s.kc0 = s.ts = 0; s.lo = s.hi = 0;
   s.pos0 = pos0; s.rope0 = rope0; s.with_heads = with_heads; s.final_ln = final_ln;
+  const int lane = threadIdx.x & 31;
+  const int att_row = ((int)blockIdx.x / p.nsplit) / p.Hkv;
+  s.my_page = (p.max_pages <= 32 && att_row < p.R && lane < p.max_pages) ? p.page_table[(size_t)att_row * p.max_pages + lane] : -1;
 }
 
 __device__ __forceinline__ const bf16* mg_lw(const bf16* base0, long long stride, int l) {
@@ -275,14 +296,15 @@ __device__ __forceinline__ bool mg_sched_next(MgSched& s, const MegaParams& p, M
         const int ts = s.ts;
         const int n = min(MG_KV_TOK, tp - ts);
         const int n1 = min(n, ZB_PAGE - ts % ZB_PAGE);         // tokens before the page boundary
-        if (lane < 4) {
-          const int run = lane >> 1, isv = lane & 1;
+        {
+          const int run = (lane >> 1) & 1, isv = lane & 1;
           const int tb = run == 0 ? ts : ts + n1;
           const int nn = run == 0 ? n1 : n - n1;
-          if (nn > 0) {
+          int page = __shfl_sync(0xffffffffu, s.my_page, (tb / ZB_PAGE) & 31);
+          if (lane < 4 && nn > 0) {
+            if (p.max_pages > 32) page = p.page_table[(size_t)it.row * p.max_pages + tb / ZB_PAGE];
             const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
             const size_t kv_stride = (size_t)p.Hkv * head_stride;
-            const int page = p.page_table[(size_t)it.row * p.max_pages + tb / ZB_PAGE];
             d.src = p.kv + (size_t)s.l * p.kv_layer_elems + (size_t)page * 2 * kv_stride + (size_t)it.kvh * head_stride +
                     (size_t)(tb % ZB_PAGE) * ZB_DH + (isv ? kv_stride : 0);
             d.bytes = nn * ZB_DH * 2;
@@ -332,14 +354,21 @@ __device__ __forceinline__ bool mg_sched_next(MgSched& s, const MegaParams& p, M
 // consumers: ring access
 // =================================================================================================================
 __device__ __forceinline__ const unsigned char* mg_cons_wait(MgCtx& cx) {
-  if (cx.prof && threadIdx.x == 0) {
-    const long long c0 = clock64();
+  // one polling lane per warp (+ __syncwarp): 256 threads spinning on try_wait contend with the producer's own
+  // barrier traffic and the TMA's complete_tx updates (scripts/ring_bench.cu: idle all-lane pollers cost 30 %)
+  const long long c0 = (cx.prof && threadIdx.x == 0) ? clock64() : 0;
+  if (cx.poll_all) {
     mg_mbar_wait(cx.full0 + 8u * cx.stage, cx.parity);
-    cx.t_full += clock64() - c0;
   } else {
-    mg_mbar_wait(cx.full0 + 8u * cx.stage, cx.parity);
+    if ((threadIdx.x & 31) == 0) mg_mbar_wait(cx.full0 + 8u * cx.stage, cx.parity);
+    __syncwarp();
   }
+  if (cx.prof && threadIdx.x == 0) cx.t_full += clock64() - c0;
   return cx.ring + (size_t)cx.stage * MG_STAGE_BYTES;
+}
+__device__ __forceinline__ uint32_t mg_cons_wait_addr(MgCtx& cx) {        // same, as a shared-space address
+  mg_cons_wait(cx);
+  return cx.ring_addr + (uint32_t)cx.stage * MG_STAGE_BYTES;
 }
 __device__ __forceinline__ void mg_cons_release(MgCtx& cx) {
   __syncwarp();
@@ -369,32 +398,37 @@ __device__ __forceinline__ void mg_unpack8(const uint4& raw, float (&v)[8]) {
 // Deliberately NOT unrolled over rows and not inlined: the persistent kernel's per-layer code must stay inside the
 // instruction cache — instruction fetches that miss compete with the saturated weight stream (the first version,
 // 360 KB of SASS, spent ~7 us per LayerNorm waiting on instruction fetch: profiles/r01_mega_trace_v1.md).
-__device__ __noinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const bf16* src, int K, int R, float eps) {
+__device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const bf16* src, int K, int R, float eps) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int e = tid * 8;
   const bool active = e < K;
   float* red = cx.red;              // [64] per-warp partials, [64..72) mean, [72..80) rstd
-  // pass 1: raw rows -> xs, row sums
-  for (int r = 0; r < R; ++r) {
-    uint4 raw = make_uint4(0, 0, 0, 0);
-    if (active) {
-      raw = mg_ldcg16(src + (size_t)r * K + e);
-      *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) = raw;
-    }
-    float v[8];
-    mg_unpack8(raw, v);
-    float t = 0.f;
+  // pass 1: raw rows -> xs, row sums.  ALL rows are requested before the first one is used: one L2 round trip, not R.
+  uint4 rawr[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) t += v[j];
-    t = warp_sum(t);
-    if (lane == 0) red[warp * 8 + r] = t;
+  for (int r = 0; r < 8; ++r) {
+    rawr[r] = make_uint4(0, 0, 0, 0);
+    if (r < R && active) rawr[r] = mg_ldcg16(src + (size_t)r * K + e);
+  }
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    if (r < R) {
+      if (active) *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) = rawr[r];
+      float v[8];
+      mg_unpack8(rawr[r], v);
+      float t = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t += v[j];
+      t = warp_sum(t);
+      if (lane == 0) red[warp * 8 + r] = t;
+    }
   }
   // affine parameters from the ring
-  const unsigned char* sp = mg_cons_wait(cx);
+  const uint32_t sp = mg_cons_wait_addr(cx);
   uint4 wr = make_uint4(0, 0, 0, 0), br = make_uint4(0, 0, 0, 0);
   if (active) {
-    wr = *reinterpret_cast<const uint4*>(sp + e * 2);
-    br = *reinterpret_cast<const uint4*>(sp + MG_ROW_BYTES + e * 2);
+    wr = mg_lds128(sp + e * 2);
+    br = mg_lds128(sp + MG_ROW_BYTES + e * 2);
   }
   mg_cons_release(cx);
   SyncConsumers::sync();
@@ -515,7 +549,7 @@ __device__ __forceinline__ void mg_epi_heads(const MegaParams& p, const MgEpi& e
 // consumers: one GEMV phase over this CTA's row range.  xs must be staged (and synced) before the call.  ONE copy of
 // this code serves all five weight matrices (runtime epilogue switch): code size matters more than a few branches.
 // =================================================================================================================
-__device__ __noinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, const bf16* xs, int ld, int K, int n_units, int gate_off,
+__device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, const bf16* xs, int ld, int K, int n_units, int gate_off,
                                            int kind, const MgEpi& epi) {
   const int NT = kind == EPI_SWIGLU ? 2 : 1;
   const int UNIT = kind == EPI_SWIGLU ? 1 : 2;
@@ -525,37 +559,111 @@ __device__ __noinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, const
   int lo, hi;
   mg_range(n_units, lo, hi);
   lo *= UNIT; hi *= UNIT;
+  const uint32_t xs_addr = mg_smem_u32(xs);
+  const bool pf1 = cx.prof && kind == EPI_SWIGLU && threadIdx.x == 0;
+  const long long pt0 = pf1 ? clock64() : 0, pfull0 = cx.t_full;
+  const bool packed = R <= 4;
   for (int n0 = lo; n0 < hi; n0 += 8) {
     const int cnt = min(8, hi - n0);
-    float acc[2][4];
+    bool used_packed = false;                      // warp-uniform, the same for every chunk of a tile (K % 2048 chunks)
+    // FOUR independent accumulator sets per tile: HMMA results chain through the accumulator, and one chain of 16
+    // dependent HMMAs per stage left the tensor pipe idle most of the time (r01 trace: the consumers, not the HBM
+    // stream, were the bottleneck).  The sets are summed once per tile.
+    float acc[2][4][4];
 #pragma unroll
-    for (int nt = 0; nt < 2; ++nt) { acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f; }
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+      for (int a = 0; a < 4; ++a) { acc[nt][a][0] = acc[nt][a][1] = acc[nt][a][2] = acc[nt][a][3] = 0.f; }
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
       if (nt < NT) {
         for (int kc0 = 0; kc0 < K; kc0 += MG_KC) {
           const int kcs = min(MG_KC, K - kc0);
-          const int slice = kcs >> 3;                  // this warp's columns of the chunk (multiple of 32)
-          const int nkb = slice >> 5;
-          const unsigned char* wp = mg_cons_wait(cx) + g * MG_ROW_BYTES + (warp * slice + t * 8) * 2;
-          const bf16* xp = xs + (size_t)g * ld + kc0 + warp * slice + t * 8;
-#pragma unroll 4
-          for (int j = 0; j < nkb; ++j) {
-            const uint4 wv = *reinterpret_cast<const uint4*>(wp + j * 64);
-            uint4 xv = make_uint4(0, 0, 0, 0);
-            if (g < R) xv = *reinterpret_cast<const uint4*>(xp + j * 32);
-            mma_bf16_16816(acc[nt], xv.x, xv.y, wv.x, wv.y);
-            mma_bf16_16816(acc[nt], xv.z, xv.w, wv.z, wv.w);
+          const uint32_t st_addr = mg_cons_wait_addr(cx);
+          if (packed && (kcs & 511) == 0) {
+            // R <= 4: the WEIGHTS are the MMA's A operand.  A rows 0..7 = the 8 weight rows over the first half of the
+            // chunk's columns, A rows 8..15 = the same weight rows over the second half; B columns 0..3 = the
+            // activation rows over the first half, columns 4..7 = over the second half.  D[i<8][n<4] and
+            // D[i>=8][n>=4] are the two K-half partial sums, the cross blocks are ignored.  One HMMA now covers
+            // 8 rows x 32 columns instead of 8 x 16: the tensor pipe (1 HMMA / 16 clk / sub-partition on sm_100,
+            // scripts/consume_bench.cu) was the bottleneck of the fc1/fc2 phases with the activations as A.
+            const int hs = kcs >> 1;                     // columns per half
+            const int slice = hs >> 3;                   // this warp's columns in each half (multiple of 32)
+            const int nkb = slice >> 5;
+            const uint32_t wa0 = st_addr + g * MG_ROW_BYTES + (warp * slice + t * 8) * 2;
+            const uint32_t wa1 = wa0 + hs * 2;
+            const int xn = g & 3, xh = g >> 2;
+            const uint32_t xa = xs_addr + ((uint32_t)xn * ld + kc0 + xh * hs + warp * slice + t * 8) * 2;
+            int j = 0;
+#pragma unroll 2
+            for (; j + 1 < nkb; j += 2) {
+              const uint4 w0 = mg_lds128(wa0 + j * 64), w1 = mg_lds128(wa1 + j * 64);
+              const uint4 w2 = mg_lds128(wa0 + j * 64 + 64), w3 = mg_lds128(wa1 + j * 64 + 64);
+              uint4 x0 = make_uint4(0, 0, 0, 0), x1 = make_uint4(0, 0, 0, 0);
+              if (xn < R) { x0 = mg_lds128(xa + j * 64); x1 = mg_lds128(xa + j * 64 + 64); }
+              mma_bf16_16816_full(acc[nt][0], w0.x, w1.x, w0.y, w1.y, x0.x, x0.y);
+              mma_bf16_16816_full(acc[nt][1], w0.z, w1.z, w0.w, w1.w, x0.z, x0.w);
+              mma_bf16_16816_full(acc[nt][2], w2.x, w3.x, w2.y, w3.y, x1.x, x1.y);
+              mma_bf16_16816_full(acc[nt][3], w2.z, w3.z, w2.w, w3.w, x1.z, x1.w);
+            }
+            if (j < nkb) {
+              const uint4 w0 = mg_lds128(wa0 + j * 64), w1 = mg_lds128(wa1 + j * 64);
+              uint4 x0 = make_uint4(0, 0, 0, 0);
+              if (xn < R) x0 = mg_lds128(xa + j * 64);
+              mma_bf16_16816_full(acc[nt][0], w0.x, w1.x, w0.y, w1.y, x0.x, x0.y);
+              mma_bf16_16816_full(acc[nt][1], w0.z, w1.z, w0.w, w1.w, x0.z, x0.w);
+            }
+            used_packed = true;
+          } else {
+            const int slice = kcs >> 3;                  // this warp's columns of the chunk (multiple of 32)
+            const int nkb = slice >> 5;
+            // explicit shared-space addresses: through generic pointers the compiler emitted LD.E.128 for the ring
+            const uint32_t wa = st_addr + g * MG_ROW_BYTES + (warp * slice + t * 8) * 2;
+            const uint32_t xa = xs_addr + ((uint32_t)g * ld + kc0 + warp * slice + t * 8) * 2;
+            int j = 0;
+#pragma unroll 2
+            for (; j + 1 < nkb; j += 2) {
+              const uint4 w0 = mg_lds128(wa + j * 64), w1 = mg_lds128(wa + j * 64 + 64);
+              uint4 x0 = make_uint4(0, 0, 0, 0), x1 = make_uint4(0, 0, 0, 0);
+              if (g < R) { x0 = mg_lds128(xa + j * 64); x1 = mg_lds128(xa + j * 64 + 64); }
+              mma_bf16_16816(acc[nt][0], x0.x, x0.y, w0.x, w0.y);
+              mma_bf16_16816(acc[nt][1], x0.z, x0.w, w0.z, w0.w);
+              mma_bf16_16816(acc[nt][2], x1.x, x1.y, w1.x, w1.y);
+              mma_bf16_16816(acc[nt][3], x1.z, x1.w, w1.z, w1.w);
+            }
+            if (j < nkb) {
+              const uint4 w0 = mg_lds128(wa + j * 64);
+              uint4 x0 = make_uint4(0, 0, 0, 0);
+              if (g < R) x0 = mg_lds128(xa + j * 64);
+              mma_bf16_16816(acc[nt][0], x0.x, x0.y, w0.x, w0.y);
+              mma_bf16_16816(acc[nt][1], x0.z, x0.w, w0.z, w0.w);
+            }
           }
           mg_cons_release(cx);
         }
       }
     }
-    // ---- reduce the K-slices of the 8 warps, run the epilogue
     float* pb = cx.part + (size_t)(cx.tile_flip & 1) * 2 * MG_WARPS * 64;
     cx.tile_flip ^= 1;
-    *reinterpret_cast<float2*>(pb + ((0 * MG_WARPS + warp) * 8 + g) * 8 + 2 * t) = make_float2(acc[0][0], acc[0][1]);
-    if (NT == 2) *reinterpret_cast<float2*>(pb + ((1 * MG_WARPS + warp) * 8 + g) * 8 + 2 * t) = make_float2(acc[1][0], acc[1][1]);
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      if (nt < NT) {
+        float s4[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) s4[i] = (acc[nt][0][i] + acc[nt][1][i]) + (acc[nt][2][i] + acc[nt][3][i]);
+        float* pw = pb + (nt * MG_WARPS + warp) * 64;          // [8 activation rows][8 weight rows]
+        if (used_packed) {
+          // lane (g, t<2): D[g][2t, 2t+1] (first K half) + lane (g, t+2): D[g+8][2t+4, 2t+5] (second K half)
+          const float v0 = s4[0] + __shfl_xor_sync(0xffffffffu, s4[2], 2);
+          const float v1 = s4[1] + __shfl_xor_sync(0xffffffffu, s4[3], 2);
+          if (t < 2) { pw[(2 * t) * 8 + g] = v0; pw[(2 * t + 1) * 8 + g] = v1; }
+        } else {
+          *reinterpret_cast<float2*>(pw + g * 8 + 2 * t) = make_float2(s4[0], s4[1]);
+        }
+      }
+    }
+    // ---- reduce the K-slices of the 8 warps, run the epilogue
+    const long long ps0 = pf1 ? clock64() : 0;
     SyncConsumers::sync();
     if (kind == EPI_SWIGLU) {
       if (tid < R * 8) {
@@ -596,7 +704,9 @@ __device__ __noinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, const
     }
     // no second barrier: the next tile writes the other half of `part`; this half is rewritten only after the NEXT
     // tile's barrier, which every epilogue thread reaches after finishing its reads.
+    if (pf1) cx.t_fc1_sync += clock64() - ps0;
   }
+  if (pf1) { cx.t_fc1 += clock64() - pt0; cx.t_fc1_full += cx.t_full - pfull0; }
 }
 
 // =================================================================================================================
@@ -631,18 +741,83 @@ __device__ __forceinline__ void mg_att_token(const uint4& kraw, const uint4& vra
   }
 }
 
+// Four tokens per half-warp at once: the scores of all of them are reduced together (16 independent shuffle chains
+// instead of 4 dependent rounds of online softmax), then ONE max / rescale / accumulate step.
 template <int G>
-__device__ __noinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const bf16* kv_layer, int pos) {
+__device__ __forceinline__ void mg_att_tokens4(const uint4 (&kraw)[4], const uint4 (&vraw)[4], const bool (&valid)[4], const float (&q)[G][8],
+                                               float (&m)[G], float (&l)[G], float (&acc)[G][8], float scale_log2) {
+  float s[4][G];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float kf[8];
+    mg_unpack8(kraw[k], kf);
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      float d = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d = fmaf(q[g][j], kf[j], d);
+      s[k][g] = d;
+    }
+  }
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1)
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int g = 0; g < G; ++g) s[k][g] += __shfl_xor_sync(0xffffffffu, s[k][g], o);
+  if (!(valid[0] || valid[1] || valid[2] || valid[3])) return;     // uniform per half-warp; no shuffles below
+  float vf[4][8];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) mg_unpack8(vraw[k], vf[k]);
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    float mn = m[g];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { s[k][g] *= scale_log2; if (valid[k]) mn = fmaxf(mn, s[k][g]); }
+    const float corr = exp2f(m[g] - mn);           // m = -inf before the first token -> 0 (mn is finite here)
+    float pr[4], ps = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { pr[k] = valid[k] ? exp2f(s[k][g] - mn) : 0.f; ps += pr[k]; }
+    l[g] = l[g] * corr + ps;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float a = acc[g][j] * corr;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) a = fmaf(pr[k], vf[k][j], a);
+      acc[g][j] = a;
+    }
+    m[g] = mn;
+  }
+}
+
+template <int G>
+__device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const bf16* kv_layer, int pos) {
   const MgAttItem it = mg_att_item(p, pos);
   if (!it.mine) return;                               // CTA-uniform
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int half = lane >> 4, l16 = lane & 15;
   const int nsplit = p.nsplit, row = it.row, kvh = it.kvh, split = it.split;
-  const int ctx = pos + 1;
 
+  // q and (warp 0) the K/V row appended in this step come from L2 in ONE round trip: both were written by other CTAs
+  // before the grid barrier.  Every later read of this phase is shared memory.
+  const int tp = min(it.t1, pos);
+  const bool has_new = it.t0 <= pos && pos < it.t1;
+  uint4 qraw[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) qraw[g] = mg_ldcg16(p.q + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + l16 * 8);
+  uint4 knew = make_uint4(0, 0, 0, 0), vnew = make_uint4(0, 0, 0, 0);
+  if (has_new && warp == 0 && half == 0) {
+    const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
+    const size_t kv_stride = (size_t)p.Hkv * head_stride;
+    const bf16* kp = kv_layer + (size_t)cx.s_page[row] * 2 * kv_stride + (size_t)kvh * head_stride + (size_t)(pos % ZB_PAGE) * ZB_DH + l16 * 8;
+    knew = mg_ldcg16(kp);
+    vnew = mg_ldcg16(kp + kv_stride);
+  }
   float q[G][8];
 #pragma unroll
-  for (int g = 0; g < G; ++g) mg_unpack8(mg_ldcg16(p.q + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + l16 * 8), q[g]);
+  for (int g = 0; g < G; ++g) mg_unpack8(qraw[g], q[g]);
+  if (cx.trace && q[0][0] == 12345.678f) cx.trace_n = 0;           // (trace only) make the stamp below wait for the q load
+  MG_STAMP();                                                     // att +0: q / new K,V arrived from L2
   float m[G], l[G], acc[G][8];
 #pragma unroll
   for (int g = 0; g < G; ++g) {
@@ -653,35 +828,36 @@ __device__ __noinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const 
   // ---- tokens of earlier steps: MG_KV_TOK per ring stage, a half-warp per token; then ONE extra pass for the row
   // appended in this step (written by other CTAs in phase 1, read from L2 by warp 0).  A single copy of the token
   // arithmetic serves both (code size).
-  const int tp = min(it.t1, pos);
-  const bool has_new = it.t0 <= pos && pos < it.t1;
   const int n_kv_stages = tp > it.t0 ? (tp - it.t0 + MG_KV_TOK - 1) / MG_KV_TOK : 0;
   for (int si = 0; si < n_kv_stages + (has_new ? 1 : 0); ++si) {
     const bool fresh = si == n_kv_stages;              // the extra pass
     const int ts = it.t0 + si * MG_KV_TOK;
     const int n = fresh ? 1 : min(MG_KV_TOK, tp - ts);
-    const unsigned char* sp = nullptr;
-    if (!fresh) sp = mg_cons_wait(cx);
-    const int i_end = fresh ? (warp == 0 ? 2 : 0) : MG_KV_TOK;
-    for (int i = 2 * warp + half; i < i_end; i += 2 * MG_WARPS) {
-      const bool valid = i < n;
-      uint4 kraw = make_uint4(0, 0, 0, 0), vraw = make_uint4(0, 0, 0, 0);
-      if (valid) {
-        if (fresh) {
-          const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
-          const size_t kv_stride = (size_t)p.Hkv * head_stride;
-          const bf16* kp = kv_layer + (size_t)cx.s_page[row] * 2 * kv_stride + (size_t)kvh * head_stride + (size_t)(pos % ZB_PAGE) * ZB_DH + l16 * 8;
-          kraw = mg_ldcg16(kp);
-          vraw = mg_ldcg16(kp + kv_stride);
-        } else {
-          kraw = *reinterpret_cast<const uint4*>(sp + i * (ZB_DH * 2) + l16 * 16);
-          vraw = *reinterpret_cast<const uint4*>(sp + MG_KV_TOK * ZB_DH * 2 + i * (ZB_DH * 2) + l16 * 16);
+    uint32_t sp = 0;
+    if (!fresh) sp = mg_cons_wait_addr(cx);
+    if (fresh) {
+      if (warp == 0) {
+        const bool valid = half == 0;
+        mg_att_token<G>(knew, vnew, valid, q, m, l, acc, p.scale_log2);
+      }
+    } else if (2 * warp < n) {                          // warp-uniform: this warp has at least one valid token
+      uint4 kraw[4], vraw[4];
+      bool valid[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int i = 2 * warp + half + 16 * k;
+        valid[k] = i < n;
+        kraw[k] = make_uint4(0, 0, 0, 0); vraw[k] = make_uint4(0, 0, 0, 0);
+        if (valid[k]) {
+          kraw[k] = mg_lds128(sp + i * (ZB_DH * 2) + l16 * 16);
+          vraw[k] = mg_lds128(sp + MG_KV_TOK * ZB_DH * 2 + i * (ZB_DH * 2) + l16 * 16);
         }
       }
-      if (__any_sync(0xffffffffu, valid)) mg_att_token<G>(kraw, vraw, valid, q, m, l, acc, p.scale_log2);
+      mg_att_tokens4<G>(kraw, vraw, valid, q, m, l, acc, p.scale_log2);
     }
     if (!fresh) mg_cons_release(cx);
   }
+  MG_STAMP();                                                     // att +1: KV stages consumed
   // merge the two half-warps
 #pragma unroll
   for (int g = 0; g < G; ++g) {
@@ -714,34 +890,39 @@ __device__ __noinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const 
   }
   SyncConsumers::sync();
   const size_t pbase = (((size_t)row * p.Hkv + kvh) * nsplit + split) * G;
+  const int nact = it.nact;
 #pragma unroll 1
   for (int oi = tid; oi < G * ZB_DH; oi += MG_CONSUMERS) {
     const int g = oi >> 7, dim = oi & (ZB_DH - 1);
     float mn = -INFINITY;
-#pragma unroll 1
+#pragma unroll
     for (int w = 0; w < MG_WARPS; ++w) mn = fmaxf(mn, s_m[w * G + g]);
     float lt = 0.f, ot = 0.f;
-#pragma unroll 1
+#pragma unroll
     for (int w = 0; w < MG_WARPS; ++w) {
       const float c = (s_m[w * G + g] == -INFINITY) ? 0.f : exp2f(s_m[w * G + g] - mn);
       lt += s_l[w * G + g] * c;
       ot += s_o[(w * G + g) * ZB_DH + dim] * c;
     }
-    p.part_o[(pbase + g) * ZB_DH + dim] = ot;
-    if (dim == 0) { p.part_ml[(pbase + g) * 2 + 0] = mn; p.part_ml[(pbase + g) * 2 + 1] = lt; }
+    if (nact == 1) {                                              // the only split: this IS the attention output
+      p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + dim] = __float2bfloat16_rn(ot / lt);
+    } else {
+      p.part_o[(pbase + g) * ZB_DH + dim] = ot;
+      if (dim == 0) { p.part_ml[(pbase + g) * 2 + 0] = mn; p.part_ml[(pbase + g) * 2 + 1] = lt; }
+    }
   }
+  if (nact == 1) return;                                          // CTA-uniform
   __threadfence();
   SyncConsumers::sync();
   if (tid == 0) {
     const int ticket = atomicAdd(&p.att_counters[row * p.Hkv + kvh], 1);
-    *s_last = (ticket == nsplit - 1);
+    *s_last = (ticket == nact - 1);
   }
   SyncConsumers::sync();
   if (!*s_last) return;                                           // CTA-uniform
   __threadfence();
   // ---- the last CTA of this (row, kv head) merges the split partials: ONE cooperative, coalesced L2 read of all of
-  // them into shared memory (a single round trip), then small runtime loops (compact code, see mg_stage_ln).
-  const int nact = min(nsplit, (ctx + it.chunk - 1) / it.chunk);
+  // them into shared memory (a single round trip), then small runtime loops.
   const size_t rbase = ((size_t)row * p.Hkv + kvh) * nsplit * G;
   float* s_po = s_o;                                              // [nact][G][128]  (<= 16 x G x 128 floats, reuses s_o)
   float* s_pml = s_ml;                                            // [nact][G][2]
@@ -824,6 +1005,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   MgCtx cx;
   cx.n_stages = p.n_stages;
   cx.ring = mg_smem;
+  cx.ring_addr = mg_smem_u32(mg_smem);
   cx.scratch = cx.ring + (size_t)p.n_stages * MG_STAGE_BYTES;
   cx.part = reinterpret_cast<float*>(cx.scratch + p.scratch_bytes);
   cx.red = cx.part + 2 * 2 * MG_WARPS * 64;
@@ -835,7 +1017,8 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   cx.empty0 = cx.full0 + 8u * MG_MAX_STAGES;
   volatile int* s_flags = reinterpret_cast<volatile int*>(bars + 16 * MG_MAX_STAGES);   // [0] stop, [1] consumer cursor, [2] misc
   cx.stage = 0; cx.parity = 0; cx.tile_flip = 0;
-  cx.prof = p.dbg != nullptr; cx.t_full = 0;
+  cx.prof = p.dbg != nullptr; cx.t_full = 0; cx.t_fc1 = cx.t_fc1_full = cx.t_fc1_sync = 0; cx.poll_all = p.poll_all != 0;
+  cx.trace = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
 
   const int tid = threadIdx.x, warp = tid >> 5;
   if (tid == 0) {
@@ -869,8 +1052,11 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         // wait for a free ring slot
         int go = 1;
         if (lane == 0) {
+          // back off between polls: the ring is full most of the time, and a hot spin here steals issue slots from
+          // consumer warps 0 and 4, which share this warp's scheduler (they became the stragglers of every tile)
           while (!mg_mbar_try_wait(cx.empty0 + 8u * cx.stage, cx.parity ^ 1)) {
             if (*s_flags) { go = 0; break; }
+            if (p.producer_sleep_ns) __nanosleep(p.producer_sleep_ns);
           }
           if (go) mg_mbar_expect_tx(cx.full0 + 8u * cx.stage, d.total);
         }
@@ -912,8 +1098,8 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   const bool embed_ahead = p.mode == MG_MODE_DECODE || p.mode == MG_MODE_FORCED;
   for (int step = 0; step < p.n_steps; ++step) {
     if (mg_ld_volatile(&st->done)) break;
-    const bool trace = p.dbg != nullptr && step == p.dbg_step;
-    int trace_n = 0;
+    cx.trace = p.dbg != nullptr && step == p.dbg_step;
+    cx.trace_n = 0;
     MG_STAMP();                                                   // 0: step start
     const int pos = mg_ld_volatile(&st->pos), col = mg_ld_volatile(&st->col), Lbuf = mg_ld_volatile(&st->L);
 
@@ -932,10 +1118,10 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
     }
     // RoPE rows of this step (ring) and the KV page of the current position
     {
-      const unsigned char* sp = mg_cons_wait(cx);
+      const uint32_t sp = mg_cons_wait_addr(cx);
       if (tid < p.R * (MG_ROPE_BYTES / 16)) {
         const int r = tid / (MG_ROPE_BYTES / 16), c = tid % (MG_ROPE_BYTES / 16);
-        *reinterpret_cast<uint4*>(cx.s_rope + r * ZB_DH + c * 4) = *reinterpret_cast<const uint4*>(sp + r * MG_ROW_BYTES + c * 16);
+        *reinterpret_cast<uint4*>(cx.s_rope + r * ZB_DH + c * 4) = mg_lds128(sp + r * MG_ROW_BYTES + c * 16);
       }
       if (tid < p.R) cx.s_page[tid] = p.page_table[tid * p.max_pages + pos / ZB_PAGE];
       mg_cons_release(cx);
@@ -1057,7 +1243,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   SyncConsumers::sync();
   if (cx.prof && tid == 0) {
     unsigned long long* o = p.dbg + (size_t)gridDim.x * MG_TRACE_SLOTS + (size_t)blockIdx.x * 8;
-    o[4] = cx.t_full; o[5] = clock64() - t_kernel0;
+    o[4] = cx.t_full; o[5] = clock64() - t_kernel0; o[6] = cx.t_fc1; o[7] = (unsigned long long)cx.t_fc1_full | ((unsigned long long)cx.t_fc1_sync << 32);
   }
   if (tid == 0) {
     s_flags[1] = cx.stage | (cx.parity << 16);

@@ -92,6 +92,9 @@ struct zb_ctx {
   int n_sms = ZB_NUM_SMS;
   int smem_optin = 0;
   int opt_mega = 1;
+  int opt_ring = 0;                    // cap on the ring depth of the persistent kernel (0 = as many stages as fit)
+  int opt_psleep = 100;                // persistent kernel: producer back-off (ns) between polls of a full ring
+  int opt_poll_all = 0;                // persistent kernel: all consumer threads poll the ring barriers (A/B switch)
   int opt_trace = 0;                   // debug: print a per-phase timeline of one step of every persistent launch
   unsigned long long* dbg = nullptr;
 };
@@ -387,8 +390,9 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   const size_t fixed = 2 * 2 * MG_WARPS * 64 * 4 + 96 * 4 + 8 * ZB_DH * 4 + 8 * MG_OWN * 4 + 64 + 16 * MG_MAX_STAGES + 64;
   int stages = (int)(((size_t)c->smem_optin - scratch - fixed) / MG_STAGE_BYTES);
   if (stages > MG_MAX_STAGES) stages = MG_MAX_STAGES;
+  if (c->opt_ring > 0 && stages > c->opt_ring) stages = c->opt_ring;
   if (stages < 2) return cudaErrorInvalidConfiguration;
-  p.n_stages = stages; p.scratch_bytes = (int)scratch;
+  p.n_stages = stages; p.scratch_bytes = (int)scratch; p.poll_all = c->opt_poll_all; p.producer_sleep_ns = (unsigned)c->opt_psleep;
   const size_t smem = (size_t)stages * MG_STAGE_BYTES + scratch + fixed;
 
   cudaError_t e = cudaMemsetAsync(c->bar_counter, 0, sizeof(unsigned), s);
@@ -428,8 +432,8 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     // whole-launch profile of the producer warp / consumer thread 0 (clock64 ticks)
     for (int j = 0; j < 3; ++j) {
       const unsigned long long* o = hbuf.data() + (size_t)c->n_sms * MG_TRACE_SLOTS + (size_t)ctas[j] * 8;
-      fprintf(stderr, "  [prof cta %3d] producer: sched %llu wait_empty %llu issue %llu ticks over %llu stages | consumer: wait_full %llu of %llu ticks\n",
-              ctas[j], o[0], o[1], o[2], o[3], o[4], o[5]);
+      fprintf(stderr, "  [prof cta %3d] producer: sched %llu wait_empty %llu issue %llu ticks over %llu stages | consumer: wait_full %llu of %llu ticks | fc1: total %llu wait_full %llu reduce+epilogue %llu\n",
+              ctas[j], o[0], o[1], o[2], o[3], o[4], o[5], o[6], o[7] & 0xffffffffull, o[7] >> 32);
     }
     return cudaSuccess;
   }
@@ -950,6 +954,9 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "gemv") c->opt_gemv = value;
   else if (k == "mega") c->opt_mega = value;
   else if (k == "trace") c->opt_trace = value;
+  else if (k == "ring") c->opt_ring = value;
+  else if (k == "poll_all") c->opt_poll_all = value;
+  else if (k == "psleep") c->opt_psleep = value;
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
   drop_graph(c);
   return ZB_OK;
