@@ -321,6 +321,75 @@ def test_batch_is_independent_batch1_runs(golden, cuda):
         assert torch.equal(out[i:i + 1], singles[i]), i
 
 
+
+# ------------------------------------------------------------------------------------------------ execution paths
+# The library has three decode paths: the persistent kernel (rows <= 8, default), the per-op CUDA-graph path
+# (mma.sync GEMVs) and the batched tcgen05 path (rows >= 9).  Every path must give the reference's logits.
+class _options:
+    def __init__(self, model, **kw):
+        self.ctx, self.kw = model._native(), kw
+        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1)
+
+    def __enter__(self):
+        for k, v in self.kw.items():
+            self.ctx.set_option(k, v)
+
+    def __exit__(self, *a):
+        for k in self.kw:
+            self.ctx.set_option(k, self.defaults[k])
+
+
+PATHS = {"per_op_graph": dict(mega=0), "batched_tcgen05": dict(mega=0, bt_min_rows=2)}
+
+
+@pytest.mark.parametrize("path", list(PATHS))
+@pytest.mark.parametrize("cname", ["tiny", "small"])
+def test_teacher_forced_logits_other_paths(golden, cuda, cname, path):
+    m = make_model(cname, cuda)
+    prefix = zo.synth_prefix_conditioning(CFGS[cname], 1, 6, 1)
+    with _options(m, **PATHS[path]):
+        got = m.compute_logits_teacher_forced(prefix, golden[f"gen.{cname}.greedy.delayed"], 40)
+    want = golden[f"gen.{cname}.greedy.logits"]
+    for s in range(41):
+        assert_logits_close(got[s], want[s:s + 1], f"{cname} {path} step {s}")
+
+
+@pytest.mark.parametrize("path", list(PATHS))
+def test_teacher_forced_logits_full_size_other_paths(golden, cuda, path):
+    m = make_model("full", cuda)
+    prefix = zo.synth_prefix_conditioning(zo.FULL_CONFIG, 1, 24, 1)
+    with _options(m, **PATHS[path]):
+        got = m.compute_logits_teacher_forced(prefix, golden["full.delayed"], 6)
+    for s in range(7):
+        assert_logits_close(got[s], golden["full.logits"][s:s + 1], f"full {path} step {s}")
+
+
+@pytest.mark.parametrize("path", list(PATHS))
+def test_greedy_stream_other_paths(golden, cuda, path):
+    m = make_model("tiny", cuda)
+    prefix = zo.synth_prefix_conditioning(zo.TINY_CONFIG, 1, 6, 1).to(cuda)
+    with _options(m, **PATHS[path]):
+        out = m.generate(prefix, max_new_tokens=48, sampling_params=dict(temperature=0), progress_bar=False)
+    first = _check_delayed(m.last_delayed_codes, golden["gen.tiny.greedy.delayed"], golden["gen.tiny.greedy.logits"], f"tiny {path}")
+    if first is None:
+        assert torch.equal(out.cpu(), golden["gen.tiny.greedy.codes"])
+
+
+def test_batched_tcgen05_equals_independent_runs(golden, cuda):
+    """Batch semantics = B independent batch-1 runs: 6 utterances (12 rows -> batched tcgen05 path by
+    default) teacher-forced on the same codes must give, per utterance, the logits of its own batch-1 run."""
+    m = make_model("small", cuda)
+    cfg = zo.SMALL_CONFIG
+    nb = 6
+    ps = [zo.synth_prefix_conditioning(cfg, 1, 6, 10 + i) for i in range(nb)]
+    delayed1 = golden["gen.small.greedy.delayed"]
+    singles = [m.compute_logits_teacher_forced(x, delayed1, 12) for x in ps]                    # persistent kernel, rows = 2
+    batch_prefix = torch.cat([torch.cat([x[:1] for x in ps]), torch.cat([x[1:] for x in ps])])
+    got = m.compute_logits_teacher_forced(batch_prefix, delayed1.expand(nb, -1, -1).contiguous(), 12)   # rows = 12
+    for i in range(nb):
+        for s in range(13):
+            assert_logits_close(got[s, i:i + 1], singles[i][s], f"utterance {i} step {s}")
+
 # ------------------------------------------------------------------------------------------------ plugin boundary
 @pytest.mark.parametrize("cname", ["tiny", "small"])
 def test_backbone_plugin_forward(golden, cuda, cname):

@@ -330,3 +330,12 @@ __global__ void __launch_bounds__(256) k_bt_heads_finish(const BtFinishParams p)
     p.logits[((size_t)b * p.n_q + k) * p.V + n] = l;
   }
 }
+
+// plugin-level forward: post-norm_f hidden state of token t -> out[row, t, :]   (backbone/_torch.py:80)
+__global__ void k_bt_store_hidden(const bf16* __restrict__ xn, bf16* __restrict__ out, int d, int S, int t) {
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+  const int row = blockIdx.x;
+  for (int e = threadIdx.x * 8; e < d; e += blockDim.x * 8)
+    *reinterpret_cast<uint4*>(out + ((size_t)row * S + t) * d + e) = *reinterpret_cast<const uint4*>(xn + (size_t)row * d + e);
+}

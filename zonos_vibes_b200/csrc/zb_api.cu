@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "attention_kernels.cuh"
+#include "bt_kernels.cuh"
 #include "decode_kernels.cuh"
 #include "gemv_mma.cuh"
 #include "mega_kernel.cuh"
@@ -84,6 +85,18 @@ struct zb_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool ev_valid = false;
   cudaStream_t cap_stream = nullptr;   // capture happens here: the caller's stream may be the legacy default stream
+  // batched tcgen05 path (bt_kernels.cuh): rows >= opt_bt_min_rows
+  typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  EncodeTiledFn encode = nullptr;
+  int opt_bt_min_rows = 9;
+  bool bt_ready = false;
+  int bt_mpad = 0;
+  bf16* bt_xn = nullptr;
+  float* bt_partial = nullptr;
+  CUtensorMap bt_map_xn{}, bt_map_y{}, bt_map_h{}, bt_map_heads{};
+  std::vector<CUtensorMap> bt_map_in, bt_map_out, bt_map_fc1, bt_map_fc2;
   // persistent decode kernel (mega_kernel.cuh)
   MegaLayer mega_l0{};
   long long mega_layer_stride = 0;
@@ -125,6 +138,11 @@ cudaError_t launch(zb_ctx* c, void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 }
 
 typedef void (*GemvKernel)(const GemvParams);
+bool use_bt(const zb_ctx* c, int rows);
+bool use_mega(const zb_ctx* c, int rows);
+cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s);
+cudaError_t enqueue_bt_heads(zb_ctx* c, float* logits, cudaStream_t s);
+int bt_setup(zb_ctx* c, int rows_pad);
 
 template <int EPI>
 GemvKernel gemv_kernel_for(int R) {
@@ -319,8 +337,13 @@ cudaError_t enqueue_decode_step(zb_ctx* c, cudaStream_t s) {
   int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
   if ((e = launch(c, k_embed, dim3(c->B), dim3(thr), 0, s, (const bf16*)c->emb, (const long long*)c->delayed, c->x,
                   g.d_model, g.n_codebooks, g.vocab, (const ZbDevState*)c->st)) != cudaSuccess) return e;
-  if ((e = enqueue_layers(c, passes, s, true)) != cudaSuccess) return e;
-  if ((e = enqueue_heads(c, passes, c->logits, s)) != cudaSuccess) return e;
+  if (use_bt(c, 2 * c->B)) {
+    if ((e = enqueue_bt_layers(c, s)) != cudaSuccess) return e;
+    if ((e = enqueue_bt_heads(c, c->logits, s)) != cudaSuccess) return e;
+  } else {
+    if ((e = enqueue_layers(c, passes, s, true)) != cudaSuccess) return e;
+    if ((e = enqueue_heads(c, passes, c->logits, s)) != cudaSuccess) return e;
+  }
   SampleParams sp;
   memset(&sp, 0, sizeof(sp));
   sp.logits = c->logits; sp.history = c->delayed; sp.hist_stride = c->L; sp.tokens = c->tokens;
@@ -440,6 +463,156 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   return cudaLaunchKernelEx(&cfg, mega_kernel(G), p);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// batched tcgen05 path
+// ---------------------------------------------------------------------------------------------------------------
+bool use_bt(const zb_ctx* c, int rows) { return c->bt_ready && rows >= c->opt_bt_min_rows && !(use_mega(c, rows)); }
+
+int bt_make_map(zb_ctx* c, CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint32_t box_rows) {
+  cuuint64_t dims[2] = {inner, rows};
+  cuuint64_t strides[1] = {inner * 2};
+  cuuint32_t box[2] = {BT_BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = c->encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return c->err.fail(ZB_ERR_CUDA, "cuTensorMapEncodeTiled failed: %d (inner=%llu rows=%llu box=%u)", (int)r,
+                                            (unsigned long long)inner, (unsigned long long)rows, box_rows);
+  return ZB_OK;
+}
+
+struct BtPlan { int n_tiles, splits, kb_per_split, num_kb; };
+BtPlan bt_plan(const zb_ctx* c, int n_tiles, int K) {
+  BtPlan pl;
+  pl.n_tiles = n_tiles; pl.num_kb = K / BT_BK;
+  int s = c->n_sms / n_tiles;
+  if (s < 1) s = 1;
+  int max_s = pl.num_kb / 4;                       // at least 4 k-blocks (32 KB of weights) per CTA
+  if (max_s < 1) max_s = 1;
+  if (s > max_s) s = max_s;
+  if (s > 8) s = 8;
+  pl.kb_per_split = (pl.num_kb + s - 1) / s;
+  pl.splits = (pl.num_kb + pl.kb_per_split - 1) / pl.kb_per_split;
+  return pl;
+}
+
+int bt_setup(zb_ctx* c, int rows_pad) {
+  const zb_config& g = c->cfg;
+  c->bt_ready = false;
+  if (!c->encode) return ZB_OK;                                   // driver without cuTensorMapEncodeTiled: per-op path only
+  const int d = g.d_model, F = g.ffn, q_size = g.num_heads * ZB_DH, qkv = (g.num_heads + 2 * g.num_heads_kv) * ZB_DH;
+  if (d % BT_BK || F % BT_BK || q_size % BT_BK || F % 64) return ZB_OK;
+  if (d < BT_BN || qkv < BT_BN || F < 64) return ZB_OK;
+  c->bt_mpad = rows_pad;
+  int maxN = qkv > d ? qkv : d;
+  if (g.n_codebooks * g.vocab > maxN) maxN = g.n_codebooks * g.vocab;
+  ZB_CUDA(c->err, cudaMalloc((void**)&c->bt_xn, (size_t)rows_pad * d * 2));
+  ZB_CUDA(c->err, cudaMemset(c->bt_xn, 0, (size_t)rows_pad * d * 2));
+  ZB_CUDA(c->err, cudaMalloc((void**)&c->bt_partial, (size_t)8 * rows_pad * maxN * 4));
+  int rc;
+  if ((rc = bt_make_map(c, &c->bt_map_xn, c->bt_xn, d, rows_pad, BT_BM))) return rc;
+  if ((rc = bt_make_map(c, &c->bt_map_y, c->y, q_size, rows_pad, BT_BM))) return rc;
+  if ((rc = bt_make_map(c, &c->bt_map_h, c->h, F, rows_pad, BT_BM))) return rc;
+  const int nl = g.n_layer;
+  c->bt_map_in.resize(nl); c->bt_map_out.resize(nl); c->bt_map_fc1.resize(nl); c->bt_map_fc2.resize(nl);
+  for (int l = 0; l < nl; ++l) {
+    const LayerW& w = c->layers[l];
+    if ((rc = bt_make_map(c, &c->bt_map_in[l], w.w_in, d, qkv, BT_BN))) return rc;
+    if ((rc = bt_make_map(c, &c->bt_map_out[l], w.w_out, q_size, d, BT_BN))) return rc;
+    if ((rc = bt_make_map(c, &c->bt_map_fc1[l], w.w_fc1, d, 2 * F, 64))) return rc;       // value box + gate box per tile
+    if ((rc = bt_make_map(c, &c->bt_map_fc2[l], w.w_fc2, F, d, BT_BN))) return rc;
+  }
+  if ((rc = bt_make_map(c, &c->bt_map_heads, c->heads, d, (uint64_t)g.n_codebooks * g.vocab, BT_BN))) return rc;
+  c->bt_ready = true;
+  return ZB_OK;
+}
+
+cudaError_t bt_gemm(zb_ctx* c, const CUtensorMap& mx, const CUtensorMap& mw, int N, int K, int mode, int* splits_out, cudaStream_t s) {
+  const int n_tiles = mode == BT_MODE_SWIGLU ? (N + 63) / 64 : (N + BT_BN - 1) / BT_BN;
+  BtPlan pl = bt_plan(c, n_tiles, K);
+  if (mode == BT_MODE_SWIGLU) { pl.splits = 1; pl.kb_per_split = pl.num_kb; }
+  BtGemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = c->rows; p.N = N; p.num_kb = pl.num_kb; p.kb_per_split = pl.kb_per_split; p.mode = mode;
+  p.partial = c->bt_partial; p.m_pad = c->bt_mpad; p.h = c->h; p.st = c->st;
+  if (splits_out) *splits_out = pl.splits;
+  const dim3 grid(n_tiles, (c->rows + BT_BM - 1) / BT_BM, pl.splits);
+  return launch(c, k_bt_gemm, grid, dim3(BT_THREADS), (size_t)BT_SMEM_BYTES, s, mx, mw, p);
+}
+
+BtFinishParams bt_finish_params(zb_ctx* c, int splits, int N) {
+  const zb_config& g = c->cfg;
+  BtFinishParams f;
+  memset(&f, 0, sizeof(f));
+  f.partial = c->bt_partial; f.splits = splits; f.m_pad = c->bt_mpad; f.N = N;
+  f.x = c->x; f.xn = c->bt_xn; f.eps = g.norm_eps; f.d = g.d_model;
+  f.q = c->q; f.page_table = c->page_table; f.max_pages = c->max_pages; f.Hkv = g.num_heads_kv;
+  f.q_size = g.num_heads * ZB_DH; f.kv_size = g.num_heads_kv * ZB_DH; f.rope = c->rope; f.rope_pos = c->rope_pos;
+  f.logits = c->logits; f.n_q = g.n_codebooks; f.V = g.vocab; f.eos = g.eos_token_id; f.B = c->rows / 2; f.st = c->st;
+  return f;
+}
+
+// x holds the layer-0 input.  Runs LN1(0) + all layers; leaves norm_f(x) in bt_xn.
+cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
+  const zb_config& g = c->cfg;
+  const int d = g.d_model, H = g.num_heads, Hkv = g.num_heads_kv, F = g.ffn;
+  const int q_size = H * ZB_DH, qkv = (H + 2 * Hkv) * ZB_DH;
+  const int rows = c->rows;
+  const size_t ln_smem = (size_t)d * 4;
+  cudaError_t e;
+  {
+    BtFinishParams f = bt_finish_params(c, 0, d);
+    f.partial = nullptr; f.ln_w = c->layers[0].ln1_w; f.ln_b = c->layers[0].ln1_b;
+    if ((e = launch(c, k_bt_resid_ln, dim3(rows), dim3(256), ln_smem, s, f)) != cudaSuccess) return e;
+  }
+  for (int l = 0; l < g.n_layer; ++l) {
+    const LayerW& w = c->layers[l];
+    bf16* kv_layer = c->kv + (size_t)l * c->kv_layer_elems;
+    int splits = 1;
+    if ((e = bt_gemm(c, c->bt_map_xn, c->bt_map_in[l], qkv, d, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
+    {
+      BtFinishParams f = bt_finish_params(c, splits, qkv);
+      f.kv_layer = kv_layer;
+      if ((e = launch(c, k_bt_qkv_finish, dim3(rows), dim3(256), 0, s, f)) != cudaSuccess) return e;
+    }
+    {
+      AttnParams a;
+      memset(&a, 0, sizeof(a));
+      a.q = c->q; a.kv_layer = kv_layer; a.page_table = c->page_table; a.max_pages = c->max_pages;
+      a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
+      a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
+      if ((e = launch(c, attn_kernel(H / Hkv), dim3(c->nsplit, Hkv, rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
+    }
+    if ((e = bt_gemm(c, c->bt_map_y, c->bt_map_out[l], d, q_size, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
+    {
+      BtFinishParams f = bt_finish_params(c, splits, d);
+      f.ln_w = w.ln2_w; f.ln_b = w.ln2_b;
+      if ((e = launch(c, k_bt_resid_ln, dim3(rows), dim3(256), ln_smem, s, f)) != cudaSuccess) return e;
+    }
+    if ((e = bt_gemm(c, c->bt_map_xn, c->bt_map_fc1[l], F, d, BT_MODE_SWIGLU, nullptr, s)) != cudaSuccess) return e;
+    if ((e = bt_gemm(c, c->bt_map_h, c->bt_map_fc2[l], d, F, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
+    {
+      BtFinishParams f = bt_finish_params(c, splits, d);
+      if (l + 1 < g.n_layer) { f.ln_w = c->layers[l + 1].ln1_w; f.ln_b = c->layers[l + 1].ln1_b; }
+      else { f.ln_w = c->normf_w; f.ln_b = c->normf_b; }
+      if ((e = launch(c, k_bt_resid_ln, dim3(rows), dim3(256), ln_smem, s, f)) != cudaSuccess) return e;
+    }
+  }
+  return cudaSuccess;
+}
+
+cudaError_t enqueue_bt_heads(zb_ctx* c, float* logits, cudaStream_t s) {
+  const zb_config& g = c->cfg;
+  const int NH = g.n_codebooks * g.vocab;
+  int splits = 1;
+  cudaError_t e;
+  if ((e = bt_gemm(c, c->bt_map_xn, c->bt_map_heads, NH, g.d_model, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
+  BtFinishParams f = bt_finish_params(c, splits, NH);
+  f.logits = logits;
+  return launch(c, k_bt_heads_finish, dim3(g.n_codebooks, c->rows / 2), dim3(256), 0, s, f);
+}
+
 void drop_graph(zb_ctx* c) {
   if (c->graph) { cudaGraphExecDestroy(c->graph); c->graph = nullptr; }
   c->graph_nodes = 0;
@@ -452,6 +625,9 @@ void free_kv(zb_ctx* c) {
   for (void* p : ptrs) if (p) cudaFree(p);
   c->kv = nullptr; c->page_table = nullptr; c->x = c->q = c->y = c->h = nullptr; c->logits = c->part_o = c->part_ml = nullptr;
   c->counters = nullptr; c->tokens = nullptr; c->remaining = c->stopping = c->out_len = c->rope_pos = nullptr;
+  if (c->bt_xn) cudaFree(c->bt_xn);
+  if (c->bt_partial) cudaFree(c->bt_partial);
+  c->bt_xn = nullptr; c->bt_partial = nullptr; c->bt_ready = false;
   c->rows = 0;
 }
 
@@ -579,6 +755,16 @@ int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) {
       return bad(ZB_ERR_NOMEM, std::string("barrier counter: ") + cudaGetErrorString(e));
     }
   }
+  if ((e = cudaFuncSetAttribute(k_bt_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM_BYTES)) != cudaSuccess) {
+    cudaFree(c->arena); delete c;
+    return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute(bt): ") + cudaGetErrorString(e));
+  }
+  {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+      c->encode = reinterpret_cast<zb_ctx::EncodeTiledFn>(fn);
+  }
   if ((e = cudaMalloc(&c->st, sizeof(ZbDevState))) != cudaSuccess) { cudaFree(c->arena); delete c; return bad(ZB_ERR_NOMEM, cudaGetErrorString(e)); }
   cudaMemset(c->st, 0, sizeof(ZbDevState));
   cudaEventCreate(&c->ev0);
@@ -646,7 +832,7 @@ int zb_kv_alloc(zb_ctx* c, int rows, int max_seqlen) {
   ns = ns < 1 ? 1 : (ns > 32 ? 32 : ns);
   c->nsplit = ns;
   const int G = g.num_heads / g.num_heads_kv;
-  const int rows_pad = (rows + 7) / 8 * 8;
+  const int rows_pad = (rows + 127) / 128 * 128;       // activation matrices are TMA operands of 128-row tiles (bt path)
 #define ZB_ALLOC(ptr, bytes) ZB_CUDA(c->err, cudaMalloc((void**)&(ptr), (bytes)))
   ZB_ALLOC(c->kv, c->kv_layer_elems * g.n_layer * sizeof(bf16));
   ZB_ALLOC(c->page_table, total_pages * sizeof(int));
@@ -667,6 +853,12 @@ int zb_kv_alloc(zb_ctx* c, int rows, int max_seqlen) {
   ZB_CUDA(c->err, cudaMemset(c->kv, 0, c->kv_layer_elems * g.n_layer * sizeof(bf16)));
   ZB_CUDA(c->err, cudaMemset(c->counters, 0, (size_t)rows * g.num_heads_kv * 4));
   ZB_CUDA(c->err, cudaMemset(c->x, 0, (size_t)rows_pad * g.d_model * 2));
+  ZB_CUDA(c->err, cudaMemset(c->y, 0, (size_t)rows_pad * g.num_heads * ZB_DH * 2));
+  ZB_CUDA(c->err, cudaMemset(c->h, 0, (size_t)rows_pad * g.ffn * 2));
+  {
+    int rc_bt = bt_setup(c, rows_pad);
+    if (rc_bt) return rc_bt;
+  }
   ZB_CUDA(c->err, cudaMemset(c->rope_pos, 0, (size_t)rows_pad * 4));
   std::vector<int> pt(total_pages);
   for (size_t i = 0; i < total_pages; ++i) pt[i] = (int)i;          // identity paging: row r owns pages [r*P, (r+1)*P)
@@ -709,6 +901,11 @@ int zb_backbone_forward(zb_ctx* c, const void* d_in, void* d_out, int rows, int 
   for (int t = 0; t < S; ++t) {
     ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, seqlen_offset + t, (const int*)d_lengths, t));
     ZB_CUDA(c->err, launch(c, k_load_hidden, dim3(rows), dim3(thr), 0, s, (const bf16*)d_in, c->x, g.d_model, S, t));
+    if (use_bt(c, rows)) {
+      ZB_CUDA(c->err, enqueue_bt_layers(c, s));                   // leaves norm_f(x) in bt_xn
+      if (d_out) ZB_CUDA(c->err, launch(c, k_bt_store_hidden, dim3(rows), dim3(thr), 0, s, (const bf16*)c->bt_xn, (bf16*)d_out, g.d_model, S, t));
+      continue;
+    }
     ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
     if (d_out)
       ZB_CUDA(c->err, launch(c, k_final_ln, dim3(rows), dim3(256), 0, s, (const bf16*)c->x, (const bf16*)c->normf_w, (const bf16*)c->normf_b,
@@ -787,8 +984,13 @@ int zb_decode_logits(zb_ctx* c, const int64_t* d_delayed, int B, int L, int col,
   int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
   ZB_CUDA(c->err, launch(c, k_embed, dim3(B), dim3(thr), 0, s, (const bf16*)c->emb, (const long long*)d_delayed, c->x,
                          g.d_model, g.n_codebooks, g.vocab, (const ZbDevState*)c->st));
-  ZB_CUDA(c->err, enqueue_layers(c, passes, s, true));
-  ZB_CUDA(c->err, enqueue_heads(c, passes, d_logits_out, s));
+  if (use_bt(c, 2 * B)) {
+    ZB_CUDA(c->err, enqueue_bt_layers(c, s));
+    ZB_CUDA(c->err, enqueue_bt_heads(c, d_logits_out, s));
+  } else {
+    ZB_CUDA(c->err, enqueue_layers(c, passes, s, true));
+    ZB_CUDA(c->err, enqueue_heads(c, passes, d_logits_out, s));
+  }
   ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
   return ZB_OK;
 }
@@ -834,7 +1036,8 @@ int zb_gen_begin(zb_ctx* c, const void* d_prefix, int B, int Lc, int64_t* d_dela
     int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
     for (int t = 0; t < Lc; ++t) {
       ZB_CUDA(c->err, launch(c, k_load_hidden, dim3(2 * B), dim3(thr), 0, s, (const bf16*)d_prefix, c->x, g.d_model, Lc, t));
-      ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
+      if (use_bt(c, 2 * B)) ZB_CUDA(c->err, enqueue_bt_layers(c, s));
+      else ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
       ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
     }
     for (int j = 0; j + 1 < prefix_cols; ++j) {      // known audio-prefix columns: no sampling
@@ -842,7 +1045,8 @@ int zb_gen_begin(zb_ctx* c, const void* d_prefix, int B, int Lc, int64_t* d_dela
       if ((rc = upload_state(c, h, s))) return rc;
       ZB_CUDA(c->err, launch(c, k_embed, dim3(B), dim3(thr), 0, s, (const bf16*)c->emb, (const long long*)c->delayed, c->x,
                              g.d_model, g.n_codebooks, g.vocab, (const ZbDevState*)c->st));
-      ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
+      if (use_bt(c, 2 * B)) ZB_CUDA(c->err, enqueue_bt_layers(c, s));
+      else ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
       ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
     }
   }
@@ -957,6 +1161,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "ring") c->opt_ring = value;
   else if (k == "poll_all") c->opt_poll_all = value;
   else if (k == "psleep") c->opt_psleep = value;
+  else if (k == "bt_min_rows") c->opt_bt_min_rows = value;
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
   drop_graph(c);
   return ZB_OK;
