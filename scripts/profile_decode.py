@@ -18,6 +18,7 @@ ap.add_argument("--batch", type=int, default=1)
 ap.add_argument("--opt", action="append", default=[])
 ap.add_argument("--dac", type=int, default=-1, help="-1: skip DAC, 0: tcgen05, 1: SIMT")
 ap.add_argument("--dac-frames", type=int, default=256)
+ap.add_argument("--steps-per-poll", type=int, default=64, help="decode steps per native call (= per persistent-kernel launch)")
 a = ap.parse_args()
 
 dev = torch.device("cuda", 0)
@@ -34,7 +35,7 @@ prefix = torch.randn(2 * a.batch, 24, 2048, device=dev).bfloat16()
 for r in range(a.runs):
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    codes = model.generate(prefix, max_new_tokens=a.frames, batch_size=a.batch, progress_bar=False, seed=r)
+    codes = model.generate(prefix, max_new_tokens=a.frames, batch_size=a.batch, progress_bar=False, seed=r, steps_per_poll=a.steps_per_poll)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     print(f"run {r}: {a.frames} frames in {dt * 1e3:.1f} ms; device us/decode-step {model.last_step_ms * 1e3:.1f}  opts={a.opt}", flush=True)

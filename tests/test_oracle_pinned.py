@@ -113,3 +113,29 @@ def test_oracle_against_live_reference():
         assert torch.equal(a, b), sp
     codes = torch.randint(0, 1024, (2, 9, 11))
     assert torch.equal(ref.pattern.apply_delay_pattern(codes, 1025), zo.apply_delay_pattern(codes, 1025))
+
+
+def test_mamba2_mixer_matches_hf_port():
+    """Row a8: the Mamba2 mixer arithmetic of oracle/hybrid_oracle.py (stepped recurrence) against the pure-torch port of
+    mamba-ssm's Mamba2 that ships with transformers (`Mamba2Mixer.torch_forward`, chunked SSD over the whole sequence;
+    same parameter layout as mamba_ssm.modules.mamba2.Mamba2).  mamba-ssm itself is not installable here."""
+    import hybrid_oracle as ho
+    mm = pytest.importorskip("transformers.models.mamba2.modeling_mamba2")
+    from transformers.models.mamba2.configuration_mamba2 import Mamba2Config
+
+    cfg = ho.HybridConfig(d_model=256, headdim=64, d_state=128)
+    hc = Mamba2Config(hidden_size=cfg.d_model, state_size=cfg.d_state, conv_kernel=cfg.d_conv, expand=cfg.expand, head_dim=cfg.headdim,
+                      n_groups=cfg.ngroups, num_heads=cfg.nheads, use_conv_bias=True, use_bias=False, rms_norm=True, chunk_size=16,
+                      layer_norm_epsilon=1e-5, num_hidden_layers=1)
+    mix = mm.Mamba2Mixer(hc, layer_idx=0).float().eval()
+    p = ho.synth_mamba2_params(cfg, 3, dtype=torch.float32)
+    with torch.no_grad():
+        for name, dst in (("in_proj.weight", mix.in_proj.weight), ("conv1d.weight", mix.conv1d.weight), ("conv1d.bias", mix.conv1d.bias),
+                          ("dt_bias", mix.dt_bias), ("A_log", mix.A_log), ("D", mix.D), ("norm.weight", mix.norm.weight),
+                          ("out_proj.weight", mix.out_proj.weight)):
+            dst.copy_(p[name])
+        u = torch.randn(2, 37, cfg.d_model, generator=torch.Generator().manual_seed(5))
+        want = mix.torch_forward(u)
+        got = ho.mamba2_mixer_sequence(cfg, p, ho.mamba2_alloc_state(cfg, 2), u)
+    assert got.shape == want.shape
+    assert (got - want).abs().max().item() < 1e-4 * want.abs().max().item()
