@@ -62,11 +62,30 @@ typedef struct {
   int32_t reserved[3];
 } zb_sampling;
 
+/* Hybrid (Mamba2 + attention) backbone: BackboneConfig.ssm_cfg / attn_layer_idx (zonos/config.py:28-39) and the Mamba2
+ * constructor defaults of mamba-ssm 2.2.4 that zonos/backbone/_mamba_ssm.py:15-33 relies on.  Layers listed in
+ * attn_layer_idx are attention + GatedMLP(ffn) blocks, every other layer is a Mamba2 block without MLP
+ * (d_intermediate = 0).  LayerNorm blocks only (rms_norm = 0). */
+typedef struct {
+  int32_t d_state;          /* 128 */
+  int32_t d_conv;           /* 4   */
+  int32_t expand;           /* 2   */
+  int32_t headdim;          /* 64  */
+  int32_t ngroups;          /* 1   */
+  int32_t n_attn_layers;
+  int32_t attn_layer_idx[64];
+  int32_t reserved[4];
+} zb_hybrid;
+
 typedef struct zb_ctx zb_ctx;
 
 /* ---- lifetime ------------------------------------------------------------------------------ */
 int  zb_abi_version(void);
 int  zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out);
+/* MambaSSMZonosBackbone (zonos/backbone/_mamba_ssm.py:8-57).  Extra tensors per Mamba2 layer i (names of mamba-ssm's
+ * Mamba2): backbone.layers.{i}.mixer.{in_proj.weight [2*d_inner+2*G*N+H, d], conv1d.weight [conv_dim,1,d_conv],
+ * conv1d.bias, norm.weight [d_inner], out_proj.weight [d, d_inner]} bf16 and {dt_bias, A_log, D} [H] fp32. */
+int  zb_ctx_create_hybrid(const zb_config* cfg, const zb_hybrid* hyb, int device, zb_ctx** out);
 int  zb_ctx_destroy(zb_ctx* ctx);
 const char* zb_last_error(const zb_ctx* ctx);   /* ctx may be NULL: last create() error */
 

@@ -54,6 +54,15 @@ class HybridConfig:
     norm_epsilon: float = 1e-5
     rms_norm: bool = False
 
+    def to_reference_dict(self) -> dict:
+        """The dict ZonosConfig.from_dict (zonos/config.py:56-62) expects for this architecture."""
+        return dict(backbone=dict(d_model=self.d_model, d_intermediate=self.d_intermediate, attn_mlp_d_intermediate=self.attn_mlp_d_intermediate,
+                                  n_layer=self.n_layer, ssm_cfg=dict(layer="Mamba2", d_state=self.d_state, d_conv=self.d_conv, expand=self.expand,
+                                                                     headdim=self.headdim, ngroups=self.ngroups),
+                                  attn_layer_idx=list(self.attn_layer_idx), attn_cfg=dict(num_heads=self.num_heads, num_heads_kv=self.num_heads_kv),
+                                  rms_norm=self.rms_norm, residual_in_fp32=False, norm_epsilon=self.norm_epsilon),
+                    prefix_conditioner=dict(conditioners=[], projection="none"), eos_token_id=1024, masked_token_id=1025)
+
     @property
     def d_inner(self) -> int:
         return self.expand * self.d_model
@@ -84,9 +93,10 @@ def synth_mamba2_params(cfg: HybridConfig, seed: int, dtype=torch.bfloat16) -> d
     p["conv1d.weight"] = ((torch.rand(cfg.conv_dim, 1, cfg.d_conv, generator=g) * 2 - 1) / math.sqrt(cfg.d_conv)).to(dtype)
     p["conv1d.bias"] = (0.1 * torch.randn(cfg.conv_dim, generator=g)).to(dtype)
     dt = torch.exp(torch.rand(cfg.nheads, generator=g) * (math.log(0.1) - math.log(0.001)) + math.log(0.001)).clamp(min=1e-4)
-    p["dt_bias"] = (dt + torch.log(-torch.expm1(-dt))).float()
-    p["A_log"] = torch.log(1 + 15 * torch.rand(cfg.nheads, generator=g)).float()
-    p["D"] = torch.ones(cfg.nheads).float() + 0.1 * torch.randn(cfg.nheads, generator=g)
+    # stored in the model dtype like every other parameter of the reference module (`.to(device, bf16)`), used in fp32
+    p["dt_bias"] = (dt + torch.log(-torch.expm1(-dt))).to(dtype).float()
+    p["A_log"] = torch.log(1 + 15 * torch.rand(cfg.nheads, generator=g)).to(dtype).float()
+    p["D"] = (torch.ones(cfg.nheads) + 0.1 * torch.randn(cfg.nheads, generator=g)).to(dtype).float()
     p["norm.weight"] = (1 + 0.1 * torch.randn(di, generator=g)).to(dtype)
     p["out_proj.weight"] = ((torch.rand(d, di, generator=g) * 2 - 1) / math.sqrt(di)).to(dtype)
     return p

@@ -78,7 +78,7 @@ def test_config_mirror_and_backbone_state_dict_keys():
     assert own == set(sd), (own ^ set(sd))                      # same keys as the reference
     for k, v in m.state_dict().items():
         assert tuple(v.shape) == tuple(sd[k].shape), k
-    assert "b200" in z.BACKBONES and z.BACKBONES["b200"].supported_architectures == ["transformer"]
+    assert "b200" in z.BACKBONES and z.BACKBONES["b200"].supported_architectures == ["transformer", "hybrid"]   # like MambaSSMZonosBackbone (_mamba_ssm.py:9)
 
 
 def test_shard_indices():
@@ -121,3 +121,18 @@ def test_replica_gather_gloo_world2(tmp_path):
         capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "GLOO_OK" in r.stdout
+
+
+def test_hybrid_backbone_state_dict_keys():
+    """Hybrid (Mamba2) holder keeps mamba-ssm's Block / Mamba2 parameter names and shapes."""
+    import hybrid_oracle as ho
+    import zonos_vibes_b200 as z
+    cfg = ho.HYBRID_TINY
+    zc = z.ZonosConfig.from_dict(cfg.to_reference_dict())
+    bb = z.BACKBONES["b200"](zc.backbone)
+    sd = {k[len("backbone."):]: v for k, v in ho.synth_hybrid_state_dict(cfg, 0).items()}
+    own = bb.state_dict()
+    assert set(own) == set(sd), set(own) ^ set(sd)
+    for k, v in own.items():
+        assert tuple(v.shape) == tuple(sd[k].shape), k
+    assert "layers.0.mixer.conv1d.weight" in own and "layers.2.mlp.fc1.weight" in own and "layers.0.mlp.fc1.weight" not in own

@@ -414,6 +414,55 @@ def test_backbone_plugin_forward(golden, cuda, cname):
         assert bool((err <= 2e-2 * want.abs() + 2e-2 * want.pow(2).mean().sqrt()).all()), err.max()
 
 
+
+# ------------------------------------------------------------------------------------------------ hybrid (Mamba2) backbone
+def test_hybrid_backbone_plugin_forward(cuda):
+    """Row a8: MambaSSMZonosBackbone (zonos/backbone/_mamba_ssm.py:8-57) through the plugin API against
+    oracle/hybrid_oracle.py (whose Mamba2 mixer is pinned to the transformers port of mamba-ssm on CPU): a prefill of 8
+    tokens, then 4 single-token decode calls; 2 rows."""
+    import hybrid_oracle as ho
+    import zonos_vibes_b200 as z
+    cfg = ho.HYBRID_TINY
+    zc = z.ZonosConfig.from_dict(cfg.to_reference_dict())
+    sd_full = ho.synth_hybrid_state_dict(cfg, 0)
+    bb = z.BACKBONES["b200"](zc.backbone).to(cuda, torch.bfloat16)
+    bb.load_state_dict({k[len("backbone."):]: v for k, v in sd_full.items()})
+    kv = bb.allocate_inference_cache(2, 32)
+    assert set(kv) == set(range(cfg.n_layer))
+    params = z.InferenceParams(32, 2, 0, 0, kv, torch.zeros(2, dtype=torch.int32, device=cuda))
+    x = torch.randn(2, 12, cfg.d_model, generator=torch.Generator().manual_seed(11)).bfloat16()
+    oracle = ho.HybridOracleBackbone(cfg, sd_full)
+    oracle.allocate(2, 32)
+    want = oracle.forward(x)
+    got = [bb(x[:, :8].to(cuda), params)]
+    params.seqlen_offset += 8
+    params.lengths_per_sample[:] += 8
+    for t in range(8, 12):
+        got.append(bb(x[:, t:t + 1].to(cuda), params))
+        params.seqlen_offset += 1
+        params.lengths_per_sample[:] += 1
+    got = torch.cat(got, dim=1).float().cpu()
+    want = want.float()
+    assert got.shape == want.shape
+    err = (got - want).abs()
+    assert bool((err <= 2e-2 * want.abs() + 2e-2 * want.pow(2).mean().sqrt()).all()), (err.max(), want.pow(2).mean().sqrt())
+
+
+def test_hybrid_generate_runs_and_is_deterministic(cuda):
+    import hybrid_oracle as ho
+    import zonos_vibes_b200 as z
+    cfg = ho.HYBRID_TINY
+    sd = ho.synth_hybrid_state_dict(cfg, 0)
+    tr = zo.synth_state_dict(zo.TINY_CONFIG, 0)                       # embeddings / heads of the same width (d_model = 256)
+    sd.update({k: v for k, v in tr.items() if k.startswith(("embeddings.", "heads."))})
+    m = z.Zonos.from_state_dict(z.ZonosConfig.from_dict(cfg.to_reference_dict()), sd, cuda)
+    prefix = zo.synth_prefix_conditioning(zo.TINY_CONFIG, 1, 6, 1).to(cuda)
+    a = m.generate(prefix, max_new_tokens=24, sampling_params=dict(min_p=0.1), progress_bar=False, seed=3)
+    b = m.generate(prefix, max_new_tokens=24, sampling_params=dict(min_p=0.1), progress_bar=False, seed=3)
+    assert a.shape[:2] == (1, 9) and a.shape[-1] <= 24 and a.dtype == torch.int64
+    assert torch.equal(a, b)                                          # recurrent state is reset per generate
+    assert int(a.min()) >= 0 and int(a.max()) < 1024
+
 # ------------------------------------------------------------------------------------------------ DAC
 def _dac(cuda):
     import zonos_vibes_b200 as z

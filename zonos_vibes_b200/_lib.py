@@ -23,6 +23,13 @@ class ZbConfig(C.Structure):
     ]
 
 
+class ZbHybrid(C.Structure):
+    _fields_ = [
+        ("d_state", C.c_int32), ("d_conv", C.c_int32), ("expand", C.c_int32), ("headdim", C.c_int32), ("ngroups", C.c_int32),
+        ("n_attn_layers", C.c_int32), ("attn_layer_idx", C.c_int32 * 64), ("reserved", C.c_int32 * 4),
+    ]
+
+
 class ZbSampling(C.Structure):
     _fields_ = [
         ("temperature", C.c_float), ("top_p", C.c_float), ("top_k", C.c_int32), ("min_p", C.c_float),
@@ -36,6 +43,7 @@ _P, _I, _I64, _U64, _F = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_float
 SIGNATURES = {
     "zb_abi_version": (_I, []),
     "zb_ctx_create": (_I, [C.POINTER(ZbConfig), _I, C.POINTER(_P)]),
+    "zb_ctx_create_hybrid": (_I, [C.POINTER(ZbConfig), C.POINTER(ZbHybrid), _I, C.POINTER(_P)]),
     "zb_ctx_destroy": (_I, [_P]),
     "zb_last_error": (C.c_char_p, [_P]),
     "zb_set_tensor": (_I, [_P, C.c_char_p, _P, _I64, _I, _P]),

@@ -32,8 +32,6 @@ class NativeContext:
     """Owns one zb_ctx (weights arena + KV pages + scratch) on one device."""
 
     def __init__(self, cfg: BackboneConfig, device: torch.device, eos_token_id: int = 1024, masked_token_id: int = 1025):
-        if cfg.ssm_cfg:
-            raise _lib.ZbError("the 'b200' backbone in this build covers the transformer architecture (ssm_cfg must be empty)")
         self.lib = _lib.load()
         self.device = torch.device(device)
         if self.device.type != "cuda":
@@ -48,7 +46,21 @@ class NativeContext:
         self.handle = C.c_void_p()
         idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
         self.device = torch.device("cuda", idx)
-        _lib.check(self.lib.zb_ctx_create(C.byref(zc), idx, C.byref(self.handle)))
+        if cfg.ssm_cfg:
+            # hybrid: MambaSSMZonosBackbone (zonos/backbone/_mamba_ssm.py:8-57) with mamba-ssm's Mamba2 defaults
+            m = mamba2_dims(cfg)
+            if cfg.rms_norm:
+                raise _lib.ZbError("the hybrid path implements LayerNorm blocks (rms_norm=False)")
+            if len(cfg.attn_layer_idx) > 64:
+                raise _lib.ZbError("at most 64 attention layers")
+            zh = _lib.ZbHybrid()
+            zh.d_state, zh.d_conv, zh.expand, zh.headdim, zh.ngroups = m["d_state"], m["d_conv"], m["expand"], m["headdim"], m["ngroups"]
+            zh.n_attn_layers = len(cfg.attn_layer_idx)
+            for j, li in enumerate(cfg.attn_layer_idx):
+                zh.attn_layer_idx[j] = int(li)
+            _lib.check(self.lib.zb_ctx_create_hybrid(C.byref(zc), C.byref(zh), idx, C.byref(self.handle)))
+        else:
+            _lib.check(self.lib.zb_ctx_create(C.byref(zc), idx, C.byref(self.handle)))
         self.rows = 0
         self.finalized = False
         head_dim = cfg.d_model // zc.num_heads
@@ -69,8 +81,10 @@ class NativeContext:
     def stream(self) -> int:
         return torch.cuda.current_stream(self.device).cuda_stream
 
+    F32_SUFFIXES = ("rope.freqs_cis", ".mixer.dt_bias", ".mixer.A_log", ".mixer.D")
+
     def set_tensor(self, name: str, t: torch.Tensor) -> None:
-        want = torch.float32 if name == "rope.freqs_cis" else torch.bfloat16
+        want = torch.float32 if name.endswith(self.F32_SUFFIXES) else torch.bfloat16
         t = t.detach().to(self.device, want).contiguous()
         with torch.cuda.device(self.device):
             self.check(self.lib.zb_set_tensor(self.handle, name.encode(), t.data_ptr(), t.numel(),
@@ -90,6 +104,22 @@ class NativeContext:
 
     def set_option(self, key: str, value: int) -> None:
         self.check(self.lib.zb_set_option(self.handle, key.encode(), int(value)))
+
+
+def mamba2_dims(cfg: BackboneConfig) -> dict:
+    """Mamba2 constructor arguments: ssm_cfg overrides on top of mamba-ssm 2.2.4's defaults (d_state=128, d_conv=4,
+    expand=2, headdim=64, ngroups=1)."""
+    sc = dict(cfg.ssm_cfg)
+    layer = sc.pop("layer", "Mamba2")
+    if layer != "Mamba2":
+        raise _lib.ZbError(f"ssm_cfg layer {layer!r} is not supported (Mamba2 only)")
+    m = dict(d_state=128, d_conv=4, expand=2, headdim=64, ngroups=1)
+    m.update({k: v for k, v in sc.items() if k in m})
+    m["d_inner"] = m["expand"] * cfg.d_model
+    m["nheads"] = m["d_inner"] // m["headdim"]
+    m["conv_dim"] = m["d_inner"] + 2 * m["ngroups"] * m["d_state"]
+    m["d_in_proj"] = 2 * m["d_inner"] + 2 * m["ngroups"] * m["d_state"] + m["nheads"]
+    return m
 
 
 class _Norm(nn.Module):
@@ -121,10 +151,41 @@ class _Mlp(nn.Module):
         self.fc2 = _Proj(cfg.d_model, cfg.attn_mlp_d_intermediate)
 
 
-class _Block(nn.Module):
+class _Conv1d(nn.Module):
+    def __init__(self, channels, k):
+        super().__init__()
+        self.weight = nn.Parameter(torch.empty(channels, 1, k).uniform_(-k ** -0.5, k ** -0.5))
+        self.bias = nn.Parameter(torch.zeros(channels))
+
+
+class _GatedNorm(nn.Module):
+    def __init__(self, d):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(d))
+
+
+class _Mamba2Mixer(nn.Module):
+    """Parameter holder with mamba_ssm.modules.mamba2.Mamba2's names and shapes."""
+
     def __init__(self, cfg: BackboneConfig):
         super().__init__()
+        m = mamba2_dims(cfg)
+        self.in_proj = _Proj(m["d_in_proj"], cfg.d_model)
+        self.conv1d = _Conv1d(m["conv_dim"], m["d_conv"])
+        self.dt_bias = nn.Parameter(torch.zeros(m["nheads"]))
+        self.A_log = nn.Parameter(torch.zeros(m["nheads"]))
+        self.D = nn.Parameter(torch.ones(m["nheads"]))
+        self.norm = _GatedNorm(m["d_inner"])
+        self.out_proj = _Proj(cfg.d_model, m["d_inner"])
+
+
+class _Block(nn.Module):
+    def __init__(self, cfg: BackboneConfig, mamba: bool = False):
+        super().__init__()
         self.norm = _Norm(cfg.d_model)
+        if mamba:                                  # _mamba_ssm.py:19-21: d_intermediate = 0 => no MLP on Mamba2 layers
+            self.mixer = _Mamba2Mixer(cfg)
+            return
         self.mixer = _Mixer(cfg)
         self.norm2 = _Norm(cfg.d_model)
         self.mlp = _Mlp(cfg)
@@ -135,13 +196,15 @@ class B200ZonosBackbone(nn.Module):
     same `allocate_inference_cache` / `forward` contract.  Parameters are plain holders: the arithmetic runs in
     libzonos_b200 from a repacked device arena that is (re)filled from them on first use."""
 
-    supported_architectures = ["transformer"]
+    supported_architectures = ["transformer", "hybrid"]
 
     def __init__(self, config: BackboneConfig):
-        assert not config.ssm_cfg, "This backbone implementation only supports the Transformer model."
         super().__init__()
         self.config = config
-        self.layers = nn.ModuleList(_Block(config) for _ in range(config.n_layer))
+        if config.ssm_cfg and config.d_intermediate != 0:
+            raise _lib.ZbError("hybrid: Mamba2 layers with an MLP (d_intermediate != 0) are not supported")
+        hybrid = bool(config.ssm_cfg)
+        self.layers = nn.ModuleList(_Block(config, mamba=hybrid and i not in config.attn_layer_idx) for i in range(config.n_layer))
         self.norm_f = _Norm(config.d_model)
         self._ctx: NativeContext | None = None
         self._extra_weights: dict[str, torch.Tensor] = {}

@@ -27,6 +27,60 @@ struct AttnParams {
   float scale_log2;         // (1/sqrt(Dh)) * log2(e)
 };
 
+__device__ __forceinline__ void att_unpack8(const uint4& raw, float (&v)[8]) {
+  v[0] = bf16lo(raw.x); v[1] = bf16hi(raw.x); v[2] = bf16lo(raw.y); v[3] = bf16hi(raw.y);
+  v[4] = bf16lo(raw.z); v[5] = bf16hi(raw.z); v[6] = bf16lo(raw.w); v[7] = bf16hi(raw.w);
+}
+
+// Four tokens per half-warp at once: the scores of all of them are reduced together (16 independent shuffle chains
+// instead of 4 dependent rounds of online softmax), then ONE max / rescale / accumulate step.
+template <int G>
+__device__ __forceinline__ void att_tokens4(const uint4 (&kraw)[4], const uint4 (&vraw)[4], const bool (&valid)[4], const float (&q)[G][8],
+                                               float (&m)[G], float (&l)[G], float (&acc)[G][8], float scale_log2) {
+  float s[4][G];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float kf[8];
+    att_unpack8(kraw[k], kf);
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      float d = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d = fmaf(q[g][j], kf[j], d);
+      s[k][g] = d;
+    }
+  }
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1)
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int g = 0; g < G; ++g) s[k][g] += __shfl_xor_sync(0xffffffffu, s[k][g], o);
+  if (!(valid[0] || valid[1] || valid[2] || valid[3])) return;     // uniform per half-warp; no shuffles below
+  float vf[4][8];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) att_unpack8(vraw[k], vf[k]);
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    float mn = m[g];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { s[k][g] *= scale_log2; if (valid[k]) mn = fmaxf(mn, s[k][g]); }
+    const float corr = exp2f(m[g] - mn);           // m = -inf before the first token -> 0 (mn is finite here)
+    float pr[4], ps = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { pr[k] = valid[k] ? exp2f(s[k][g] - mn) : 0.f; ps += pr[k]; }
+    l[g] = l[g] * corr + ps;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float a = acc[g][j] * corr;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) a = fmaf(pr[k], vf[k][j], a);
+      acc[g][j] = a;
+    }
+    m[g] = mn;
+  }
+}
+
 template <int G>
 __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode(const AttnParams p) {
   pdl_launch_dependents();
@@ -63,50 +117,36 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode(const AttnParams p)
   const size_t kv_stride = (size_t)p.Hkv * head_stride;           // K -> V inside a page
   const size_t page_stride = 2 * kv_stride;
 
-  // warp w handles token pairs (t0 + 2*(w + ATT_WARPS*i)) ; batches of ATT_UB pairs
-  for (int base = t0 + 2 * warp; base < t1; base += 2 * ATT_WARPS * ATT_UB) {
-    uint4 kraw[ATT_UB], vraw[ATT_UB];
-    bool valid[ATT_UB];
+  // warp w handles token pairs (t0 + 2*(w + ATT_WARPS*i)); batches of ATT_UB pairs, double-buffered: the loads of the
+  // next batch are in flight while the current one is reduced (16 x 128-bit loads per lane outstanding).
+  auto load_batch = [&](int base, uint4 (&kr)[ATT_UB], uint4 (&vr)[ATT_UB], bool (&vl)[ATT_UB]) {
 #pragma unroll
     for (int i = 0; i < ATT_UB; ++i) {
       const int t = base + 2 * ATT_WARPS * i + half;
-      valid[i] = t < t1;
-      kraw[i] = make_uint4(0, 0, 0, 0);
-      vraw[i] = make_uint4(0, 0, 0, 0);
-      if (valid[i]) {
+      vl[i] = t < t1;
+      kr[i] = make_uint4(0, 0, 0, 0);
+      vr[i] = make_uint4(0, 0, 0, 0);
+      if (vl[i]) {
         const int page = pt[t / ZB_PAGE];
         const bf16* kp = p.kv_layer + (size_t)page * page_stride + (size_t)kvh * head_stride + (size_t)(t % ZB_PAGE) * ZB_DH + l16 * 8;
-        kraw[i] = ldg_stream(kp);
-        vraw[i] = ldg_stream(kp + kv_stride);
+        kr[i] = ldg_stream(kp);
+        vr[i] = ldg_stream(kp + kv_stride);
       }
     }
-#pragma unroll
-    for (int i = 0; i < ATT_UB; ++i) {
-      const float kf[8] = {bf16lo(kraw[i].x), bf16hi(kraw[i].x), bf16lo(kraw[i].y), bf16hi(kraw[i].y),
-                           bf16lo(kraw[i].z), bf16hi(kraw[i].z), bf16lo(kraw[i].w), bf16hi(kraw[i].w)};
-      const float vf[8] = {bf16lo(vraw[i].x), bf16hi(vraw[i].x), bf16lo(vraw[i].y), bf16hi(vraw[i].y),
-                           bf16lo(vraw[i].z), bf16hi(vraw[i].z), bf16lo(vraw[i].w), bf16hi(vraw[i].w)};
-#pragma unroll
-      for (int g = 0; g < G; ++g) {
-        float s = 0.f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) s = fmaf(q[g][j], kf[j], s);
-        // sum over the 16 lanes of this half-warp
-        s += __shfl_xor_sync(0xffffffffu, s, 8);
-        s += __shfl_xor_sync(0xffffffffu, s, 4);
-        s += __shfl_xor_sync(0xffffffffu, s, 2);
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        if (valid[i]) {
-          s *= p.scale_log2;
-          const float mn = fmaxf(m[g], s);
-          const float corr = exp2f(m[g] - mn);       // m = -inf on first token -> 0
-          const float pr = exp2f(s - mn);
-          l[g] = l[g] * corr + pr;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[g][j] = fmaf(pr, vf[j], acc[g][j] * corr);
-          m[g] = mn;
-        }
-      }
+  };
+  const int bstep = 2 * ATT_WARPS * ATT_UB;
+  uint4 ka[ATT_UB], va[ATT_UB], kb[ATT_UB], vb[ATT_UB];
+  bool la[ATT_UB], lb[ATT_UB];
+  int base = t0 + 2 * warp;
+  if (base < t1) load_batch(base, ka, va, la);
+  while (base < t1) {
+    if (base + bstep < t1) load_batch(base + bstep, kb, vb, lb);
+    att_tokens4<G>(ka, va, la, q, m, l, acc, p.scale_log2);
+    base += bstep;
+    if (base < t1) {
+      if (base + bstep < t1) load_batch(base + bstep, ka, va, la);
+      att_tokens4<G>(kb, vb, lb, q, m, l, acc, p.scale_log2);
+      base += bstep;
     }
   }
 
@@ -154,9 +194,14 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode(const AttnParams p)
       lt += s_l[w][g] * c;
       ot += s_o[w][g][tid] * c;
     }
-    p.part_o[(pbase + g) * ZB_DH + tid] = ot;
-    if (tid == 0) { p.part_ml[(pbase + g) * 2 + 0] = mn; p.part_ml[(pbase + g) * 2 + 1] = lt; }
+    if (nsplit == 1) {                               // the only split: this IS the attention output (no partials, no ticket)
+      p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + tid] = __float2bfloat16_rn(ot / lt);
+    } else {
+      p.part_o[(pbase + g) * ZB_DH + tid] = ot;
+      if (tid == 0) { p.part_ml[(pbase + g) * 2 + 0] = mn; p.part_ml[(pbase + g) * 2 + 1] = lt; }
+    }
   }
+  if (nsplit == 1) return;
   __threadfence();
   __syncthreads();
   if (tid == 0) {

@@ -228,6 +228,27 @@ __device__ __forceinline__ float bt_split_sum(const float* partial, int splits, 
   return s;
 }
 
+// 8 consecutive columns: all split partials are requested before the first add (one L2 round trip), fixed summation order
+__device__ __forceinline__ void bt_split_sum8(const float* partial, int splits, size_t split_stride, size_t off, float (&a)[8]) {
+  float4 lo[8], hi[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    if (i < splits) {
+      lo[i] = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)i * split_stride + off));
+      hi[i] = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)i * split_stride + off + 4));
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a[j] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    if (i < splits) {
+      a[0] += lo[i].x; a[1] += lo[i].y; a[2] += lo[i].z; a[3] += lo[i].w;
+      a[4] += hi[i].x; a[5] += hi[i].y; a[6] += hi[i].z; a[7] += hi[i].w;
+    }
+  }
+}
+
 // x[row] += bf16(sum of the split partials)  (bf16 residual stream, _torch.py:100-101), then xn[row] = LayerNorm(x[row])
 // with the NEXT norm's parameters (F.layer_norm: biased variance, eps inside the sqrt, fp32 statistics).
 // grid = rows, block = 256; d <= 2048 * k handled by a strided loop with the row kept in shared memory.
@@ -239,18 +260,22 @@ __global__ void __launch_bounds__(256) k_bt_resid_ln(const BtFinishParams p) {
   const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const size_t split_stride = (size_t)p.m_pad * p.N;
   float sum = 0.f;
-  for (int e = tid * 2; e < p.d; e += 512) {
-    __nv_bfloat162* px = reinterpret_cast<__nv_bfloat162*>(p.x + (size_t)row * p.d + e);
-    float2 v = __bfloat1622float2(*px);
+  for (int e = tid * 8; e < p.d; e += 2048) {
+    uint4* px = reinterpret_cast<uint4*>(p.x + (size_t)row * p.d + e);
+    const uint4 xr = *px;
+    float v[8] = {bf16lo(xr.x), bf16hi(xr.x), bf16lo(xr.y), bf16hi(xr.y), bf16lo(xr.z), bf16hi(xr.z), bf16lo(xr.w), bf16hi(xr.w)};
     if (p.partial) {
-      const float a0 = bt_split_sum(p.partial, p.splits, split_stride, (size_t)row * p.N + e);
-      const float a1 = bt_split_sum(p.partial, p.splits, split_stride, (size_t)row * p.N + e + 1);
-      const __nv_bfloat162 o = __floats2bfloat162_rn(v.x + bf16_round(a0), v.y + bf16_round(a1));
-      *px = o;
-      v = __bfloat1622float2(o);
+      float a[8];
+      bt_split_sum8(p.partial, p.splits, split_stride, (size_t)row * p.N + e, a);
+      __nv_bfloat162 o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) o[j] = __floats2bfloat162_rn(v[2 * j] + bf16_round(a[2 * j]), v[2 * j + 1] + bf16_round(a[2 * j + 1]));
+      *px = *reinterpret_cast<uint4*>(o);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { const float2 f = __bfloat1622float2(o[j]); v[2 * j] = f.x; v[2 * j + 1] = f.y; }
     }
-    bt_row[e] = v.x; bt_row[e + 1] = v.y;
-    sum += v.x + v.y;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { bt_row[e + j] = v[j]; sum += v[j]; }
   }
   if (!p.xn) return;
   sum = warp_sum(sum);
@@ -286,27 +311,31 @@ __global__ void __launch_bounds__(256) k_bt_qkv_finish(const BtFinishParams p) {
   const size_t split_stride = (size_t)p.m_pad * p.N;
   const int page = p.page_table[(size_t)row * p.max_pages + pos / ZB_PAGE];
   const float* cs_row = p.rope + (size_t)p.rope_pos[row] * (ZB_DH / 2) * 2;
-  for (int n0 = threadIdx.x * 2; n0 < p.N; n0 += 512) {
-    const float v0 = bf16_round(bt_split_sum(p.partial, p.splits, split_stride, (size_t)row * p.N + n0));
-    const float v1 = bf16_round(bt_split_sum(p.partial, p.splits, split_stride, (size_t)row * p.N + n0 + 1));
-    if (n0 < p.q_size + p.kv_size) {
-      const int i = (n0 % ZB_DH) >> 1;
-      const float2 cs = *reinterpret_cast<const float2*>(cs_row + i * 2);
-      const float o0 = __fsub_rn(__fmul_rn(v0, cs.x), __fmul_rn(v1, cs.y));
-      const float o1 = __fadd_rn(__fmul_rn(v1, cs.x), __fmul_rn(v0, cs.y));
-      const __nv_bfloat162 o = __floats2bfloat162_rn(o0, o1);
-      if (n0 < p.q_size) {
-        *reinterpret_cast<__nv_bfloat162*>(p.q + (size_t)row * p.q_size + n0) = o;
+  for (int n8 = threadIdx.x * 8; n8 < p.N; n8 += 2048) {
+    float a[8];
+    bt_split_sum8(p.partial, p.splits, split_stride, (size_t)row * p.N + n8, a);
+    __nv_bfloat162 o[4];
+    const bool roped = n8 < p.q_size + p.kv_size;                 // 8 | 128: a group of 8 columns never straddles q / k / v
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float v0 = bf16_round(a[2 * j]), v1 = bf16_round(a[2 * j + 1]);
+      if (roped) {
+        const int i = ((n8 + 2 * j) % ZB_DH) >> 1;
+        const float2 cs = *reinterpret_cast<const float2*>(cs_row + i * 2);
+        o[j] = __floats2bfloat162_rn(__fsub_rn(__fmul_rn(v0, cs.x), __fmul_rn(v1, cs.y)), __fadd_rn(__fmul_rn(v1, cs.x), __fmul_rn(v0, cs.y)));
       } else {
-        const int m = n0 - p.q_size;
-        bf16* dst = p.kv_layer + ((((size_t)page * 2 + 0) * p.Hkv + m / ZB_DH) * ZB_PAGE + pos % ZB_PAGE) * ZB_DH + m % ZB_DH;
-        *reinterpret_cast<__nv_bfloat162*>(dst) = o;
+        o[j] = __floats2bfloat162_rn(v0, v1);
       }
-    } else {
-      const int m = n0 - p.q_size - p.kv_size;
-      bf16* dst = p.kv_layer + ((((size_t)page * 2 + 1) * p.Hkv + m / ZB_DH) * ZB_PAGE + pos % ZB_PAGE) * ZB_DH + m % ZB_DH;
-      *reinterpret_cast<__nv_bfloat162*>(dst) = __floats2bfloat162_rn(v0, v1);
     }
+    bf16* dst;
+    if (n8 < p.q_size) {
+      dst = p.q + (size_t)row * p.q_size + n8;
+    } else {
+      const int isv = n8 >= p.q_size + p.kv_size;
+      const int m = n8 - p.q_size - (isv ? p.kv_size : 0);
+      dst = p.kv_layer + ((((size_t)page * 2 + isv) * p.Hkv + m / ZB_DH) * ZB_PAGE + pos % ZB_PAGE) * ZB_DH + m % ZB_DH;
+    }
+    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<uint4*>(o);
   }
 }
 

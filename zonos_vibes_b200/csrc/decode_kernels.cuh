@@ -14,7 +14,7 @@
 #pragma once
 #include "zb_common.cuh"
 
-enum { EPI_QKV = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_HEADS = 3 };
+enum { EPI_QKV = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_HEADS = 3, EPI_PLAIN = 4 };   // PLAIN: out = bf16(W x) (MMA kernel only)
 
 #define GEMV_THREADS 256
 #define GEMV_CTAS_PER_SM 2

@@ -42,6 +42,8 @@ __device__ __forceinline__ void gm_epilogue_pair(const GemvParams& p, int a /*ac
     __nv_bfloat162* px = reinterpret_cast<__nv_bfloat162*>(p.out + (size_t)a * p.out_stride + n0);
     const float2 old = __bfloat1622float2(*px);
     *px = __floats2bfloat162_rn(old.x + bf16_round(s0), old.y + bf16_round(s1));
+  } else if constexpr (EPI == EPI_PLAIN) {
+    *reinterpret_cast<__nv_bfloat162*>(p.out + (size_t)a * p.out_stride + n0) = __floats2bfloat162_rn(s0, s1);
   } else if constexpr (EPI == EPI_QKV) {
     const int pos = p.st->pos;
     const float v0 = bf16_round(s0), v1 = bf16_round(s1);

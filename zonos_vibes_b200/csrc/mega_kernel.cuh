@@ -741,55 +741,6 @@ __device__ __forceinline__ void mg_att_token(const uint4& kraw, const uint4& vra
   }
 }
 
-// Four tokens per half-warp at once: the scores of all of them are reduced together (16 independent shuffle chains
-// instead of 4 dependent rounds of online softmax), then ONE max / rescale / accumulate step.
-template <int G>
-__device__ __forceinline__ void mg_att_tokens4(const uint4 (&kraw)[4], const uint4 (&vraw)[4], const bool (&valid)[4], const float (&q)[G][8],
-                                               float (&m)[G], float (&l)[G], float (&acc)[G][8], float scale_log2) {
-  float s[4][G];
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    float kf[8];
-    mg_unpack8(kraw[k], kf);
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-      float d = 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) d = fmaf(q[g][j], kf[j], d);
-      s[k][g] = d;
-    }
-  }
-#pragma unroll
-  for (int o = 8; o > 0; o >>= 1)
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-#pragma unroll
-      for (int g = 0; g < G; ++g) s[k][g] += __shfl_xor_sync(0xffffffffu, s[k][g], o);
-  if (!(valid[0] || valid[1] || valid[2] || valid[3])) return;     // uniform per half-warp; no shuffles below
-  float vf[4][8];
-#pragma unroll
-  for (int k = 0; k < 4; ++k) mg_unpack8(vraw[k], vf[k]);
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-    float mn = m[g];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { s[k][g] *= scale_log2; if (valid[k]) mn = fmaxf(mn, s[k][g]); }
-    const float corr = exp2f(m[g] - mn);           // m = -inf before the first token -> 0 (mn is finite here)
-    float pr[4], ps = 0.f;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { pr[k] = valid[k] ? exp2f(s[k][g] - mn) : 0.f; ps += pr[k]; }
-    l[g] = l[g] * corr + ps;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float a = acc[g][j] * corr;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) a = fmaf(pr[k], vf[k][j], a);
-      acc[g][j] = a;
-    }
-    m[g] = mn;
-  }
-}
-
 template <int G>
 __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const bf16* kv_layer, int pos) {
   const MgAttItem it = mg_att_item(p, pos);
@@ -853,7 +804,7 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
           vraw[k] = mg_lds128(sp + MG_KV_TOK * ZB_DH * 2 + i * (ZB_DH * 2) + l16 * 16);
         }
       }
-      mg_att_tokens4<G>(kraw, vraw, valid, q, m, l, acc, p.scale_log2);
+      att_tokens4<G>(kraw, vraw, valid, q, m, l, acc, p.scale_log2);
     }
     if (!fresh) mg_cons_release(cx);
   }

@@ -10,6 +10,7 @@
 #include "bt_kernels.cuh"
 #include "decode_kernels.cuh"
 #include "gemv_mma.cuh"
+#include "hybrid_kernels.cuh"
 #include "mega_kernel.cuh"
 #include "sample_kernels.cuh"
 
@@ -37,6 +38,11 @@ struct Slot {
 
 struct LayerW {
   bf16 *ln1_w, *ln1_b, *w_in, *w_out, *ln2_w, *ln2_b, *w_fc1, *w_fc2;
+};
+
+struct LayerM {   // Mamba2 layer (hybrid backbone)
+  bf16 *ln_w, *ln_b, *w_in, *conv_w, *conv_b, *norm_w, *w_out;
+  float *dt_bias, *A_log, *D;
 };
 
 struct Pass {   // one GEMV launch covers template rows mapped by (base0, base1, lim0, lim1)
@@ -85,6 +91,16 @@ struct zb_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool ev_valid = false;
   cudaStream_t cap_stream = nullptr;   // capture happens here: the caller's stream may be the legacy default stream
+  // hybrid backbone (hybrid_kernels.cuh)
+  bool hybrid = false;
+  zb_hybrid hyb{};
+  std::vector<int> is_mamba;           // per layer
+  std::vector<int> kv_slot;            // attention layers: index into the KV cache; Mamba2 layers: index into the states
+  int n_attn = 0, n_mamba = 0;
+  std::vector<LayerM> mlayers;
+  int m_dinner = 0, m_nheads = 0, m_convdim = 0, m_dinproj = 0;
+  float *m_conv_state = nullptr, *m_ssm_state = nullptr, *m_xbc = nullptr;
+  bf16 *m_zx = nullptr, *m_y = nullptr, *m_ynorm = nullptr;
   // batched tcgen05 path (bt_kernels.cuh): rows >= opt_bt_min_rows
   typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -179,6 +195,7 @@ GemvKernel gemv_mma_kernel(int R, int epi) {
     case EPI_RESID: return gemv_mma_kernel_for<EPI_RESID>(R);
     case EPI_SWIGLU: return gemv_mma_kernel_for<EPI_SWIGLU>(R);
     case EPI_HEADS: return gemv_mma_kernel_for<EPI_HEADS>(R);
+    case EPI_PLAIN: return gemv_mma_kernel_for<EPI_PLAIN>(R);
   }
   return nullptr;
 }
@@ -251,11 +268,45 @@ cudaError_t launch_gemv(zb_ctx* c, int epi, const Pass& ps, const GemvParams& pi
   GemvParams p = pin;
   // rows that produce outputs: SwiGLU pairs value row i with gate row i+F (n_tasks == F); the others use adjacent pairs
   p.n_rows = epi == EPI_SWIGLU ? pin.n_tasks : pin.n_tasks * 2;
-  if (c->opt_gemv == 0) {     // SIMT cross-check path
+  if (c->opt_gemv == 0 && epi != EPI_PLAIN) {     // SIMT cross-check path
     return launch(c, gemv_kernel(ps.R, epi), dim3(ZB_NUM_SMS * GEMV_CTAS_PER_SM), dim3(GEMV_THREADS), gemv_smem(ps.R, p.K), s, p);
   }
   p.n_tasks = (p.n_rows + GM_ROWS - 1) / GM_ROWS;
   return launch(c, gemv_mma_kernel(ps.R, epi), dim3(ZB_NUM_SMS * 2), dim3(GM_THREADS), gemv_mma_smem(ps.R, p.K, epi), s, p);
+}
+
+// One Mamba2 layer for the current token (hybrid backbone): x <- x + out_proj(gated_norm(ssm(conv(in_proj(LN(x))))))
+cudaError_t enqueue_mamba_layer(zb_ctx* c, int l, const std::vector<Pass>& passes, cudaStream_t s) {
+  const zb_config& g = c->cfg;
+  const LayerM& w = c->mlayers[l];
+  const int d = g.d_model, rows = c->rows;
+  cudaError_t e;
+  for (const Pass& ps : passes) {   // LN + in_proj -> zxbcdt
+    GemvParams p = base_params(c, ps);
+    p.W = w.w_in; p.K = d; p.n_tasks = c->m_dinproj / 2; p.row0_mul = 2; p.row1_off = 1;
+    p.x = c->x; p.ln_w = w.ln_w; p.ln_b = w.ln_b;
+    p.out = c->m_zx; p.out_stride = c->m_dinproj;
+    if ((e = launch_gemv(c, EPI_PLAIN, ps, p, s)) != cudaSuccess) return e;
+  }
+  M2Params m;
+  memset(&m, 0, sizeof(m));
+  m.zx = c->m_zx; m.d_in_proj = c->m_dinproj; m.d_inner = c->m_dinner; m.conv_dim = c->m_convdim; m.d_conv = c->hyb.d_conv;
+  m.nheads = c->m_nheads; m.headdim = c->hyb.headdim; m.d_state = c->hyb.d_state; m.ngroups = c->hyb.ngroups;
+  m.conv_w = w.conv_w; m.conv_b = w.conv_b; m.dt_bias = w.dt_bias; m.A_log = w.A_log; m.D = w.D; m.norm_w = w.norm_w;
+  const int slot = c->kv_slot[l];
+  m.conv_state = c->m_conv_state + (size_t)slot * rows * c->m_convdim * c->hyb.d_conv;
+  m.ssm_state = c->m_ssm_state + (size_t)slot * rows * c->m_nheads * c->hyb.headdim * c->hyb.d_state;
+  m.xbc = c->m_xbc; m.y = c->m_y; m.ynorm = c->m_ynorm; m.eps = 1e-5f; m.st = c->st;
+  if ((e = launch(c, k_m2_conv, dim3((c->m_convdim + 255) / 256, rows), dim3(256), 0, s, m)) != cudaSuccess) return e;
+  if ((e = launch(c, k_m2_ssm, dim3(c->m_nheads, rows), dim3(256), 0, s, m)) != cudaSuccess) return e;
+  if ((e = launch(c, k_m2_gated_norm, dim3(rows), dim3(256), 0, s, m)) != cudaSuccess) return e;
+  for (const Pass& ps : passes) {   // out_proj + residual
+    GemvParams p = base_params(c, ps);
+    p.W = w.w_out; p.K = c->m_dinner; p.n_tasks = d / 2; p.row0_mul = 2; p.row1_off = 1;
+    p.x = c->m_ynorm; p.out = c->x; p.out_stride = d;
+    if ((e = launch_gemv(c, EPI_RESID, ps, p, s)) != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 // all transformer layers for the current token (x in c->x, positions in device state)
@@ -265,8 +316,12 @@ cudaError_t enqueue_layers(zb_ctx* c, const std::vector<Pass>& passes, cudaStrea
   const int q_size = H * ZB_DH, kv_size = Hkv * ZB_DH;
   cudaError_t e;
   for (int l = 0; l < g.n_layer; ++l) {
+    if (c->is_mamba[l]) {
+      if ((e = enqueue_mamba_layer(c, l, passes, s)) != cudaSuccess) return e;
+      continue;
+    }
     const LayerW& w = c->layers[l];
-    bf16* kv_layer = c->kv + (size_t)l * c->kv_layer_elems;
+    bf16* kv_layer = c->kv + (size_t)c->kv_slot[l] * c->kv_layer_elems;
     for (const Pass& ps : passes) {   // LN1 + in_proj + RoPE + KV append
       GemvParams p = base_params(c, ps);
       p.W = w.w_in; p.K = d; p.n_tasks = (q_size + 2 * kv_size) / 2; p.row0_mul = 2; p.row1_off = 1;
@@ -305,7 +360,7 @@ cudaError_t enqueue_layers(zb_ctx* c, const std::vector<Pass>& passes, cudaStrea
       p.W = w.w_fc2; p.K = F; p.n_tasks = d / 2; p.row0_mul = 2; p.row1_off = 1;
       p.x = c->h; p.out = c->x; p.out_stride = d;
       NextW nx;
-      if (l + 1 < g.n_layer) nx = NextW{c->layers[l + 1].w_in, (size_t)(q_size + 2 * kv_size) * d * 2, 0};
+      if (l + 1 < g.n_layer && !c->is_mamba[l + 1]) nx = NextW{c->layers[l + 1].w_in, (size_t)(q_size + 2 * kv_size) * d * 2, 0};
       else if (heads_follow) nx = NextW{c->heads, (size_t)g.n_codebooks * g.vocab * d * 2, 0};
       set_prefetch(c, p, nx);
       if ((e = launch_gemv(c, EPI_RESID, ps, p, s)) != cudaSuccess) return e;
@@ -323,7 +378,7 @@ cudaError_t enqueue_heads(zb_ctx* c, const std::vector<Pass>& passes, float* log
     p.x = c->x; p.ln_w = c->normf_w; p.ln_b = c->normf_b;
     p.logits = logits; p.n_q = g.n_codebooks; p.V = g.vocab; p.eos = g.eos_token_id;
     const LayerW& w0 = c->layers[0];
-    set_prefetch(c, p, NextW{w0.w_in, (size_t)(g.num_heads + 2 * g.num_heads_kv) * ZB_DH * g.d_model * 2, 0});
+    if (!c->is_mamba[0]) set_prefetch(c, p, NextW{w0.w_in, (size_t)(g.num_heads + 2 * g.num_heads_kv) * ZB_DH * g.d_model * 2, 0});
     if ((e = launch_gemv(c, EPI_HEADS, ps, p, s)) != cudaSuccess) return e;
   }
   return cudaSuccess;
@@ -467,7 +522,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
 // ---------------------------------------------------------------------------------------------------------------
 // batched tcgen05 path
 // ---------------------------------------------------------------------------------------------------------------
-bool use_bt(const zb_ctx* c, int rows) { return c->bt_ready && rows >= c->opt_bt_min_rows && !(use_mega(c, rows)); }
+bool use_bt(const zb_ctx* c, int rows) { return c->bt_ready && !c->hybrid && rows >= c->opt_bt_min_rows && !(use_mega(c, rows)); }
 
 int bt_make_map(zb_ctx* c, CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint32_t box_rows) {
   cuuint64_t dims[2] = {inner, rows};
@@ -500,7 +555,7 @@ BtPlan bt_plan(const zb_ctx* c, int n_tiles, int K) {
 int bt_setup(zb_ctx* c, int rows_pad) {
   const zb_config& g = c->cfg;
   c->bt_ready = false;
-  if (!c->encode) return ZB_OK;                                   // driver without cuTensorMapEncodeTiled: per-op path only
+  if (!c->encode || c->hybrid) return ZB_OK;                                   // driver without cuTensorMapEncodeTiled: per-op path only
   const int d = g.d_model, F = g.ffn, q_size = g.num_heads * ZB_DH, qkv = (g.num_heads + 2 * g.num_heads_kv) * ZB_DH;
   if (d % BT_BK || F % BT_BK || q_size % BT_BK || F % 64) return ZB_OK;
   if (d < BT_BN || qkv < BT_BN || F < 64) return ZB_OK;
@@ -568,7 +623,7 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
   }
   for (int l = 0; l < g.n_layer; ++l) {
     const LayerW& w = c->layers[l];
-    bf16* kv_layer = c->kv + (size_t)l * c->kv_layer_elems;
+    bf16* kv_layer = c->kv + (size_t)c->kv_slot[l] * c->kv_layer_elems;
     int splits = 1;
     if ((e = bt_gemm(c, c->bt_map_xn, c->bt_map_in[l], qkv, d, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
     {
@@ -625,6 +680,9 @@ void free_kv(zb_ctx* c) {
   for (void* p : ptrs) if (p) cudaFree(p);
   c->kv = nullptr; c->page_table = nullptr; c->x = c->q = c->y = c->h = nullptr; c->logits = c->part_o = c->part_ml = nullptr;
   c->counters = nullptr; c->tokens = nullptr; c->remaining = c->stopping = c->out_len = c->rope_pos = nullptr;
+  void* mptrs[] = {c->m_conv_state, c->m_ssm_state, c->m_xbc, c->m_zx, c->m_y, c->m_ynorm};
+  for (void* q : mptrs) if (q) cudaFree(q);
+  c->m_conv_state = c->m_ssm_state = c->m_xbc = nullptr; c->m_zx = c->m_y = c->m_ynorm = nullptr;
   if (c->bt_xn) cudaFree(c->bt_xn);
   if (c->bt_partial) cudaFree(c->bt_partial);
   c->bt_xn = nullptr; c->bt_partial = nullptr; c->bt_ready = false;
@@ -640,10 +698,26 @@ int zb_abi_version(void) { return ZB_ABI_VERSION; }
 
 const char* zb_last_error(const zb_ctx* ctx) { return ctx ? ctx->err.msg.c_str() : g_create_error.c_str(); }
 
-int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) {
+static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int device, zb_ctx** out);
+int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) { return ctx_create_impl(cfg, nullptr, device, out); }
+int zb_ctx_create_hybrid(const zb_config* cfg, const zb_hybrid* hyb, int device, zb_ctx** out) {
+  if (!hyb) { g_create_error = "null hybrid config"; return ZB_ERR_ARG; }
+  return ctx_create_impl(cfg, hyb, device, out);
+}
+
+static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int device, zb_ctx** out) {
   ZbErr tmp;
   auto bad = [&](int code, const std::string& m) { g_create_error = m; return code; };
   if (!cfg || !out) return bad(ZB_ERR_ARG, "null argument");
+  if (hyb) {
+    if (hyb->d_state != 128 || hyb->d_conv < 2 || hyb->d_conv > 8 || hyb->ngroups != 1 || hyb->headdim <= 0 || hyb->expand <= 0)
+      return bad(ZB_ERR_ARG, "hybrid: d_state must be 128, ngroups 1, d_conv in [2,8]");
+    if ((hyb->expand * cfg->d_model) % hyb->headdim != 0 || (hyb->expand * cfg->d_model) % 256 != 0)
+      return bad(ZB_ERR_ARG, "hybrid: d_inner must be a multiple of headdim and of 256");
+    if (hyb->n_attn_layers < 0 || hyb->n_attn_layers > 64) return bad(ZB_ERR_ARG, "hybrid: at most 64 attention layers");
+    const int dinp = 2 * hyb->expand * cfg->d_model + 2 * hyb->d_state + hyb->expand * cfg->d_model / hyb->headdim;
+    if (dinp % 8 != 0) return bad(ZB_ERR_ARG, "hybrid: in_proj rows must be a multiple of 8");
+  }
   if (cfg->d_model <= 0 || cfg->d_model % 256 != 0 || cfg->d_model > GEMV_MAX_LN_DIM)
     return bad(ZB_ERR_ARG, "d_model must be a multiple of 256 and <= 2048");
   if (cfg->num_heads <= 0 || cfg->d_model != cfg->num_heads * ZB_DH) return bad(ZB_ERR_ARG, "head_dim must be 128");
@@ -678,10 +752,35 @@ int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) {
     off = align_up(off + (size_t)numel * (dtype == ZB_F32 ? 4 : 2), 256);
     c->slots[name] = s;
   };
+  c->is_mamba.assign(nl, 0);
+  c->kv_slot.assign(nl, 0);
+  if (hyb) {
+    c->hybrid = true;
+    c->hyb = *hyb;
+    c->m_dinner = hyb->expand * d;
+    c->m_nheads = c->m_dinner / hyb->headdim;
+    c->m_convdim = c->m_dinner + 2 * hyb->ngroups * hyb->d_state;
+    c->m_dinproj = 2 * c->m_dinner + 2 * hyb->ngroups * hyb->d_state + c->m_nheads;
+    for (int l = 0; l < nl; ++l) c->is_mamba[l] = 1;
+    for (int i = 0; i < hyb->n_attn_layers; ++i)
+      if (hyb->attn_layer_idx[i] >= 0 && hyb->attn_layer_idx[i] < nl) c->is_mamba[hyb->attn_layer_idx[i]] = 0;
+  }
+  for (int l = 0; l < nl; ++l) c->kv_slot[l] = c->is_mamba[l] ? c->n_mamba++ : c->n_attn++;
   for (int l = 0; l < nl; ++l) {
     const std::string p = "backbone.layers." + std::to_string(l);
     carve(p + ".norm.weight", d, ZB_BF16);
     carve(p + ".norm.bias", d, ZB_BF16);
+    if (c->is_mamba[l]) {
+      carve(p + ".mixer.in_proj.weight", (int64_t)c->m_dinproj * d, ZB_BF16);
+      carve(p + ".mixer.conv1d.weight", (int64_t)c->m_convdim * hyb->d_conv, ZB_BF16);
+      carve(p + ".mixer.conv1d.bias", c->m_convdim, ZB_BF16);
+      carve(p + ".mixer.dt_bias", c->m_nheads, ZB_F32);
+      carve(p + ".mixer.A_log", c->m_nheads, ZB_F32);
+      carve(p + ".mixer.D", c->m_nheads, ZB_F32);
+      carve(p + ".mixer.norm.weight", c->m_dinner, ZB_BF16);
+      carve(p + ".mixer.out_proj.weight", (int64_t)d * c->m_dinner, ZB_BF16);
+      continue;
+    }
     carve(p + ".mixer.in_proj.weight", (int64_t)qkv * d, ZB_BF16);
     carve(p + ".mixer.out_proj.weight", (int64_t)d * cfg->num_heads * ZB_DH, ZB_BF16);
     carve(p + ".norm2.weight", d, ZB_BF16);
@@ -703,8 +802,17 @@ int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) {
   for (auto& kv : c->slots) kv.second.ptr = c->arena + reinterpret_cast<size_t>(kv.second.ptr);
   auto W = [&](const std::string& n) { return reinterpret_cast<bf16*>(c->slots[n].ptr); };
   c->layers.resize(nl);
+  c->mlayers.resize(nl);
+  auto Wf = [&](const std::string& n) { return reinterpret_cast<float*>(c->slots[n].ptr); };
   for (int l = 0; l < nl; ++l) {
     const std::string p = "backbone.layers." + std::to_string(l);
+    if (c->is_mamba[l]) {
+      c->layers[l] = LayerW{};
+      c->mlayers[l] = LayerM{W(p + ".norm.weight"), W(p + ".norm.bias"), W(p + ".mixer.in_proj.weight"), W(p + ".mixer.conv1d.weight"),
+                             W(p + ".mixer.conv1d.bias"), W(p + ".mixer.norm.weight"), W(p + ".mixer.out_proj.weight"),
+                             Wf(p + ".mixer.dt_bias"), Wf(p + ".mixer.A_log"), Wf(p + ".mixer.D")};
+      continue;
+    }
     c->layers[l] = LayerW{W(p + ".norm.weight"), W(p + ".norm.bias"), W(p + ".mixer.in_proj.weight"), W(p + ".mixer.out_proj.weight"),
                           W(p + ".norm2.weight"), W(p + ".norm2.bias"), W(p + ".mlp.fc1.weight"), W(p + ".mlp.fc2.weight")};
   }
@@ -715,16 +823,19 @@ int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) {
   c->rope = reinterpret_cast<float*>(c->slots["rope.freqs_cis"].ptr);
   if (((size_t)cfg->vocab * d * 2) % 256 != 0) { cudaFree(c->arena); delete c; return bad(ZB_ERR_ARG, "vocab*d_model*2 must be a multiple of 256"); }
   // algorithmic bytes streamed per decode step: layer weights + LN params + final LN + real head rows
-  c->step_weight_bytes = (int64_t)nl * ((int64_t)qkv * d + (int64_t)d * d + (int64_t)2 * F * d + (int64_t)d * F + 4 * d) * 2 +
+  c->step_weight_bytes = (int64_t)c->n_attn * ((int64_t)qkv * d + (int64_t)d * d + (int64_t)2 * F * d + (int64_t)d * F + 4 * d) * 2 +
                          (int64_t)2 * d * 2 + (int64_t)cfg->n_codebooks * (cfg->vocab - 1) * d * 2;
+  if (hyb)   // Mamba2 layer: LN + in_proj + conv + per-head scalars + gated-norm weight + out_proj
+    c->step_weight_bytes += (int64_t)c->n_mamba * (((int64_t)c->m_dinproj * d + (int64_t)c->m_convdim * (hyb->d_conv + 1) + c->m_dinner +
+                                                    (int64_t)d * c->m_dinner + 2 * d) * 2 + (int64_t)3 * c->m_nheads * 4);
 
   // opt-in to large dynamic shared memory for every GEMV instantiation.  The attribute is per FUNCTION (shared by all
   // contexts of the process), so it is always raised to the device maximum: a context for a small config created
   // after a large one must not shrink it.
   const int max_smem = (int)prop.sharedMemPerBlockOptin;
   for (int R = 2; R <= 8; R += 2)
-    for (int epi = 0; epi < 4; ++epi) {
-      if ((e = cudaFuncSetAttribute(gemv_kernel(R, epi), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
+    for (int epi = 0; epi < 5; ++epi) {
+      if ((epi < 4 && (e = cudaFuncSetAttribute(gemv_kernel(R, epi), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess) ||
           (e = cudaFuncSetAttribute(gemv_mma_kernel(R, epi), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess) {
         cudaFree(c->arena); delete c;
         return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e));
@@ -742,7 +853,7 @@ int zb_ctx_create(const zb_config* cfg, int device, zb_ctx** out) {
     const LayerW& w0 = c->layers[0];
     c->mega_l0 = MegaLayer{w0.ln1_w, w0.ln1_b, w0.w_in, w0.w_out, w0.ln2_w, w0.ln2_b, w0.w_fc1, w0.w_fc2};
     c->mega_layer_stride = nl > 1 ? (long long)((const char*)c->layers[1].ln1_w - (const char*)w0.ln1_w) : 0;
-    c->mega_ok = true;
+    c->mega_ok = !c->hybrid;
     for (int l = 0; l < nl; ++l) {
       const LayerW& w = c->layers[l];
       const bf16* a[8] = {w.ln1_w, w.ln1_b, w.w_in, w.w_out, w.ln2_w, w.ln2_b, w.w_fc1, w.w_fc2};
@@ -834,7 +945,20 @@ int zb_kv_alloc(zb_ctx* c, int rows, int max_seqlen) {
   const int G = g.num_heads / g.num_heads_kv;
   const int rows_pad = (rows + 127) / 128 * 128;       // activation matrices are TMA operands of 128-row tiles (bt path)
 #define ZB_ALLOC(ptr, bytes) ZB_CUDA(c->err, cudaMalloc((void**)&(ptr), (bytes)))
-  ZB_ALLOC(c->kv, c->kv_layer_elems * g.n_layer * sizeof(bf16));
+  const size_t n_kv_layers = c->n_attn > 0 ? c->n_attn : 1;
+  ZB_ALLOC(c->kv, c->kv_layer_elems * n_kv_layers * sizeof(bf16));
+  if (c->hybrid && c->n_mamba > 0) {
+    const size_t cs = (size_t)c->n_mamba * rows * c->m_convdim * c->hyb.d_conv, ss = (size_t)c->n_mamba * rows * c->m_nheads * c->hyb.headdim * c->hyb.d_state;
+    ZB_ALLOC(c->m_conv_state, cs * 4);
+    ZB_ALLOC(c->m_ssm_state, ss * 4);
+    ZB_ALLOC(c->m_xbc, (size_t)rows_pad * c->m_convdim * 4);
+    ZB_ALLOC(c->m_zx, (size_t)rows_pad * c->m_dinproj * 2);
+    ZB_ALLOC(c->m_y, (size_t)rows_pad * c->m_dinner * 2);
+    ZB_ALLOC(c->m_ynorm, (size_t)rows_pad * c->m_dinner * 2);
+    ZB_CUDA(c->err, cudaMemset(c->m_conv_state, 0, cs * 4));
+    ZB_CUDA(c->err, cudaMemset(c->m_ssm_state, 0, ss * 4));
+    ZB_CUDA(c->err, cudaMemset(c->m_ynorm, 0, (size_t)rows_pad * c->m_dinner * 2));
+  }
   ZB_ALLOC(c->page_table, total_pages * sizeof(int));
   ZB_ALLOC(c->x, (size_t)rows_pad * g.d_model * 2);
   ZB_ALLOC(c->q, (size_t)rows_pad * g.num_heads * ZB_DH * 2);
@@ -850,7 +974,7 @@ int zb_kv_alloc(zb_ctx* c, int rows, int max_seqlen) {
   ZB_ALLOC(c->out_len, (size_t)rows_pad * 4);
   ZB_ALLOC(c->rope_pos, (size_t)rows_pad * 4);
 #undef ZB_ALLOC
-  ZB_CUDA(c->err, cudaMemset(c->kv, 0, c->kv_layer_elems * g.n_layer * sizeof(bf16)));
+  ZB_CUDA(c->err, cudaMemset(c->kv, 0, c->kv_layer_elems * n_kv_layers * sizeof(bf16)));
   ZB_CUDA(c->err, cudaMemset(c->counters, 0, (size_t)rows * g.num_heads_kv * 4));
   ZB_CUDA(c->err, cudaMemset(c->x, 0, (size_t)rows_pad * g.d_model * 2));
   ZB_CUDA(c->err, cudaMemset(c->y, 0, (size_t)rows_pad * g.num_heads * ZB_DH * 2));
@@ -872,6 +996,10 @@ int zb_kv_reset(zb_ctx* c, void* stream) {
   ZB_CUDA(c->err, cudaSetDevice(c->device));
   ZB_CUDA(c->err, cudaMemsetAsync(c->st, 0, sizeof(ZbDevState), s));
   ZB_CUDA(c->err, cudaMemsetAsync(c->rope_pos, 0, (size_t)c->rows * 4, s));
+  if (c->hybrid && c->n_mamba > 0) {      // recurrent state starts from zero for every new sequence
+    ZB_CUDA(c->err, cudaMemsetAsync(c->m_conv_state, 0, (size_t)c->n_mamba * c->rows * c->m_convdim * c->hyb.d_conv * 4, s));
+    ZB_CUDA(c->err, cudaMemsetAsync(c->m_ssm_state, 0, (size_t)c->n_mamba * c->rows * c->m_nheads * c->hyb.headdim * c->hyb.d_state * 4, s));
+  }
   return ZB_OK;
 }
 
@@ -1173,6 +1301,7 @@ int zb_bench_kernel(zb_ctx* c, const char* name, int iters, float* ms_out, void*
   int rc = check_ready(c);
   if (rc) return rc;
   if (!name || !ms_out || iters <= 0) return ZB_ERR_ARG;
+  if (c->hybrid) return c->err.fail(ZB_ERR_ARG, "zb_bench_kernel covers the transformer layers only");
   cudaStream_t s = (cudaStream_t)stream;
   ZB_CUDA(c->err, cudaSetDevice(c->device));
   const zb_config& g = c->cfg;
