@@ -153,6 +153,63 @@ def random_backbone_state_dict(dev, seed=0):
     return sd
 
 
+HYBRID = dict(n_layer=46, attn_layer_idx=[9, 18, 27, 36, 45], d_state=128, d_conv=4, expand=2, headdim=64, ngroups=1)
+"""Synthetic hybrid architecture (BASELINE config 5).  The checkpoint's config.json is not in the reference repo and
+mamba-ssm is not installable here (SURVEY App. C: dims UNVERIFIED): d_model 2048, Mamba2 defaults, 46 layers of which 5 are
+attention + GatedMLP(8192) blocks."""
+
+
+def hybrid_config_dict():
+    return dict(backbone=dict(d_model=FULL["d_model"], d_intermediate=0, attn_mlp_d_intermediate=FULL["ffn"], n_layer=HYBRID["n_layer"],
+                              ssm_cfg=dict(layer="Mamba2"), attn_layer_idx=HYBRID["attn_layer_idx"],
+                              attn_cfg=dict(num_heads=FULL["num_heads"], num_heads_kv=FULL["num_heads_kv"]),
+                              rms_norm=False, residual_in_fp32=False, norm_epsilon=1e-5),
+                prefix_conditioner=dict(conditioners=[], projection="none"), eos_token_id=1025)
+
+
+def random_hybrid_state_dict(dev, seed=0):
+    g = torch.Generator(device=dev).manual_seed(seed)
+    d, f = FULL["d_model"], FULL["ffn"]
+    qkv = (FULL["num_heads"] + 2 * FULL["num_heads_kv"]) * 128
+    di = HYBRID["expand"] * d
+    nh = di // HYBRID["headdim"]
+    conv_dim = di + 2 * HYBRID["ngroups"] * HYBRID["d_state"]
+    d_in_proj = 2 * di + 2 * HYBRID["ngroups"] * HYBRID["d_state"] + nh
+
+    def lin(o, i):
+        return ((torch.rand(o, i, generator=g, device=dev) * 2 - 1) / math.sqrt(i)).bfloat16()
+
+    def ln(sd, p):
+        sd[p + ".weight"] = (1 + 0.1 * torch.randn(d, generator=g, device=dev)).bfloat16()
+        sd[p + ".bias"] = (0.1 * torch.randn(d, generator=g, device=dev)).bfloat16()
+
+    sd = {}
+    for i in range(HYBRID["n_layer"]):
+        p = f"backbone.layers.{i}"
+        ln(sd, p + ".norm")
+        if i in HYBRID["attn_layer_idx"]:
+            sd[p + ".mixer.in_proj.weight"] = lin(qkv, d)
+            sd[p + ".mixer.out_proj.weight"] = lin(d, d)
+            ln(sd, p + ".norm2")
+            sd[p + ".mlp.fc1.weight"] = lin(2 * f, d)
+            sd[p + ".mlp.fc2.weight"] = lin(d, f)
+        else:
+            sd[p + ".mixer.in_proj.weight"] = lin(d_in_proj, d)
+            sd[p + ".mixer.conv1d.weight"] = ((torch.rand(conv_dim, 1, HYBRID["d_conv"], generator=g, device=dev) * 2 - 1) / 2).bfloat16()
+            sd[p + ".mixer.conv1d.bias"] = (0.1 * torch.randn(conv_dim, generator=g, device=dev)).bfloat16()
+            dt = torch.exp(torch.rand(nh, generator=g, device=dev) * (math.log(0.1) - math.log(0.001)) + math.log(0.001))
+            sd[p + ".mixer.dt_bias"] = (dt + torch.log(-torch.expm1(-dt))).bfloat16()
+            sd[p + ".mixer.A_log"] = torch.log(1 + 15 * torch.rand(nh, generator=g, device=dev)).bfloat16()
+            sd[p + ".mixer.D"] = torch.ones(nh, device=dev).bfloat16()
+            sd[p + ".mixer.norm.weight"] = (1 + 0.1 * torch.randn(di, generator=g, device=dev)).bfloat16()
+            sd[p + ".mixer.out_proj.weight"] = lin(d, di)
+    ln(sd, "backbone.norm_f")
+    for k in range(9):
+        sd[f"embeddings.{k}.weight"] = torch.randn(1026, d, generator=g, device=dev).bfloat16()
+        sd[f"heads.{k}.weight"] = lin(1025, d)
+    return sd
+
+
 def random_dac_state_dict(dev, seed=2):
     g = torch.Generator(device=dev).manual_seed(seed)
     sd = {}
@@ -195,6 +252,12 @@ def cpu_reference_sample(n_decode_steps=None, dac_frames=43, budget_s=12.0):
     import dac_oracle as do
     import zonos_oracle as zo
 
+    # all host threads this process may use (torchrun exports OMP_NUM_THREADS=1, which would make this a 1-thread baseline)
+    try:
+        ncpu = len(os.sched_getaffinity(0))
+    except AttributeError:
+        ncpu = os.cpu_count() or 1
+    torch.set_num_threads(max(1, ncpu))
     cfg = zo.OracleConfig(eos_token_id=1025)
     sd = zo.synth_state_dict(cfg, 0)
     o = zo.OracleZonos(cfg, sd)

@@ -18,6 +18,7 @@ ap.add_argument("--batch", type=int, default=1)
 ap.add_argument("--opt", action="append", default=[])
 ap.add_argument("--dac", type=int, default=-1, help="-1: skip DAC, 0: tcgen05, 1: SIMT")
 ap.add_argument("--dac-frames", type=int, default=256)
+ap.add_argument("--hybrid", action="store_true", help="synthetic hybrid (Mamba2 + attention) architecture, BASELINE config 5")
 ap.add_argument("--steps-per-poll", type=int, default=64, help="decode steps per native call (= per persistent-kernel launch)")
 a = ap.parse_args()
 
@@ -25,7 +26,9 @@ dev = torch.device("cuda", 0)
 cfgd = dict(backbone=dict(d_model=2048, d_intermediate=0, attn_mlp_d_intermediate=8192, n_layer=26, ssm_cfg={}, attn_layer_idx=[],
                           attn_cfg=dict(num_heads=16, num_heads_kv=4), rms_norm=False, residual_in_fp32=False, norm_epsilon=1e-5),
             prefix_conditioner=dict(conditioners=[], projection="none"), eos_token_id=1025)
-model = z.Zonos.from_state_dict(z.ZonosConfig.from_dict(cfgd), bench.random_backbone_state_dict(dev), dev,
+if a.hybrid:
+    cfgd = bench.hybrid_config_dict()
+model = z.Zonos.from_state_dict(z.ZonosConfig.from_dict(cfgd), bench.random_hybrid_state_dict(dev) if a.hybrid else bench.random_backbone_state_dict(dev), dev,
                                 dac_state_dict=bench.random_dac_state_dict(dev) if a.dac >= 0 else None)
 ctx = model._native()
 for kv in a.opt:
