@@ -197,7 +197,7 @@ int conv_tc(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half* 
   p.n_tile = pick_n_tile(c.Cout);
   p.tmem_cols = p.n_tile <= 32 ? 32 : p.n_tile <= 64 ? 64 : p.n_tile <= 128 ? 128 : 256;
   const int stage_bytes = TC_A_BYTES + p.n_tile * 128;
-  int stages = (108 * 1024) / stage_bytes;               // two CTAs per SM
+  int stages = (108 * 1024 - TC_TAB_BYTES) / stage_bytes;   // two CTAs per SM
   if (stages < 2) stages = 2;
   if (stages > 8) stages = 8;
   p.stages = stages;
@@ -206,7 +206,7 @@ int conv_tc(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half* 
   int rc;
   if ((rc = make_map(d, &mx, x, c.Cin, T_in, TC_BM))) return rc;
   if ((rc = make_map(d, &mw, c.w_koi, c.Cin, (uint64_t)c.K * c.Cout, p.n_tile))) return rc;
-  const size_t smem = 1024 + (size_t)stages * stage_bytes + 256;
+  const size_t smem = 1024 + (size_t)stages * stage_bytes + 256 + TC_TAB_BYTES;
   dim3 grid((p.m_rows + TC_BM - 1) / TC_BM, c.Cout / p.n_tile, c.stride > 1 ? c.stride : 1);
   k_dac_conv_tc<<<grid, TC_THREADS, smem, s>>>(mx, mw, p);
   d->launches++;
@@ -252,7 +252,10 @@ int decode_one_tc(zb_dac* d, const long long* codes, float* wav, int T, cudaStre
   float bias_h = 0.f;
   ZB_CUDA(d->err, cudaMemcpyAsync(&bias_h, c.bias, 4, cudaMemcpyDeviceToHost, s));
   ZB_CUDA(d->err, cudaStreamSynchronize(s));
-  k_dac_final_conv<<<ZB_NUM_SMS * 8, 256, 0, s>>>(A, c.w_kio, bias_h, wav, Tl, c.Cin, c.K, c.pad);
+  {
+    const size_t fsm = (size_t)(FC_TILE + c.K - 1) * ((c.Cin / 2) | 1) * 4 + (size_t)c.K * c.Cin * 4;
+    k_dac_final_conv<<<(Tl + FC_TILE - 1) / FC_TILE, FC_TILE, fsm, s>>>(A, c.w_kio, bias_h, wav, Tl, c.Cin, c.K, c.pad);
+  }
   d->launches++;
   ZB_CUDA(d->err, cudaGetLastError());
   return ZB_OK;
@@ -371,6 +374,7 @@ int zb_dac_finalize(zb_dac* d, void* stream) {
   ZB_CUDA(d->err, cudaStreamSynchronize(s));
   // opt-in to large dynamic smem for the tensor-core kernel
   ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_final_conv, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   d->finalized = true;
   return ZB_OK;
 }

@@ -24,6 +24,7 @@
 #define TC_BK 64
 #define TC_A_BYTES (TC_BM * TC_BK * 2)     // 16 KB
 #define TC_MAX_TAPS 8
+#define TC_TAB_BYTES (3 * 256 * 4)          // bias / alpha / 1/(alpha + 1e-9) of the CTA's <= 256 output channels
 
 struct TcConvParams {
   int ntaps;                 // conv: K taps; transposed conv: 2 taps per phase
@@ -62,6 +63,11 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
   auto empty_bar = [&](int s) { return bar_base + 8u * (uint32_t)(p.stages + s); };
   const uint32_t tmem_full_bar = bar_base + 8u * (uint32_t)(2 * p.stages);
   const uint32_t tmem_slot = tmem_full_bar + 8u;
+  // per-channel epilogue constants: one shared-memory broadcast read per element instead of two global loads and a
+  // reciprocal per element and thread (the epilogue, not the MMA, bounds the small-channel layers)
+  float* s_bias = reinterpret_cast<float*>(tc_smem_raw + (((tmem_slot + 16u + 15u) & ~15u) - raw));
+  float* s_alpha = s_bias + 256;
+  float* s_inv = s_alpha + 256;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(tc_smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -130,6 +136,13 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
     int out_row;
     if (p.stride > 1) out_row = m * p.stride + phase - p.pad; else out_row = m;
     const bool valid = (m < p.m_rows) && (out_row >= 0) && (out_row < p.T_out);
+    for (int i = threadIdx.x - 64; i < p.n_tile; i += 128) {
+      s_bias[i] = __ldg(p.bias + n0 + i);
+      const float a = p.out_act ? __ldg(p.alpha_next + n0 + i) : 1.f;
+      s_alpha[i] = a;
+      s_inv[i] = 1.0f / (a + 1e-9f);
+    }
+    asm volatile("bar.sync 2, 128;" ::: "memory");          // the 4 epilogue warps
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     const size_t row_base = (size_t)(valid ? out_row : 0) * p.Cout + n0;
@@ -139,7 +152,7 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
       if (valid) {
         float f[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __ldg(p.bias + n0 + c0 + j);
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + s_bias[c0 + j];
         if (p.residual) {
           const uint4* rp = reinterpret_cast<const uint4*>(p.residual + row_base + c0);
 #pragma unroll
@@ -167,9 +180,9 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
             __half2 h[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const float a0 = __ldg(p.alpha_next + n0 + c0 + q * 8 + 2 * j), a1 = __ldg(p.alpha_next + n0 + c0 + q * 8 + 2 * j + 1);
-              h[j] = __floats2half2_rn(snake_fast(f[q * 8 + 2 * j], a0, 1.0f / (a0 + 1e-9f)),
-                                       snake_fast(f[q * 8 + 2 * j + 1], a1, 1.0f / (a1 + 1e-9f)));
+              const int cc = c0 + q * 8 + 2 * j;
+              h[j] = __floats2half2_rn(snake_fast(f[q * 8 + 2 * j], s_alpha[cc], s_inv[cc]),
+                                       snake_fast(f[q * 8 + 2 * j + 1], s_alpha[cc + 1], s_inv[cc + 1]));
             }
             op[q] = *reinterpret_cast<uint4*>(h);
           }
@@ -185,21 +198,42 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
 }
 
 // Final conv (Cin -> 1 channel, k taps) + tanh: pure bandwidth, SIMT.  x fp16 [T][C] (already snaked), w fp32 [K][C].
-__global__ void __launch_bounds__(256) k_dac_final_conv(const __half* __restrict__ x, const float* __restrict__ w, float bias,
-                                                        float* __restrict__ out, int T, int C, int K, int pad) {
-  // one warp per output sample; lanes over (tap, channel)
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  const int nw = (gridDim.x * blockDim.x) >> 5;
-  for (int t = warp; t < T; t += nw) {
-    float acc = 0.f;
-    for (int i = lane; i < K * C; i += 32) {
-      const int j = i / C, c = i % C;
-      const int tt = t + j - pad;
-      if (tt >= 0 && tt < T) acc = fmaf(__half2float(x[(size_t)tt * C + c]), w[i], acc);
-    }
-    acc = warp_sum(acc);
-    if (lane == 0) out[t] = tanhf(acc + bias);
+// One block = FC_TILE output samples: the [FC_TILE + K - 1][C] input window is staged in shared memory with coalesced
+// 16 B loads (the first version used one warp per output sample and ran at 0.15 TB/s, 13 % of the whole decode), rows
+// padded to an odd number of 32-bit words so that 32 consecutive samples read 32 different banks.
+#define FC_TILE 256
+__global__ void __launch_bounds__(FC_TILE) k_dac_final_conv(const __half* __restrict__ x, const float* __restrict__ w, float bias,
+                                                            float* __restrict__ out, int T, int C, int K, int pad) {
+  extern __shared__ __align__(16) unsigned char fc_smem[];
+  const int ldw = (C / 2) | 1;                                   // row stride in 32-bit words (odd)
+  uint32_t* xs = reinterpret_cast<uint32_t*>(fc_smem);           // [FC_TILE + K - 1][ldw]
+  float* ws = reinterpret_cast<float*>(xs + (size_t)(FC_TILE + K - 1) * ldw);   // [K][C]
+  const int t0 = blockIdx.x * FC_TILE;
+  const int rows = FC_TILE + K - 1;
+  const int wpr = C / 2;                                         // words per row
+  for (int i = threadIdx.x; i < rows * wpr; i += FC_TILE) {
+    const int r = i / wpr, c2 = i % wpr;
+    const int tt = t0 + r - pad;
+    uint32_t v = 0u;
+    if (tt >= 0 && tt < T) v = *reinterpret_cast<const uint32_t*>(x + (size_t)tt * C + 2 * c2);
+    xs[(size_t)r * ldw + c2] = v;
   }
+  for (int i = threadIdx.x; i < K * C; i += FC_TILE) ws[i] = w[i];
+  __syncthreads();
+  const int t = t0 + threadIdx.x;
+  if (t >= T) return;
+  float acc0 = 0.f, acc1 = 0.f;
+  for (int j = 0; j < K; ++j) {
+    const uint32_t* xr = xs + (size_t)(threadIdx.x + j) * ldw;
+    const float* wr = ws + j * C;
+#pragma unroll 4
+    for (int c2 = 0; c2 < wpr; ++c2) {
+      const float2 v = __half22float2(*reinterpret_cast<const __half2*>(xr + c2));
+      acc0 = fmaf(v.x, wr[2 * c2], acc0);
+      acc1 = fmaf(v.y, wr[2 * c2 + 1], acc1);
+    }
+  }
+  out[t] = tanhf(acc0 + acc1 + bias);
 }
 
 // fp32 [T][C] -> fp16 [T][C] with optional snake (used to feed SIMT-produced activations into the TC path in tests)
