@@ -156,7 +156,8 @@ int  zb_dac_destroy(zb_dac* dac);
 const char* zb_dac_last_error(const zb_dac* dac);
 int  zb_dac_set_tensor(zb_dac* dac, const char* name, const float* d_ptr, int64_t numel, void* stream);
 int  zb_dac_finalize(zb_dac* dac, void* stream);
-/* d_codes int64 [B, 9, T] in [0,1023]; d_wav fp32 [B, 1, 512*T].  impl: 0 = tcgen05 bf16 (default), 1 = SIMT fp32. */
+/* d_codes int64 [B, 9, T] in [0,1023]; d_wav fp32 [B, 1, 512*T].  impl: 0 = tcgen05 fp16 (default),
+ * 1 = SIMT fp32 cross-check, 2 / 3 = force the one-tile-per-CTA / the persistent tcgen05 kernel for every layer. */
 int  zb_dac_decode(zb_dac* dac, const int64_t* d_codes, float* d_wav, int B, int T, int impl, void* stream);
 /* debug/parity: copy an intermediate of the last decode ("latent", "conv1", "block0".."block3") as fp32
  * [B, C, T_l] (reference layout) into d_out; returns ZB_ERR_ARG if the name is unknown. */

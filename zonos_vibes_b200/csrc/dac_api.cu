@@ -8,6 +8,7 @@
 
 #include "dac_simt.cuh"
 #include "dac_tc.cuh"
+#include "dac_tc2.cuh"
 
 namespace {
 
@@ -214,7 +215,62 @@ int conv_tc(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half* 
   return ZB_OK;
 }
 
-int decode_one_tc(zb_dac* d, const long long* codes, float* wav, int T, cudaStream_t s) {
+
+// second-generation persistent kernel (dac_tc2.cuh): window reuse across taps, 256-row tiles, double-buffered TMEM
+int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half* residual, __half* out_raw, __half* out_act,
+             const float* alpha_next, cudaStream_t s) {
+  if (c.Cout > TC2_MAX_COUT) return d->err.fail(ZB_ERR_ARG, "conv_tc2: Cout %d > %d", c.Cout, TC2_MAX_COUT);
+  TcConv2Params p;
+  memset(&p, 0, sizeof(p));
+  p.ntaps = c.stride > 1 ? 2 : c.K;
+  p.dil = c.dil; p.pad = c.pad; p.stride = c.stride;
+  p.kchunks = (c.Cin + TC_BK - 1) / TC_BK;
+  p.T_out = T_in * c.stride;
+  p.m_rows = c.stride > 1 ? T_in + 1 : T_in;
+  p.Cout = c.Cout;
+  p.n_tile = c.Cout % 128 == 0 ? 128 : c.Cout % 96 == 0 ? 96 : c.Cout % 64 == 0 ? 64 : 32;
+  p.n_tiles = c.Cout / p.n_tile;
+  p.phases = c.stride > 1 ? c.stride : 1;
+  p.acc_cols = 128; p.acc_stages = 2;
+  // 256-row tiles halve the weight traffic; keep 128-row tiles when there would be too few tiles to balance 148 SMs
+  const long tiles2 = (long)((p.m_rows + 2 * TC_BM - 1) / (2 * TC_BM)) * p.n_tiles * p.phases;
+  p.mt = tiles2 >= 8L * ZB_NUM_SMS ? 2 : 1;
+  p.m_tiles = (p.m_rows + p.mt * TC_BM - 1) / (p.mt * TC_BM);
+  p.lead = c.stride > 1 ? p.ntaps - 1 : c.pad;
+  const int win_rows = p.mt * TC_BM + (c.stride > 1 ? p.ntaps - 1 : (c.K - 1) * c.dil);
+  p.n_aload = win_rows > 256 ? 2 : 1;
+  p.box_rows = (((win_rows + p.n_aload - 1) / p.n_aload) + 7) & ~7;
+  p.a_bytes = p.n_aload * p.box_rows * 128;
+  p.a_slots = p.kchunks >= 3 ? 3 : 2;
+  const int b_bytes = p.n_tile * 128;
+  const int budget = 227 * 1024 - 1024 - 512 - TC2_TAB_BYTES;
+  if (p.a_slots * p.a_bytes + 4 * b_bytes > budget) p.a_slots = 2;
+  int bs = (budget - p.a_slots * p.a_bytes) / b_bytes;
+  if (bs > TC2_MAX_B_STAGES) bs = TC2_MAX_B_STAGES;
+  if (bs < 2) return d->err.fail(ZB_ERR_ARG, "conv_tc2: shared memory budget");
+  p.b_stages = bs;
+  p.bias = c.bias; p.residual = residual; p.out_raw = out_raw; p.out_act = out_act; p.alpha_next = alpha_next;
+  CUtensorMap mx, mw;
+  int rc;
+  if ((rc = make_map(d, &mx, x, c.Cin, T_in, p.box_rows))) return rc;
+  if ((rc = make_map(d, &mw, c.w_koi, c.Cin, (uint64_t)c.K * c.Cout, p.n_tile))) return rc;
+  const size_t smem = 1024 + (size_t)p.a_slots * p.a_bytes + (size_t)p.b_stages * b_bytes + 512 + TC2_TAB_BYTES;
+  const long tiles = (long)p.m_tiles * p.n_tiles * p.phases;
+  const int grid = (int)(tiles < ZB_NUM_SMS ? tiles : ZB_NUM_SMS);
+  k_dac_conv_tc2<<<grid, TC2_THREADS, smem, s>>>(mx, mw, p);
+  d->launches++;
+  ZB_CUDA(d->err, cudaGetLastError());
+  return ZB_OK;
+}
+
+int decode_one_tc(zb_dac* d, const long long* codes, float* wav, int T, cudaStream_t s, int impl) {
+  auto conv_tc = [&](zb_dac* dd, const ConvW& c, const __half* x, int T_in, const __half* residual, __half* out_raw, __half* out_act,
+                     const float* alpha_next, cudaStream_t st) {
+    // impl 0: per layer — the wide layers (Cout >= 768) run best on the N=256 one-tile-per-CTA kernel (two CTAs per SM),
+    // everything else on the persistent window-reuse kernel; impl 2 / 3 force one kernel everywhere (A/B runs)
+    const bool v1 = impl == 2 || (impl == 0 && c.Cout >= 768);
+    return v1 ? ::conv_tc(dd, c, x, T_in, residual, out_raw, out_act, alpha_next, st) : conv_tc2(dd, c, x, T_in, residual, out_raw, out_act, alpha_next, st);
+  };
   int rc;
   __half *A = d->f16buf[0], *R = d->f16buf[1], *Y = d->f16buf[2], *A2 = d->f16buf[3], *R2 = d->f16buf[4];
   const bool keep = d->keep != 0;
@@ -374,6 +430,7 @@ int zb_dac_finalize(zb_dac* d, void* stream) {
   ZB_CUDA(d->err, cudaStreamSynchronize(s));
   // opt-in to large dynamic smem for the tensor-core kernel
   ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+  ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc2, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_final_conv, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   d->finalized = true;
   return ZB_OK;
@@ -390,7 +447,7 @@ int zb_dac_decode(zb_dac* d, const int64_t* d_codes, float* d_wav, int B, int T,
   for (int b = 0; b < B; ++b) {
     const long long* codes = reinterpret_cast<const long long*>(d_codes) + (size_t)b * kNq * T;
     float* wav = d_wav + (size_t)b * 512 * T;
-    rc = impl == 1 ? decode_one_simt(d, codes, wav, T, s) : decode_one_tc(d, codes, wav, T, s);
+    rc = impl == 1 ? decode_one_simt(d, codes, wav, T, s) : decode_one_tc(d, codes, wav, T, s, impl);
     if (rc) return rc;
   }
   return ZB_OK;

@@ -11,7 +11,7 @@
 // (`tcgen05.ld.32x32b.x32`) which fuse bias, residual add, the NEXT layer's Snake activation and the fp16 store.
 // A ConvTranspose1d (k=2s, stride s) is s independent 2-tap GEMMs, one per output phase (grid.z).
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..5 = epilogue.
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..9 = epilogue (two per TMEM lane quarter).
 // One output tile per CTA; two CTAs co-reside per SM so one tile's epilogue overlaps the other's main loop.
 #pragma once
 #include <cuda.h>
@@ -19,7 +19,7 @@
 
 #include "zb_common.cuh"
 
-#define TC_THREADS 192
+#define TC_THREADS 320                      // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two warps per TMEM lane quarter)
 #define TC_BM 128
 #define TC_BK 64
 #define TC_A_BYTES (TC_BM * TC_BK * 2)     // 16 KB
@@ -50,7 +50,86 @@ __device__ __forceinline__ float snake_fast(float x, float alpha, float inv_alph
   return fmaf(inv_alpha, s * s, x);
 }
 
-// grid = (ceil(m_rows/128), Cout/n_tile, phases); block = 192; dyn smem = 1024 (align) + stages*(16K + n_tile*128) + 256
+// ---- shared epilogue: one 32-column chunk of one accumulator row per thread ------------------------------------
+// Thread `lane` holds row `lane` of the chunk (tcgen05.ld 32x32b).  A row-per-thread 16-byte access touches 32
+// different sectors per warp instruction and uses half of each (ncu: "16 of 32 bytes per sector", 50 % excessive
+// sectors on the k=1 layers).  Lanes 2i / 2i+1 therefore swap halves so that every LDG/STG covers whole 32-byte
+// sectors: instruction j of the pair handles row 2i (j < 2) or 2i+1 (j >= 2), the even lane the even 16-byte quad.
+__device__ __forceinline__ uint4 tc_shfl_xor1(const uint4 v) {
+  uint4 r;
+  r.x = __shfl_xor_sync(0xffffffffu, v.x, 1); r.y = __shfl_xor_sync(0xffffffffu, v.y, 1);
+  r.z = __shfl_xor_sync(0xffffffffu, v.z, 1); r.w = __shfl_xor_sync(0xffffffffu, v.w, 1);
+  return r;
+}
+__device__ __forceinline__ uint4 tc_sel(bool c, const uint4 a, const uint4 b) { return c ? a : b; }
+
+// rowA/rowB: element offsets (row * Cout + first column of the chunk) of the pair's even/odd row, valid only when
+// okA/okB.  All 32 lanes must call this (shuffles).
+__device__ __forceinline__ void tc_epilogue_chunk(const uint32_t (&v)[32], const float* __restrict__ sb, const float* __restrict__ sa,
+                                                  const float* __restrict__ si, const __half* __restrict__ residual,
+                                                  __half* __restrict__ out_raw, __half* __restrict__ out_act, size_t rowA, size_t rowB,
+                                                  bool okA, bool okB, bool odd) {
+  float f[32];
+#pragma unroll
+  for (int j4 = 0; j4 < 8; ++j4) {
+    const float4 b = reinterpret_cast<const float4*>(sb)[j4];
+    f[4 * j4 + 0] = __uint_as_float(v[4 * j4 + 0]) + b.x; f[4 * j4 + 1] = __uint_as_float(v[4 * j4 + 1]) + b.y;
+    f[4 * j4 + 2] = __uint_as_float(v[4 * j4 + 2]) + b.z; f[4 * j4 + 3] = __uint_as_float(v[4 * j4 + 3]) + b.w;
+  }
+  const int qlo = odd ? 1 : 0, qhi = odd ? 3 : 2;             // the 16-byte quads this lane touches in memory
+  if (residual) {
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    const uint4 l0 = okA ? *reinterpret_cast<const uint4*>(residual + rowA + 8 * qlo) : z;
+    const uint4 l1 = okA ? *reinterpret_cast<const uint4*>(residual + rowA + 8 * qhi) : z;
+    const uint4 l2 = okB ? *reinterpret_cast<const uint4*>(residual + rowB + 8 * qlo) : z;
+    const uint4 l3 = okB ? *reinterpret_cast<const uint4*>(residual + rowB + 8 * qhi) : z;
+    const uint4 r0 = tc_shfl_xor1(odd ? l0 : l2), r1 = tc_shfl_xor1(odd ? l1 : l3);
+    const uint4 q[4] = {tc_sel(odd, r0, l0), tc_sel(odd, l2, r0), tc_sel(odd, r1, l1), tc_sel(odd, l3, r1)};
+#pragma unroll
+    for (int qq = 0; qq < 4; ++qq) {
+      const __half2* h = reinterpret_cast<const __half2*>(&q[qq]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { const float2 t = __half22float2(h[j]); f[qq * 8 + 2 * j] += t.x; f[qq * 8 + 2 * j + 1] += t.y; }
+    }
+  }
+  auto store_rows = [&](__half* __restrict__ out, const uint4 (&q)[4]) {
+    const uint4 r0 = tc_shfl_xor1(odd ? q[0] : q[1]), r1 = tc_shfl_xor1(odd ? q[2] : q[3]);
+    if (okA) {
+      *reinterpret_cast<uint4*>(out + rowA + 8 * qlo) = tc_sel(odd, r0, q[0]);
+      *reinterpret_cast<uint4*>(out + rowA + 8 * qhi) = tc_sel(odd, r1, q[2]);
+    }
+    if (okB) {
+      *reinterpret_cast<uint4*>(out + rowB + 8 * qlo) = tc_sel(odd, q[1], r0);
+      *reinterpret_cast<uint4*>(out + rowB + 8 * qhi) = tc_sel(odd, q[3], r1);
+    }
+  };
+  if (out_raw) {
+    uint4 q[4];
+#pragma unroll
+    for (int qq = 0; qq < 4; ++qq) {
+      __half2* h = reinterpret_cast<__half2*>(&q[qq]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) h[j] = __floats2half2_rn(f[qq * 8 + 2 * j], f[qq * 8 + 2 * j + 1]);
+    }
+    store_rows(out_raw, q);
+  }
+  if (out_act) {
+    uint4 q[4];
+#pragma unroll
+    for (int qq = 0; qq < 4; ++qq) {
+      __half2* h = reinterpret_cast<__half2*>(&q[qq]);
+      const float4 a0 = reinterpret_cast<const float4*>(sa)[2 * qq], a1 = reinterpret_cast<const float4*>(sa)[2 * qq + 1];
+      const float4 i0 = reinterpret_cast<const float4*>(si)[2 * qq], i1 = reinterpret_cast<const float4*>(si)[2 * qq + 1];
+      h[0] = __floats2half2_rn(snake_fast(f[qq * 8 + 0], a0.x, i0.x), snake_fast(f[qq * 8 + 1], a0.y, i0.y));
+      h[1] = __floats2half2_rn(snake_fast(f[qq * 8 + 2], a0.z, i0.z), snake_fast(f[qq * 8 + 3], a0.w, i0.w));
+      h[2] = __floats2half2_rn(snake_fast(f[qq * 8 + 4], a1.x, i1.x), snake_fast(f[qq * 8 + 5], a1.y, i1.y));
+      h[3] = __floats2half2_rn(snake_fast(f[qq * 8 + 6], a1.z, i1.z), snake_fast(f[qq * 8 + 7], a1.w, i1.w));
+    }
+    store_rows(out_act, q);
+  }
+}
+
+// grid = (ceil(m_rows/128), Cout/n_tile, phases); block = 320; dyn smem = 1024 (align) + stages*(16K + n_tile*128) + 256
 __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constant__ CUtensorMap map_x,
                                                             const __grid_constant__ CUtensorMap map_w, const TcConvParams p) {
   extern __shared__ unsigned char tc_smem_raw[];
@@ -136,58 +215,24 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
     int out_row;
     if (p.stride > 1) out_row = m * p.stride + phase - p.pad; else out_row = m;
     const bool valid = (m < p.m_rows) && (out_row >= 0) && (out_row < p.T_out);
-    for (int i = threadIdx.x - 64; i < p.n_tile; i += 128) {
+    for (int i = threadIdx.x - 64; i < p.n_tile; i += 256) {
       s_bias[i] = __ldg(p.bias + n0 + i);
       const float a = p.out_act ? __ldg(p.alpha_next + n0 + i) : 1.f;
       s_alpha[i] = a;
       s_inv[i] = 1.0f / (a + 1e-9f);
     }
-    asm volatile("bar.sync 2, 128;" ::: "memory");          // the 4 epilogue warps
+    asm volatile("bar.sync 2, 256;" ::: "memory");          // the 8 epilogue warps
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
-    const size_t row_base = (size_t)(valid ? out_row : 0) * p.Cout + n0;
-    for (int c0 = 0; c0 < p.n_tile; c0 += 32) {
+    const bool odd = lane & 1;
+    const int vA = __shfl_sync(0xffffffffu, (int)valid, lane & ~1), vB = __shfl_sync(0xffffffffu, (int)valid, lane | 1);
+    const int orA = __shfl_sync(0xffffffffu, out_row, lane & ~1), orB = __shfl_sync(0xffffffffu, out_row, lane | 1);
+    const size_t rowA = (size_t)(vA ? orA : 0) * p.Cout + n0, rowB = (size_t)(vB ? orB : 0) * p.Cout + n0;
+    const int chalf = (warp - 2) >> 2;                      // the two warps of a lane quarter alternate 32-column chunks
+    for (int c0 = chalf * 32; c0 < p.n_tile; c0 += 64) {
       uint32_t v[32];
       tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
-      if (valid) {
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + s_bias[c0 + j];
-        if (p.residual) {
-          const uint4* rp = reinterpret_cast<const uint4*>(p.residual + row_base + c0);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const uint4 r = rp[q];
-            const __half2* h = reinterpret_cast<const __half2*>(&r);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) { const float2 t = __half22float2(h[j]); f[q * 8 + 2 * j] += t.x; f[q * 8 + 2 * j + 1] += t.y; }
-          }
-        }
-        if (p.out_raw) {
-          uint4* op = reinterpret_cast<uint4*>(p.out_raw + row_base + c0);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            __half2 h[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) h[j] = __floats2half2_rn(f[q * 8 + 2 * j], f[q * 8 + 2 * j + 1]);
-            op[q] = *reinterpret_cast<uint4*>(h);
-          }
-        }
-        if (p.out_act) {
-          uint4* op = reinterpret_cast<uint4*>(p.out_act + row_base + c0);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            __half2 h[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int cc = c0 + q * 8 + 2 * j;
-              h[j] = __floats2half2_rn(snake_fast(f[q * 8 + 2 * j], s_alpha[cc], s_inv[cc]),
-                                       snake_fast(f[q * 8 + 2 * j + 1], s_alpha[cc + 1], s_inv[cc + 1]));
-            }
-            op[q] = *reinterpret_cast<uint4*>(h);
-          }
-        }
-      }
+      tc_epilogue_chunk(v, s_bias + c0, s_alpha + c0, s_inv + c0, p.residual, p.out_raw, p.out_act, rowA + c0, rowB + c0, vA != 0, vB != 0, odd);
     }
   }
   tc_fence_before();
