@@ -15,6 +15,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--frames", type=int, default=16)
 ap.add_argument("--runs", type=int, default=2)
 ap.add_argument("--batch", type=int, default=1)
+ap.add_argument("--prefix-len", type=int, default=24, help="conditioning length (the decode steps then run at ctx >= this)")
 ap.add_argument("--opt", action="append", default=[])
 ap.add_argument("--dac", type=int, default=-1, help="-1: skip DAC, 0: tcgen05, 1: SIMT")
 ap.add_argument("--dac-frames", type=int, default=256)
@@ -34,7 +35,7 @@ ctx = model._native()
 for kv in a.opt:
     k, v = kv.split("=")
     ctx.set_option(k, int(v))
-prefix = torch.randn(2 * a.batch, 24, 2048, device=dev).bfloat16()
+prefix = torch.randn(2 * a.batch, a.prefix_len, 2048, device=dev).bfloat16()
 for r in range(a.runs):
     torch.cuda.synchronize()
     t0 = time.perf_counter()

@@ -81,6 +81,77 @@ __device__ __forceinline__ void att_tokens4(const uint4 (&kraw)[4], const uint4 
   }
 }
 
+// Cross-warp merge of the per-warp online-softmax states in shared memory, then (nsplit > 1) the ticketed merge of the
+// split partials by the last CTA of the (row, kv-head).  Shared by the SIMT and the mma.sync kernels.
+template <int G>
+__device__ __forceinline__ void att_finish(const AttnParams& p, int row, int kvh, int split, int nsplit, int ctx, int chunk,
+                                           float (*s_o)[G][ZB_DH], float (*s_m)[G], float (*s_l)[G]) {
+  __shared__ int s_last;
+  const int tid = threadIdx.x;
+  __syncthreads();
+  // thread `tid` owns dim tid (ATT_THREADS == ZB_DH)
+  const size_t pbase = (((size_t)row * p.Hkv + kvh) * nsplit + split) * G;
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    float mn = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < ATT_WARPS; ++w) mn = fmaxf(mn, s_m[w][g]);
+    float lt = 0.f, ot = 0.f;
+#pragma unroll
+    for (int w = 0; w < ATT_WARPS; ++w) {
+      const float c = (s_m[w][g] == -INFINITY) ? 0.f : exp2f(s_m[w][g] - mn);
+      lt += s_l[w][g] * c;
+      ot += s_o[w][g][tid] * c;
+    }
+    if (nsplit == 1) {                               // the only split: this IS the attention output (no partials, no ticket)
+      p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + tid] = __float2bfloat16_rn(ot / lt);
+    } else {
+      p.part_o[(pbase + g) * ZB_DH + tid] = ot;
+      if (tid == 0) { p.part_ml[(pbase + g) * 2 + 0] = mn; p.part_ml[(pbase + g) * 2 + 1] = lt; }
+    }
+  }
+  if (nsplit == 1) return;
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const int ticket = atomicAdd(&p.counters[row * p.Hkv + kvh], 1);
+    s_last = (ticket == nsplit - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // ---- merge of the split partials by the last CTA.  Only the first `nact` splits saw tokens.  (m, l) of all splits are
+  // staged in shared memory with one parallel load; the partial outputs are then read 8 splits at a time so the L2
+  // round trips overlap instead of serialising (the first version of this loop cost 26 us per launch, r01 launch list).
+  __shared__ float s_ml[32 * 8 * 2];
+  const int nact = min(nsplit, (ctx + chunk - 1) / chunk);
+  const size_t rbase = ((size_t)row * p.Hkv + kvh) * nsplit * G;
+  for (int i = tid; i < nact * G * 2; i += ATT_THREADS) s_ml[i] = __ldcg(&p.part_ml[rbase * 2 + i]);
+  __syncthreads();
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    float mn = -INFINITY;
+    for (int s2 = 0; s2 < nact; ++s2) mn = fmaxf(mn, s_ml[(s2 * G + g) * 2]);
+    float lt = 0.f, ot = 0.f;
+    for (int s0 = 0; s0 < nact; s0 += 8) {
+      float o[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) o[u] = (s0 + u < nact) ? __ldcg(&p.part_o[(rbase + (size_t)(s0 + u) * G + g) * ZB_DH + tid]) : 0.f;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if (s0 + u < nact) {
+          const float ms = s_ml[((s0 + u) * G + g) * 2];
+          const float c = (ms == -INFINITY) ? 0.f : exp2f(ms - mn);
+          lt += s_ml[((s0 + u) * G + g) * 2 + 1] * c;
+          ot += o[u] * c;
+        }
+      }
+    }
+    p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + tid] = __float2bfloat16_rn(ot / lt);
+  }
+  if (tid == 0) p.counters[row * p.Hkv + kvh] = 0;
+}
+
 template <int G>
 __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode(const AttnParams p) {
   pdl_launch_dependents();
@@ -170,7 +241,6 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode(const AttnParams p)
   // merge warps through shared memory
   __shared__ float s_o[ATT_WARPS][G][ZB_DH];
   __shared__ float s_m[ATT_WARPS][G], s_l[ATT_WARPS][G];
-  __shared__ int s_last;
   if (half == 0) {
 #pragma unroll
     for (int g = 0; g < G; ++g) {
@@ -179,66 +249,152 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode(const AttnParams p)
       if (l16 == 0) { s_m[warp][g] = m[g]; s_l[warp][g] = l[g]; }
     }
   }
-  __syncthreads();
-  // thread `tid` owns dim tid (ATT_THREADS == ZB_DH)
-  const size_t pbase = (((size_t)row * p.Hkv + kvh) * nsplit + split) * G;
+  att_finish<G>(p, row, kvh, split, nsplit, ctx, chunk, s_o, s_m, s_l);
+}
+
+// =====================================================================================================================
+// mma.sync variant.  The SIMT kernel above spends ~65 warp instructions per cached token (bf16 unpack, 1024 FMAs, 16
+// shuffle chains), which makes long-context decode issue-bound at ~40 % of the KV stream's HBM time once 128 rows are in
+// flight (B = 64).  Here a warp owns 16 tokens at a time and both contractions run on the tensor cores straight from
+// the registers the coalesced 128-bit global loads land in — no shared-memory staging, no ldmatrix:
+//   S[head, tok]   = Q K^T     m16n8k16, A = Q (rows = the G <= 8 heads of the kv head), B = K.  The contraction index
+//                              is a free permutation of the 128 dims, so lane (g, t) feeds the 8 consecutive dims of
+//                              its 16-byte load of token g as the (k, k+1 | k+8, k+9) pairs of two k-steps and Q is
+//                              loaded once with the same permutation.
+//   O^T[dim, head] = V^T P^T   A = V^T: lane (g, t) loads dims [16g, 16g+16) of tokens {2t, 2t+1, 2t+8, 2t+9}; one
+//                              PRMT pairs the two tokens of a dim into an A register (the dim order of O is a free
+//                              permutation too); B = P^T is exactly the layout S's accumulators already have.
+// 24 HMMA + 32 PRMT + a 4-lane softmax reduction per 16 tokens: ~8 warp instructions per token.  P is rounded to bf16
+// before the PV product (as flash-attention / SDPA's fused kernels do); m, l and O stay fp32.
+__device__ __forceinline__ void att_mma(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t att_pack_bf16(float lo, float hi) {
+  const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+struct AttFrag {
+  uint4 k[2][4];      // token g (+8): dims 32s + 8t .. +8
+  uint4 v[4][2];      // tokens 2t, 2t+1, 2t+8, 2t+9: dims 16g .. +16
+};
+
+// per-warp running state: lanes 4h..4h+3 hold (m, l) of head h; o[j] = O^T tile j (dims 16g + 2j, 16g + 2j + 1; heads 2t, 2t+1)
+template <int G>
+__device__ __forceinline__ void att_group16(const AttFrag& f, int tb, int t1, const uint32_t (&qa)[8][2], float& m, float& l,
+                                            float (&o)[8][4], float scale_log2, int lane) {
+  const int t = lane & 3;
+  float c0[4] = {0.f, 0.f, 0.f, 0.f}, c1[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-  for (int g = 0; g < G; ++g) {
-    float mn = -INFINITY;
+  for (int s = 0; s < 4; ++s) {
+    att_mma(c0, qa[2 * s][0], 0u, qa[2 * s][1], 0u, f.k[0][s].x, f.k[0][s].y);
+    att_mma(c1, qa[2 * s][0], 0u, qa[2 * s][1], 0u, f.k[1][s].x, f.k[1][s].y);
+    att_mma(c0, qa[2 * s + 1][0], 0u, qa[2 * s + 1][1], 0u, f.k[0][s].z, f.k[0][s].w);
+    att_mma(c1, qa[2 * s + 1][0], 0u, qa[2 * s + 1][1], 0u, f.k[1][s].z, f.k[1][s].w);
+  }
+  // scores of head g for tokens tb + {2t, 2t+1, 8+2t, 9+2t}
+  const int ta = tb + 2 * t;
+  float s00 = ta < t1 ? c0[0] * scale_log2 : -INFINITY, s01 = ta + 1 < t1 ? c0[1] * scale_log2 : -INFINITY;
+  float s10 = ta + 8 < t1 ? c1[0] * scale_log2 : -INFINITY, s11 = ta + 9 < t1 ? c1[1] * scale_log2 : -INFINITY;
+  float mx = fmaxf(fmaxf(s00, s01), fmaxf(s10, s11));
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+  mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+  const float mn = fmaxf(m, mx);                        // finite: token tb itself is valid
+  const float corr = exp2f(m - mn);                     // m = -inf before the first group -> 0
+  const float p00 = exp2f(s00 - mn), p01 = exp2f(s01 - mn), p10 = exp2f(s10 - mn), p11 = exp2f(s11 - mn);
+  float ps = (p00 + p01) + (p10 + p11);
+  ps += __shfl_xor_sync(0xffffffffu, ps, 1);
+  ps += __shfl_xor_sync(0xffffffffu, ps, 2);
+  l = l * corr + ps;
+  m = mn;
+  const uint32_t b0 = att_pack_bf16(p00, p01), b1 = att_pack_bf16(p10, p11);
+  // O^T columns of this lane are heads 2t and 2t+1: fetch their rescale factors from the lanes that own those heads
+  const float ca = __shfl_sync(0xffffffffu, corr, 8 * t), cb = __shfl_sync(0xffffffffu, corr, 8 * t + 4);
 #pragma unroll
-    for (int w = 0; w < ATT_WARPS; ++w) mn = fmaxf(mn, s_m[w][g]);
-    float lt = 0.f, ot = 0.f;
+  for (int j = 0; j < 8; ++j) {
+    o[j][0] *= ca; o[j][1] *= cb; o[j][2] *= ca; o[j][3] *= cb;
+    const uint32_t w0 = j < 4 ? (&f.v[0][0].x)[j] : (&f.v[0][1].x)[j - 4], w1 = j < 4 ? (&f.v[1][0].x)[j] : (&f.v[1][1].x)[j - 4];
+    const uint32_t w2 = j < 4 ? (&f.v[2][0].x)[j] : (&f.v[2][1].x)[j - 4], w3 = j < 4 ? (&f.v[3][0].x)[j] : (&f.v[3][1].x)[j - 4];
+    att_mma(o[j], __byte_perm(w0, w1, 0x5410), __byte_perm(w0, w1, 0x7632), __byte_perm(w2, w3, 0x5410), __byte_perm(w2, w3, 0x7632), b0, b1);
+  }
+}
+
+template <int G>
+__global__ void __launch_bounds__(ATT_THREADS) k_attn_decode_mma(const AttnParams p) {
+  static_assert(G <= 8, "the heads of one kv head are the n8 dimension of the PV product");
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+  if (p.st->done) return;
+
+  const int split = blockIdx.x, nsplit = gridDim.x, kvh = blockIdx.y, row = blockIdx.z;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int ctx = p.st->pos + 1;
+  int chunk = (ctx + nsplit - 1) / nsplit;
+  chunk = (chunk + 15) & ~15;                                     // 16-token groups never straddle a page (ZB_PAGE % 16 == 0)
+  const int t0 = split * chunk;
+  const int t1 = min(ctx, t0 + chunk);
+
+  uint32_t qa[8][2];
 #pragma unroll
-    for (int w = 0; w < ATT_WARPS; ++w) {
-      const float c = (s_m[w][g] == -INFINITY) ? 0.f : exp2f(s_m[w][g] - mn);
-      lt += s_l[w][g] * c;
-      ot += s_o[w][g][tid] * c;
+  for (int s = 0; s < 4; ++s) {
+    uint4 w = make_uint4(0, 0, 0, 0);
+    if (g < G) w = *reinterpret_cast<const uint4*>(p.q + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + 32 * s + 8 * t);
+    qa[2 * s][0] = w.x; qa[2 * s][1] = w.y; qa[2 * s + 1][0] = w.z; qa[2 * s + 1][1] = w.w;
+  }
+  float m = -INFINITY, l = 0.f, o[8][4];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
+
+  const int* pt = p.page_table + (size_t)row * p.max_pages;
+  const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
+  const size_t kv_stride = (size_t)p.Hkv * head_stride;
+  const size_t page_stride = 2 * kv_stride;
+  auto load_group = [&](int tb, AttFrag& f) {
+    const int page = pt[tb / ZB_PAGE];
+    const bf16* kbase = p.kv_layer + (size_t)page * page_stride + (size_t)kvh * head_stride + (size_t)(tb % ZB_PAGE) * ZB_DH;
+    const uint4 z = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+      const bool ok = tb + 8 * n + g < t1;
+#pragma unroll
+      for (int s = 0; s < 4; ++s) f.k[n][s] = ok ? ldg_stream(kbase + (size_t)(8 * n + g) * ZB_DH + 32 * s + 8 * t) : z;
     }
-    if (nsplit == 1) {                               // the only split: this IS the attention output (no partials, no ticket)
-      p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + tid] = __float2bfloat16_rn(ot / lt);
-    } else {
-      p.part_o[(pbase + g) * ZB_DH + tid] = ot;
-      if (tid == 0) { p.part_ml[(pbase + g) * 2 + 0] = mn; p.part_ml[(pbase + g) * 2 + 1] = lt; }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int tok = 2 * t + (u & 1) + 8 * (u >> 1);
+      const bool ok = tb + tok < t1;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) f.v[u][h] = ok ? ldg_stream(kbase + kv_stride + (size_t)tok * ZB_DH + 16 * g + 8 * h) : z;
+    }
+  };
+  // warp w handles groups t0 + 16*(w + ATT_WARPS*i); the next group's 16 loads are in flight while this one is reduced
+  const int gstep = 16 * ATT_WARPS;
+  AttFrag fa, fb;
+  int tb = t0 + 16 * warp;
+  if (tb < t1) load_group(tb, fa);
+  while (tb < t1) {
+    if (tb + gstep < t1) load_group(tb + gstep, fb);
+    att_group16<G>(fa, tb, t1, qa, m, l, o, p.scale_log2, lane);
+    tb += gstep;
+    if (tb < t1) {
+      if (tb + gstep < t1) load_group(tb + gstep, fa);
+      att_group16<G>(fb, tb, t1, qa, m, l, o, p.scale_log2, lane);
+      tb += gstep;
     }
   }
-  if (nsplit == 1) return;
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) {
-    const int ticket = atomicAdd(&p.counters[row * p.Hkv + kvh], 1);
-    s_last = (ticket == nsplit - 1);
+
+  __shared__ float s_o[ATT_WARPS][G][ZB_DH];
+  __shared__ float s_m[ATT_WARPS][G], s_l[ATT_WARPS][G];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int d = 16 * g + 2 * j;
+    if (2 * t < G) { s_o[warp][2 * t][d] = o[j][0]; s_o[warp][2 * t][d + 1] = o[j][2]; }
+    if (2 * t + 1 < G) { s_o[warp][2 * t + 1][d] = o[j][1]; s_o[warp][2 * t + 1][d + 1] = o[j][3]; }
   }
-  __syncthreads();
-  if (!s_last) return;
-  __threadfence();
-  // ---- merge of the split partials by the last CTA.  Only the first `nact` splits saw tokens.  (m, l) of all splits are
-  // staged in shared memory with one parallel load; the partial outputs are then read 8 splits at a time so the L2
-  // round trips overlap instead of serialising (the first version of this loop cost 26 us per launch, r01 launch list).
-  __shared__ float s_ml[32 * 8 * 2];
-  const int nact = min(nsplit, (ctx + chunk - 1) / chunk);
-  const size_t rbase = ((size_t)row * p.Hkv + kvh) * nsplit * G;
-  for (int i = tid; i < nact * G * 2; i += ATT_THREADS) s_ml[i] = __ldcg(&p.part_ml[rbase * 2 + i]);
-  __syncthreads();
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-    float mn = -INFINITY;
-    for (int s2 = 0; s2 < nact; ++s2) mn = fmaxf(mn, s_ml[(s2 * G + g) * 2]);
-    float lt = 0.f, ot = 0.f;
-    for (int s0 = 0; s0 < nact; s0 += 8) {
-      float o[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) o[u] = (s0 + u < nact) ? __ldcg(&p.part_o[(rbase + (size_t)(s0 + u) * G + g) * ZB_DH + tid]) : 0.f;
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        if (s0 + u < nact) {
-          const float ms = s_ml[((s0 + u) * G + g) * 2];
-          const float c = (ms == -INFINITY) ? 0.f : exp2f(ms - mn);
-          lt += s_ml[((s0 + u) * G + g) * 2 + 1] * c;
-          ot += o[u] * c;
-        }
-      }
-    }
-    p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + tid] = __float2bfloat16_rn(ot / lt);
-  }
-  if (tid == 0) p.counters[row * p.Hkv + kvh] = 0;
+  if (t == 0 && g < G) { s_m[warp][g] = m; s_l[warp][g] = l; }
+  att_finish<G>(p, row, kvh, split, nsplit, ctx, chunk, s_o, s_m, s_l);
 }

@@ -38,6 +38,11 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 
 struct zb_dac {
   int device = 0;
+  // tuning knobs of the tcgen05 path (zb_dac_set_option; defaults are the measured best, profiles/r01_summary.md)
+  int ew_multi = 8;         // epilogue warps of the persistent kernel on multi-tap layers
+  int ew_k1 = 8;            // ... on k=1 layers
+  int wide_cout = 768;      // layers with Cout >= this run on the one-tile-per-CTA kernel (impl 0)
+  int mt2_min_waves = 8;    // 256-row tiles only when that still leaves this many tiles per SM
   ZbErr err;
   std::map<std::string, RawT> raw;
   bool finalized = false;
@@ -234,7 +239,7 @@ int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half*
   p.acc_cols = 128; p.acc_stages = 2;
   // 256-row tiles halve the weight traffic; keep 128-row tiles when there would be too few tiles to balance 148 SMs
   const long tiles2 = (long)((p.m_rows + 2 * TC_BM - 1) / (2 * TC_BM)) * p.n_tiles * p.phases;
-  p.mt = tiles2 >= 8L * ZB_NUM_SMS ? 2 : 1;
+  p.mt = tiles2 >= (long)d->mt2_min_waves * ZB_NUM_SMS ? 2 : 1;
   p.m_tiles = (p.m_rows + p.mt * TC_BM - 1) / (p.mt * TC_BM);
   p.lead = c.stride > 1 ? p.ntaps - 1 : c.pad;
   const int win_rows = p.mt * TC_BM + (c.stride > 1 ? p.ntaps - 1 : (c.K - 1) * c.dil);
@@ -257,7 +262,8 @@ int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half*
   const size_t smem = 1024 + (size_t)p.a_slots * p.a_bytes + (size_t)p.b_stages * b_bytes + 512 + TC2_TAB_BYTES;
   const long tiles = (long)p.m_tiles * p.n_tiles * p.phases;
   const int grid = (int)(tiles < ZB_NUM_SMS ? tiles : ZB_NUM_SMS);
-  k_dac_conv_tc2<<<grid, TC2_THREADS, smem, s>>>(mx, mw, p);
+  if ((p.ntaps > 1 ? d->ew_multi : d->ew_k1) == 16) k_dac_conv_tc2<16><<<grid, 64 + 32 * 16, smem, s>>>(mx, mw, p);
+  else k_dac_conv_tc2<8><<<grid, 64 + 32 * 8, smem, s>>>(mx, mw, p);
   d->launches++;
   ZB_CUDA(d->err, cudaGetLastError());
   return ZB_OK;
@@ -268,7 +274,7 @@ int decode_one_tc(zb_dac* d, const long long* codes, float* wav, int T, cudaStre
                      const float* alpha_next, cudaStream_t st) {
     // impl 0: per layer — the wide layers (Cout >= 768) run best on the N=256 one-tile-per-CTA kernel (two CTAs per SM),
     // everything else on the persistent window-reuse kernel; impl 2 / 3 force one kernel everywhere (A/B runs)
-    const bool v1 = impl == 2 || (impl == 0 && c.Cout >= 768);
+    const bool v1 = impl == 2 || (impl == 0 && c.Cout >= d->wide_cout);
     return v1 ? ::conv_tc(dd, c, x, T_in, residual, out_raw, out_act, alpha_next, st) : conv_tc2(dd, c, x, T_in, residual, out_raw, out_act, alpha_next, st);
   };
   int rc;
@@ -430,7 +436,8 @@ int zb_dac_finalize(zb_dac* d, void* stream) {
   ZB_CUDA(d->err, cudaStreamSynchronize(s));
   // opt-in to large dynamic smem for the tensor-core kernel
   ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-  ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc2, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc2<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc2<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_final_conv, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
   d->finalized = true;
   return ZB_OK;
@@ -464,7 +471,15 @@ int zb_dac_get_intermediate(zb_dac* d, const char* name, float* d_out, int64_t n
 
 int zb_dac_set_option(zb_dac* d, const char* key, int value) {
   if (!d || !key) return ZB_ERR_ARG;
-  if (std::string(key) == "keep_intermediates") { d->keep = value; return ZB_OK; }
+  const std::string k(key);
+  if (k == "keep_intermediates") { d->keep = value; return ZB_OK; }
+  if (k == "ew_multi" || k == "ew_k1") {
+    if (value != 8 && value != 16) return d->err.fail(ZB_ERR_ARG, "%s must be 8 or 16", key);
+    (k == "ew_multi" ? d->ew_multi : d->ew_k1) = value;
+    return ZB_OK;
+  }
+  if (k == "wide_cout") { d->wide_cout = value; return ZB_OK; }
+  if (k == "mt2_min_waves") { d->mt2_min_waves = value; return ZB_OK; }
   return d->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
 }
 

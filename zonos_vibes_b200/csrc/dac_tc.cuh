@@ -65,8 +65,19 @@ __device__ __forceinline__ uint4 tc_sel(bool c, const uint4 a, const uint4 b) { 
 
 // rowA/rowB: element offsets (row * Cout + first column of the chunk) of the pair's even/odd row, valid only when
 // okA/okB.  All 32 lanes must call this (shuffles).
+// the pair's residual quads as they sit in memory (issued early so that their latency hides behind the MMA wait)
+__device__ __forceinline__ void tc_res_load(const __half* __restrict__ residual, size_t rowA, size_t rowB, bool okA, bool okB, bool odd,
+                                            uint4 (&l)[4]) {
+  const int qlo = odd ? 1 : 0, qhi = odd ? 3 : 2;
+  const uint4 z = make_uint4(0, 0, 0, 0);
+  l[0] = okA ? *reinterpret_cast<const uint4*>(residual + rowA + 8 * qlo) : z;
+  l[1] = okA ? *reinterpret_cast<const uint4*>(residual + rowA + 8 * qhi) : z;
+  l[2] = okB ? *reinterpret_cast<const uint4*>(residual + rowB + 8 * qlo) : z;
+  l[3] = okB ? *reinterpret_cast<const uint4*>(residual + rowB + 8 * qhi) : z;
+}
+
 __device__ __forceinline__ void tc_epilogue_chunk(const uint32_t (&v)[32], const float* __restrict__ sb, const float* __restrict__ sa,
-                                                  const float* __restrict__ si, const __half* __restrict__ residual,
+                                                  const float* __restrict__ si, bool has_res, const uint4 (&l)[4],
                                                   __half* __restrict__ out_raw, __half* __restrict__ out_act, size_t rowA, size_t rowB,
                                                   bool okA, bool okB, bool odd) {
   float f[32];
@@ -77,12 +88,8 @@ __device__ __forceinline__ void tc_epilogue_chunk(const uint32_t (&v)[32], const
     f[4 * j4 + 2] = __uint_as_float(v[4 * j4 + 2]) + b.z; f[4 * j4 + 3] = __uint_as_float(v[4 * j4 + 3]) + b.w;
   }
   const int qlo = odd ? 1 : 0, qhi = odd ? 3 : 2;             // the 16-byte quads this lane touches in memory
-  if (residual) {
-    const uint4 z = make_uint4(0, 0, 0, 0);
-    const uint4 l0 = okA ? *reinterpret_cast<const uint4*>(residual + rowA + 8 * qlo) : z;
-    const uint4 l1 = okA ? *reinterpret_cast<const uint4*>(residual + rowA + 8 * qhi) : z;
-    const uint4 l2 = okB ? *reinterpret_cast<const uint4*>(residual + rowB + 8 * qlo) : z;
-    const uint4 l3 = okB ? *reinterpret_cast<const uint4*>(residual + rowB + 8 * qhi) : z;
+  if (has_res) {
+    const uint4 l0 = l[0], l1 = l[1], l2 = l[2], l3 = l[3];
     const uint4 r0 = tc_shfl_xor1(odd ? l0 : l2), r1 = tc_shfl_xor1(odd ? l1 : l3);
     const uint4 q[4] = {tc_sel(odd, r0, l0), tc_sel(odd, l2, r0), tc_sel(odd, r1, l1), tc_sel(odd, l3, r1)};
 #pragma unroll
@@ -232,7 +239,10 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
     for (int c0 = chalf * 32; c0 < p.n_tile; c0 += 64) {
       uint32_t v[32];
       tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
-      tc_epilogue_chunk(v, s_bias + c0, s_alpha + c0, s_inv + c0, p.residual, p.out_raw, p.out_act, rowA + c0, rowB + c0, vA != 0, vB != 0, odd);
+      uint4 res[4];
+      if (p.residual) tc_res_load(p.residual, rowA + c0, rowB + c0, vA != 0, vB != 0, odd, res);
+      tc_epilogue_chunk(v, s_bias + c0, s_alpha + c0, s_inv + c0, p.residual != nullptr, res, p.out_raw, p.out_act, rowA + c0, rowB + c0,
+                        vA != 0, vB != 0, odd);
     }
   }
   tc_fence_before();

@@ -11,12 +11,14 @@
 //   * a tile is 256 time rows: each weight tile feeds two accumulators, halving the weight traffic per output row;
 //   * CTAs are persistent (one per SM) and the accumulators are double-buffered in TMEM (2 stages x 2 x <=128 columns),
 //     so the epilogue of tile i overlaps the MMAs of tile i+1 while the TMA producer runs ahead across tile borders.
-// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2..9 = epilogue
-// (warps 2-5 drain accumulator 0, warps 6-9 accumulator 1; with a single accumulator they split its columns).
+// Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2.. = EW epilogue warps.  A warp can
+// only read the TMEM lane quarter (warp % 4); the EW/4 warps of a quarter split the accumulators and their 32-column
+// chunks.  EW = 8 is the default everywhere; the k=1 layers are bound by their residual / output streams and prefetch
+// all residual rows of a tile into registers before the accumulator wait.  EW = 16 (zb_dac_set_option "ew_multi" /
+// "ew_k1") was measured in the same process with scripts/dac_ab.py: no gain on the multi-tap layers, a loss on k=1.
 #pragma once
 #include "dac_tc.cuh"
 
-#define TC2_THREADS 320
 #define TC2_MAX_COUT 1536
 #define TC2_TAB_BYTES (3 * TC2_MAX_COUT * 4)
 #define TC2_MAX_A_SLOTS 4
@@ -46,8 +48,10 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
-// grid = min(tiles, SMs); block = 320; dyn smem = 1024 + a_slots*a_bytes + b_stages*n_tile*128 + 512 + TC2_TAB_BYTES
-__global__ void __launch_bounds__(TC2_THREADS, 1) k_dac_conv_tc2(const __grid_constant__ CUtensorMap map_x,
+// EW = epilogue warps (8 or 16).  grid = min(tiles, SMs); block = 64 + 32*EW;
+// dyn smem = 1024 + a_slots*a_bytes + b_stages*n_tile*128 + 512 + TC2_TAB_BYTES
+template <int EW>
+__global__ void __launch_bounds__(64 + 32 * EW, 1) k_dac_conv_tc2(const __grid_constant__ CUtensorMap map_x,
                                                                  const __grid_constant__ CUtensorMap map_w, const TcConv2Params p) {
   extern __shared__ unsigned char tc2_smem_raw[];
   const uint32_t raw = smem_u32(tc2_smem_raw);
@@ -77,14 +81,14 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_dac_conv_tc2(const __grid_co
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
     for (int s = 0; s < p.a_slots; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); }
     for (int s = 0; s < p.b_stages; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(t_full(s), 1); mbar_init(t_empty(s), 8); }
+    for (int s = 0; s < 2; ++s) { mbar_init(t_full(s), 1); mbar_init(t_empty(s), EW); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  for (int i = threadIdx.x; i < p.Cout; i += TC2_THREADS) {
+  for (int i = threadIdx.x; i < p.Cout; i += 64 + 32 * EW) {
     s_bias[i] = __ldg(p.bias + i);
     const float a = p.out_act ? __ldg(p.alpha_next + i) : 1.f;
     s_alpha[i] = a;
@@ -174,10 +178,13 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_dac_conv_tc2(const __grid_co
   } else {
     // ===== epilogue =====
     const int lg = warp & 3;
-    const int ew = warp - 2;                                   // 0..7
-    const int acc = p.mt == 2 ? (ew >> 2) : 0;
-    const int c_first = p.mt == 2 ? 0 : (ew >> 2) * 32;
-    const int c_step = p.mt == 2 ? 32 : 64;
+    const int ew = warp - 2;                                   // 0..EW-1; quarter-mates = EW/4 warps
+    constexpr int QM = EW / 4;                                 // warps per TMEM lane quarter
+    constexpr int NCH = 8 / QM;                                // max 32-column chunks per warp (n_tile <= 128, <= 2 accumulators)
+    const int qi = ew >> 2;                                    // index among the quarter-mates
+    const int acc = p.mt == 2 ? (qi & 1) : 0;
+    const int c_first = (p.mt == 2 ? (qi >> 1) : qi) * 32;
+    const int c_step = (p.mt == 2 ? QM / 2 : QM) * 32;
     int as = 0;
     uint32_t t_par = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -190,14 +197,27 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_dac_conv_tc2(const __grid_co
       const int vA = __shfl_sync(0xffffffffu, (int)valid, lane & ~1), vB = __shfl_sync(0xffffffffu, (int)valid, lane | 1);
       const int orA = __shfl_sync(0xffffffffu, out_row, lane & ~1), orB = __shfl_sync(0xffffffffu, out_row, lane | 1);
       const size_t rowA = (size_t)(vA ? orA : 0) * p.Cout + n0, rowB = (size_t)(vB ? orB : 0) * p.Cout + n0;
+      // the warp's residual rows of the whole tile are requested before the accumulator wait
+      uint4 res[NCH][4];
+      if (p.residual) {
+#pragma unroll
+        for (int ci = 0; ci < NCH; ++ci) {
+          const int c0 = c_first + ci * c_step;
+          if (c0 < p.n_tile) tc_res_load(p.residual, rowA + c0, rowB + c0, vA != 0, vB != 0, odd, res[ci]);
+        }
+      }
       mbar_wait(t_full(as), t_par);
       tc_fence_after();
       const uint32_t t0 = tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)((as * p.mt + acc) * p.acc_cols);
-      for (int c0 = c_first; c0 < p.n_tile; c0 += c_step) {
-        uint32_t v[32];
-        tmem_ld32(t0 + (uint32_t)c0, v);
-        tc_epilogue_chunk(v, s_bias + n0 + c0, s_alpha + n0 + c0, s_inv + n0 + c0, p.residual, p.out_raw, p.out_act, rowA + c0, rowB + c0,
-                          vA != 0, vB != 0, odd);
+#pragma unroll
+      for (int ci = 0; ci < NCH; ++ci) {
+        const int c0 = c_first + ci * c_step;
+        if (c0 < p.n_tile) {
+          uint32_t v[32];
+          tmem_ld32(t0 + (uint32_t)c0, v);
+          tc_epilogue_chunk(v, s_bias + n0 + c0, s_alpha + n0 + c0, s_inv + n0 + c0, p.residual != nullptr, res[ci], p.out_raw, p.out_act,
+                            rowA + c0, rowB + c0, vA != 0, vB != 0, odd);
+        }
       }
       // accumulator stage drained (tcgen05.ld completed inside tmem_ld32): hand it back to the MMA warp
       tc_fence_before();

@@ -86,6 +86,7 @@ struct zb_ctx {
   long long* graph_delayed = nullptr;
   // options
   int opt_pdl = 1, opt_l2_prefetch_mb = 0, opt_graph = 1, opt_gemv = 1;
+  int opt_attn_mma = 1;     // 1: mma.sync attention kernel, 0: SIMT (A/B and cross-check)
   int64_t launches = 0;
   bool counting = true;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -206,12 +207,12 @@ size_t gemv_mma_smem(int R, int K, int epi) {
 size_t gemv_smem(int R, int K) { return (size_t)R * K * sizeof(bf16) + (size_t)(GEMV_THREADS / 32) * R * sizeof(float); }
 
 typedef void (*AttnKernel)(const AttnParams);
-AttnKernel attn_kernel(int G) {
+AttnKernel attn_kernel(int G, bool mma = true) {
   switch (G) {
-    case 1: return k_attn_decode<1>;
-    case 2: return k_attn_decode<2>;
-    case 4: return k_attn_decode<4>;
-    case 8: return k_attn_decode<8>;
+    case 1: return mma ? k_attn_decode_mma<1> : k_attn_decode<1>;
+    case 2: return mma ? k_attn_decode_mma<2> : k_attn_decode<2>;
+    case 4: return mma ? k_attn_decode_mma<4> : k_attn_decode<4>;
+    case 8: return mma ? k_attn_decode_mma<8> : k_attn_decode<8>;
   }
   return nullptr;
 }
@@ -338,7 +339,7 @@ cudaError_t enqueue_layers(zb_ctx* c, const std::vector<Pass>& passes, cudaStrea
       a.q = c->q; a.kv_layer = kv_layer; a.page_table = c->page_table; a.max_pages = c->max_pages;
       a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
       a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
-      if ((e = launch(c, attn_kernel(H / Hkv), dim3(c->nsplit, Hkv, c->rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
+      if ((e = launch(c, attn_kernel(H / Hkv, c->opt_attn_mma != 0), dim3(c->nsplit, Hkv, c->rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
     }
     for (const Pass& ps : passes) {   // out_proj + residual
       GemvParams p = base_params(c, ps);
@@ -637,7 +638,7 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
       a.q = c->q; a.kv_layer = kv_layer; a.page_table = c->page_table; a.max_pages = c->max_pages;
       a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
       a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
-      if ((e = launch(c, attn_kernel(H / Hkv), dim3(c->nsplit, Hkv, rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
+      if ((e = launch(c, attn_kernel(H / Hkv, c->opt_attn_mma != 0), dim3(c->nsplit, Hkv, rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
     }
     if ((e = bt_gemm(c, c->bt_map_y, c->bt_map_out[l], d, q_size, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
     {
@@ -1290,6 +1291,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "poll_all") c->opt_poll_all = value;
   else if (k == "psleep") c->opt_psleep = value;
   else if (k == "bt_min_rows") c->opt_bt_min_rows = value;
+  else if (k == "attn_mma") c->opt_attn_mma = value;
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
   drop_graph(c);
   return ZB_OK;
@@ -1346,7 +1348,7 @@ int zb_bench_kernel(zb_ctx* c, const char* name, int iters, float* ms_out, void*
       a.q = c->q; a.kv_layer = c->kv + (size_t)l * c->kv_layer_elems; a.page_table = c->page_table; a.max_pages = c->max_pages;
       a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
       a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
-      e = launch(c, attn_kernel(H / Hkv), dim3(c->nsplit, Hkv, c->rows), dim3(ATT_THREADS), 0, s, a);
+      e = launch(c, attn_kernel(H / Hkv, c->opt_attn_mma != 0), dim3(c->nsplit, Hkv, c->rows), dim3(ATT_THREADS), 0, s, a);
     } else {
       c->counting = counting;
       return c->err.fail(ZB_ERR_ARG, "unknown kernel '%s'", name);
