@@ -746,99 +746,87 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
   const MgAttItem it = mg_att_item(p, pos);
   if (!it.mine) return;                               // CTA-uniform
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int half = lane >> 4, l16 = lane & 15;
+  const int g = lane >> 2, t = lane & 3;                // mma.sync fragment coordinates (attention_kernels.cuh, att_group16)
   const int nsplit = p.nsplit, row = it.row, kvh = it.kvh, split = it.split;
 
   // q and (warp 0) the K/V row appended in this step come from L2 in ONE round trip: both were written by other CTAs
-  // before the grid barrier.  Every later read of this phase is shared memory.
+  // before the grid barrier.  Every later read of this phase is shared memory.  Both are loaded straight into the
+  // fragment layout of the tensor-core contraction.
   const int tp = min(it.t1, pos);
   const bool has_new = it.t0 <= pos && pos < it.t1;
-  uint4 qraw[G];
+  const uint4 z4 = make_uint4(0, 0, 0, 0);
+  uint32_t qa[8][2];
+  {
+    uint4 qw[4];
 #pragma unroll
-  for (int g = 0; g < G; ++g) qraw[g] = mg_ldcg16(p.q + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + l16 * 8);
-  uint4 knew = make_uint4(0, 0, 0, 0), vnew = make_uint4(0, 0, 0, 0);
-  if (has_new && warp == 0 && half == 0) {
-    const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
-    const size_t kv_stride = (size_t)p.Hkv * head_stride;
-    const bf16* kp = kv_layer + (size_t)cx.s_page[row] * 2 * kv_stride + (size_t)kvh * head_stride + (size_t)(pos % ZB_PAGE) * ZB_DH + l16 * 8;
-    knew = mg_ldcg16(kp);
-    vnew = mg_ldcg16(kp + kv_stride);
-  }
-  float q[G][8];
+    for (int s = 0; s < 4; ++s)
+      qw[s] = g < G ? mg_ldcg16(p.q + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + 32 * s + 8 * t) : z4;
+    AttFrag fn;                                         // the fresh row is token 0 of a one-token group
+    if (has_new && warp == 0) {
+      const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
+      const size_t kv_stride = (size_t)p.Hkv * head_stride;
+      const bf16* kp = kv_layer + (size_t)cx.s_page[row] * 2 * kv_stride + (size_t)kvh * head_stride + (size_t)(pos % ZB_PAGE) * ZB_DH;
 #pragma unroll
-  for (int g = 0; g < G; ++g) mg_unpack8(qraw[g], q[g]);
-  if (cx.trace && q[0][0] == 12345.678f) cx.trace_n = 0;           // (trace only) make the stamp below wait for the q load
-  MG_STAMP();                                                     // att +0: q / new K,V arrived from L2
-  float m[G], l[G], acc[G][8];
+      for (int s = 0; s < 4; ++s) { fn.k[0][s] = g == 0 ? mg_ldcg16(kp + 32 * s + 8 * t) : z4; fn.k[1][s] = z4; }
 #pragma unroll
-  for (int g = 0; g < G; ++g) {
-    m[g] = -INFINITY; l[g] = 0.f;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[g][j] = 0.f;
-  }
-  // ---- tokens of earlier steps: MG_KV_TOK per ring stage, a half-warp per token; then ONE extra pass for the row
-  // appended in this step (written by other CTAs in phase 1, read from L2 by warp 0).  A single copy of the token
-  // arithmetic serves both (code size).
-  const int n_kv_stages = tp > it.t0 ? (tp - it.t0 + MG_KV_TOK - 1) / MG_KV_TOK : 0;
-  for (int si = 0; si < n_kv_stages + (has_new ? 1 : 0); ++si) {
-    const bool fresh = si == n_kv_stages;              // the extra pass
-    const int ts = it.t0 + si * MG_KV_TOK;
-    const int n = fresh ? 1 : min(MG_KV_TOK, tp - ts);
-    uint32_t sp = 0;
-    if (!fresh) sp = mg_cons_wait_addr(cx);
-    if (fresh) {
-      if (warp == 0) {
-        const bool valid = half == 0;
-        mg_att_token<G>(knew, vnew, valid, q, m, l, acc, p.scale_log2);
+      for (int h = 0; h < 2; ++h) {
+        fn.v[0][h] = t == 0 ? mg_ldcg16(kp + kv_stride + 16 * g + 8 * h) : z4;
+        fn.v[1][h] = z4; fn.v[2][h] = z4; fn.v[3][h] = z4;
       }
-    } else if (2 * warp < n) {                          // warp-uniform: this warp has at least one valid token
-      uint4 kraw[4], vraw[4];
-      bool valid[4];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int i = 2 * warp + half + 16 * k;
-        valid[k] = i < n;
-        kraw[k] = make_uint4(0, 0, 0, 0); vraw[k] = make_uint4(0, 0, 0, 0);
-        if (valid[k]) {
-          kraw[k] = mg_lds128(sp + i * (ZB_DH * 2) + l16 * 16);
-          vraw[k] = mg_lds128(sp + MG_KV_TOK * ZB_DH * 2 + i * (ZB_DH * 2) + l16 * 16);
-        }
-      }
-      att_tokens4<G>(kraw, vraw, valid, q, m, l, acc, p.scale_log2);
     }
-    if (!fresh) mg_cons_release(cx);
-  }
-  MG_STAMP();                                                     // att +1: KV stages consumed
-  // merge the two half-warps
 #pragma unroll
-  for (int g = 0; g < G; ++g) {
-    const float mo = __shfl_xor_sync(0xffffffffu, m[g], 16);
-    const float lo = __shfl_xor_sync(0xffffffffu, l[g], 16);
-    const float mn = fmaxf(m[g], mo);
-    const float cs = (m[g] == -INFINITY) ? 0.f : exp2f(m[g] - mn);
-    const float co = (mo == -INFINITY) ? 0.f : exp2f(mo - mn);
-    l[g] = l[g] * cs + lo * co;
+    for (int s = 0; s < 4; ++s) { qa[2 * s][0] = qw[s].x; qa[2 * s][1] = qw[s].y; qa[2 * s + 1][0] = qw[s].z; qa[2 * s + 1][1] = qw[s].w; }
+    if (cx.trace && qa[0][0] == 0x12345678u) cx.trace_n = 0;        // (trace only) make the stamp below wait for the q load
+    MG_STAMP();                                                     // att +0: q / new K,V arrived from L2
+    float m = -INFINITY, l = 0.f, o[8][4];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
+    // ---- tokens of earlier steps: MG_KV_TOK = 64 per ring stage = four 16-token groups.  Warps 0-3 take the groups of
+    // the even stages, warps 4-7 those of the odd ones (every warp still passes every stage's barriers).
+    const int n_kv_stages = tp > it.t0 ? (tp - it.t0 + MG_KV_TOK - 1) / MG_KV_TOK : 0;
+    for (int si = 0; si < n_kv_stages; ++si) {
+      const int ts = it.t0 + si * MG_KV_TOK;
+      const int n = min(MG_KV_TOK, tp - ts);
+      const uint32_t sp = mg_cons_wait_addr(cx);
+      const int tl = 16 * (warp & 3);                   // first token of this warp's group inside the stage
+      if ((si & 1) == (warp >> 2) && tl < n) {          // warp-uniform
+        AttFrag f;
+#pragma unroll
+        for (int nn = 0; nn < 2; ++nn) {
+          const int tok = tl + 8 * nn + g;
+#pragma unroll
+          for (int s = 0; s < 4; ++s) f.k[nn][s] = tok < n ? mg_lds128(sp + tok * (ZB_DH * 2) + (32 * s + 8 * t) * 2) : z4;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int tok = tl + 2 * t + (u & 1) + 8 * (u >> 1);
+#pragma unroll
+          for (int h = 0; h < 2; ++h)
+            f.v[u][h] = tok < n ? mg_lds128(sp + MG_KV_TOK * ZB_DH * 2 + tok * (ZB_DH * 2) + (16 * g + 8 * h) * 2) : z4;
+        }
+        att_group16<G>(f, ts + tl, ts + n, qa, m, l, o, p.scale_log2, lane);
+      }
+      mg_cons_release(cx);
+    }
+    if (has_new && warp == 0) att_group16<G>(fn, pos, pos + 1, qa, m, l, o, p.scale_log2, lane);
+    MG_STAMP();                                                     // att +1: KV stages consumed
+    // per-warp states -> shared memory
+    float* s_o = reinterpret_cast<float*>(cx.scratch);              // [8][G][128]
+    float* s_m = s_o + MG_WARPS * G * ZB_DH;                        // [8][G]
+    float* s_l = s_m + MG_WARPS * G;                                // [8][G]
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float ao = __shfl_xor_sync(0xffffffffu, acc[g][j], 16);
-      acc[g][j] = acc[g][j] * cs + ao * co;
+      const int d = 16 * g + 2 * j;
+      if (2 * t < G) { s_o[(warp * G + 2 * t) * ZB_DH + d] = o[j][0]; s_o[(warp * G + 2 * t) * ZB_DH + d + 1] = o[j][2]; }
+      if (2 * t + 1 < G) { s_o[(warp * G + 2 * t + 1) * ZB_DH + d] = o[j][1]; s_o[(warp * G + 2 * t + 1) * ZB_DH + d + 1] = o[j][3]; }
     }
-    m[g] = mn;
+    if (t == 0 && g < G) { s_m[warp * G + g] = m; s_l[warp * G + g] = l; }
   }
-  // merge the 8 warps through shared memory
   float* s_o = reinterpret_cast<float*>(cx.scratch);              // [8][G][128]
   float* s_m = s_o + MG_WARPS * G * ZB_DH;                        // [8][G]
   float* s_l = s_m + MG_WARPS * G;                                // [8][G]
   float* s_ml = s_l + MG_WARPS * G;                               // [32 * 8 * 2]
   int* s_last = reinterpret_cast<int*>(s_ml + 32 * 8 * 2);
-  if (half == 0) {
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s_o[(warp * G + g) * ZB_DH + l16 * 8 + j] = acc[g][j];
-      if (l16 == 0) { s_m[warp * G + g] = m[g]; s_l[warp * G + g] = l[g]; }
-    }
-  }
   SyncConsumers::sync();
   const size_t pbase = (((size_t)row * p.Hkv + kvh) * nsplit + split) * G;
   const int nact = it.nact;
