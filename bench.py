@@ -244,6 +244,18 @@ def random_dac_state_dict(dev, seed=2):
 # ----------------------------------------------------------------------------------------------------------------
 # CPU baseline (the oracle port of the reference's PyTorch path) — the ONLY place bench.py touches oracle/
 # ----------------------------------------------------------------------------------------------------------------
+def ncu_traffic_per_step(args):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the persistent decode kernel, per decode step, from the committed
+    `ncu --set full` capture (profiles/r01_traffic.json); None when the run is not the configuration that was captured."""
+    if args.batch != 1 or "mega=0" in args.opt:
+        return None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            return float(json.load(f)["dram_bytes_per_step"])
+    except Exception:
+        return None
+
+
 def cpu_reference_sample(n_decode_steps=None, dac_frames=43, budget_s=12.0):
     """Times the reference algorithm (oracle port, torch CPU, all host threads) on a bounded sample of the workload:
     full-size model, batch 1 + CFG, prefill of Lc+1 tokens then decode steps at the start of the utterance, and a DAC
@@ -430,7 +442,7 @@ def run_b200(args, world, rank, local):
         "realtime_factor": value,
         "roofline": {"bound": "hbm", "kernel": kernel_name,
                      "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": step_gbs / hbm_peak, "frac_of_8TBs_nominal": step_gbs / 8000.0,
-                     "peak_kind": peak_kind, "traffic": None, "bytes_per_launch": step_bytes,
+                     "peak_kind": peak_kind, "traffic": ncu_traffic_per_step(args), "bytes_per_launch": step_bytes,
                      "dominant_kernel": {"name": "k_gemv_mma<2,SWIGLU> (ln2+fc1+swiglu of the per-op path)", "achieved": fc1_gbs, "frac": fc1_gbs / hbm_peak,
                                          "bytes_per_launch": fc1_bytes, "timed": "isolated, back to back over the 26 layers"}},
         "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": prefix_host.numel() * 2,

@@ -9,11 +9,12 @@ from zonos_vibes_b200.autoencoder import DACAutoencoder
 ap = argparse.ArgumentParser()
 ap.add_argument("--frames", type=int, default=2580)
 ap.add_argument("--reps", type=int, default=7)
+ap.add_argument("--batch", type=int, default=1, help="utterances per call (BASELINE config 4 = 32 x 2580 frames)")
 ap.add_argument("variants", nargs="*", default=["base"])
 a = ap.parse_args()
 dev = torch.device("cuda:0")
 dac = DACAutoencoder(bench.random_dac_state_dict(dev), dev)
-codes = torch.randint(0, 1024, (1, 9, a.frames), device=dev)
+codes = torch.randint(0, 1024, (a.batch, 9, a.frames), device=dev)
 DEFAULTS = {"ew_multi": 8, "ew_k1": 8, "wide_cout": 768, "mt2_min_waves": 8, "impl": 0}
 times = {v: [] for v in a.variants}
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -39,4 +40,4 @@ for rep in range(a.reps + 1):
             times[v].append(e0.elapsed_time(e1))
 for v in a.variants:
     t = times[v]
-    print(f"{v:40s} min {min(t):.3f} ms  median {statistics.median(t):.3f} ms  -> {1.608302592e-3 * a.frames / (min(t) * 1e-3):.0f} TFLOP/s (best)", flush=True)
+    print(f"{v:40s} min {min(t):.3f} ms  median {statistics.median(t):.3f} ms  -> {1.608302592e-3 * a.frames * a.batch / (min(t) * 1e-3):.0f} TFLOP/s (best), {a.batch * a.frames / (min(t) * 1e-3):.0f} frames/s", flush=True)

@@ -39,6 +39,8 @@ struct P {
   int mode;                   // 0: wait+release, 1: + LDS everything, 2: LDS + MMA (decode-like)
   int poll_all;               // 1: all lanes poll the full barrier, 0: lane 0 polls + __syncwarp
   int direct;                 // 1: no ring — consumers ld.global.nc straight to registers (8 x 16 B in flight per thread)
+  long long wrap_iters;        // > 0: the producer re-reads the first wrap_iters stages over and over (L2-resident source)
+  long long n_iter;            // > 0: stages per CTA (with wrap_iters)
   float* sink;
 };
 
@@ -55,7 +57,7 @@ __global__ void __launch_bounds__(288, 1) k_ring(const P p) {
   }
   __syncthreads();
   const int payload = p.rows * p.row_bytes;
-  const long long n_iter = (long long)(p.per_cta / payload);
+  const long long n_iter = p.n_iter > 0 ? p.n_iter : (long long)(p.per_cta / payload);
   const unsigned char* base = p.src + (size_t)blockIdx.x * p.per_cta;
   if (p.direct) {
     if (warp == 8) return;
@@ -78,7 +80,8 @@ __global__ void __launch_bounds__(288, 1) k_ring(const P p) {
   }
   if (warp == 8) {
     int st = 0, par = 0;
-    for (long long it = 0; it < n_iter; ++it) {
+    for (long long it0 = 0; it0 < n_iter; ++it0) {
+      const long long it = p.wrap_iters > 0 ? it0 % p.wrap_iters : it0;
       if (lane == 0) {
         while (!mbar_try(empty0 + 8u * st, par ^ 1)) {}
         mbar_expect(full0 + 8u * st, payload);
@@ -169,7 +172,7 @@ int main() {
   for (const Cfg& c : cfgs) {
     P p;
     p.src = buf; p.per_cta = total / 148; p.n_stages = c.n_stages; p.rows = c.rows; p.row_bytes = c.row_bytes; p.row_stride = c.row_stride;
-    p.src_row_stride = c.src_stride; p.mode = c.mode; p.poll_all = c.poll_all; p.direct = c.direct; p.sink = sink;
+    p.src_row_stride = c.src_stride; p.mode = c.mode; p.poll_all = c.poll_all; p.direct = c.direct; p.sink = sink; p.wrap_iters = 0; p.n_iter = 0;
     const size_t smem = (size_t)c.n_stages * c.rows * c.row_stride + 16 * c.n_stages + 64;
     float best = 1e30f;
     for (int rep = 0; rep < 3; ++rep) {
@@ -184,6 +187,30 @@ int main() {
     }
     printf("%-42s smem %6zu  %8.3f ms  %8.1f GB/s\n", c.name, smem, best, total / (best * 1e-3) / 1e9);
     fflush(stdout);
+  }
+  // ---- L2-resident source: every CTA loops over its own first `wrap` stages (148 x wrap x 32 KB in total), so after the
+  // first pass the ring is fed from L2: the ceiling of an L2-prefetched weight stream
+  for (int wrap : {4, 8, 16, 32}) {
+    for (int mode : {0, 2}) {
+      P p;
+      p.src = buf; p.per_cta = total / 148; p.n_stages = 5; p.rows = 8; p.row_bytes = 4096; p.row_stride = 4160;
+      p.src_row_stride = 4096; p.mode = mode; p.poll_all = 0; p.direct = 0; p.sink = sink; p.wrap_iters = wrap; p.n_iter = 4096;
+      const size_t smem = (size_t)5 * 8 * 4160 + 16 * 5 + 64;
+      float best = 1e30f;
+      for (int rep = 0; rep < 3; ++rep) {
+        CK(cudaEventRecord(e0));
+        k_ring<<<148, 288, smem>>>(p);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        CK(cudaGetLastError());
+        float ms;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (ms < best) best = ms;
+      }
+      const double bytes = 148.0 * 4096 * 32768;
+      printf("L2-resident 8x4KB st5 mode%d wrap %2d (%5.1f MB set)   %8.3f ms  %8.1f GB/s\n", mode, wrap, 148.0 * wrap * 32768 / 1e6, best, bytes / (best * 1e-3) / 1e9);
+      fflush(stdout);
+    }
   }
   return 0;
 }

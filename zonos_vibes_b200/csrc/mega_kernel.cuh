@@ -83,6 +83,7 @@ struct MegaParams {
   int scratch_bytes;           // activation staging / attention / sampling scratch
   unsigned long long* dbg;     // optional trace: [grid][MG_TRACE_SLOTS] globaltimer stamps of step dbg_step (thread 0)
   int dbg_step;
+  int dbg_fine;                // trace variant: stage-level stamps of ONE fc1 phase (layer 1 of step dbg_step) instead of the per-phase timeline
 };
 #define MG_TRACE_SLOTS 64
 __device__ __forceinline__ unsigned long long mg_globaltimer() {
@@ -167,6 +168,7 @@ struct MgCtx {
   bool prof;                 // debug profile on
   bool poll_all;             // every consumer thread polls the full barriers (A/B switch)
   bool trace;                // this step is being traced
+  bool fine;                 // stage-level trace of one fc1 phase (MegaParams::dbg_fine)
   int trace_n;
   unsigned long long* trace_out;
   long long t_full;          // clock64 ticks thread 0 spent waiting on full barriers (prof)
@@ -222,6 +224,7 @@ struct MgDesc {              // per-lane view of one stage
   uint32_t bytes;
   uint32_t dst_off;          // offset inside the stage
   uint32_t total;            // bytes of the whole stage (warp-uniform)
+  uint32_t tag;              // tile phases: phase | layer << 8 | step << 16 (trace only)
 };
 
 struct MgSched {
@@ -264,7 +267,7 @@ __device__ __forceinline__ void mg_phase_weights(const MegaParams& p, int l, int
 // Advance to the next stage of the schedule.  Warp-uniform control flow; returns false at the end of the launch.
 __device__ __forceinline__ bool mg_sched_next(MgSched& s, const MegaParams& p, MgDesc& d) {
   const int lane = threadIdx.x & 31;
-  d.src = nullptr; d.bytes = 0; d.dst_off = 0; d.total = 0;
+  d.src = nullptr; d.bytes = 0; d.dst_off = 0; d.total = 0; d.tag = 0;
   for (;;) {
     if (s.step >= p.n_steps) return false;
     switch (s.ph) {
@@ -338,6 +341,7 @@ __device__ __forceinline__ bool mg_sched_next(MgSched& s, const MegaParams& p, M
           d.bytes = kcs * 2; d.dst_off = lane * MG_ROW_BYTES;
         }
         d.total = cnt * kcs * 2;
+        d.tag = (uint32_t)s.ph | ((uint32_t)s.l << 8) | ((uint32_t)s.step << 16);
         s.kc0 += MG_KC;
         if (s.kc0 >= K) { s.kc0 = 0; if (++s.nt == NT) { s.nt = 0; s.n0 += 8; } }
         return true;
@@ -493,6 +497,7 @@ struct MgEpi {
   float cfg_scale;
   int eos_bias;
   float* logits;
+  int layer;
 };
 
 __device__ __forceinline__ void mg_epi_resid(const MgCtx& cx, const MgEpi& e, int a, int n0, float s0, float s1) {
@@ -580,6 +585,8 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
         for (int kc0 = 0; kc0 < K; kc0 += MG_KC) {
           const int kcs = min(MG_KC, K - kc0);
           const uint32_t st_addr = mg_cons_wait_addr(cx);
+          const bool fstamp = cx.fine && kind == EPI_SWIGLU && epi.layer == 1 && threadIdx.x == 0 && cx.trace_n < 32;
+          if (fstamp) cx.trace_out[cx.trace_n++] = mg_globaltimer();        // stage data seen by warp 0
           if (packed && (kcs & 511) == 0) {
             // R <= 4: the WEIGHTS are the MMA's A operand.  A rows 0..7 = the 8 weight rows over the first half of the
             // chunk's columns, A rows 8..15 = the same weight rows over the second half; B columns 0..3 = the
@@ -640,6 +647,7 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
             }
           }
           mg_cons_release(cx);
+          if (fstamp && cx.trace_n < 32) cx.trace_out[cx.trace_n++] = mg_globaltimer();      // warp 0 done with the stage
         }
       }
     }
@@ -957,7 +965,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   volatile int* s_flags = reinterpret_cast<volatile int*>(bars + 16 * MG_MAX_STAGES);   // [0] stop, [1] consumer cursor, [2] misc
   cx.stage = 0; cx.parity = 0; cx.tile_flip = 0;
   cx.prof = p.dbg != nullptr; cx.t_full = 0; cx.t_fc1 = cx.t_fc1_full = cx.t_fc1_sync = 0; cx.poll_all = p.poll_all != 0;
-  cx.trace = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
+  cx.trace = false; cx.fine = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
 
   const int tid = threadIdx.x, warp = tid >> 5;
   if (tid == 0) {
@@ -983,6 +991,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       MgDesc d;
       // optional profile of this warp (clock64 ticks): [0] schedule arithmetic, [1] waiting for a free slot, [2] issue, [3] stages
       long long t_sched = 0, t_wait = 0, t_issue = 0, n_ld = 0;
+      int n_fine = 0;
       const bool prof = p.dbg != nullptr;
       for (;;) {
         const long long c0 = prof ? clock64() : 0;
@@ -1001,6 +1010,8 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         }
         if (!__shfl_sync(0xffffffffu, go, 0)) break;
         const long long c2 = prof ? clock64() : 0;
+        if (prof && p.dbg_fine && lane == 0 && d.tag == ((uint32_t)MG_PH_FC1 | (1u << 8) | ((uint32_t)p.dbg_step << 16)) && n_fine < 32)
+          p.dbg[(size_t)blockIdx.x * MG_TRACE_SLOTS + 32 + n_fine++] = mg_globaltimer();     // issue time of this fc1 stage
         if (d.src != nullptr)
           mg_bulk_g2s(mg_smem_u32(cx.ring + (size_t)cx.stage * MG_STAGE_BYTES + d.dst_off), d.src, d.bytes, cx.full0 + 8u * cx.stage);
         mg_advance(cx);
@@ -1037,7 +1048,8 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   const bool embed_ahead = p.mode == MG_MODE_DECODE || p.mode == MG_MODE_FORCED;
   for (int step = 0; step < p.n_steps; ++step) {
     if (mg_ld_volatile(&st->done)) break;
-    cx.trace = p.dbg != nullptr && step == p.dbg_step;
+    cx.trace = p.dbg != nullptr && step == p.dbg_step && !p.dbg_fine;
+    cx.fine = p.dbg != nullptr && step == p.dbg_step && p.dbg_fine;
     cx.trace_n = 0;
     MG_STAMP();                                                   // 0: step start
     const int pos = mg_ld_volatile(&st->pos), col = mg_ld_volatile(&st->col), Lbuf = mg_ld_volatile(&st->L);
@@ -1077,6 +1089,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
     epi.pos = pos; epi.own_lo = own_lo;
     epi.cfg_scale = 0.f; epi.eos_bias = 0; epi.logits = p.logits;
     for (int l = 0; l < p.n_layer; ++l) {
+      epi.layer = l;
       bf16* kv_layer = p.kv + (size_t)l * p.kv_layer_elems;
       // P1: LN1 + in_proj + RoPE + KV append
       mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);

@@ -491,7 +491,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     const size_t nb = (size_t)c->n_sms * (MG_TRACE_SLOTS + 8) * sizeof(unsigned long long);
     if (!c->dbg && (e = cudaMalloc(&c->dbg, nb)) != cudaSuccess) return e;
     cudaMemsetAsync(c->dbg, 0, nb, s);
-    p.dbg = c->dbg; p.dbg_step = n_steps / 2;
+    p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2;
     e = cudaLaunchKernelEx(&cfg, mega_kernel(G), p);
     if (e != cudaSuccess) return e;
     std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8));
@@ -500,7 +500,8 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     const int ctas[3] = {0, c->n_sms / 2, c->n_sms - 1};
     fprintf(stderr, "[mega trace] mode %d steps %d step %d: ns since step start (cta %d / %d / %d)\n", mode, n_steps, p.dbg_step, ctas[0], ctas[1], ctas[2]);
     for (int i = 0; i < MG_TRACE_SLOTS; ++i) {
-      if (!hbuf[i]) break;
+      if (!hbuf[i] && !p.dbg_fine) break;
+      if (!hbuf[i]) continue;
       fprintf(stderr, "  slot %2d:", i);
       for (int j = 0; j < 3; ++j) {
         const unsigned long long* row = hbuf.data() + (size_t)ctas[j] * MG_TRACE_SLOTS;
