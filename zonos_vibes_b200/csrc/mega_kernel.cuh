@@ -29,7 +29,12 @@
 #include "sample_kernels.cuh"
 
 #define MG_CONSUMERS 256
-#define MG_THREADS 288               // 8 consumer warps + 1 producer warp
+#define MG_THREADS 320               // 8 MMA consumer warps + 1 producer warp + 1 epilogue warp
+#define MG_EPI_WARP 9
+#define MG_HANDOFF 288               // threads on the tile hand-off barriers: the 8 MMA warps + the epilogue warp
+// named barriers: 0 __syncthreads, 1 SyncConsumers (8 MMA warps), 2/3 partial buffer 0/1 full, 4/5 partial buffer 0/1 free,
+// 6 GEMV phase done, 7 step start
+enum { MG_BAR_FULL = 2, MG_BAR_FREE = 4, MG_BAR_PHASE = 6, MG_BAR_STEP = 7 };
 #define MG_WARPS 8
 #define MG_KC 2048                   // weight columns per ring stage (4 KB per row copy)
 #define MG_ROW_BYTES (MG_KC * 2 + 64)   // stage row stride: +64 B => 8 rows x 16 B quarter-warp reads hit 32 distinct banks
@@ -129,6 +134,8 @@ __device__ __forceinline__ void mg_bulk_g2s(uint32_t dst, const void* src, uint3
                "r"(bytes), "r"(bar)
                : "memory");
 }
+__device__ __forceinline__ void mg_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void mg_bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ uint4 mg_lds128(uint32_t addr) {
   uint4 r;
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
@@ -399,33 +406,39 @@ __device__ __forceinline__ void mg_unpack8(const uint4& raw, float (&v)[8]) {
 
 // LayerNorm (F.layer_norm: biased variance, eps inside the sqrt, fp32 statistics, bf16 result) of rows r < R of src
 // into xs.  The affine parameters arrive through the ring (stage rows 0 / 1).  K <= 2048 (one uint4 per thread per row).
-// Deliberately NOT unrolled over rows and not inlined: the persistent kernel's per-layer code must stay inside the
-// instruction cache — instruction fetches that miss compete with the saturated weight stream (the first version,
-// 360 KB of SASS, spent ~7 us per LayerNorm waiting on instruction fetch: profiles/r01_mega_trace_v1.md).
+// Three CTA barriers instead of five: every thread sums the 8 warp partials itself (same warp order, so the statistics
+// are bit-identical to the two-stage reduction of the per-op path), and the rows are walked by runtime loops.
 __device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const bf16* src, int K, int R, float eps) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int e = tid * 8;
   const bool active = e < K;
-  float* red = cx.red;              // [64] per-warp partials, [64..72) mean, [72..80) rstd
-  // pass 1: raw rows -> xs, row sums.  ALL rows are requested before the first one is used: one L2 round trip, not R.
-  uint4 rawr[8];
+  float* red1 = cx.red;             // [8 warps][8 rows] partial sums
+  float* red2 = cx.part;            // [8 warps][8 rows] partial sums of squared deviations (the GEMV partial buffer is idle here)
+  const float fk = (float)K;
+  // pass 1: raw rows -> xs.  ALL rows are requested before the first one is used: one L2 round trip, not R.
+  {
+    uint4 rawr[8];
 #pragma unroll
-  for (int r = 0; r < 8; ++r) {
-    rawr[r] = make_uint4(0, 0, 0, 0);
-    if (r < R && active) rawr[r] = mg_ldcg16(src + (size_t)r * K + e);
+    for (int r = 0; r < 8; ++r) {
+      rawr[r] = make_uint4(0, 0, 0, 0);
+      if (r < R && active) rawr[r] = mg_ldcg16(src + (size_t)r * K + e);
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+      if (r < R && active) *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) = rawr[r];
   }
-#pragma unroll
-  for (int r = 0; r < 8; ++r) {
-    if (r < R) {
-      if (active) *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) = rawr[r];
+  // row sums (each thread re-reads the 16 B it has just written)
+#pragma unroll 1
+  for (int r = 0; r < R; ++r) {
+    float t = 0.f;
+    if (active) {
       float v[8];
-      mg_unpack8(rawr[r], v);
-      float t = 0.f;
+      mg_unpack8(*reinterpret_cast<const uint4*>(xs + (size_t)r * ld + e), v);
 #pragma unroll
       for (int j = 0; j < 8; ++j) t += v[j];
-      t = warp_sum(t);
-      if (lane == 0) red[warp * 8 + r] = t;
     }
+    t = warp_sum(t);
+    if (lane == 0) red1[warp * 8 + r] = t;
   }
   // affine parameters from the ring
   const uint32_t sp = mg_cons_wait_addr(cx);
@@ -436,16 +449,13 @@ __device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const b
   }
   mg_cons_release(cx);
   SyncConsumers::sync();
-  if (tid < R) {
-    float t = 0.f;
-#pragma unroll
-    for (int w = 0; w < MG_WARPS; ++w) t += red[w * 8 + tid];
-    red[64 + tid] = t / (float)K;
-  }
-  SyncConsumers::sync();
-  // pass 2: variance (each thread re-reads its own 16 B from xs)
+  // pass 2: variance around the mean (every thread sums the 8 warp partials itself, in warp order)
+#pragma unroll 1
   for (int r = 0; r < R; ++r) {
-    const float mean = red[64 + r];
+    float m = 0.f;
+#pragma unroll
+    for (int w = 0; w < MG_WARPS; ++w) m += red1[w * 8 + r];
+    const float mean = m / fk;
     float t = 0.f;
     if (active) {
       float v[8];
@@ -454,22 +464,19 @@ __device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const b
       for (int j = 0; j < 8; ++j) { const float dlt = v[j] - mean; t += dlt * dlt; }
     }
     t = warp_sum(t);
-    if (lane == 0) red[warp * 8 + r] = t;
+    if (lane == 0) red2[warp * 8 + r] = t;
   }
   SyncConsumers::sync();
-  if (tid < R) {
-    float t = 0.f;
+  float g[8], bb[8];
+  mg_unpack8(wr, g);
+  mg_unpack8(br, bb);
+#pragma unroll 1
+  for (int r = 0; r < R; ++r) {
+    float m = 0.f, q = 0.f;
 #pragma unroll
-    for (int w = 0; w < MG_WARPS; ++w) t += red[w * 8 + tid];
-    red[72 + tid] = rsqrtf(t / (float)K + eps);
-  }
-  SyncConsumers::sync();
-  if (active) {
-    float g[8], bb[8];
-    mg_unpack8(wr, g);
-    mg_unpack8(br, bb);
-    for (int r = 0; r < R; ++r) {
-      const float mean = red[64 + r], rstd = red[72 + r];
+    for (int w = 0; w < MG_WARPS; ++w) { m += red1[w * 8 + r]; q += red2[w * 8 + r]; }
+    const float mean = m / fk, rstd = rsqrtf(q / fk + eps);
+    if (active) {
       float v[8];
       mg_unpack8(*reinterpret_cast<const uint4*>(xs + (size_t)r * ld + e), v);
       __nv_bfloat162 o[4];
@@ -568,6 +575,7 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
   const bool pf1 = cx.prof && kind == EPI_SWIGLU && threadIdx.x == 0;
   const long long pt0 = pf1 ? clock64() : 0, pfull0 = cx.t_full;
   const bool packed = R <= 4;
+  int ti = 0;                                    // tile counter of this phase (partial buffer = ti & 1)
   for (int n0 = lo; n0 < hi; n0 += 8) {
     const int cnt = min(8, hi - n0);
     bool used_packed = false;                      // warp-uniform, the same for every chunk of a tile (K % 2048 chunks)
@@ -651,8 +659,15 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
         }
       }
     }
-    float* pb = cx.part + (size_t)(cx.tile_flip & 1) * 2 * MG_WARPS * 64;
-    cx.tile_flip ^= 1;
+    // ---- hand the tile to the epilogue warp.  The stage-level trace of the version in which the MMA warps did the
+    // cross-warp reduce + epilogue themselves (profiles/r01_fc1_stage_trace.txt) showed a 0.6 us tail per 8-row tile
+    // (partial store, CTA barrier, 8-warp reduce, SwiGLU on warp 0) against 2 x 0.35 us of MMA work: the GEMV phases were
+    // bound by that serial tail, not by HBM.  Here the MMA warps only store their partials and arrive on a named
+    // barrier; warp 9 reduces and runs the epilogue while they are already in the next tile.
+    const int f = ti & 1;
+    float* pb = cx.part + (size_t)f * 2 * MG_WARPS * 64;
+    if (ti >= 2) mg_bar_sync(MG_BAR_FREE + f, MG_HANDOFF);        // the epilogue warp is done with tile ti - 2
+    ++ti;
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
       if (nt < NT) {
@@ -670,12 +685,32 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
         }
       }
     }
-    // ---- reduce the K-slices of the 8 warps, run the epilogue
-    const long long ps0 = pf1 ? clock64() : 0;
-    SyncConsumers::sync();
+    __threadfence_block();
+    mg_bar_arrive(MG_BAR_FULL + f, MG_HANDOFF);
+  }
+  mg_bar_sync(MG_BAR_PHASE, MG_HANDOFF);     // every epilogue store of this phase has been issued (the grid barrier follows)
+  if (pf1) { cx.t_fc1 += clock64() - pt0; cx.t_fc1_full += cx.t_full - pfull0; }
+}
+
+// The epilogue warp's side of one GEMV phase: per tile, wait for the 8 MMA warps' partials, reduce them in warp order
+// (fixed summation order: reproducible tokens) and run the fused epilogue; same arithmetic as gm_epilogue_* in gemv_mma.cuh.
+__device__ __forceinline__ void mg_gemv_epi(const MegaParams& p, const MgCtx& cx, int n_units, int kind, const MgEpi& epi) {
+  const int UNIT = kind == EPI_SWIGLU ? 1 : 2;
+  const int lane = threadIdx.x & 31;
+  const int R = p.R;
+  int lo, hi;
+  mg_range(n_units, lo, hi);
+  lo *= UNIT; hi *= UNIT;
+  const int n_tiles = (hi - lo + 7) >> 3;
+  int ti = 0;
+  for (int n0 = lo; n0 < hi; n0 += 8, ++ti) {
+    const int cnt = min(8, hi - n0);
+    const int f = ti & 1;
+    const float* pb = cx.part + (size_t)f * 2 * MG_WARPS * 64;
+    mg_bar_sync(MG_BAR_FULL + f, MG_HANDOFF);
     if (kind == EPI_SWIGLU) {
-      if (tid < R * 8) {
-        const int r = tid >> 3, n = tid & 7;
+      for (int i = lane; i < R * 8; i += 32) {
+        const int r = i >> 3, n = i & 7;
         float yv = 0.f, gt = 0.f;
 #pragma unroll
         for (int w = 0; w < MG_WARPS; ++w) { yv += pb[((0 * MG_WARPS + w) * 8 + r) * 8 + n]; gt += pb[((1 * MG_WARPS + w) * 8 + r) * 8 + n]; }
@@ -688,8 +723,8 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
       }
     } else if (kind == EPI_HEADS) {
       const int B = R >> 1;
-      if (tid < B * 4) {
-        const int b = tid >> 2, j = tid & 3;
+      for (int i = lane; i < B * 4; i += 32) {
+        const int b = i >> 2, j = i & 3;
         float c0 = 0.f, c1 = 0.f, u0 = 0.f, u1 = 0.f;
 #pragma unroll
         for (int w = 0; w < MG_WARPS; ++w) {
@@ -699,8 +734,8 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
         if (2 * j < cnt) mg_epi_heads(p, epi, b, n0 + 2 * j, c0, c1, u0, u1);
       }
     } else {
-      if (tid < R * 4) {
-        const int r = tid >> 2, j = tid & 3;
+      for (int i = lane; i < R * 4; i += 32) {
+        const int r = i >> 2, j = i & 3;
         float s0 = 0.f, s1 = 0.f;
 #pragma unroll
         for (int w = 0; w < MG_WARPS; ++w) { s0 += pb[(w * 8 + r) * 8 + 2 * j]; s1 += pb[(w * 8 + r) * 8 + 2 * j + 1]; }
@@ -710,11 +745,13 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
         }
       }
     }
-    // no second barrier: the next tile writes the other half of `part`; this half is rewritten only after the NEXT
-    // tile's barrier, which every epilogue thread reaches after finishing its reads.
-    if (pf1) cx.t_fc1_sync += clock64() - ps0;
+    __syncwarp();
+    if (ti + 2 < n_tiles) {                      // the MMA warps wait for this buffer again only before tile ti + 2
+      __threadfence_block();
+      mg_bar_arrive(MG_BAR_FREE + f, MG_HANDOFF);
+    }
   }
-  if (pf1) { cx.t_fc1 += clock64() - pt0; cx.t_fc1_full += cx.t_full - pfull0; }
+  mg_bar_sync(MG_BAR_PHASE, MG_HANDOFF);
 }
 
 // =================================================================================================================
@@ -784,8 +821,6 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
     }
 #pragma unroll
     for (int s = 0; s < 4; ++s) { qa[2 * s][0] = qw[s].x; qa[2 * s][1] = qw[s].y; qa[2 * s + 1][0] = qw[s].z; qa[2 * s + 1][1] = qw[s].w; }
-    if (cx.trace && qa[0][0] == 0x12345678u) cx.trace_n = 0;        // (trace only) make the stamp below wait for the q load
-    MG_STAMP();                                                     // att +0: q / new K,V arrived from L2
     float m = -INFINITY, l = 0.f, o[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
@@ -817,7 +852,6 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
       mg_cons_release(cx);
     }
     if (has_new && warp == 0) att_group16<G>(fn, pos, pos + 1, qa, m, l, o, p.scale_log2, lane);
-    MG_STAMP();                                                     // att +1: KV stages consumed
     // per-warp states -> shared memory
     float* s_o = reinterpret_cast<float*>(cx.scratch);              // [8][G][128]
     float* s_m = s_o + MG_WARPS * G * ZB_DH;                        // [8][G]
@@ -962,7 +996,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   unsigned char* bars = reinterpret_cast<unsigned char*>(cx.s_page + 16);
   cx.full0 = mg_smem_u32(bars);
   cx.empty0 = cx.full0 + 8u * MG_MAX_STAGES;
-  volatile int* s_flags = reinterpret_cast<volatile int*>(bars + 16 * MG_MAX_STAGES);   // [0] stop, [1] consumer cursor, [2] misc
+  volatile int* s_flags = reinterpret_cast<volatile int*>(bars + 16 * MG_MAX_STAGES);   // [0] stop, [1] consumer cursor, [2] misc, [3] step mailbox for the epilogue warp (KV position, -1 = stop)
   cx.stage = 0; cx.parity = 0; cx.tile_flip = 0;
   cx.prof = p.dbg != nullptr; cx.t_full = 0; cx.t_fc1 = cx.t_fc1_full = cx.t_fc1_sync = 0; cx.poll_all = p.poll_all != 0;
   cx.trace = false; cx.fine = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
@@ -970,7 +1004,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   const int tid = threadIdx.x, warp = tid >> 5;
   if (tid == 0) {
     for (int s = 0; s < p.n_stages; ++s) { mg_mbar_init(cx.full0 + 8u * s, 1); mg_mbar_init(cx.empty0 + 8u * s, MG_WARPS); }
-    s_flags[0] = 0; s_flags[1] = 0; s_flags[2] = 0;
+    s_flags[0] = 0; s_flags[1] = 0; s_flags[2] = 0; s_flags[3] = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -1036,6 +1070,39 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
     return;
   }
 
+  if (warp == MG_EPI_WARP) {
+    // ================================================ epilogue warp ================================================
+    // Mirrors the consumers' step / layer / phase nest; blocks on the hand-off barriers in between (LayerNorm staging,
+    // attention, grid barriers and sampling are the MMA warps' business).
+    MgEpi epi;
+    { int own_hi; mg_range(p.d / 2, epi.own_lo, own_hi); epi.own_lo *= 2; }
+    epi.logits = p.logits;
+    for (int step = 0; step < p.n_steps; ++step) {
+      mg_bar_sync(MG_BAR_STEP, MG_HANDOFF);
+      const int pos = s_flags[3];
+      if (pos < 0) break;
+      epi.pos = pos; epi.cfg_scale = 0.f; epi.eos_bias = 0;
+      for (int l = 0; l < p.n_layer; ++l) {
+        epi.layer = l;
+        epi.kv_layer = p.kv + (size_t)l * p.kv_layer_elems;
+        epi.out = p.q; epi.out_stride = p.q_size;
+        mg_gemv_epi(p, cx, qkv_rows / 2, EPI_QKV, epi);
+        epi.out = p.x; epi.out_stride = p.d;
+        mg_gemv_epi(p, cx, p.d / 2, EPI_RESID, epi);
+        epi.out = p.h; epi.out_stride = p.F;
+        mg_gemv_epi(p, cx, p.F, EPI_SWIGLU, epi);
+        epi.out = p.x; epi.out_stride = p.d;
+        mg_gemv_epi(p, cx, p.d / 2, EPI_RESID, epi);
+      }
+      if (with_heads) {
+        epi.cfg_scale = *reinterpret_cast<const volatile float*>(&st->cfg_scale);
+        epi.eos_bias = mg_ld_volatile(&st->apply_eos_bias);
+        mg_gemv_epi(p, cx, p.n_q * p.V / 2, EPI_HEADS, epi);
+      }
+    }
+    return;
+  }
+
   // ================================================== consumer warps ==================================================
   unsigned bar_target = 0;
   const long long t_kernel0 = clock64();
@@ -1047,7 +1114,13 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
 
   const bool embed_ahead = p.mode == MG_MODE_DECODE || p.mode == MG_MODE_FORCED;
   for (int step = 0; step < p.n_steps; ++step) {
-    if (mg_ld_volatile(&st->done)) break;
+    {
+      // step mailbox: the epilogue warp learns the KV position of this step (or that the launch is over)
+      const int done = mg_ld_volatile(&st->done);
+      if (tid == 0) s_flags[3] = done ? -1 : mg_ld_volatile(&st->pos);
+      mg_bar_sync(MG_BAR_STEP, MG_HANDOFF);
+      if (done) break;
+    }
     cx.trace = p.dbg != nullptr && step == p.dbg_step && !p.dbg_fine;
     cx.fine = p.dbg != nullptr && step == p.dbg_step && p.dbg_fine;
     cx.trace_n = 0;

@@ -4,6 +4,7 @@
 
 #include <map>
 #include <string>
+#include <algorithm>
 #include <vector>
 
 #include "attention_kernels.cuh"
@@ -508,6 +509,22 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
         fprintf(stderr, " %9lld (+%6lld)", (long long)(row[i] - hbuf[0]), i ? (long long)(row[i] - row[i - 1]) : 0LL);
       }
       fprintf(stderr, "\n");
+    }
+    if (!p.dbg_fine) {
+      // skew: for every stamp, the earliest / median / latest CTA (all CTAs take the same stamps) and who was last
+      fprintf(stderr, "[mega skew] slot: min / median / max over %d CTAs (ns since CTA 0's step start), last CTA\n", c->n_sms);
+      std::vector<long long> v(c->n_sms);
+      for (int i = 0; i < MG_TRACE_SLOTS; ++i) {
+        if (!hbuf[i]) break;
+        int last = 0;
+        for (int j = 0; j < c->n_sms; ++j) {
+          v[j] = (long long)(hbuf[(size_t)j * MG_TRACE_SLOTS + i] - hbuf[0]);
+          if (v[j] > v[last]) last = j;
+        }
+        const long long vmax = v[last];
+        std::sort(v.begin(), v.end());
+        fprintf(stderr, "  skew %2d: %9lld %9lld %9lld  (spread %6lld) last cta %d\n", i, v[0], v[c->n_sms / 2], vmax, vmax - v[0], last);
+      }
     }
     // whole-launch profile of the producer warp / consumer thread 0 (clock64 ticks)
     for (int j = 0; j < 3; ++j) {
