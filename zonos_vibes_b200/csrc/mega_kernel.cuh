@@ -42,7 +42,7 @@ enum { MG_BAR_FULL = 2, MG_BAR_FREE = 4, MG_BAR_PHASE = 6, MG_BAR_STEP = 7 };
 #define MG_MAX_STAGES 8
 #define MG_XPAD 32                   // bf16 elements of padding per staged activation row
 #define MG_KV_TOK 64                 // tokens per KV stage: K rows at [0, 16 KB), V rows at [16 KB, 32 KB)
-#define MG_MAX_SPLIT 8              // KV splits per (row, kv head): the merge stages all partials in the s_o scratch ([8][G][128])
+#define MG_MAX_SPLIT 16             // KV splits per (row, kv head): the merge stages all partials in the s_o scratch ([16][G][128])
 #define MG_OWN 16                    // residual-stream columns a CTA can own (2 * ceil(d/2 / grid) <= 16)
 #define MG_ROPE_BYTES (ZB_DH / 2 * 2 * 4)   // one RoPE table row: 64 x (cos, sin) fp32
 
@@ -70,7 +70,7 @@ struct MegaParams {
   int max_pages;
   float *part_o, *part_ml;     // split-KV partials [R][Hkv][nsplit][G][Dh], [...][2]
   int* att_counters;           // [R][Hkv] tickets (zero between launches)
-  int nsplit;
+  int nsplit, min_chunk, single_ctx;
   int R, B;                    // activation rows (= 2B in the CFG modes) and utterances
   ZbDevState* st;
   int* rope_pos;               // [R]
@@ -99,6 +99,11 @@ __device__ __forceinline__ unsigned long long mg_globaltimer() {
 #define MG_STAMP()                                                                                         \
   do {                                                                                                     \
     if (cx.trace && threadIdx.x == 0 && cx.trace_n < MG_TRACE_SLOTS) cx.trace_out[cx.trace_n++] = mg_globaltimer(); \
+  } while (0)
+
+#define MG_ASTAMP()                                                                                        \
+  do {                                                                                                     \
+    if (cx.afine && threadIdx.x == 0 && cx.trace_n < MG_TRACE_SLOTS) cx.trace_out[cx.trace_n++] = mg_globaltimer(); \
   } while (0)
 
 // ---- PTX helpers ------------------------------------------------------------------------------------------------
@@ -175,7 +180,8 @@ struct MgCtx {
   bool prof;                 // debug profile on
   bool poll_all;             // every consumer thread polls the full barriers (A/B switch)
   bool trace;                // this step is being traced
-  bool fine;                 // stage-level trace of one fc1 phase (MegaParams::dbg_fine)
+  bool fine;                 // stage-level trace of one fc1 phase (MegaParams::dbg_fine == 1)
+  bool afine;                // step-level trace of one attention phase (dbg_fine == 2, layer 1)
   int trace_n;
   unsigned long long* trace_out;
   long long t_full;          // clock64 ticks thread 0 spent waiting on full barriers (prof)
@@ -197,7 +203,6 @@ struct MgAttItem {
   bool mine;
   int row, kvh, split, t0, t1, chunk, nact;
 };
-#define MG_MIN_CHUNK 256             // tokens per split at least: short contexts use ONE split and skip the partial merge
 __device__ __forceinline__ MgAttItem mg_att_item(const MegaParams& p, int pos) {
   MgAttItem it;
   const int nsplit = p.nsplit;
@@ -208,7 +213,10 @@ __device__ __forceinline__ MgAttItem mg_att_item(const MegaParams& p, int pos) {
   const int ctx = pos + 1;
   int chunk = (ctx + nsplit - 1) / nsplit;
   chunk = (chunk + 7) & ~7;
-  if (chunk < MG_MIN_CHUNK) chunk = MG_MIN_CHUNK;
+  if (chunk < p.min_chunk) chunk = p.min_chunk;        // tokens per split at least
+  // short contexts use ONE split and skip the partial merge: a split costs ~2.5 us of ticket + merge latency, which
+  // 128 tokens of K/V per CTA (one 16-token group per warp, ~1.2 us) repay only from ~3 groups per warp on
+  if (ctx <= p.single_ctx) chunk = (ctx + 7) & ~7;
   it.chunk = chunk;
   it.nact = (ctx + chunk - 1) / chunk;                 // splits that own tokens (<= nsplit)
   it.mine = (int)blockIdx.x < p.R * p.Hkv * nsplit && it.split < it.nact;
@@ -789,7 +797,8 @@ __device__ __forceinline__ void mg_att_token(const uint4& kraw, const uint4& vra
 template <int G>
 __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const bf16* kv_layer, int pos) {
   const MgAttItem it = mg_att_item(p, pos);
-  if (!it.mine) return;                               // CTA-uniform
+  if (!it.mine) return;
+  MG_ASTAMP();                                                      // a0: phase entered                               // CTA-uniform
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, t = lane & 3;                // mma.sync fragment coordinates (attention_kernels.cuh, att_group16)
   const int nsplit = p.nsplit, row = it.row, kvh = it.kvh, split = it.split;
@@ -821,6 +830,8 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
     }
 #pragma unroll
     for (int s = 0; s < 4; ++s) { qa[2 * s][0] = qw[s].x; qa[2 * s][1] = qw[s].y; qa[2 * s + 1][0] = qw[s].z; qa[2 * s + 1][1] = qw[s].w; }
+    if (cx.afine && qa[0][0] == 0x12345678u) cx.trace_n = 0;        // (trace only) make the next stamp wait for the q load
+    MG_ASTAMP();                                                    // a1: q arrived from L2
     float m = -INFINITY, l = 0.f, o[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
@@ -850,11 +861,13 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
         att_group16<G>(f, ts + tl, ts + n, qa, m, l, o, p.scale_log2, lane);
       }
       mg_cons_release(cx);
+      MG_ASTAMP();                                                  // per KV stage: warp 0 done
     }
     if (has_new && warp == 0) att_group16<G>(fn, pos, pos + 1, qa, m, l, o, p.scale_log2, lane);
+    MG_ASTAMP();                                                    // fresh row done
     // per-warp states -> shared memory
-    float* s_o = reinterpret_cast<float*>(cx.scratch);              // [8][G][128]
-    float* s_m = s_o + MG_WARPS * G * ZB_DH;                        // [8][G]
+    float* s_o = reinterpret_cast<float*>(cx.scratch);              // [MG_MAX_SPLIT >= 8][G][128]
+    float* s_m = s_o + MG_MAX_SPLIT * G * ZB_DH;                    // [8][G]
     float* s_l = s_m + MG_WARPS * G;                                // [8][G]
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -864,8 +877,8 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
     }
     if (t == 0 && g < G) { s_m[warp * G + g] = m; s_l[warp * G + g] = l; }
   }
-  float* s_o = reinterpret_cast<float*>(cx.scratch);              // [8][G][128]
-  float* s_m = s_o + MG_WARPS * G * ZB_DH;                        // [8][G]
+  float* s_o = reinterpret_cast<float*>(cx.scratch);              // [MG_MAX_SPLIT >= 8][G][128]
+  float* s_m = s_o + MG_MAX_SPLIT * G * ZB_DH;                    // [8][G]
   float* s_l = s_m + MG_WARPS * G;                                // [8][G]
   float* s_ml = s_l + MG_WARPS * G;                               // [32 * 8 * 2]
   int* s_last = reinterpret_cast<int*>(s_ml + 32 * 8 * 2);
@@ -892,16 +905,20 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
       if (dim == 0) { p.part_ml[(pbase + g) * 2 + 0] = mn; p.part_ml[(pbase + g) * 2 + 1] = lt; }
     }
   }
+  MG_ASTAMP();                                                      // partials (or y) stored
   if (nact == 1) return;                                          // CTA-uniform
-  __threadfence();
+  // Ticket with ONE release/acquire by thread 0 after the CTA barrier (cumulativity makes every thread's partial stores
+  // visible before the ticket, exactly like the grid barrier).  The attention trace (--opt trace=3) showed 1.1-1.8 us
+  // spent in a __threadfence() executed by all 256 threads here, and again on the last arriver's side.
   SyncConsumers::sync();
   if (tid == 0) {
-    const int ticket = atomicAdd(&p.att_counters[row * p.Hkv + kvh], 1);
+    int ticket;
+    asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;" : "=r"(ticket) : "l"(&p.att_counters[row * p.Hkv + kvh]) : "memory");
     *s_last = (ticket == nact - 1);
   }
   SyncConsumers::sync();
+  MG_ASTAMP();                                                      // ticket taken
   if (!*s_last) return;                                           // CTA-uniform
-  __threadfence();
   // ---- the last CTA of this (row, kv head) merges the split partials: ONE cooperative, coalesced L2 read of all of
   // them into shared memory (a single round trip), then small runtime loops.
   const size_t rbase = ((size_t)row * p.Hkv + kvh) * nsplit * G;
@@ -916,23 +933,33 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
     for (int i = tid; i < nact * G * 2; i += MG_CONSUMERS) s_pml[i] = __ldcg(&p.part_ml[rbase * 2 + i]);
   }
   SyncConsumers::sync();
-#pragma unroll 1
-  for (int oi = tid; oi < G * ZB_DH; oi += MG_CONSUMERS) {
-    const int g = oi >> 7, dim = oi & (ZB_DH - 1);
+  MG_ASTAMP();                                                      // last arriver: all partials staged
+  // rescale factor of every (split, head) once (the trace showed 1.4 us here when each of the 2 outputs per thread
+  // recomputed nact exp2f's in a serial loop); summation order over the splits is unchanged
+  float* s_c = s_ml + 256;                                          // [nact][G]
+  if (tid < nact * G) {
+    const int g = tid % G;
     float mn = -INFINITY;
 #pragma unroll 1
     for (int s2 = 0; s2 < nact; ++s2) mn = fmaxf(mn, s_pml[(s2 * G + g) * 2]);
-    float lt = 0.f, ot = 0.f;
+    const float ms = s_pml[tid * 2];
+    s_c[tid] = (ms == -INFINITY) ? 0.f : exp2f(ms - mn);
+  }
+  SyncConsumers::sync();
 #pragma unroll 1
+  for (int oi = tid; oi < G * ZB_DH; oi += MG_CONSUMERS) {
+    const int g = oi >> 7, dim = oi & (ZB_DH - 1);
+    float lt = 0.f, ot = 0.f;
+#pragma unroll 4
     for (int s2 = 0; s2 < nact; ++s2) {
-      const float ms = s_pml[(s2 * G + g) * 2];
-      const float c = (ms == -INFINITY) ? 0.f : exp2f(ms - mn);
+      const float c = s_c[s2 * G + g];
       lt += s_pml[(s2 * G + g) * 2 + 1] * c;
       ot += s_po[(s2 * G + g) * ZB_DH + dim] * c;
     }
     p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + dim] = __float2bfloat16_rn(ot / lt);
   }
   if (tid == 0) p.att_counters[row * p.Hkv + kvh] = 0;
+  MG_ASTAMP();                                                      // last arriver: y stored
 }
 
 // =================================================================================================================
@@ -999,7 +1026,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   volatile int* s_flags = reinterpret_cast<volatile int*>(bars + 16 * MG_MAX_STAGES);   // [0] stop, [1] consumer cursor, [2] misc, [3] step mailbox for the epilogue warp (KV position, -1 = stop)
   cx.stage = 0; cx.parity = 0; cx.tile_flip = 0;
   cx.prof = p.dbg != nullptr; cx.t_full = 0; cx.t_fc1 = cx.t_fc1_full = cx.t_fc1_sync = 0; cx.poll_all = p.poll_all != 0;
-  cx.trace = false; cx.fine = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
+  cx.trace = false; cx.fine = false; cx.afine = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
 
   const int tid = threadIdx.x, warp = tid >> 5;
   if (tid == 0) {
@@ -1044,7 +1071,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         }
         if (!__shfl_sync(0xffffffffu, go, 0)) break;
         const long long c2 = prof ? clock64() : 0;
-        if (prof && p.dbg_fine && lane == 0 && d.tag == ((uint32_t)MG_PH_FC1 | (1u << 8) | ((uint32_t)p.dbg_step << 16)) && n_fine < 32)
+        if (prof && p.dbg_fine == 1 && lane == 0 && d.tag == ((uint32_t)MG_PH_FC1 | (1u << 8) | ((uint32_t)p.dbg_step << 16)) && n_fine < 32)
           p.dbg[(size_t)blockIdx.x * MG_TRACE_SLOTS + 32 + n_fine++] = mg_globaltimer();     // issue time of this fc1 stage
         if (d.src != nullptr)
           mg_bulk_g2s(mg_smem_u32(cx.ring + (size_t)cx.stage * MG_STAGE_BYTES + d.dst_off), d.src, d.bytes, cx.full0 + 8u * cx.stage);
@@ -1122,7 +1149,8 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       if (done) break;
     }
     cx.trace = p.dbg != nullptr && step == p.dbg_step && !p.dbg_fine;
-    cx.fine = p.dbg != nullptr && step == p.dbg_step && p.dbg_fine;
+    cx.fine = p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 1;
+    const bool afine_step = p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 2;
     cx.trace_n = 0;
     MG_STAMP();                                                   // 0: step start
     const int pos = mg_ld_volatile(&st->pos), col = mg_ld_volatile(&st->col), Lbuf = mg_ld_volatile(&st->L);
@@ -1173,7 +1201,9 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       mg_grid_sync(p.bar_counter, bar_target);
       MG_STAMP();                                                 // +2: barrier
       // P2: attention
+      cx.afine = afine_step && l == 1;
       mg_attention<G>(p, cx, kv_layer, pos);
+      cx.afine = false;
       MG_STAMP();                                                 // +3: attention done
       mg_grid_sync(p.bar_counter, bar_target);
       MG_STAMP();                                                 // +4: barrier

@@ -126,6 +126,8 @@ struct zb_ctx {
   int opt_ring = 0;                    // cap on the ring depth of the persistent kernel (0 = as many stages as fit)
   int opt_psleep = 100;                // persistent kernel: producer back-off (ns) between polls of a full ring
   int opt_poll_all = 0;                // persistent kernel: all consumer threads poll the ring barriers (A/B switch)
+  int opt_att_single = 256;            // persistent kernel: contexts up to this many tokens are not split over CTAs
+  int opt_att_chunk = 96;             // persistent kernel: tokens per KV split at least (short contexts use fewer splits)
   int opt_trace = 0;                   // debug: print a per-phase timeline of one step of every persistent launch
   unsigned long long* dbg = nullptr;
 };
@@ -454,7 +456,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   int ns = c->n_sms / (R * g.num_heads_kv);
   ns = ns < 1 ? 1 : (ns > c->nsplit ? c->nsplit : ns);
   if (ns > MG_MAX_SPLIT) ns = MG_MAX_SPLIT;
-  p.nsplit = ns;
+  p.nsplit = ns; p.min_chunk = c->opt_att_chunk < 8 ? 8 : (c->opt_att_chunk + 7) & ~7; p.single_ctx = c->opt_att_single;
   p.R = R; p.B = B; p.st = c->st; p.rope_pos = c->rope_pos; p.delayed = c->delayed; p.tokens = c->tokens;
   p.remaining = c->remaining; p.stopping = c->stopping; p.out_len = c->out_len; p.bar_counter = c->bar_counter;
   p.mode = mode; p.n_steps = n_steps;
@@ -463,7 +465,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   int maxK = g.d_model > p.q_size ? g.d_model : p.q_size;
   if (g.ffn > maxK) maxK = g.ffn;
   size_t scratch = (size_t)R * (maxK + MG_XPAD) * 2;
-  const size_t att = ((size_t)MG_WARPS * G * ZB_DH + 2 * MG_WARPS * G + 32 * 8 * 2) * 4 + 16;
+  const size_t att = ((size_t)MG_MAX_SPLIT * G * ZB_DH + 2 * MG_WARPS * G + 32 * 8 * 2) * 4 + 16;
   if (att > scratch) scratch = att;
   if ((size_t)SMP_SMEM_BYTES > scratch) scratch = SMP_SMEM_BYTES;
   scratch = align_up(scratch, 128);
@@ -492,13 +494,13 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     const size_t nb = (size_t)c->n_sms * (MG_TRACE_SLOTS + 8) * sizeof(unsigned long long);
     if (!c->dbg && (e = cudaMalloc(&c->dbg, nb)) != cudaSuccess) return e;
     cudaMemsetAsync(c->dbg, 0, nb, s);
-    p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2;
+    p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2 ? 1 : (c->opt_trace == 3 ? 2 : 0);
     e = cudaLaunchKernelEx(&cfg, mega_kernel(G), p);
     if (e != cudaSuccess) return e;
     std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8));
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
     cudaMemcpy(hbuf.data(), c->dbg, nb, cudaMemcpyDeviceToHost);
-    const int ctas[3] = {0, c->n_sms / 2, c->n_sms - 1};
+    const int ctas[3] = {0, p.dbg_fine == 2 ? 5 : c->n_sms / 2, p.dbg_fine == 2 ? 41 : c->n_sms - 1};
     fprintf(stderr, "[mega trace] mode %d steps %d step %d: ns since step start (cta %d / %d / %d)\n", mode, n_steps, p.dbg_step, ctas[0], ctas[1], ctas[2]);
     for (int i = 0; i < MG_TRACE_SLOTS; ++i) {
       if (!hbuf[i] && !p.dbg_fine) break;
@@ -510,20 +512,24 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
       }
       fprintf(stderr, "\n");
     }
-    if (!p.dbg_fine) {
-      // skew: for every stamp, the earliest / median / latest CTA (all CTAs take the same stamps) and who was last
-      fprintf(stderr, "[mega skew] slot: min / median / max over %d CTAs (ns since CTA 0's step start), last CTA\n", c->n_sms);
-      std::vector<long long> v(c->n_sms);
+    if (p.dbg_fine != 1) {
+      // skew: for every stamp, the earliest / median / latest CTA among those that took it, and who was last
+      fprintf(stderr, "[mega skew] slot: CTAs / min / median / max (ns since CTA 0's first stamp), last CTA\n");
+      std::vector<long long> v;
       for (int i = 0; i < MG_TRACE_SLOTS; ++i) {
-        if (!hbuf[i]) break;
-        int last = 0;
+        v.clear();
+        int last = -1;
+        long long vmax = 0;
         for (int j = 0; j < c->n_sms; ++j) {
-          v[j] = (long long)(hbuf[(size_t)j * MG_TRACE_SLOTS + i] - hbuf[0]);
-          if (v[j] > v[last]) last = j;
+          const unsigned long long t = hbuf[(size_t)j * MG_TRACE_SLOTS + i];
+          if (!t) continue;
+          const long long d = (long long)(t - hbuf[0]);
+          if (last < 0 || d > vmax) { vmax = d; last = j; }
+          v.push_back(d);
         }
-        const long long vmax = v[last];
+        if (v.empty()) break;
         std::sort(v.begin(), v.end());
-        fprintf(stderr, "  skew %2d: %9lld %9lld %9lld  (spread %6lld) last cta %d\n", i, v[0], v[c->n_sms / 2], vmax, vmax - v[0], last);
+        fprintf(stderr, "  skew %2d: n=%3d %9lld %9lld %9lld  (spread %6lld) last cta %d\n", i, (int)v.size(), v[0], v[v.size() / 2], vmax, vmax - v[0], last);
       }
     }
     // whole-launch profile of the producer warp / consumer thread 0 (clock64 ticks)
@@ -1305,6 +1311,8 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "gemv") c->opt_gemv = value;
   else if (k == "mega") c->opt_mega = value;
   else if (k == "trace") c->opt_trace = value;
+  else if (k == "att_chunk") c->opt_att_chunk = value;
+  else if (k == "att_single") c->opt_att_single = value;
   else if (k == "ring") c->opt_ring = value;
   else if (k == "poll_all") c->opt_poll_all = value;
   else if (k == "psleep") c->opt_psleep = value;
