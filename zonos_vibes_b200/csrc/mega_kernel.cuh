@@ -78,6 +78,9 @@ struct MegaParams {
   long long* tokens;           // [B][n_q]
   int *remaining, *stopping, *out_len;
   unsigned* bar_counter;       // grid barrier (zero at launch)
+  unsigned long long* x_ll;    // [2][8][d/2] residual stream as (bf16 pair, epoch) 8-byte words: data that carries its own 'ready' flag
+  int use_ll;                  // 1: LayerNorm staging polls x_ll and the grid barriers after out_proj / fc2 are skipped
+  unsigned epoch_base;         // launch number << 20: epochs never repeat while an x_ll word can still be around
   int mode, n_steps;
   const bf16* hidden_in;       // MG_MODE_HIDDEN: x <- hidden_in[r, t0 + i, :], row stride hidden_S tokens
   bf16* hidden_out;            // optional: post-norm_f hidden states, same indexing
@@ -161,6 +164,12 @@ __device__ __forceinline__ void mg_grid_sync(unsigned* counter, unsigned& target
     } while (v < target);
   }
   SyncConsumers::sync();
+}
+
+// Epoch of the x_ll words written by out_proj (which = 0) / fc2 (which = 1) of layer l in step `step` of this launch.
+// Never 0 (the buffer is zero-filled at creation); the two phases write different halves of x_ll.
+__device__ __forceinline__ unsigned mg_ll_epoch(const MegaParams& p, int step, int l, int which) {
+  return p.epoch_base | (((unsigned)step & 0x1fffu) << 7) | (unsigned)(2 * l + which + 1);
 }
 
 // ---- per-CTA context ----------------------------------------------------------------------------------------------
@@ -416,7 +425,8 @@ __device__ __forceinline__ void mg_unpack8(const uint4& raw, float (&v)[8]) {
 // into xs.  The affine parameters arrive through the ring (stage rows 0 / 1).  K <= 2048 (one uint4 per thread per row).
 // Three CTA barriers instead of five: every thread sums the 8 warp partials itself (same warp order, so the statistics
 // are bit-identical to the two-stage reduction of the per-op path), and the rows are walked by runtime loops.
-__device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const bf16* src, int K, int R, float eps) {
+__device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const bf16* src, int K, int R, float eps,
+                                            const unsigned long long* ll = nullptr, unsigned ll_epoch = 0) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int e = tid * 8;
   const bool active = e < K;
@@ -424,7 +434,29 @@ __device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const b
   float* red2 = cx.part;            // [8 warps][8 rows] partial sums of squared deviations (the GEMV partial buffer is idle here)
   const float fk = (float)K;
   // pass 1: raw rows -> xs.  ALL rows are requested before the first one is used: one L2 round trip, not R.
-  {
+  if (ll != nullptr) {
+    // epoch-tagged source (x_ll): every 8-byte word is (bf16 pair, epoch).  Poll the words themselves until all of
+    // them carry this phase's epoch — this replaces "grid barrier, then load" (two dependent L2 round trips plus the
+    // barrier's own fence + atomic) by the load alone.  A thread only spins on its own 4 words per row.
+    for (int r0 = 0; r0 < R && active; r0 += 2) {          // two rows per round trip (R = 2 at batch 1: one round)
+      const bool two = r0 + 1 < R;
+      const unsigned long long* wp0 = ll + (size_t)r0 * (K >> 1) + (e >> 1);
+      const unsigned long long* wp1 = two ? wp0 + (K >> 1) : wp0;
+      unsigned long long w[8];
+      for (;;) {
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(wp0) : "memory");
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(wp0 + 2) : "memory");
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[4]), "=l"(w[5]) : "l"(wp1) : "memory");
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[6]), "=l"(w[7]) : "l"(wp1 + 2) : "memory");
+        bool ok = true;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ok = ok && (unsigned)(w[i] >> 32) == ll_epoch;
+        if (ok) break;
+      }
+      *reinterpret_cast<uint4*>(xs + (size_t)r0 * ld + e) = make_uint4((unsigned)w[0], (unsigned)w[1], (unsigned)w[2], (unsigned)w[3]);
+      if (two) *reinterpret_cast<uint4*>(xs + (size_t)(r0 + 1) * ld + e) = make_uint4((unsigned)w[4], (unsigned)w[5], (unsigned)w[6], (unsigned)w[7]);
+    }
+  } else {
     uint4 rawr[8];
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
@@ -513,6 +545,8 @@ struct MgEpi {
   int eos_bias;
   float* logits;
   int layer;
+  unsigned long long* ll;  // RESID: x_ll buffer of this phase
+  unsigned ll_epoch;
 };
 
 __device__ __forceinline__ void mg_epi_resid(const MgCtx& cx, const MgEpi& e, int a, int n0, float s0, float s1) {
@@ -520,6 +554,12 @@ __device__ __forceinline__ void mg_epi_resid(const MgCtx& cx, const MgEpi& e, in
   float* xo = cx.s_xown + a * MG_OWN + (n0 - e.own_lo);
   const __nv_bfloat162 o = __floats2bfloat162_rn(xo[0] + bf16_round(s0), xo[1] + bf16_round(s1));
   *reinterpret_cast<__nv_bfloat162*>(e.out + (size_t)a * e.out_stride + n0) = o;
+  {
+    // the same pair again, tagged with this phase's epoch, for the LayerNorm staging of the next phase: its readers
+    // poll the data itself instead of meeting at a grid barrier first (8-byte stores are single-copy atomic)
+    const unsigned long long w = ((unsigned long long)e.ll_epoch << 32) | (unsigned long long)(*reinterpret_cast<const unsigned*>(&o));
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(e.ll + (size_t)a * (e.out_stride >> 1) + (n0 >> 1)), "l"(w) : "memory");
+  }
   const float2 f = __bfloat1622float2(o);
   xo[0] = f.x; xo[1] = f.y;
 }
@@ -842,6 +882,7 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
       const int ts = it.t0 + si * MG_KV_TOK;
       const int n = min(MG_KV_TOK, tp - ts);
       const uint32_t sp = mg_cons_wait_addr(cx);
+      MG_ASTAMP();                                                  // per KV stage: data seen by warp 0
       const int tl = 16 * (warp & 3);                   // first token of this warp's group inside the stage
       if ((si & 1) == (warp >> 2) && tl < n) {          // warp-uniform
         AttFrag f;
@@ -1103,7 +1144,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
     // attention, grid barriers and sampling are the MMA warps' business).
     MgEpi epi;
     { int own_hi; mg_range(p.d / 2, epi.own_lo, own_hi); epi.own_lo *= 2; }
-    epi.logits = p.logits;
+    epi.logits = p.logits; epi.ll = p.x_ll; epi.ll_epoch = 0;
     for (int step = 0; step < p.n_steps; ++step) {
       mg_bar_sync(MG_BAR_STEP, MG_HANDOFF);
       const int pos = s_flags[3];
@@ -1115,10 +1156,12 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         epi.out = p.q; epi.out_stride = p.q_size;
         mg_gemv_epi(p, cx, qkv_rows / 2, EPI_QKV, epi);
         epi.out = p.x; epi.out_stride = p.d;
+        epi.ll = p.x_ll; epi.ll_epoch = mg_ll_epoch(p, step, l, 0);
         mg_gemv_epi(p, cx, p.d / 2, EPI_RESID, epi);
         epi.out = p.h; epi.out_stride = p.F;
         mg_gemv_epi(p, cx, p.F, EPI_SWIGLU, epi);
         epi.out = p.x; epi.out_stride = p.d;
+        epi.ll = p.x_ll + (size_t)8 * (p.d >> 1); epi.ll_epoch = mg_ll_epoch(p, step, l, 1);
         mg_gemv_epi(p, cx, p.d / 2, EPI_RESID, epi);
       }
       if (with_heads) {
@@ -1187,13 +1230,17 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
     }
 
     MgEpi epi;
-    epi.pos = pos; epi.own_lo = own_lo;
+    epi.pos = pos; epi.own_lo = own_lo; epi.ll = p.x_ll; epi.ll_epoch = 0;
+    const bool ll = p.use_ll != 0;
+    const unsigned long long* x_ll1 = p.x_ll + (size_t)8 * (p.d >> 1);      // fc2's half of x_ll
     epi.cfg_scale = 0.f; epi.eos_bias = 0; epi.logits = p.logits;
     for (int l = 0; l < p.n_layer; ++l) {
       epi.layer = l;
       bf16* kv_layer = p.kv + (size_t)l * p.kv_layer_elems;
-      // P1: LN1 + in_proj + RoPE + KV append
-      mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
+      // P1: LN1 + in_proj + RoPE + KV append.  From layer 1 on, x comes from the previous layer's fc2 epilogues through
+      // the epoch-tagged x_ll words: no grid barrier between fc2 and this LayerNorm.
+      if (ll && l > 0) mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps, x_ll1, mg_ll_epoch(p, step, l - 1, 1));
+      else mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
       MG_STAMP();                                                 // per layer +0: LN1 staged
       epi.out = p.q; epi.out_stride = p.q_size; epi.kv_layer = kv_layer;
       mg_gemv_phase(p, cx, xs, ld_d, p.d, qkv_rows / 2, 0, EPI_QKV, epi);
@@ -1212,10 +1259,11 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       epi.out = p.x; epi.out_stride = p.d;
       mg_gemv_phase(p, cx, xs, ld_q, p.q_size, p.d / 2, 0, EPI_RESID, epi);
       MG_STAMP();                                                 // +5: out_proj done
-      mg_grid_sync(p.bar_counter, bar_target);
+      if (!ll) mg_grid_sync(p.bar_counter, bar_target);
       MG_STAMP();                                                 // +6: barrier
       // P4: LN2 + fc1 + SwiGLU
-      mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
+      if (ll) mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps, p.x_ll, mg_ll_epoch(p, step, l, 0));
+      else mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
       MG_STAMP();                                                 // +7: LN2 staged
       epi.out = p.h; epi.out_stride = p.F;
       mg_gemv_phase(p, cx, xs, ld_d, p.d, p.F, p.F, EPI_SWIGLU, epi);
@@ -1228,13 +1276,14 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       epi.out = p.x; epi.out_stride = p.d;
       mg_gemv_phase(p, cx, xs, ld_f, p.F, p.d / 2, 0, EPI_RESID, epi);
       MG_STAMP();                                                 // +11: fc2 done
-      mg_grid_sync(p.bar_counter, bar_target);
+      if (!ll) mg_grid_sync(p.bar_counter, bar_target);
       MG_STAMP();                                                 // +12: barrier
     }
 
     if (with_heads) {
       // final LN + 9 heads + CFG + pad mask (+ logit bias)   (model.py:100-116,266-267,280)
-      mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
+      if (ll) mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps, x_ll1, mg_ll_epoch(p, step, p.n_layer - 1, 1));
+      else mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
       epi.cfg_scale = *reinterpret_cast<const volatile float*>(&st->cfg_scale);
       epi.eos_bias = mg_ld_volatile(&st->apply_eos_bias);
       mg_gemv_phase(p, cx, xs, ld_d, p.d, p.n_q * p.V / 2, 0, EPI_HEADS, epi);
@@ -1266,7 +1315,8 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
     } else if (final_ln) {
       // plugin-level forward: norm_f of the residual stream (backbone/_torch.py:80)
       const int r = blockIdx.x;
-      mg_stage_ln(cx, xs, ld_d, p.x + (size_t)r * p.d, p.d, 1, p.eps);
+      if (ll) mg_stage_ln(cx, xs, ld_d, p.x + (size_t)r * p.d, p.d, 1, p.eps, x_ll1 + (size_t)r * (p.d >> 1), mg_ll_epoch(p, step, p.n_layer - 1, 1));
+      else mg_stage_ln(cx, xs, ld_d, p.x + (size_t)r * p.d, p.d, 1, p.eps);
       bf16* dst = p.hidden_out + ((size_t)r * p.hidden_S + p.hidden_t0 + step) * p.d;
       for (int e = tid * 8; e < p.d; e += MG_CONSUMERS * 8) *reinterpret_cast<uint4*>(dst + e) = *reinterpret_cast<const uint4*>(xs + e);
     }

@@ -120,6 +120,9 @@ struct zb_ctx {
   long long mega_layer_stride = 0;
   bool mega_ok = false;
   unsigned* bar_counter = nullptr;
+  unsigned long long* x_ll = nullptr;  // persistent kernel: epoch-tagged residual stream [2][8][d/2]
+  unsigned launch_seq = 0;             // persistent-kernel launches so far (epoch base of x_ll)
+  int opt_ll = 1;                      // persistent kernel: poll x_ll instead of the grid barriers after out_proj / fc2
   int n_sms = ZB_NUM_SMS;
   int smem_optin = 0;
   int opt_mega = 1;
@@ -460,6 +463,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   p.R = R; p.B = B; p.st = c->st; p.rope_pos = c->rope_pos; p.delayed = c->delayed; p.tokens = c->tokens;
   p.remaining = c->remaining; p.stopping = c->stopping; p.out_len = c->out_len; p.bar_counter = c->bar_counter;
   p.mode = mode; p.n_steps = n_steps;
+  p.x_ll = c->x_ll; p.use_ll = c->opt_ll && n_steps < 8192 && R <= 4;     // R > 4: the polling loader needs > 2 round trips, the barrier is cheaper p.epoch_base = ((++c->launch_seq) & 0xfffu) << 20;
   p.hidden_in = (const bf16*)hidden_in; p.hidden_out = (bf16*)hidden_out; p.hidden_S = hidden_S; p.hidden_t0 = hidden_t0;
   // shared memory plan: [ring][scratch][partials 8 KB][red 256 B][barriers][flags]
   int maxK = g.d_model > p.q_size ? g.d_model : p.q_size;
@@ -890,6 +894,11 @@ static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int devic
       cudaFree(c->arena); delete c;
       return bad(ZB_ERR_NOMEM, std::string("barrier counter: ") + cudaGetErrorString(e));
     }
+    const size_t ll_bytes = (size_t)2 * 8 * (c->cfg.d_model / 2) * sizeof(unsigned long long);
+    if ((e = cudaMalloc(&c->x_ll, ll_bytes)) != cudaSuccess || (e = cudaMemset(c->x_ll, 0, ll_bytes)) != cudaSuccess) {
+      cudaFree(c->arena); delete c;
+      return bad(ZB_ERR_NOMEM, std::string("x_ll: ") + cudaGetErrorString(e));
+    }
   }
   if ((e = cudaFuncSetAttribute(k_bt_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM_BYTES)) != cudaSuccess) {
     cudaFree(c->arena); delete c;
@@ -918,6 +927,7 @@ int zb_ctx_destroy(zb_ctx* c) {
   if (c->arena) cudaFree(c->arena);
   if (c->st) cudaFree(c->st);
   if (c->bar_counter) cudaFree(c->bar_counter);
+  if (c->x_ll) cudaFree(c->x_ll);
   if (c->dbg) cudaFree(c->dbg);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
@@ -1312,6 +1322,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "mega") c->opt_mega = value;
   else if (k == "trace") c->opt_trace = value;
   else if (k == "att_chunk") c->opt_att_chunk = value;
+  else if (k == "ll") c->opt_ll = value;
   else if (k == "att_single") c->opt_att_single = value;
   else if (k == "ring") c->opt_ring = value;
   else if (k == "poll_all") c->opt_poll_all = value;
