@@ -463,7 +463,9 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   p.R = R; p.B = B; p.st = c->st; p.rope_pos = c->rope_pos; p.delayed = c->delayed; p.tokens = c->tokens;
   p.remaining = c->remaining; p.stopping = c->stopping; p.out_len = c->out_len; p.bar_counter = c->bar_counter;
   p.mode = mode; p.n_steps = n_steps;
-  p.x_ll = c->x_ll; p.use_ll = c->opt_ll && n_steps < 8192 && R <= 4;     // R > 4: the polling loader needs > 2 round trips, the barrier is cheaper p.epoch_base = ((++c->launch_seq) & 0xfffu) << 20;
+  p.x_ll = c->x_ll;
+  p.use_ll = c->opt_ll && n_steps < 8192 && R <= 4;     // R > 4: the polling loader needs > 2 round trips, the barrier is cheaper
+  p.epoch_base = ((++c->launch_seq) & 0xfffu) << 20;    // epochs of different launches never coincide
   p.hidden_in = (const bf16*)hidden_in; p.hidden_out = (bf16*)hidden_out; p.hidden_S = hidden_S; p.hidden_t0 = hidden_t0;
   // shared memory plan: [ring][scratch][partials 8 KB][red 256 B][barriers][flags]
   int maxK = g.d_model > p.q_size ? g.d_model : p.q_size;
