@@ -136,3 +136,25 @@ def test_hybrid_backbone_state_dict_keys():
     for k, v in own.items():
         assert tuple(v.shape) == tuple(sd[k].shape), k
     assert "layers.0.mixer.conv1d.weight" in own and "layers.2.mlp.fc1.weight" in own and "layers.0.mlp.fc1.weight" not in own
+
+
+def test_bench_reports_ncu_traffic_only_for_the_captured_configuration():
+    """bench.py's roofline.traffic comes from the committed ncu capture of the persistent kernel (batch 1); any other
+    configuration reports null rather than a number that was not measured for it."""
+    import argparse
+    import importlib
+    import json
+    import os
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    bench = importlib.import_module("bench")
+    t = bench.ncu_traffic_per_step(argparse.Namespace(batch=1, opt=[]))
+    with open(os.path.join(root, "profiles", "r01_traffic.json")) as f:
+        rec = json.load(f)
+    assert t == float(rec["dram_bytes_per_step"])
+    # traffic must be close to (and not below) the algorithmic bytes: every weight byte read once per step
+    assert 0.99 * rec["algorithmic_bytes_per_step_at_this_ctx"] <= t <= 1.05 * rec["algorithmic_bytes_per_step_at_this_ctx"]
+    assert bench.ncu_traffic_per_step(argparse.Namespace(batch=64, opt=[])) is None
+    assert bench.ncu_traffic_per_step(argparse.Namespace(batch=1, opt=["mega=0"])) is None

@@ -328,7 +328,7 @@ def test_batch_is_independent_batch1_runs(golden, cuda):
 class _options:
     def __init__(self, model, **kw):
         self.ctx, self.kw = model._native(), kw
-        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1)
+        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=1)
 
     def __enter__(self):
         for k, v in self.kw.items():
@@ -362,6 +362,26 @@ def test_teacher_forced_logits_full_size_other_paths(golden, cuda, path):
         got = m.compute_logits_teacher_forced(prefix, golden["full.delayed"], 6)
     for s in range(7):
         assert_logits_close(got[s], golden["full.logits"][s:s + 1], f"full {path} step {s}")
+
+
+@pytest.mark.parametrize("cname", ["tiny", "full"])
+def test_persistent_kernel_epoch_tagged_stream_equals_grid_barriers(golden, cuda, cname):
+    """The persistent kernel hands the residual stream from out_proj / fc2 to the next LayerNorm either through grid
+    barriers (ll=0) or as epoch-tagged words that the readers poll (ll=1, default).  Only the synchronisation differs:
+    the logits must be bit-identical, step after step, over several launches (the epoch changes with every launch)."""
+    m = make_model(cname, cuda)
+    cfg = CFGS[cname] if cname in CFGS else zo.FULL_CONFIG
+    if cname == "full":
+        prefix, delayed, n = zo.synth_prefix_conditioning(zo.FULL_CONFIG, 1, 24, 1), golden["full.delayed"], 6
+    else:
+        prefix, delayed, n = zo.synth_prefix_conditioning(cfg, 1, 6, 1), golden[f"gen.{cname}.greedy.delayed"], 40
+    with _options(m, ll=0):
+        want = m.compute_logits_teacher_forced(prefix, delayed, n).float().cpu()
+    for _ in range(2):
+        got = m.compute_logits_teacher_forced(prefix, delayed, n).float().cpu()
+        assert torch.equal(torch.isfinite(got), torch.isfinite(want))
+        fin = torch.isfinite(want)
+        assert torch.equal(got[fin], want[fin]), f"{cname}: epoch-tagged path differs from the grid-barrier path"
 
 
 @pytest.mark.parametrize("path", list(PATHS))
