@@ -1280,8 +1280,6 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       MG_STAMP();                                                 // +12: barrier
     }
 
-    if (p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 3) { cx.trace = true; cx.trace_n = 0; }     // tail-of-step trace
-    MG_STAMP();                                                   // tail 0: last layer done
     if (with_heads) {
       // final LN + 9 heads + CFG + pad mask (+ logit bias)   (model.py:100-116,266-267,280)
       if (ll) mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps, x_ll1, mg_ll_epoch(p, step, p.n_layer - 1, 1));
@@ -1289,9 +1287,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       epi.cfg_scale = *reinterpret_cast<const volatile float*>(&st->cfg_scale);
       epi.eos_bias = mg_ld_volatile(&st->apply_eos_bias);
       mg_gemv_phase(p, cx, xs, ld_d, p.d, p.n_q * p.V / 2, 0, EPI_HEADS, epi);
-      MG_STAMP();                                                 // tail 1: final LN + heads done
       mg_grid_sync(p.bar_counter, bar_target);
-      MG_STAMP();                                                 // tail 2: barrier
       if (p.mode == MG_MODE_DECODE) {
         if ((int)blockIdx.x < p.n_q * p.B) {
           SampleParams sp;
@@ -1314,9 +1310,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
             asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(rowp), "r"(p.d * 2) : "memory");
           }
         }
-        MG_STAMP();                                               // tail 3: sampled (CTAs < n_q * B)
         mg_grid_sync(p.bar_counter, bar_target);
-        MG_STAMP();                                               // tail 4: barrier
       }
     } else if (final_ln) {
       // plugin-level forward: norm_f of the residual stream (backbone/_torch.py:80)
@@ -1347,9 +1341,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
           for (int b = 0; b < p.B; ++b) mg_embed_row(p, b, col + 1, Lbuf);
       }
     }
-    MG_STAMP();                                                   // tail 5: state machine + next step's embedding (CTA 0)
     mg_grid_sync(p.bar_counter, bar_target);
-    MG_STAMP();                                                   // tail 6: end-of-step barrier
   }
 
   // ---- tell the producer where the consumers stopped

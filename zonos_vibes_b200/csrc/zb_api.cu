@@ -500,7 +500,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     const size_t nb = (size_t)c->n_sms * (MG_TRACE_SLOTS + 8) * sizeof(unsigned long long);
     if (!c->dbg && (e = cudaMalloc(&c->dbg, nb)) != cudaSuccess) return e;
     cudaMemsetAsync(c->dbg, 0, nb, s);
-    p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2 ? 1 : (c->opt_trace == 3 ? 2 : (c->opt_trace == 4 ? 3 : 0));
+    p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2 ? 1 : (c->opt_trace == 3 ? 2 : 0);
     e = cudaLaunchKernelEx(&cfg, mega_kernel(G), p);
     if (e != cudaSuccess) return e;
     std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8));
