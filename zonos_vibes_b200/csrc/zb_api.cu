@@ -426,12 +426,12 @@ cudaError_t enqueue_decode_step(zb_ctx* c, cudaStream_t s) {
 // persistent decode kernel
 // ---------------------------------------------------------------------------------------------------------------
 typedef void (*MegaKernel)(const MegaParams);
-MegaKernel mega_kernel(int G) {
+MegaKernel mega_kernel(int G, bool trace) {
   switch (G) {
-    case 1: return k_decode_mega<1>;
-    case 2: return k_decode_mega<2>;
-    case 4: return k_decode_mega<4>;
-    case 8: return k_decode_mega<8>;
+    case 1: return trace ? k_decode_mega<1, true> : k_decode_mega<1, false>;
+    case 2: return trace ? k_decode_mega<2, true> : k_decode_mega<2, false>;
+    case 4: return trace ? k_decode_mega<4, true> : k_decode_mega<4, false>;
+    case 8: return trace ? k_decode_mega<8, true> : k_decode_mega<8, false>;
   }
   return nullptr;
 }
@@ -501,7 +501,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     if (!c->dbg && (e = cudaMalloc(&c->dbg, nb)) != cudaSuccess) return e;
     cudaMemsetAsync(c->dbg, 0, nb, s);
     p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2 ? 1 : (c->opt_trace == 3 ? 2 : 0);
-    e = cudaLaunchKernelEx(&cfg, mega_kernel(G), p);
+    e = cudaLaunchKernelEx(&cfg, mega_kernel(G, true), p);
     if (e != cudaSuccess) return e;
     std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8));
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
@@ -546,7 +546,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     }
     return cudaSuccess;
   }
-  return cudaLaunchKernelEx(&cfg, mega_kernel(G), p);
+  return cudaLaunchKernelEx(&cfg, mega_kernel(G, false), p);
 }
 
 
@@ -875,7 +875,8 @@ static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int devic
   c->n_sms = prop.multiProcessorCount;
   c->smem_optin = max_smem;
   for (int G2 = 1; G2 <= 8; G2 *= 2)
-    if ((e = cudaFuncSetAttribute(mega_kernel(G2), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess) {
+    if ((e = cudaFuncSetAttribute(mega_kernel(G2, false), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(mega_kernel(G2, true), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess) {
       cudaFree(c->arena); delete c;
       return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute(mega): ") + cudaGetErrorString(e));
     }
