@@ -1,4 +1,4 @@
-# same-box A/B: lib_prev (committed) vs lib_new (trace code compiled out of the production kernel), then parity suite + a trace run on the new one
+# same-box A/B: lib_prev (committed) vs lib_new (packed MMA layout as a compile-time variant), then parity suite + a trace run on the new one
 mkdir -p gpurun_out
 L=zonos_vibes_b200/libzonos_b200.so
 for rep in 1 2; do

@@ -609,6 +609,9 @@ __device__ __forceinline__ void mg_epi_heads(const MegaParams& p, const MgEpi& e
 // consumers: one GEMV phase over this CTA's row range.  xs must be staged (and synced) before the call.  ONE copy of
 // this code serves all five weight matrices (runtime epilogue switch): code size matters more than a few branches.
 // =================================================================================================================
+// PK (compile time): packed-K MMA layout — at most 4 activation rows and every contraction length a multiple of 512 (the
+// host checks both); only ONE of the two MMA loop variants exists in a given instantiation (code size: see k_decode_mega).
+template <bool PK>
 __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, const bf16* xs, int ld, int K, int n_units, int gate_off,
                                            int kind, const MgEpi& epi) {
   const int NT = kind == EPI_SWIGLU ? 2 : 1;
@@ -622,11 +625,9 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
   const uint32_t xs_addr = mg_smem_u32(xs);
   const bool pf1 = cx.prof && kind == EPI_SWIGLU && threadIdx.x == 0;
   const long long pt0 = pf1 ? clock64() : 0, pfull0 = cx.t_full;
-  const bool packed = R <= 4;
   int ti = 0;                                    // tile counter of this phase (partial buffer = ti & 1)
   for (int n0 = lo; n0 < hi; n0 += 8) {
     const int cnt = min(8, hi - n0);
-    bool used_packed = false;                      // warp-uniform, the same for every chunk of a tile (K % 2048 chunks)
     // FOUR independent accumulator sets per tile: HMMA results chain through the accumulator, and one chain of 16
     // dependent HMMAs per stage left the tensor pipe idle most of the time (r01 trace: the consumers, not the HBM
     // stream, were the bottleneck).  The sets are summed once per tile.
@@ -643,7 +644,7 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
           const uint32_t st_addr = mg_cons_wait_addr(cx);
           const bool fstamp = cx.fine && kind == EPI_SWIGLU && epi.layer == 1 && threadIdx.x == 0 && cx.trace_n < 32;
           if (fstamp) cx.trace_out[cx.trace_n++] = mg_globaltimer();        // stage data seen by warp 0
-          if (packed && (kcs & 511) == 0) {
+          if (PK) {
             // R <= 4: the WEIGHTS are the MMA's A operand.  A rows 0..7 = the 8 weight rows over the first half of the
             // chunk's columns, A rows 8..15 = the same weight rows over the second half; B columns 0..3 = the
             // activation rows over the first half, columns 4..7 = over the second half.  D[i<8][n<4] and
@@ -676,7 +677,6 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
               mma_bf16_16816_full(acc[nt][0], w0.x, w1.x, w0.y, w1.y, x0.x, x0.y);
               mma_bf16_16816_full(acc[nt][1], w0.z, w1.z, w0.w, w1.w, x0.z, x0.w);
             }
-            used_packed = true;
           } else {
             const int slice = kcs >> 3;                  // this warp's columns of the chunk (multiple of 32)
             const int nkb = slice >> 5;
@@ -723,7 +723,7 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
 #pragma unroll
         for (int i = 0; i < 4; ++i) s4[i] = (acc[nt][0][i] + acc[nt][1][i]) + (acc[nt][2][i] + acc[nt][3][i]);
         float* pw = pb + (nt * MG_WARPS + warp) * 64;          // [8 activation rows][8 weight rows]
-        if (used_packed) {
+        if (PK) {
           // lane (g, t<2): D[g][2t, 2t+1] (first K half) + lane (g, t+2): D[g+8][2t+4, 2t+5] (second K half)
           const float v0 = s4[0] + __shfl_xor_sync(0xffffffffu, s4[2], 2);
           const float v1 = s4[1] + __shfl_xor_sync(0xffffffffu, s4[3], 2);
@@ -1050,7 +1050,7 @@ __device__ __noinline__ void mg_update(const UpdateParams& up, int* s_alive) { u
 // =================================================================================================================
 // TR = false (production): every trace / profile stamp is compiled out.  A build with seven more stamps in the step tail
 // benched 3.7 % slower: instrumentation in this kernel is not free even when it is switched off at run time.
-template <int G, bool TR>
+template <int G, bool TR, bool PK>
 __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_constant__ MegaParams p) {
   extern __shared__ __align__(128) unsigned char mg_smem[];
   MgCtx cx;
@@ -1245,7 +1245,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       else mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
       MG_STAMP();                                                 // per layer +0: LN1 staged
       epi.out = p.q; epi.out_stride = p.q_size; epi.kv_layer = kv_layer;
-      mg_gemv_phase(p, cx, xs, ld_d, p.d, qkv_rows / 2, 0, EPI_QKV, epi);
+      mg_gemv_phase<PK>(p, cx, xs, ld_d, p.d, qkv_rows / 2, 0, EPI_QKV, epi);
       MG_STAMP();                                                 // +1: in_proj done
       mg_grid_sync(p.bar_counter, bar_target);
       MG_STAMP();                                                 // +2: barrier
@@ -1259,7 +1259,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       // P3: out_proj + residual
       mg_stage_copy(xs, ld_q, p.y, p.q_size, p.R);
       epi.out = p.x; epi.out_stride = p.d;
-      mg_gemv_phase(p, cx, xs, ld_q, p.q_size, p.d / 2, 0, EPI_RESID, epi);
+      mg_gemv_phase<PK>(p, cx, xs, ld_q, p.q_size, p.d / 2, 0, EPI_RESID, epi);
       MG_STAMP();                                                 // +5: out_proj done
       if (!ll) mg_grid_sync(p.bar_counter, bar_target);
       MG_STAMP();                                                 // +6: barrier
@@ -1268,7 +1268,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       else mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
       MG_STAMP();                                                 // +7: LN2 staged
       epi.out = p.h; epi.out_stride = p.F;
-      mg_gemv_phase(p, cx, xs, ld_d, p.d, p.F, p.F, EPI_SWIGLU, epi);
+      mg_gemv_phase<PK>(p, cx, xs, ld_d, p.d, p.F, p.F, EPI_SWIGLU, epi);
       MG_STAMP();                                                 // +8: fc1 done
       mg_grid_sync(p.bar_counter, bar_target);
       MG_STAMP();                                                 // +9: barrier
@@ -1276,7 +1276,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       mg_stage_copy(xs, ld_f, p.h, p.F, p.R);
       MG_STAMP();                                                 // +10: h staged
       epi.out = p.x; epi.out_stride = p.d;
-      mg_gemv_phase(p, cx, xs, ld_f, p.F, p.d / 2, 0, EPI_RESID, epi);
+      mg_gemv_phase<PK>(p, cx, xs, ld_f, p.F, p.d / 2, 0, EPI_RESID, epi);
       MG_STAMP();                                                 // +11: fc2 done
       if (!ll) mg_grid_sync(p.bar_counter, bar_target);
       MG_STAMP();                                                 // +12: barrier
@@ -1288,7 +1288,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       else mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
       epi.cfg_scale = *reinterpret_cast<const volatile float*>(&st->cfg_scale);
       epi.eos_bias = mg_ld_volatile(&st->apply_eos_bias);
-      mg_gemv_phase(p, cx, xs, ld_d, p.d, p.n_q * p.V / 2, 0, EPI_HEADS, epi);
+      mg_gemv_phase<PK>(p, cx, xs, ld_d, p.d, p.n_q * p.V / 2, 0, EPI_HEADS, epi);
       mg_grid_sync(p.bar_counter, bar_target);
       if (p.mode == MG_MODE_DECODE) {
         if ((int)blockIdx.x < p.n_q * p.B) {

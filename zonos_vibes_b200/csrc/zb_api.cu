@@ -426,14 +426,23 @@ cudaError_t enqueue_decode_step(zb_ctx* c, cudaStream_t s) {
 // persistent decode kernel
 // ---------------------------------------------------------------------------------------------------------------
 typedef void (*MegaKernel)(const MegaParams);
-MegaKernel mega_kernel(int G, bool trace) {
+template <int G>
+MegaKernel mega_kernel_g(bool trace, bool packed) {
+  if (trace) return packed ? k_decode_mega<G, true, true> : k_decode_mega<G, true, false>;
+  return packed ? k_decode_mega<G, false, true> : k_decode_mega<G, false, false>;
+}
+MegaKernel mega_kernel(int G, bool trace, bool packed) {
   switch (G) {
-    case 1: return trace ? k_decode_mega<1, true> : k_decode_mega<1, false>;
-    case 2: return trace ? k_decode_mega<2, true> : k_decode_mega<2, false>;
-    case 4: return trace ? k_decode_mega<4, true> : k_decode_mega<4, false>;
-    case 8: return trace ? k_decode_mega<8, true> : k_decode_mega<8, false>;
+    case 1: return mega_kernel_g<1>(trace, packed);
+    case 2: return mega_kernel_g<2>(trace, packed);
+    case 4: return mega_kernel_g<4>(trace, packed);
+    case 8: return mega_kernel_g<8>(trace, packed);
   }
   return nullptr;
+}
+// packed-K MMA layout of the persistent kernel's GEMV phases: <= 4 activation rows, every contraction length % 512 == 0
+bool mega_packed(const zb_config& g, int R) {
+  return R <= 4 && g.d_model % 512 == 0 && (g.num_heads * ZB_DH) % 512 == 0 && g.ffn % 512 == 0;
 }
 
 bool use_mega(const zb_ctx* c, int rows) {
@@ -501,7 +510,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     if (!c->dbg && (e = cudaMalloc(&c->dbg, nb)) != cudaSuccess) return e;
     cudaMemsetAsync(c->dbg, 0, nb, s);
     p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2 ? 1 : (c->opt_trace == 3 ? 2 : 0);
-    e = cudaLaunchKernelEx(&cfg, mega_kernel(G, true), p);
+    e = cudaLaunchKernelEx(&cfg, mega_kernel(G, true, mega_packed(g, R)), p);
     if (e != cudaSuccess) return e;
     std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8));
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
@@ -546,7 +555,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     }
     return cudaSuccess;
   }
-  return cudaLaunchKernelEx(&cfg, mega_kernel(G, false), p);
+  return cudaLaunchKernelEx(&cfg, mega_kernel(G, false, mega_packed(g, R)), p);
 }
 
 
@@ -875,8 +884,10 @@ static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int devic
   c->n_sms = prop.multiProcessorCount;
   c->smem_optin = max_smem;
   for (int G2 = 1; G2 <= 8; G2 *= 2)
-    if ((e = cudaFuncSetAttribute(mega_kernel(G2, false), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(mega_kernel(G2, true), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess) {
+    if ((e = cudaFuncSetAttribute(mega_kernel(G2, false, false), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(mega_kernel(G2, false, true), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(mega_kernel(G2, true, false), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(mega_kernel(G2, true, true), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess) {
       cudaFree(c->arena); delete c;
       return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute(mega): ") + cudaGetErrorString(e));
     }
