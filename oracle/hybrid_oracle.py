@@ -53,13 +53,18 @@ class HybridConfig:
     ngroups: int = 1
     norm_epsilon: float = 1e-5
     rms_norm: bool = False
+    # attn_cfg keys forwarded to mamba-ssm's MHA by create_block (_mamba_ssm.py:15-33); MHA's own default is
+    # rotary_emb_interleaved=False (GPT-NeoX half-split pairs (i, i + rotary_dim/2), flash_attn/layers/rotary.py:14-35)
+    rotary_emb_dim: int = 128
+    rotary_emb_interleaved: bool = False
 
     def to_reference_dict(self) -> dict:
         """The dict ZonosConfig.from_dict (zonos/config.py:56-62) expects for this architecture."""
         return dict(backbone=dict(d_model=self.d_model, d_intermediate=self.d_intermediate, attn_mlp_d_intermediate=self.attn_mlp_d_intermediate,
                                   n_layer=self.n_layer, ssm_cfg=dict(layer="Mamba2", d_state=self.d_state, d_conv=self.d_conv, expand=self.expand,
                                                                      headdim=self.headdim, ngroups=self.ngroups),
-                                  attn_layer_idx=list(self.attn_layer_idx), attn_cfg=dict(num_heads=self.num_heads, num_heads_kv=self.num_heads_kv),
+                                  attn_layer_idx=list(self.attn_layer_idx), attn_cfg=dict(num_heads=self.num_heads, num_heads_kv=self.num_heads_kv, rotary_emb_dim=self.rotary_emb_dim,
+                                                rotary_emb_interleaved=self.rotary_emb_interleaved),
                                   rms_norm=self.rms_norm, residual_in_fp32=False, norm_epsilon=self.norm_epsilon),
                     prefix_conditioner=dict(conditioners=[], projection="none"), eos_token_id=1024, masked_token_id=1025)
 
@@ -206,7 +211,7 @@ class HybridOracleBackbone:
         self.pos = 0
 
     def _attn(self, i: int, h: torch.Tensor) -> torch.Tensor:
-        """_torch.py:117-141 semantics for one token (interleaved RoPE over the full head dim, GQA)."""
+        """MHA semantics for one token: RoPE over the full head dim (interleaved or half-split pairs per attn_cfg), GQA."""
         c, sd = self.cfg, self.sd
         B = h.shape[0]
         H, Hkv = c.num_heads, c.num_heads_kv
@@ -218,9 +223,15 @@ class HybridOracleBackbone:
         cos, sin = torch.cos(ang), torch.sin(ang)
 
         def rope(x):
-            xf = x.float().reshape(*x.shape[:-1], 64, 2)
-            out = torch.stack([xf[..., 0] * cos - xf[..., 1] * sin, xf[..., 1] * cos + xf[..., 0] * sin], -1)
-            return out.flatten(-2).to(x.dtype)
+            if c.rotary_emb_dim == 0:
+                return x
+            assert c.rotary_emb_dim == 128, "rotary over the full head dim (or none)"
+            if c.rotary_emb_interleaved:              # pairs (2i, 2i+1), like _torch.py:18-30
+                xf = x.float().reshape(*x.shape[:-1], 64, 2)
+                out = torch.stack([xf[..., 0] * cos - xf[..., 1] * sin, xf[..., 1] * cos + xf[..., 0] * sin], -1)
+                return out.flatten(-2).to(x.dtype)
+            x1, x2 = x.float()[..., :64], x.float()[..., 64:]          # pairs (i, i + 64): rotate_half form
+            return torch.cat([x1 * cos - x2 * sin, x2 * cos + x1 * sin], -1).to(x.dtype)
 
         q, k = rope(q), rope(k)
         st = self.state[i]

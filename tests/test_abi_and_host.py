@@ -158,3 +158,24 @@ def test_bench_reports_ncu_traffic_only_for_the_captured_configuration():
     assert 0.99 * rec["algorithmic_bytes_per_step_at_this_ctx"] <= t <= 1.05 * rec["algorithmic_bytes_per_step_at_this_ctx"]
     assert bench.ncu_traffic_per_step(argparse.Namespace(batch=64, opt=[])) is None
     assert bench.ncu_traffic_per_step(argparse.Namespace(batch=1, opt=["mega=0"])) is None
+
+
+def test_from_state_dict_accepts_padded_heads():
+    """a state_dict taken from a LOADED reference model has 1026-row heads (post-load pad hook,
+    model.py:46-51); from_state_dict must accept it (device 'cpu' only builds the holder: no native call here)."""
+    import torch.nn.functional as F
+    import zonos_oracle as zo
+    import zonos_vibes_b200 as z
+    cfg = zo.TINY_CONFIG
+    sd = zo.synth_state_dict(cfg, 0)
+    padded = {k: (F.pad(v, (0, 0, 0, 1)) if k.startswith("heads.") else v) for k, v in sd.items()}
+    assert padded["heads.0.weight"].shape[0] == 1026
+    m = z.Zonos.from_state_dict(z.ZonosConfig.from_dict(cfg.to_reference_dict()), padded, "cpu")
+    assert m.heads[0].weight.shape[0] == 1025
+    assert torch.equal(m.heads[3].weight.detach(), sd["heads.3.weight"])
+
+
+def test_hybrid_rejects_fp32_residual_and_reads_rotary_cfg():
+    import hybrid_oracle as ho
+    d = ho.HYBRID_TINY.to_reference_dict()
+    assert d["backbone"]["attn_cfg"]["rotary_emb_interleaved"] is False and d["backbone"]["attn_cfg"]["rotary_emb_dim"] == 128

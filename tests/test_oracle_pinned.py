@@ -139,3 +139,45 @@ def test_mamba2_mixer_matches_hf_port():
         got = ho.mamba2_mixer_sequence(cfg, p, ho.mamba2_alloc_state(cfg, 2), u)
     assert got.shape == want.shape
     assert (got - want).abs().max().item() < 1e-4 * want.abs().max().item()
+
+
+# ---- round 2: long-context / audio-prefix / long-DAC fixtures (oracle/make_golden_long.py, frozen from the imported reference)
+@pytest.fixture(scope="module")
+def golden_long():
+    import os
+    return torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_long.pt"))
+
+
+@pytest.mark.parametrize("p", [5, 300])
+def test_generate_with_audio_prefix_golden(golden_long, p):
+    """model.py:246-264: the oracle's audio-prefix path against the reference's generate(audio_prefix_codes=...)."""
+    cfg = zo.SMALL_CONFIG
+    o = zo.OracleZonos(cfg, zo.synth_state_dict(cfg, 0))
+    prefix = zo.synth_prefix_conditioning(cfg, 1, 6, 1)
+    tr = {}
+    out = o.generate(prefix, audio_prefix_codes=golden_long[f"prefix.p{p}.audio_prefix_codes"], max_new_tokens=24,
+                     sampling_params=dict(temperature=0), trace=tr)
+    assert torch.equal(out, golden_long[f"prefix.p{p}.codes"])
+    assert torch.equal(tr["delayed"], golden_long[f"prefix.p{p}.delayed"])
+    assert torch.equal(torch.cat(tr["logits"], 0), golden_long[f"prefix.p{p}.logits"])
+
+
+def test_dac_long_windows_golden(golden_long):
+    """T = 2580 fixture: the oracle decodes each 32-frame window with a 16-frame halo (window decode equals the
+    full decode in the interior) and must reproduce the reference waveform there."""
+    dsd = do.synth_dac_state_dict(2)
+    codes = golden_long["dac.long.codes"]
+    T = codes.shape[-1]
+    for f, want in list(zip(golden_long["dac.long.window_frames"].tolist(), golden_long["dac.long.windows"]))[:3]:
+        lo, hi = max(0, f - 16), min(T, f + 32 + 16)
+        wav = do.dac_decode(dsd, codes[..., lo:hi])
+        got = wav[0, 0, 512 * (f - lo): 512 * (f - lo + 32)]
+        assert (got - want).abs().max().item() <= 1e-4, f
+
+
+def test_long_fixture_shapes(golden_long):
+    for p in (1290, 2560):
+        assert golden_long[f"long.p{p}.logits"].shape == (9, 9, 1026)
+        assert golden_long[f"long.p{p}.delayed"].shape == (1, 9, p + 12 + 9)
+        assert bool(torch.isfinite(golden_long[f"long.p{p}.logits"][..., :1024]).all())
+    assert golden_long["full.truth_logits"].shape == (7, 9, 1026)

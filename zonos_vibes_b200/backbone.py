@@ -51,6 +51,9 @@ class NativeContext:
             m = mamba2_dims(cfg)
             if cfg.rms_norm:
                 raise _lib.ZbError("the hybrid path implements LayerNorm blocks (rms_norm=False)")
+            if cfg.residual_in_fp32:
+                raise _lib.ZbError("the hybrid path keeps a bf16 residual stream (residual_in_fp32=False); "
+                                   "mamba-ssm's fp32 residual is not implemented")
             if len(cfg.attn_layer_idx) > 64:
                 raise _lib.ZbError("at most 64 attention layers")
             zh = _lib.ZbHybrid()
@@ -64,7 +67,20 @@ class NativeContext:
         self.rows = 0
         self.finalized = False
         head_dim = cfg.d_model // zc.num_heads
-        self.set_tensor("rope.freqs_cis", precompute_freqs_cis(ROPE_TABLE_LEN, head_dim).to(self.device))
+        table = precompute_freqs_cis(ROPE_TABLE_LEN, head_dim)
+        # Hybrid attention layers are mamba-ssm's MHA, which takes its rotary settings from attn_cfg
+        # (_mamba_ssm.py:15-33): rotary_emb_dim (0 = no rotary) and rotary_emb_interleaved (default False = half-split
+        # pairs (i, i + Dh/2)).  The torch backbone ignores both keys (_torch.py:18-30: interleaved, full head dim).
+        self.rope_half_split = False
+        if cfg.ssm_cfg:
+            rd = int(cfg.attn_cfg.get("rotary_emb_dim", head_dim))
+            if rd == 0:
+                table = torch.stack([torch.ones_like(table[..., 0]), torch.zeros_like(table[..., 1])], dim=-1).contiguous()
+            elif rd != head_dim:
+                raise _lib.ZbError(f"hybrid: rotary_emb_dim {rd} must be 0 or the head dim ({head_dim})")
+            self.rope_half_split = rd != 0 and not bool(cfg.attn_cfg.get("rotary_emb_interleaved", False))
+        self.head_dim = head_dim
+        self.set_tensor("rope.freqs_cis", table.to(self.device))
 
     def __del__(self):
         try:
@@ -83,8 +99,21 @@ class NativeContext:
 
     F32_SUFFIXES = ("rope.freqs_cis", ".mixer.dt_bias", ".mixer.A_log", ".mixer.D")
 
+    def _half_split_to_interleaved(self, w: torch.Tensor) -> torch.Tensor:
+        """Half-split RoPE pairs rows (i, i + Dh/2) of every q / k head; the kernels rotate adjacent rows (2i, 2i+1).
+        Permuting the q and k rows of in_proj identically (new 2i <- old i, new 2i+1 <- old i + Dh/2) makes the two the
+        same rotation, and q.k is invariant under a permutation applied to both.  V rows are untouched."""
+        dh = self.head_dim
+        n_qk = (self.zc.num_heads + self.zc.num_heads_kv) * dh
+        perm = torch.stack([torch.arange(dh // 2), torch.arange(dh // 2) + dh // 2], dim=1).flatten()
+        idx = (torch.arange(n_qk // dh)[:, None] * dh + perm[None, :]).flatten()
+        idx = torch.cat([idx, torch.arange(n_qk, w.shape[0])]).to(w.device)
+        return w[idx]
+
     def set_tensor(self, name: str, t: torch.Tensor) -> None:
         want = torch.float32 if name.endswith(self.F32_SUFFIXES) else torch.bfloat16
+        if self.rope_half_split and name.endswith(".mixer.in_proj.weight") and t.shape[0] == (self.zc.num_heads + 2 * self.zc.num_heads_kv) * self.head_dim:
+            t = self._half_split_to_interleaved(t.detach())
         t = t.detach().to(self.device, want).contiguous()
         with torch.cuda.device(self.device):
             self.check(self.lib.zb_set_tensor(self.handle, name.encode(), t.data_ptr(), t.numel(),

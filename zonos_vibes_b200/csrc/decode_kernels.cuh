@@ -396,7 +396,7 @@ __global__ void k_final_ln(const bf16* __restrict__ x, const bf16* __restrict__ 
 __global__ void k_set_pos(ZbDevState* st, int* rope_pos, int R, int pos, const int* lengths, int add) {
   pdl_launch_dependents();
   pdl_wait_prior_grid();
-  if (threadIdx.x == 0) st->pos = pos;
+  if (threadIdx.x == 0) { st->pos = pos; st->done = 0; }    // a plugin-level forward after a finished generate must not be skipped
   for (int r = threadIdx.x; r < R; r += blockDim.x) rope_pos[r] = lengths ? lengths[r] + add : pos;
 }
 __global__ void k_advance(ZbDevState* st, int* rope_pos, int R) {

@@ -1323,6 +1323,10 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       for (int e = tid * 8; e < p.d; e += MG_CONSUMERS * 8) *reinterpret_cast<uint4*>(dst + e) = *reinterpret_cast<const uint4*>(xs + e);
     }
 
+    // Without a heads phase nothing has waited for the other CTAs' fc2 epilogues yet when the barrier after fc2 is
+    // replaced by the epoch-tagged words (ll): CTA 0's embed-ahead below would overwrite p.x while they are still storing
+    // their columns of this step into it (MG_MODE_FORCED, the audio-prefix columns of zb_gen_begin).
+    if (ll && !with_heads && embed_ahead) mg_grid_sync(p.bar_counter, bar_target);
     // ---- advance the device state (CTA 0), then make it visible to everyone
     if (blockIdx.x == 0) {
       if (p.mode == MG_MODE_DECODE) {

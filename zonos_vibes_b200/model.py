@@ -61,6 +61,12 @@ class Zonos(nn.Module):
         model = cls(config, autoencoder=dac, prefix_conditioner=prefix_conditioner).to(device, torch.bfloat16)
         own = model.state_dict()
         sd = {k: v for k, v in state_dict.items() if k in own}
+        for k in range(N_CODEBOOKS):
+            # a state_dict taken from a LOADED reference model has 1026-row heads (post-load pad hook, model.py:46-51 /
+            # utils.py:12-27: one zero row appended); the holder keeps the 1025 real rows and the library re-pads
+            w = sd.get(f"heads.{k}.weight")
+            if w is not None and w.shape[0] == VOCAB:
+                sd[f"heads.{k}.weight"] = w[: VOCAB - 1]
         missing = [k for k in own if k not in sd and not k.startswith("prefix_conditioner.")]
         if missing:
             raise KeyError(f"state_dict lacks {missing[:4]}{'...' if len(missing) > 4 else ''}")
@@ -127,10 +133,12 @@ class Zonos(nn.Module):
 
     @torch.inference_mode()
     def compute_logits_teacher_forced(self, prefix_conditioning: torch.Tensor, delayed_codes: torch.Tensor, n_steps: int,
-                                      cfg_scale: float = 2.0) -> torch.Tensor:
+                                      cfg_scale: float = 2.0, skip: int = 0) -> torch.Tensor:
         """Parity helper: logits of the prefill and of `n_steps` decode steps when the model is fed the given,
         fully known delayed codes [B, 9, L] (= what `_prefill` / `_decode_one_token` + logit_bias return in
-        model.py:253-280).  Returns fp32 [1 + n_steps, B, 9, 1026]."""
+        model.py:253-280).  Returns fp32 [1 + n_steps, B, 9, 1026].  `skip` = number of leading audio-prefix columns
+        that are part of the prefill (model.py:253-255 with audio_prefix_codes of `skip` frames): they are fed through
+        the same decode path, their logits are dropped, and entry 0 of the result is the logits of column `skip`."""
         ctx = self._native()
         b = delayed_codes.shape[0]
         delayed = delayed_codes.to(ctx.device, torch.int64).contiguous()
@@ -138,11 +146,13 @@ class Zonos(nn.Module):
         lc = prefix.shape[1]
         self.setup_cache(2 * b, lc + delayed.shape[2] + 9)
         out = torch.empty((1 + n_steps, b, N_CODEBOOKS, VOCAB), dtype=torch.float32, device=ctx.device)
+        scratch = torch.empty((b, N_CODEBOOKS, VOCAB), dtype=torch.float32, device=ctx.device)
         with torch.cuda.device(ctx.device):
             ctx.check(ctx.lib.zb_backbone_forward(ctx.handle, prefix.data_ptr(), None, 2 * b, lc, 0, None, ctx.stream))
-            for s in range(1 + n_steps):
+            for s in range(skip + 1 + n_steps):
+                dst = out[s - skip] if s >= skip else scratch
                 ctx.check(ctx.lib.zb_decode_logits(ctx.handle, delayed.data_ptr(), b, delayed.shape[2], s, float(cfg_scale),
-                                                   1 if s > 0 else 0, out[s].data_ptr(), ctx.stream))
+                                                   1 if s > skip else 0, dst.data_ptr(), ctx.stream))
         return out
 
     @torch.inference_mode()
