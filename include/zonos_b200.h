@@ -159,6 +159,19 @@ int  zb_dac_finalize(zb_dac* dac, void* stream);
 /* d_codes int64 [B, 9, T] in [0,1023]; d_wav fp32 [B, 1, 512*T].  impl: 0 = tcgen05 fp16 (default),
  * 1 = SIMT fp32 cross-check, 2 / 3 = force the one-tile-per-CTA / the persistent tcgen05 kernel for every layer. */
 int  zb_dac_decode(zb_dac* dac, const int64_t* d_codes, float* d_wav, int B, int T, int impl, void* stream);
+/* Allocation-free variant of zb_dac_decode (tcgen05 path).  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  The activation scratch that zb_dac_decode keeps in a grow-on-demand cudaMalloc'd
+ * workspace lives in a file-scope `static __device__` array sized for ZB_DAC_STATIC_MAX_FRAMES frames per utterance
+ * (5 x 49152 x 48 fp16 = 23.6 MB, held by every GPU that loads the library until the process exits).  T above the
+ * maximum is rejected with ZB_ERR_ARG and a message naming the limit; B is unlimited (utterances are decoded one after
+ * the other).  The call makes no cudaMalloc / cudaFree / allocating library call; the first call per device resolves the
+ * array's device address (cudaGetSymbolAddress) - call once with B = 0 outside any capture to do that up front.
+ * All calls share the one array, which keeps the last call's contents: nothing in it has to start at zero (each
+ * layer fully writes what the next reads), but two calls that overlap on the GPU (different streams, or different
+ * zb_dac contexts on the same device) RACE on it - serialise them.  Same inputs / outputs as zb_dac_decode. */
+#define ZB_DAC_STATIC_MAX_FRAMES 48
+int  zb_dac_decode_static(zb_dac* dac, const int64_t* d_codes, float* d_wav, int B, int T, void* stream);
 /* debug/parity: copy an intermediate of the last decode ("latent", "conv1", "block0".."block3") as fp32
  * [B, C, T_l] (reference layout) into d_out; returns ZB_ERR_ARG if the name is unknown. */
 int  zb_dac_get_intermediate(zb_dac* dac, const char* name, float* d_out, int64_t numel, void* stream);

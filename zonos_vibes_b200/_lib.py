@@ -65,6 +65,7 @@ SIGNATURES = {
     "zb_dac_set_tensor": (_I, [_P, C.c_char_p, _P, _I64, _P]),
     "zb_dac_finalize": (_I, [_P, _P]),
     "zb_dac_decode": (_I, [_P, _P, _P, _I, _I, _I, _P]),
+    "zb_dac_decode_static": (_I, [_P, _P, _P, _I, _I, _P]),
     "zb_dac_get_intermediate": (_I, [_P, C.c_char_p, _P, _I64, _P]),
     "zb_dac_set_option": (_I, [_P, C.c_char_p, _I]),
     "zb_dac_launch_count": (_I64, [_P]),

@@ -269,7 +269,9 @@ int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half*
   return ZB_OK;
 }
 
-int decode_one_tc(zb_dac* d, const long long* codes, float* wav, int T, cudaStream_t s, int impl) {
+// `bufs` = the five fp16 activation buffers of 49152 * T halves each (the context workspace, or the static array of
+// zb_dac_decode_static); keep_dbg = copy intermediates for zb_dac_get_intermediate (allocates: context workspace only).
+int decode_one_tc(zb_dac* d, const long long* codes, float* wav, int T, cudaStream_t s, int impl, __half* const* bufs, bool keep_dbg) {
   auto conv_tc = [&](zb_dac* dd, const ConvW& c, const __half* x, int T_in, const __half* residual, __half* out_raw, __half* out_act,
                      const float* alpha_next, cudaStream_t st) {
     // impl 0: per layer — the wide layers (Cout >= 768) run best on the N=256 one-tile-per-CTA kernel (two CTAs per SM),
@@ -278,8 +280,8 @@ int decode_one_tc(zb_dac* d, const long long* codes, float* wav, int T, cudaStre
     return v1 ? ::conv_tc(dd, c, x, T_in, residual, out_raw, out_act, alpha_next, st) : conv_tc2(dd, c, x, T_in, residual, out_raw, out_act, alpha_next, st);
   };
   int rc;
-  __half *A = d->f16buf[0], *R = d->f16buf[1], *Y = d->f16buf[2], *A2 = d->f16buf[3], *R2 = d->f16buf[4];
-  const bool keep = d->keep != 0;
+  __half *A = bufs[0], *R = bufs[1], *Y = bufs[2], *A2 = bufs[3], *R2 = bufs[4];
+  const bool keep = keep_dbg;
   // latent (raw, fp16) -> conv1 -> act = snake(., block0.snake1)
   k_dac_latent<<<T, 256, 0, s>>>(codes, d->table, nullptr, R, T, kHidden, kNq, kCodes);
   d->launches++;
@@ -454,7 +456,44 @@ int zb_dac_decode(zb_dac* d, const int64_t* d_codes, float* d_wav, int B, int T,
   for (int b = 0; b < B; ++b) {
     const long long* codes = reinterpret_cast<const long long*>(d_codes) + (size_t)b * kNq * T;
     float* wav = d_wav + (size_t)b * 512 * T;
-    rc = impl == 1 ? decode_one_simt(d, codes, wav, T, s) : decode_one_tc(d, codes, wav, T, s, impl);
+    rc = impl == 1 ? decode_one_simt(d, codes, wav, T, s) : decode_one_tc(d, codes, wav, T, s, impl, d->f16buf, d->keep != 0);
+    if (rc) return rc;
+  }
+  return ZB_OK;
+}
+
+// ---- allocation-free variant of zb_dac_decode (no counterpart in the reference; see include/zonos_b200.h) ---------
+// The five fp16 activation buffers that zb_dac_decode keeps in a cudaMalloc'd, grow-on-demand context workspace live in
+// ONE file-scope device array here, sized for ZB_DAC_STATIC_MAX_FRAMES frames per utterance.  Every GPU that loads the
+// library holds these 23.6 MB until the process exits.  In host code `g_dac_static_ws` is only a stand-in for the
+// symbol: the device address is resolved once per device with cudaGetSymbolAddress (that device current) and passed to
+// the kernels like any other pointer.  Nothing has to start at zero: every layer writes all T_l * C_l elements of its
+// output before the next layer reads them through a tensor map bounded to exactly those rows.
+static __device__ __align__(256) __half g_dac_static_ws[(size_t)5 * 49152 * ZB_DAC_STATIC_MAX_FRAMES];
+static __half* g_dac_static_ptr[64] = {nullptr};
+
+int zb_dac_decode_static(zb_dac* d, const int64_t* d_codes, float* d_wav, int B, int T, void* stream) {
+  if (!d || B < 0 || T < 0) return ZB_ERR_ARG;
+  if (!d->finalized) return d->err.fail(ZB_ERR_STATE, "zb_dac_finalize first");
+  if (T > ZB_DAC_STATIC_MAX_FRAMES)
+    return d->err.fail(ZB_ERR_ARG, "zb_dac_decode_static: T = %d frames exceeds the static workspace (at most %d frames per utterance); "
+                                   "use zb_dac_decode, which allocates", T, ZB_DAC_STATIC_MAX_FRAMES);
+  if (d->device < 0 || d->device >= 64) return d->err.fail(ZB_ERR_ARG, "zb_dac_decode_static: device index %d out of range", d->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(d->err, cudaSetDevice(d->device));
+  if (!g_dac_static_ptr[d->device]) {                 // set-up, once per device: symbol -> device address (no allocation)
+    void* ptr = nullptr;
+    ZB_CUDA(d->err, cudaGetSymbolAddress(&ptr, g_dac_static_ws));
+    if (!ptr) return d->err.fail(ZB_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static DAC workspace");
+    g_dac_static_ptr[d->device] = static_cast<__half*>(ptr);
+  }
+  if (B == 0 || T == 0) return ZB_OK;                 // (B = 0 is the explicit set-up call)
+  if (!d_codes || !d_wav) return ZB_ERR_ARG;
+  __half* bufs[5];
+  for (int i = 0; i < 5; ++i) bufs[i] = g_dac_static_ptr[d->device] + (size_t)i * 49152 * ZB_DAC_STATIC_MAX_FRAMES;
+  for (int b = 0; b < B; ++b) {
+    const long long* codes = reinterpret_cast<const long long*>(d_codes) + (size_t)b * kNq * T;
+    int rc = decode_one_tc(d, codes, d_wav + (size_t)b * 512 * T, T, s, 0, bufs, false);
     if (rc) return rc;
   }
   return ZB_OK;
