@@ -86,9 +86,9 @@ struct MegaParams {
   bf16* hidden_out;            // optional: post-norm_f hidden states, same indexing
   int hidden_S, hidden_t0;
   int n_stages;                // ring stages
-  int poll_all;                // 1: all consumer threads poll the full barriers; 0: one lane per warp
   unsigned producer_sleep_ns;  // producer back-off between polls of a full ring (0 = hot spin)
   int scratch_bytes;           // activation staging / attention / sampling scratch
+  int stream_evict_first;      // 1: weight tiles are loaded with the L2 evict_first policy (A/B switch "evict")
   unsigned long long* dbg;     // optional trace: [grid][MG_TRACE_SLOTS] globaltimer stamps of step dbg_step (thread 0)
   int dbg_step;
   int dbg_fine;                // trace variant: stage-level stamps of ONE fc1 phase (layer 1 of step dbg_step) instead of the per-phase timeline
@@ -107,6 +107,11 @@ __device__ __forceinline__ unsigned long long mg_globaltimer() {
 #define MG_ASTAMP()                                                                                        \
   do {                                                                                                     \
     if (cx.afine && threadIdx.x == 0 && cx.trace_n < MG_TRACE_SLOTS) cx.trace_out[cx.trace_n++] = mg_globaltimer(); \
+  } while (0)
+
+#define MG_TSTAMP()                                                                                        \
+  do {                                                                                                     \
+    if (cx.tfine && threadIdx.x == 0 && cx.trace_n < MG_TRACE_SLOTS) cx.trace_out[cx.trace_n++] = mg_globaltimer(); \
   } while (0)
 
 // ---- PTX helpers ------------------------------------------------------------------------------------------------
@@ -141,6 +146,21 @@ __device__ __forceinline__ void mg_bulk_g2s(uint32_t dst, const void* src, uint3
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
                "r"(bytes), "r"(bar)
                : "memory");
+}
+// The same with an L2 eviction-priority hint.  The weight stream (3.2 GB per step, each byte used once) is marked
+// evict_first so that it does not push everything else out of the 126 MB L2 every step: the kernel's own instructions
+// (311 KB of SASS, refetched by every SM), the KV cache of the previous steps, the activations and the embedding rows.
+// The step-tail trace (--opt trace=4) showed code that runs once per step (sampling, state machine, embedding gather)
+// taking 9-22 us for a handful of dependent L2 round trips: its instructions came from DRAM every step.
+__device__ __forceinline__ void mg_bulk_g2s_hint(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+               : "memory");
+}
+__device__ __forceinline__ uint64_t mg_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
 }
 __device__ __forceinline__ void mg_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void mg_bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
@@ -187,10 +207,10 @@ struct MgCtx {
   int stage, parity;         // ring cursor of this role
   int tile_flip;             // partial-buffer parity (consumers)
   bool prof;                 // debug profile on
-  bool poll_all;             // every consumer thread polls the full barriers (A/B switch)
   bool trace;                // this step is being traced
   bool fine;                 // stage-level trace of one fc1 phase (MegaParams::dbg_fine == 1)
   bool afine;                // step-level trace of one attention phase (dbg_fine == 2, layer 1)
+  bool tfine;                // trace of the step tail (dbg_fine == 3): final LN + heads, sampling, state machine, next embedding
   int trace_n;
   unsigned long long* trace_out;
   long long t_full;          // clock64 ticks thread 0 spent waiting on full barriers (prof)
@@ -385,12 +405,8 @@ __device__ __forceinline__ const unsigned char* mg_cons_wait(MgCtx& cx) {
   // one polling lane per warp (+ __syncwarp): 256 threads spinning on try_wait contend with the producer's own
   // barrier traffic and the TMA's complete_tx updates (scripts/ring_bench.cu: idle all-lane pollers cost 30 %)
   const long long c0 = (cx.prof && threadIdx.x == 0) ? clock64() : 0;
-  if (cx.poll_all) {
-    mg_mbar_wait(cx.full0 + 8u * cx.stage, cx.parity);
-  } else {
-    if ((threadIdx.x & 31) == 0) mg_mbar_wait(cx.full0 + 8u * cx.stage, cx.parity);
-    __syncwarp();
-  }
+  if ((threadIdx.x & 31) == 0) mg_mbar_wait(cx.full0 + 8u * cx.stage, cx.parity);
+  __syncwarp();
   if (cx.prof && threadIdx.x == 0) cx.t_full += clock64() - c0;
   return cx.ring + (size_t)cx.stage * MG_STAGE_BYTES;
 }
@@ -613,7 +629,7 @@ __device__ __forceinline__ void mg_epi_heads(const MegaParams& p, const MgEpi& e
 // host checks both); only ONE of the two MMA loop variants exists in a given instantiation (code size: see k_decode_mega).
 template <bool PK>
 __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, const bf16* xs, int ld, int K, int n_units, int gate_off,
-                                           int kind, const MgEpi& epi) {
+                                           int kind, int layer) {
   const int NT = kind == EPI_SWIGLU ? 2 : 1;
   const int UNIT = kind == EPI_SWIGLU ? 1 : 2;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -642,7 +658,7 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
         for (int kc0 = 0; kc0 < K; kc0 += MG_KC) {
           const int kcs = min(MG_KC, K - kc0);
           const uint32_t st_addr = mg_cons_wait_addr(cx);
-          const bool fstamp = cx.fine && kind == EPI_SWIGLU && epi.layer == 1 && threadIdx.x == 0 && cx.trace_n < 32;
+          const bool fstamp = cx.fine && kind == EPI_SWIGLU && layer == 1 && threadIdx.x == 0 && cx.trace_n < 32;
           if (fstamp) cx.trace_out[cx.trace_n++] = mg_globaltimer();        // stage data seen by warp 0
           if (PK) {
             // R <= 4: the WEIGHTS are the MMA's A operand.  A rows 0..7 = the 8 weight rows over the first half of the
@@ -1007,28 +1023,38 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
 // consumers: step input
 // =================================================================================================================
 __device__ __noinline__ void mg_embed_row(const MegaParams& p, int b, int col, int L) {
-  // model.py:97-98,141-142: x[b] = x[B+b] = ((E0[c0] + E1[c1]) + ...), sequential bf16 adds.  All table rows are
-  // requested before the first one is used (they are HBM-cold and the memory queues are full of the weight stream).
-  const int d = p.d;
-  for (int e = threadIdx.x * 8; e < d; e += MG_CONSUMERS * 8) {
-    uint4 raw[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      raw[k] = make_uint4(0, 0, 0, 0);
-      if (k < p.n_q) {
-        long long id = __ldcg(p.delayed + ((size_t)b * p.n_q + k) * L + col);
-        id = id < 0 ? 0 : (id >= p.V ? p.V - 1 : id);
-        raw[k] = *reinterpret_cast<const uint4*>(p.emb + ((size_t)k * p.V + id) * d + e);
-      }
-    }
+  // model.py:97-98,141-142: x[b] = x[B+b] = ((E0[c0] + E1[c1]) + ...), sequential bf16 adds.  Runs once per step and is
+  // instruction-cache cold every time: the fully unrolled first version (16 predicated rows, 14 KB of SASS) took 18 us
+  // for two L2 round trips.  Lane k fetches id k, the ids travel by shuffle, rows go three at a time.
+  const int d = p.d, lane = threadIdx.x & 31;
+  int myid = 0;
+  if (lane < p.n_q) {
+    long long id = __ldcg(p.delayed + ((size_t)b * p.n_q + lane) * L + col);
+    myid = (int)(id < 0 ? 0 : (id >= p.V ? p.V - 1 : id));
+  }
+#pragma unroll 1
+  for (int e = threadIdx.x * 8; e < d; e += MG_CONSUMERS * 8) {        // warp-uniform trip count (d % 256 == 0)
     float acc[8];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      if (k < p.n_q) {
-        float v[8];
-        mg_unpack8(raw[k], v);
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll 1
+    for (int k0 = 0; k0 < p.n_q; k0 += 3) {
+      uint4 raw[3];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = k == 0 ? v[j] : bf16_round(acc[j] + v[j]);
+      for (int u = 0; u < 3; ++u) {
+        const int k = k0 + u;
+        const int id = __shfl_sync(0xffffffffu, myid, k & 31);
+        raw[u] = make_uint4(0, 0, 0, 0);
+        if (k < p.n_q) raw[u] = *reinterpret_cast<const uint4*>(p.emb + ((size_t)k * p.V + id) * d + e);
+      }
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        if (k0 + u < p.n_q) {
+          float v[8];
+          mg_unpack8(raw[u], v);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = (k0 + u) == 0 ? v[j] : bf16_round(acc[j] + v[j]);
+        }
       }
     }
     __nv_bfloat162 o[4];
@@ -1068,8 +1094,8 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   cx.empty0 = cx.full0 + 8u * MG_MAX_STAGES;
   volatile int* s_flags = reinterpret_cast<volatile int*>(bars + 16 * MG_MAX_STAGES);   // [0] stop, [1] consumer cursor, [2] misc, [3] step mailbox for the epilogue warp (KV position, -1 = stop)
   cx.stage = 0; cx.parity = 0; cx.tile_flip = 0;
-  cx.prof = TR && p.dbg != nullptr; cx.t_full = 0; cx.t_fc1 = cx.t_fc1_full = cx.t_fc1_sync = 0; cx.poll_all = p.poll_all != 0;
-  cx.trace = false; cx.fine = false; cx.afine = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
+  cx.prof = TR && p.dbg != nullptr; cx.t_full = 0; cx.t_fc1 = cx.t_fc1_full = cx.t_fc1_sync = 0;
+  cx.trace = false; cx.fine = false; cx.afine = false; cx.tfine = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
 
   const int tid = threadIdx.x, warp = tid >> 5;
   if (tid == 0) {
@@ -1092,6 +1118,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
     if (!mg_ld_volatile(&st->done)) {
       MgSched ld;
       mg_sched_init(ld, p, pos0, rope0, with_heads, final_ln);
+      const uint64_t pol_stream = mg_policy_evict_first();
       MgDesc d;
       // optional profile of this warp (clock64 ticks): [0] schedule arithmetic, [1] waiting for a free slot, [2] issue, [3] stages
       long long t_sched = 0, t_wait = 0, t_issue = 0, n_ld = 0;
@@ -1116,8 +1143,11 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         const long long c2 = prof ? clock64() : 0;
         if (prof && p.dbg_fine == 1 && lane == 0 && d.tag == ((uint32_t)MG_PH_FC1 | (1u << 8) | ((uint32_t)p.dbg_step << 16)) && n_fine < 32)
           p.dbg[(size_t)blockIdx.x * MG_TRACE_SLOTS + 32 + n_fine++] = mg_globaltimer();     // issue time of this fc1 stage
-        if (d.src != nullptr)
-          mg_bulk_g2s(mg_smem_u32(cx.ring + (size_t)cx.stage * MG_STAGE_BYTES + d.dst_off), d.src, d.bytes, cx.full0 + 8u * cx.stage);
+        if (d.src != nullptr) {
+          const uint32_t dst = mg_smem_u32(cx.ring + (size_t)cx.stage * MG_STAGE_BYTES + d.dst_off);
+          if (d.tag != 0 && p.stream_evict_first) mg_bulk_g2s_hint(dst, d.src, d.bytes, cx.full0 + 8u * cx.stage, pol_stream);   // weight tiles
+          else mg_bulk_g2s(dst, d.src, d.bytes, cx.full0 + 8u * cx.stage);
+        }
         mg_advance(cx);
         if (prof) { const long long c3 = clock64(); t_sched += c1 - c0; t_wait += c2 - c1; t_issue += c3 - c2; ++n_ld; }
       }
@@ -1152,24 +1182,30 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       const int pos = s_flags[3];
       if (pos < 0) break;
       epi.pos = pos; epi.cfg_scale = 0.f; epi.eos_bias = 0;
-      for (int l = 0; l < p.n_layer; ++l) {
+      // ONE mg_gemv_epi call site for all five phase kinds (layer n_layer = the heads pseudo-layer): every copy of this
+      // code that the layer loop does not contain is instruction-cache footprint the SM does not have to refetch 26 times
+      // per step (cold straight-line code runs at ~0.2 us per 128-byte line here, profiles/r02_summary.md)
+      for (int l = 0; l <= p.n_layer; ++l) {
+        const bool heads_l = l == p.n_layer;
+        if (heads_l && !with_heads) break;
         epi.layer = l;
         epi.kv_layer = p.kv + (size_t)l * p.kv_layer_elems;
-        epi.out = p.q; epi.out_stride = p.q_size;
-        mg_gemv_epi(p, cx, qkv_rows / 2, EPI_QKV, epi);
-        epi.out = p.x; epi.out_stride = p.d;
-        epi.ll = p.x_ll; epi.ll_epoch = mg_ll_epoch(p, step, l, 0);
-        mg_gemv_epi(p, cx, p.d / 2, EPI_RESID, epi);
-        epi.out = p.h; epi.out_stride = p.F;
-        mg_gemv_epi(p, cx, p.F, EPI_SWIGLU, epi);
-        epi.out = p.x; epi.out_stride = p.d;
-        epi.ll = p.x_ll + (size_t)8 * (p.d >> 1); epi.ll_epoch = mg_ll_epoch(p, step, l, 1);
-        mg_gemv_epi(p, cx, p.d / 2, EPI_RESID, epi);
-      }
-      if (with_heads) {
-        epi.cfg_scale = *reinterpret_cast<const volatile float*>(&st->cfg_scale);
-        epi.eos_bias = mg_ld_volatile(&st->apply_eos_bias);
-        mg_gemv_epi(p, cx, p.n_q * p.V / 2, EPI_HEADS, epi);
+        if (heads_l) {
+          epi.cfg_scale = *reinterpret_cast<const volatile float*>(&st->cfg_scale);
+          epi.eos_bias = mg_ld_volatile(&st->apply_eos_bias);
+        }
+        const int n_ph = heads_l ? 1 : 4;
+#pragma unroll 1
+        for (int ph = 0; ph < n_ph; ++ph) {
+          int n_units, kind;
+          if (ph == 0) { kind = heads_l ? EPI_HEADS : EPI_QKV; n_units = heads_l ? p.n_q * p.V / 2 : qkv_rows / 2; epi.out = p.q; epi.out_stride = p.q_size; }
+          else if (ph == 2) { kind = EPI_SWIGLU; n_units = p.F; epi.out = p.h; epi.out_stride = p.F; }
+          else {
+            kind = EPI_RESID; n_units = p.d / 2; epi.out = p.x; epi.out_stride = p.d;
+            epi.ll = p.x_ll + (ph == 3 ? (size_t)8 * (p.d >> 1) : 0); epi.ll_epoch = mg_ll_epoch(p, step, l, ph == 3);
+          }
+          mg_gemv_epi(p, cx, n_units, kind, epi);
+        }
       }
     }
     return;
@@ -1179,7 +1215,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   unsigned bar_target = 0;
   const long long t_kernel0 = clock64();
   bf16* xs = reinterpret_cast<bf16*>(cx.scratch);
-  const int ld_d = p.d + MG_XPAD, ld_q = p.q_size + MG_XPAD, ld_f = p.F + MG_XPAD;
+  const int ld_d = p.d + MG_XPAD;
   int own_lo, own_hi;                                 // residual-stream columns owned by this CTA (out_proj / fc2 rows)
   mg_range(p.d / 2, own_lo, own_hi);
   own_lo *= 2; own_hi *= 2;
@@ -1196,7 +1232,9 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
     cx.trace = TR && p.dbg != nullptr && step == p.dbg_step && !p.dbg_fine;
     cx.fine = TR && p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 1;
     const bool afine_step = TR && p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 2;
+    cx.tfine = TR && p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 3;
     cx.trace_n = 0;
+    MG_TSTAMP();                                                  // t0: step start
     MG_STAMP();                                                   // 0: step start
     const int pos = mg_ld_volatile(&st->pos), col = mg_ld_volatile(&st->col), Lbuf = mg_ld_volatile(&st->L);
 
@@ -1231,65 +1269,71 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       if (own_lo + i < own_hi) cx.s_xown[r * MG_OWN + i] = __bfloat162float(__ldcg(p.x + (size_t)r * p.d + own_lo + i));
     }
 
-    MgEpi epi;
-    epi.pos = pos; epi.own_lo = own_lo; epi.ll = p.x_ll; epi.ll_epoch = 0;
     const bool ll = p.use_ll != 0;
     const unsigned long long* x_ll1 = p.x_ll + (size_t)8 * (p.d >> 1);      // fc2's half of x_ll
-    epi.cfg_scale = 0.f; epi.eos_bias = 0; epi.logits = p.logits;
-    for (int l = 0; l < p.n_layer; ++l) {
-      epi.layer = l;
+    // Layer loop with ONE call site each for the LayerNorm staging, the plain staging, the attention and the GEMV phase
+    // (layer n_layer = final LN + heads).  The first version had every phase inlined separately (5 GEMV phases, 8
+    // LayerNorm stagings): ~94 KB of SASS per trip of the layer loop, refetched by every SM 26 times per step.
+#pragma unroll 1
+    for (int l = 0; l <= p.n_layer; ++l) {
+      const bool heads_l = l == p.n_layer;
+      if (heads_l) {
+        MG_TSTAMP();                                              // t1: layers done
+        if (!with_heads) {
+          // No heads phase follows: without the epoch-tagged stream the last fc2 still needs its barrier (final_ln reads
+          // p.x), and with it CTA 0's embed-ahead below must not overwrite p.x while other CTAs' fc2 epilogues are still
+          // storing their columns of this step into it (MG_MODE_FORCED: the audio-prefix columns of zb_gen_begin).
+          if (!ll || embed_ahead) mg_grid_sync(p.bar_counter, bar_target);
+          break;
+        }
+      }
       bf16* kv_layer = p.kv + (size_t)l * p.kv_layer_elems;
-      // P1: LN1 + in_proj + RoPE + KV append.  From layer 1 on, x comes from the previous layer's fc2 epilogues through
-      // the epoch-tagged x_ll words: no grid barrier between fc2 and this LayerNorm.
-      if (ll && l > 0) mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps, x_ll1, mg_ll_epoch(p, step, l - 1, 1));
-      else mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
-      MG_STAMP();                                                 // per layer +0: LN1 staged
-      epi.out = p.q; epi.out_stride = p.q_size; epi.kv_layer = kv_layer;
-      mg_gemv_phase<PK>(p, cx, xs, ld_d, p.d, qkv_rows / 2, 0, EPI_QKV, epi);
-      MG_STAMP();                                                 // +1: in_proj done
-      mg_grid_sync(p.bar_counter, bar_target);
-      MG_STAMP();                                                 // +2: barrier
-      // P2: attention
-      cx.afine = afine_step && l == 1;
-      mg_attention<G>(p, cx, kv_layer, pos);
-      cx.afine = false;
-      MG_STAMP();                                                 // +3: attention done
-      mg_grid_sync(p.bar_counter, bar_target);
-      MG_STAMP();                                                 // +4: barrier
-      // P3: out_proj + residual
-      mg_stage_copy(xs, ld_q, p.y, p.q_size, p.R);
-      epi.out = p.x; epi.out_stride = p.d;
-      mg_gemv_phase<PK>(p, cx, xs, ld_q, p.q_size, p.d / 2, 0, EPI_RESID, epi);
-      MG_STAMP();                                                 // +5: out_proj done
-      if (!ll) mg_grid_sync(p.bar_counter, bar_target);
-      MG_STAMP();                                                 // +6: barrier
-      // P4: LN2 + fc1 + SwiGLU
-      if (ll) mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps, p.x_ll, mg_ll_epoch(p, step, l, 0));
-      else mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
-      MG_STAMP();                                                 // +7: LN2 staged
-      epi.out = p.h; epi.out_stride = p.F;
-      mg_gemv_phase<PK>(p, cx, xs, ld_d, p.d, p.F, p.F, EPI_SWIGLU, epi);
-      MG_STAMP();                                                 // +8: fc1 done
-      mg_grid_sync(p.bar_counter, bar_target);
-      MG_STAMP();                                                 // +9: barrier
-      // P5: fc2 + residual
-      mg_stage_copy(xs, ld_f, p.h, p.F, p.R);
-      MG_STAMP();                                                 // +10: h staged
-      epi.out = p.x; epi.out_stride = p.d;
-      mg_gemv_phase<PK>(p, cx, xs, ld_f, p.F, p.d / 2, 0, EPI_RESID, epi);
-      MG_STAMP();                                                 // +11: fc2 done
-      if (!ll) mg_grid_sync(p.bar_counter, bar_target);
-      MG_STAMP();                                                 // +12: barrier
+      const int n_ph = heads_l ? 1 : 4;
+#pragma unroll 1
+      for (int ph = 0; ph < n_ph; ++ph) {
+        // ---- cross-CTA dependencies of this phase
+        if (ph == 1) {
+          mg_grid_sync(p.bar_counter, bar_target);
+          MG_STAMP();                                             // +2: barrier
+          cx.afine = afine_step && l == 1;
+          mg_attention<G>(p, cx, kv_layer, pos);
+          cx.afine = false;
+          MG_STAMP();                                             // +3: attention done
+          mg_grid_sync(p.bar_counter, bar_target);
+          MG_STAMP();                                             // +4: barrier
+        } else if (ph == 3 || (!ll && (ph == 2 || l > 0))) {
+          // fc1 -> fc2 always meets at a barrier; out_proj -> LN2 and fc2 -> next LN1 only without the epoch-tagged stream
+          mg_grid_sync(p.bar_counter, bar_target);
+          MG_STAMP();
+        }
+        // ---- activation staging + GEMV phase parameters
+        int K, n_units, gate_off = 0, kind;
+        if (ph == 0 || ph == 2) {
+          K = p.d;
+          const unsigned long long* src_ll = nullptr;
+          unsigned epoch = 0;
+          if (ph == 2) { kind = EPI_SWIGLU; n_units = p.F; gate_off = p.F; if (ll) { src_ll = p.x_ll; epoch = mg_ll_epoch(p, step, l, 0); } }
+          else {
+            kind = heads_l ? EPI_HEADS : EPI_QKV; n_units = heads_l ? p.n_q * p.V / 2 : qkv_rows / 2;
+            if (ll && l > 0) { src_ll = x_ll1; epoch = mg_ll_epoch(p, step, l - 1, 1); }
+          }
+          mg_stage_ln(cx, xs, K + MG_XPAD, p.x, K, p.R, p.eps, src_ll, epoch);
+        } else {
+          K = ph == 1 ? p.q_size : p.F;
+          kind = EPI_RESID; n_units = p.d / 2;
+          mg_stage_copy(xs, K + MG_XPAD, ph == 1 ? p.y : p.h, K, p.R);
+        }
+        MG_STAMP();                                               // activations staged
+        if (heads_l) MG_TSTAMP();                                 // t2: final LN staged
+        mg_gemv_phase<PK>(p, cx, xs, K + MG_XPAD, K, n_units, gate_off, kind, l);
+        MG_STAMP();                                               // GEMV phase done
+      }
     }
 
     if (with_heads) {
-      // final LN + 9 heads + CFG + pad mask (+ logit bias)   (model.py:100-116,266-267,280)
-      if (ll) mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps, x_ll1, mg_ll_epoch(p, step, p.n_layer - 1, 1));
-      else mg_stage_ln(cx, xs, ld_d, p.x, p.d, p.R, p.eps);
-      epi.cfg_scale = *reinterpret_cast<const volatile float*>(&st->cfg_scale);
-      epi.eos_bias = mg_ld_volatile(&st->apply_eos_bias);
-      mg_gemv_phase<PK>(p, cx, xs, ld_d, p.d, p.n_q * p.V / 2, 0, EPI_HEADS, epi);
+      MG_TSTAMP();                                                // t3: heads done
       mg_grid_sync(p.bar_counter, bar_target);
+      MG_TSTAMP();                                                // t4: barrier
       if (p.mode == MG_MODE_DECODE) {
         if ((int)blockIdx.x < p.n_q * p.B) {
           SampleParams sp;
@@ -1303,6 +1347,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
           sp.seed = *reinterpret_cast<const volatile unsigned long long*>(&st->seed);
           sp.step = (unsigned long long)mg_ld_volatile(&st->step);
           sp.st = nullptr;
+          sp.dbg = (cx.tfine && blockIdx.x == 0) ? p.dbg + (size_t)gridDim.x * MG_TRACE_SLOTS + (size_t)gridDim.x * 8 : nullptr;
           mg_sample(sp, blockIdx.x % p.n_q, blockIdx.x / p.n_q, cx.scratch);
           if (tid == 0) {
             // hint: pull the embedding row of the sampled token into L2 now; CTA 0 gathers it after the write-back
@@ -1312,7 +1357,9 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
             asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(rowp), "r"(p.d * 2) : "memory");
           }
         }
+        MG_TSTAMP();                                              // t5: sampled
         mg_grid_sync(p.bar_counter, bar_target);
+        MG_TSTAMP();                                              // t6: barrier
       }
     } else if (final_ln) {
       // plugin-level forward: norm_f of the residual stream (backbone/_torch.py:80)
@@ -1323,10 +1370,6 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       for (int e = tid * 8; e < p.d; e += MG_CONSUMERS * 8) *reinterpret_cast<uint4*>(dst + e) = *reinterpret_cast<const uint4*>(xs + e);
     }
 
-    // Without a heads phase nothing has waited for the other CTAs' fc2 epilogues yet when the barrier after fc2 is
-    // replaced by the epoch-tagged words (ll): CTA 0's embed-ahead below would overwrite p.x while they are still storing
-    // their columns of this step into it (MG_MODE_FORCED, the audio-prefix columns of zb_gen_begin).
-    if (ll && !with_heads && embed_ahead) mg_grid_sync(p.bar_counter, bar_target);
     // ---- advance the device state (CTA 0), then make it visible to everyone
     if (blockIdx.x == 0) {
       if (p.mode == MG_MODE_DECODE) {
@@ -1334,6 +1377,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         up.st = st; up.delayed = p.delayed; up.tokens = p.tokens; up.remaining = p.remaining; up.stopping = p.stopping;
         up.out_len = p.out_len; up.rope_pos = p.rope_pos; up.rows = p.R; up.n_q = p.n_q; up.eos = p.eos; up.mask = p.mask_tok;
         mg_update(up, const_cast<int*>(&s_flags[2]));
+        MG_TSTAMP();                                              // t7 (CTA 0): state machine done
       } else {
         if (tid == 0) {
           st->pos = pos + 1;
@@ -1345,9 +1389,11 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         SyncConsumers::sync();                                    // the frame write-back above is visible CTA-wide
         if (!mg_ld_volatile(&st->done))
           for (int b = 0; b < p.B; ++b) mg_embed_row(p, b, col + 1, Lbuf);
+        MG_TSTAMP();                                              // t8 (CTA 0): next input embedded
       }
     }
     mg_grid_sync(p.bar_counter, bar_target);
+    MG_TSTAMP();                                                  // end-of-step barrier
   }
 
   // ---- tell the producer where the consumers stopped

@@ -12,7 +12,7 @@
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
-#pragma unroll
+#pragma unroll 1
   for (int i = 0; i < 10; ++i) {
     const uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
     const uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
@@ -24,33 +24,31 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
 // uniform in (0, 1]
 __device__ __forceinline__ float u01(uint32_t r) { return ((float)(r >> 8) + 1.0f) * (1.0f / 16777216.0f); }
 
+// Block reductions over SMP_THREADS threads.  Out of line and shared by all call sites: this code runs once per decode
+// step inside the persistent kernel, where it is instruction-cache cold every time (~0.15 us per 128-byte line of
+// straight-line code, profiles/r02_summary.md) - compactness is what makes it fast.  The summation order (own elements
+// ascending, xor butterfly inside the warp, warps in order) is fixed, so results are reproducible.
 template <class Sync>
-__device__ __forceinline__ float block_reduce_sum(float v, float* red) {
+__device__ __noinline__ float block_reduce(float v, float* red, const bool is_max) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  v = warp_sum(v);
+  v = is_max ? warp_max(v) : warp_sum(v);
   Sync::sync();
   if (lane == 0) red[warp] = v;
   Sync::sync();
-  float t = 0.f;
-  for (int w = 0; w < SMP_THREADS / 32; ++w) t += red[w];
+  float t = is_max ? -INFINITY : 0.f;
+#pragma unroll 1
+  for (int w = 0; w < SMP_THREADS / 32; ++w) t = is_max ? fmaxf(t, red[w]) : t + red[w];
   return t;
 }
 template <class Sync>
-__device__ __forceinline__ float block_reduce_max(float v, float* red) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  v = warp_max(v);
-  Sync::sync();
-  if (lane == 0) red[warp] = v;
-  Sync::sync();
-  float t = -INFINITY;
-  for (int w = 0; w < SMP_THREADS / 32; ++w) t = fmaxf(t, red[w]);
-  return t;
-}
+__device__ __forceinline__ float block_reduce_sum(float v, float* red) { return block_reduce<Sync>(v, red, false); }
+template <class Sync>
+__device__ __forceinline__ float block_reduce_max(float v, float* red) { return block_reduce<Sync>(v, red, true); }
 // argmax with first-index tie break (torch.argmax)
 template <class Sync>
-__device__ __forceinline__ int block_argmax(float v, int idx, float* red, int* redi) {
+__device__ __noinline__ int block_argmax(float v, int idx, float* red, int* redi) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
+#pragma unroll 1
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, v, o);
     const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
@@ -60,6 +58,7 @@ __device__ __forceinline__ int block_argmax(float v, int idx, float* red, int* r
   if (lane == 0) { red[warp] = v; redi[warp] = idx; }
   Sync::sync();
   float bv = red[0]; int bi = redi[0];
+#pragma unroll 1
   for (int w = 1; w < SMP_THREADS / 32; ++w)
     if (red[w] > bv || (red[w] == bv && redi[w] < bi)) { bv = red[w]; bi = redi[w]; }
   return bi;
@@ -76,7 +75,16 @@ struct SampleParams {
   zb_sampling sp;
   unsigned long long seed, step;
   const ZbDevState* st;         // non-NULL: sampling params / history bounds / seed / step come from device state
+  unsigned long long* dbg;      // optional (traced persistent kernel only): %globaltimer stamps of thread 0
 };
+#define SMP_STAMP()                                                                             \
+  do {                                                                                          \
+    if (dbg_q != nullptr && threadIdx.x == 0) {                                                 \
+      unsigned long long t_;                                                                    \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                    \
+      *dbg_q++ = t_;                                                                            \
+    }                                                                                           \
+  } while (0)
 
 // Shared-memory scratch of one sampling block (SMP_THREADS threads): 3 * SMP_MAXV * 4 + 80 bytes.
 struct SampleSmem {
@@ -109,6 +117,8 @@ __device__ void sample_body(const SampleParams& p, const int k, const int b, con
   float* const red = sm.red;
   int* const redi = sm.redi;
 
+  unsigned long long* dbg_q = p.dbg;
+  SMP_STAMP();                                   // s0: entered
   zb_sampling sp = p.sp;
   unsigned long long seed = p.seed, step = p.step;
   int hist_len = p.hist_len;
@@ -119,86 +129,90 @@ __device__ void sample_body(const SampleParams& p, const int k, const int b, con
   }
   const int tid = threadIdx.x, V = p.V;
   const float* lg = p.logits + ((size_t)b * p.n_q + k) * V;
+  // The working vector lives in shared memory (s_p) and every pass is a rolled loop over this thread's elements
+  // i = tid, tid + SMP_THREADS, ... (ascending, as before: the per-thread accumulation order is unchanged).
 
-  // ---- repetition penalty (sampling.py:99-114): factor = penalty^(#occurrences in the window), ids clamped to V-1
-  float x[SMP_PER];
-#pragma unroll
-  for (int j = 0; j < SMP_PER; ++j) {
-    const int i = tid + j * SMP_THREADS;
-    x[j] = i < V ? __ldcg(lg + i) : -INFINITY;
-  }
-  // factor = penalty^count by repeated multiplication, exactly like scatter_reduce(prod) over ones.
+  // ---- repetition penalty (sampling.py:99-114): factor = penalty^(#occurrences in the window), ids clamped to V-1;
+  // factor built by repeated multiplication, exactly like scatter_reduce(prod) over ones.
+  int win = 0;
+  const long long* h = nullptr;
   if (sp.repetition_penalty != 1.0f && p.history != nullptr && hist_len > 0) {
-    const int win = min(sp.repetition_penalty_window, hist_len);
-    const long long* h = p.history + ((size_t)b * p.n_q + k) * p.hist_stride;
-#pragma unroll
-    for (int j = 0; j < SMP_PER; ++j) {
-      const int i = tid + j * SMP_THREADS;
-      if (i < V) {
-        float f = 1.0f;
-        for (int w = 0; w < win; ++w) {
-          long long tok = __ldcg(h + hist_len - win + w);
-          if (tok > V - 1) tok = V - 1;
-          if ((long long)i == tok) f *= sp.repetition_penalty;
-        }
-        const float raw = __ldcg(lg + i);
-        x[j] = raw <= 0.f ? raw * f : raw / f;
-      }
+    win = min(sp.repetition_penalty_window, hist_len);
+    h = p.history + ((size_t)b * p.n_q + k) * p.hist_stride + hist_len - win;
+#pragma unroll 1
+    for (int w = tid; w < min(win, SMP_MAXV); w += SMP_THREADS) {       // window tokens staged once (s_idx is free until the sort)
+      const long long tok = __ldcg(h + w);
+      s_idx[w] = (int)(tok > V - 1 ? V - 1 : tok);
     }
   }
+  Sync::sync();
+#pragma unroll 1
+  for (int i = tid; i < V; i += SMP_THREADS) {
+    const float raw = __ldcg(lg + i);
+    float f = 1.0f;
+#pragma unroll 1
+    for (int w = 0; w < win; ++w) {
+      long long tok = w < SMP_MAXV ? (long long)s_idx[w] : __ldcg(h + w);
+      if (tok > V - 1) tok = V - 1;
+      if ((long long)i == tok) f *= sp.repetition_penalty;
+    }
+    s_p[i] = win > 0 ? (raw <= 0.f ? raw * f : raw / f) : raw;
+  }
+  Sync::sync();                                  // s_idx is reused below
+  SMP_STAMP();                                   // s1: logits (+ history) loaded, penalty applied
 
   int token;
   if (sp.temperature > 0.f) {
     // ---- softmax(logits / T)
     float mx = -INFINITY;
-#pragma unroll
-    for (int j = 0; j < SMP_PER; ++j) { x[j] = x[j] / sp.temperature; mx = fmaxf(mx, x[j]); }
+#pragma unroll 1
+    for (int i = tid; i < V; i += SMP_THREADS) { const float v = s_p[i] / sp.temperature; s_p[i] = v; mx = fmaxf(mx, v); }
     mx = block_reduce_max<Sync>(mx, red);
     float sum = 0.f;
-#pragma unroll
-    for (int j = 0; j < SMP_PER; ++j) { x[j] = (tid + j * SMP_THREADS < V) ? expf(x[j] - mx) : 0.f; sum += x[j]; }
+#pragma unroll 1
+    for (int i = tid; i < V; i += SMP_THREADS) { const float e = expf(s_p[i] - mx); s_p[i] = e; sum += e; }
     sum = block_reduce_sum<Sync>(sum, red);
-#pragma unroll
-    for (int j = 0; j < SMP_PER; ++j) x[j] = x[j] / sum;
+#pragma unroll 1
+    for (int i = tid; i < V; i += SMP_THREADS) s_p[i] = s_p[i] / sum;
+    SMP_STAMP();                                 // s2: softmax done
 
-    // ---- unified sampler (sampling.py:29-43)
+    // ---- unified sampler (sampling.py:29-43); s_key holds log p
     if (sp.linear > 0.f) {
       float ent = 0.f;
-      float lp[SMP_PER];
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) {
-        lp[j] = logf(fmaxf(x[j], 1e-20f));
-        if (tid + j * SMP_THREADS < V) ent += x[j] * lp[j];
-      }
+#pragma unroll 1
+      for (int i = tid; i < V; i += SMP_THREADS) { const float x = s_p[i], lp = logf(fmaxf(x, 1e-20f)); s_key[i] = lp; ent += x * lp; }
       ent = -block_reduce_sum<Sync>(ent, red);
       float mx2 = -INFINITY;
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) {
-        const float raw = lp[j] * (sp.linear + ent * sp.conf) - lp[j] * lp[j] * sp.quad;
-        x[j] = (tid + j * SMP_THREADS < V) ? raw : -INFINITY;
-        mx2 = fmaxf(mx2, x[j]);
+#pragma unroll 1
+      for (int i = tid; i < V; i += SMP_THREADS) {
+        const float lp = s_key[i];
+        const float raw = lp * (sp.linear + ent * sp.conf) - lp * lp * sp.quad;
+        s_p[i] = raw;
+        mx2 = fmaxf(mx2, raw);
       }
       mx2 = block_reduce_max<Sync>(mx2, red);
       float sum2 = 0.f;
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) { x[j] = (tid + j * SMP_THREADS < V) ? expf(x[j] - mx2) : 0.f; sum2 += x[j]; }
+#pragma unroll 1
+      for (int i = tid; i < V; i += SMP_THREADS) { const float e = expf(s_p[i] - mx2); s_p[i] = e; sum2 += e; }
       sum2 = block_reduce_sum<Sync>(sum2, red);
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) x[j] = x[j] / sum2;
+#pragma unroll 1
+      for (int i = tid; i < V; i += SMP_THREADS) s_p[i] = s_p[i] / sum2;
     }
 
     // ---- top-p / top-k need the descending order: bitonic sort of (prob, index) in shared memory
     if (sp.top_p > 0.f || sp.top_k > 0) {
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) {
-        const int i = tid + j * SMP_THREADS;
-        s_key[i] = i < V ? x[j] : -1.f;          // padding sorts last
+#pragma unroll 1
+      for (int i = tid; i < SMP_MAXV; i += SMP_THREADS) {
+        s_key[i] = i < V ? s_p[i] : -1.f;          // padding sorts last
         s_idx[i] = i;
-        s_p[i] = i < V ? x[j] : 0.f;
+        if (i >= V) s_p[i] = 0.f;
       }
       Sync::sync();
+#pragma unroll 1
       for (int size = 2; size <= SMP_MAXV; size <<= 1) {
+#pragma unroll 1
         for (int strd = size >> 1; strd > 0; strd >>= 1) {
+#pragma unroll 1
           for (int t = tid; t < SMP_MAXV / 2; t += SMP_THREADS) {
             const int lo = 2 * t - (t & (strd - 1));
             const int hi = lo + strd;
@@ -217,6 +231,7 @@ __device__ void sample_body(const SampleParams& p, const int k, const int b, con
         // mask = cumsum - p_sorted > top_p  (sampling.py:73-75)
         if (tid == 0) {
           double c = 0.0;
+#pragma unroll 1
           for (int r = 0; r < V; ++r) {
             c += (double)s_key[r];
             const float incl = (float)c;
@@ -226,11 +241,11 @@ __device__ void sample_body(const SampleParams& p, const int k, const int b, con
         }
         Sync::sync();
         float sum3 = 0.f;
-#pragma unroll
-        for (int j = 0; j < SMP_PER; ++j) { const int i = tid + j * SMP_THREADS; x[j] = i < V ? s_p[i] : 0.f; sum3 += x[j]; }
+#pragma unroll 1
+        for (int i = tid; i < V; i += SMP_THREADS) sum3 += s_p[i];
         sum3 = block_reduce_sum<Sync>(sum3, red);
-#pragma unroll
-        for (int j = 0; j < SMP_PER; ++j) { x[j] = x[j] / sum3; const int i = tid + j * SMP_THREADS; if (i < V) s_p[i] = x[j]; }
+#pragma unroll 1
+        for (int i = tid; i < V; i += SMP_THREADS) s_p[i] = s_p[i] / sum3;
         Sync::sync();
       }
       if (sp.top_k > 0) {
@@ -239,67 +254,56 @@ __device__ void sample_body(const SampleParams& p, const int k, const int b, con
         Sync::sync();
         const float kth = *sm.s_kth;
         float sum4 = 0.f;
-#pragma unroll
-        for (int j = 0; j < SMP_PER; ++j) { if (x[j] < kth) x[j] = 0.f; sum4 += x[j]; }
+#pragma unroll 1
+        for (int i = tid; i < V; i += SMP_THREADS) { float x = s_p[i]; if (x < kth) x = 0.f; s_p[i] = x; sum4 += x; }
         sum4 = block_reduce_sum<Sync>(sum4, red);
-#pragma unroll
-        for (int j = 0; j < SMP_PER; ++j) x[j] = x[j] / sum4;
+#pragma unroll 1
+        for (int i = tid; i < V; i += SMP_THREADS) s_p[i] = s_p[i] / sum4;
       }
     }
+    SMP_STAMP();                                 // s3: unified / top-p / top-k done
     // ---- min-p (sampling.py:82-96)
     if (sp.min_p > 0.f) {
       float top = 0.f;
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) top = fmaxf(top, x[j]);
+#pragma unroll 1
+      for (int i = tid; i < V; i += SMP_THREADS) top = fmaxf(top, s_p[i]);
       top = block_reduce_max<Sync>(top, red);
       const float thr = sp.min_p * top;
       float sum5 = 0.f;
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) { if (x[j] < thr) x[j] = 0.f; sum5 += x[j]; }
+#pragma unroll 1
+      for (int i = tid; i < V; i += SMP_THREADS) { float x = s_p[i]; if (x < thr) x = 0.f; s_p[i] = x; sum5 += x; }
       sum5 = block_reduce_sum<Sync>(sum5, red);
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) x[j] = x[j] / sum5;
+#pragma unroll 1
+      for (int i = tid; i < V; i += SMP_THREADS) s_p[i] = s_p[i] / sum5;
     }
-    if (p.probs_out) {
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) {
-        const int i = tid + j * SMP_THREADS;
-        if (i < V) p.probs_out[((size_t)b * p.n_q + k) * V + i] = x[j];
-      }
-    }
+    SMP_STAMP();                                 // s4: min-p done
     // ---- exponential race (sampling.py:19-21): argmax_i p_i / q_i, q_i ~ Exp(1) = -log(u_i)
     float best = -1.f; int besti = 0x7fffffff;
-#pragma unroll
-    for (int j = 0; j < SMP_PER; ++j) {
-      const int i = tid + j * SMP_THREADS;
-      if (i < V) {
-        const uint4 r = philox4x32_10(make_uint4((uint32_t)(i >> 2), (uint32_t)(b * p.n_q + k), (uint32_t)step, (uint32_t)(step >> 32)),
-                                      make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
-        const uint32_t bits = (i & 3) == 0 ? r.x : (i & 3) == 1 ? r.y : (i & 3) == 2 ? r.z : r.w;
-        const float qe = -logf(u01(bits));
-        const float sc = x[j] / fmaxf(qe, 1e-30f);
-        if (sc > best || (sc == best && i < besti)) { best = sc; besti = i; }
-      }
+#pragma unroll 1
+    for (int i = tid; i < V; i += SMP_THREADS) {
+      const float x = s_p[i];
+      if (p.probs_out) p.probs_out[((size_t)b * p.n_q + k) * V + i] = x;
+      const uint4 r = philox4x32_10(make_uint4((uint32_t)(i >> 2), (uint32_t)(b * p.n_q + k), (uint32_t)step, (uint32_t)(step >> 32)),
+                                    make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+      const uint32_t bits = (i & 3) == 0 ? r.x : (i & 3) == 1 ? r.y : (i & 3) == 2 ? r.z : r.w;
+      const float qe = -logf(u01(bits));
+      const float sc = x / fmaxf(qe, 1e-30f);
+      if (sc > best || (sc == best && i < besti)) { best = sc; besti = i; }
     }
     token = block_argmax<Sync>(best, besti, red, redi);
   } else {
     // greedy: argmax of the (penalised) logits, first index on ties (sampling.py:180)
     float best = -INFINITY; int besti = 0x7fffffff;
-#pragma unroll
-    for (int j = 0; j < SMP_PER; ++j) {
-      const int i = tid + j * SMP_THREADS;
-      if (i < V && (x[j] > best || (x[j] == best && i < besti) || besti == 0x7fffffff)) { best = x[j]; besti = i; }
+#pragma unroll 1
+    for (int i = tid; i < V; i += SMP_THREADS) {
+      const float x = s_p[i];
+      if (p.probs_out) p.probs_out[((size_t)b * p.n_q + k) * V + i] = x;
+      if (x > best || (x == best && i < besti) || besti == 0x7fffffff) { best = x; besti = i; }
     }
     token = block_argmax<Sync>(best, besti, red, redi);
-    if (p.probs_out) {
-#pragma unroll
-      for (int j = 0; j < SMP_PER; ++j) {
-        const int i = tid + j * SMP_THREADS;
-        if (i < V) p.probs_out[((size_t)b * p.n_q + k) * V + i] = x[j];
-      }
-    }
   }
   if (tid == 0) p.tokens[(size_t)b * p.n_q + k] = token;
+  SMP_STAMP();                                   // s5: token drawn and stored
 }
 
 // grid = (n_q, B), block = SMP_THREADS
@@ -327,7 +331,10 @@ struct UpdateParams {
   int eos, mask;
 };
 
-// One block; threads 0..nthreads-1 all call it.  `s_alive` is one int of shared memory.
+// One block; threads 0..nthreads-1 all call it (nthreads a multiple of 32).  `s_alive` is one int of shared memory.
+// One WARP per utterance: lane k owns codebook k, so the nine cells of the written column are read in one round trip and
+// masked_scatter_'s sequential routing (source element j goes to the j-th unknown cell) is a ballot +
+// popcount instead of nine dependent load-test-store rounds.  Compact on purpose: this runs once per step, cold.
 template <class Sync>
 __device__ void update_body(const UpdateParams& p, int* s_alive_p, const int nthreads) {
   ZbDevState* st = p.st;
@@ -336,41 +343,48 @@ __device__ void update_body(const UpdateParams& p, int* s_alive_p, const int nth
   if (threadIdx.x == 0) s_alive = 0;
   Sync::sync();
   const int B = st->B, L = st->L, col = st->col, wcol = col + 1, nq = p.n_q;
-  for (int b = threadIdx.x; b < B; b += nthreads) {
+  const int eos_logic = st->eos_logic, compat = st->compat_scatter;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = nthreads >> 5;
+#pragma unroll 1
+  for (int b = warp; b < B; b += nwarps) {
     int rem = p.remaining[b];
-    if (rem > 0) {                                    // finished utterances are frozen (independent batch-1 runs)
-      long long tok[16];
-      for (int k = 0; k < nq; ++k) tok[k] = __ldcg(p.tokens + (size_t)b * nq + k);
-      if (st->eos_logic) {
-        if (tok[0] == p.eos) { rem = min(rem, nq); p.stopping[b] = 1; }
-        if (p.stopping[b]) {
-          const int idx = min(nq - rem, nq - 1);
-          for (int k = 0; k < idx; ++k) tok[k] = p.mask;
-          tok[idx] = p.eos;
-        }
+    if (rem <= 0) continue;                           // finished utterances are frozen (independent batch-1 runs)
+    long long tok = lane < nq ? __ldcg(p.tokens + (size_t)b * nq + lane) : 0;
+    if (eos_logic) {
+      const long long tok0 = __shfl_sync(0xffffffffu, tok, 0);
+      int stop = p.stopping[b];
+      if (tok0 == p.eos) { rem = min(rem, nq); stop = 1; if (lane == 0) p.stopping[b] = 1; }
+      if (stop) {
+        const int idx = min(nq - rem, nq - 1);
+        if (lane < idx) tok = p.mask;
+        if (lane == idx) tok = p.eos;
       }
-      if (wcol < L) {
-        int j = 0;
-        for (int k = 0; k < nq; ++k) {
-          long long* cell = p.delayed + ((size_t)b * nq + k) * L + wcol;
-          if (*cell == -1) { *cell = st->compat_scatter ? tok[j] : tok[k]; ++j; }
-        }
-      }
-      if (st->eos_logic) {
-        rem -= 1;
+    }
+    if (wcol < L) {
+      long long* cell = p.delayed + ((size_t)b * nq + lane) * L + wcol;
+      const bool unk = lane < nq && *cell == -1;
+      const unsigned m = __ballot_sync(0xffffffffu, unk);
+      const int j = __popc(m & ((1u << lane) - 1u));
+      const long long routed = __shfl_sync(0xffffffffu, tok, j);
+      if (unk) *cell = compat ? routed : tok;
+    }
+    if (eos_logic) {
+      rem -= 1;
+      if (lane == 0) {
         p.remaining[b] = rem;
         if (rem <= 0) p.out_len[b] = wcol - nq;      // out_codes[..., :offset - 9], offset = wcol
       }
-      if (rem > 0) atomicOr(&s_alive, 1);
     }
+    if (rem > 0 && lane == 0) atomicOr(&s_alive, 1);
   }
   Sync::sync();
   if (threadIdx.x == 0) {
     st->col = wcol;
     st->pos += 1;
     st->step += 1;
-    if (st->eos_logic && !s_alive) st->done = 1;
+    if (eos_logic && !s_alive) st->done = 1;
   }
+#pragma unroll 1
   for (int r = threadIdx.x; r < p.rows; r += nthreads) p.rope_pos[r] += 1;
 }
 

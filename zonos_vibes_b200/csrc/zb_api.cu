@@ -90,8 +90,14 @@ struct zb_ctx {
   int opt_attn_mma = 1;     // 1: mma.sync attention kernel, 0: SIMT (A/B and cross-check)
   int64_t launches = 0;
   bool counting = true;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  bool ev_valid = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;     // zb_bench_kernel
+  // zb_gen_steps calls in flight: each has its own event pair and a pinned snapshot of the device state taken right
+  // after it, so that the host can enqueue call k+1 before it waits for call k (zb_gen_poll pops the oldest)
+  struct GenSlot { cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr; ZbDevState* h_st = nullptr; int32_t* h_len = nullptr; };
+  static constexpr int kGenSlots = 4, kGenMaxB = 1024;
+  GenSlot gen[kGenSlots];
+  int gen_head = 0, gen_tail = 0;               // issued / polled counters (slot = counter % kGenSlots)
+  float last_ms = -1.f;
   cudaStream_t cap_stream = nullptr;   // capture happens here: the caller's stream may be the legacy default stream
   // hybrid backbone (hybrid_kernels.cuh)
   bool hybrid = false;
@@ -128,9 +134,9 @@ struct zb_ctx {
   int opt_mega = 1;
   int opt_ring = 0;                    // cap on the ring depth of the persistent kernel (0 = as many stages as fit)
   int opt_psleep = 100;                // persistent kernel: producer back-off (ns) between polls of a full ring
-  int opt_poll_all = 0;                // persistent kernel: all consumer threads poll the ring barriers (A/B switch)
   int opt_att_single = 256;            // persistent kernel: contexts up to this many tokens are not split over CTAs
   int opt_att_chunk = 96;             // persistent kernel: tokens per KV split at least (short contexts use fewer splits)
+  int opt_evict = 1;                   // persistent kernel: weight stream carries the L2 evict_first hint
   int opt_trace = 0;                   // debug: print a per-phase timeline of one step of every persistent launch
   unsigned long long* dbg = nullptr;
 };
@@ -416,8 +422,7 @@ cudaError_t enqueue_decode_step(zb_ctx* c, cudaStream_t s) {
   up.st = c->st; up.delayed = c->delayed; up.tokens = c->tokens; up.remaining = c->remaining; up.stopping = c->stopping;
   up.out_len = c->out_len; up.rope_pos = c->rope_pos; up.rows = 2 * c->B; up.n_q = g.n_codebooks;
   up.eos = g.eos_token_id; up.mask = g.masked_token_id;
-  int ub = c->B < 32 ? 32 : (c->B + 31) / 32 * 32;
-  if (ub > 1024) ub = 1024;
+  const int ub = c->B <= 8 ? 32 * c->B : 256;        // one warp per utterance
   if ((e = launch(c, k_update, dim3(1), dim3(ub), 0, s, up)) != cudaSuccess) return e;
   return cudaSuccess;
 }
@@ -489,7 +494,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   if (stages > MG_MAX_STAGES) stages = MG_MAX_STAGES;
   if (c->opt_ring > 0 && stages > c->opt_ring) stages = c->opt_ring;
   if (stages < 2) return cudaErrorInvalidConfiguration;
-  p.n_stages = stages; p.scratch_bytes = (int)scratch; p.poll_all = c->opt_poll_all; p.producer_sleep_ns = (unsigned)c->opt_psleep;
+  p.n_stages = stages; p.scratch_bytes = (int)scratch; p.producer_sleep_ns = (unsigned)c->opt_psleep; p.stream_evict_first = c->opt_evict;
   const size_t smem = (size_t)stages * MG_STAGE_BYTES + scratch + fixed;
 
   cudaError_t e = cudaMemsetAsync(c->bar_counter, 0, sizeof(unsigned), s);
@@ -506,13 +511,13 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   cfg.numAttrs = 1;
   if (c->counting) c->launches += 1;
   if (c->opt_trace) {
-    const size_t nb = (size_t)c->n_sms * (MG_TRACE_SLOTS + 8) * sizeof(unsigned long long);
+    const size_t nb = ((size_t)c->n_sms * (MG_TRACE_SLOTS + 8) + 16) * sizeof(unsigned long long);
     if (!c->dbg && (e = cudaMalloc(&c->dbg, nb)) != cudaSuccess) return e;
     cudaMemsetAsync(c->dbg, 0, nb, s);
-    p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2 ? 1 : (c->opt_trace == 3 ? 2 : 0);
+    p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2 ? 1 : (c->opt_trace == 3 ? 2 : (c->opt_trace == 4 ? 3 : 0));
     e = cudaLaunchKernelEx(&cfg, mega_kernel(G, true, mega_packed(g, R)), p);
     if (e != cudaSuccess) return e;
-    std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8));
+    std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8) + 16);
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
     cudaMemcpy(hbuf.data(), c->dbg, nb, cudaMemcpyDeviceToHost);
     const int ctas[3] = {0, p.dbg_fine == 2 ? 5 : c->n_sms / 2, p.dbg_fine == 2 ? 41 : c->n_sms - 1};
@@ -546,6 +551,12 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
         std::sort(v.begin(), v.end());
         fprintf(stderr, "  skew %2d: n=%3d %9lld %9lld %9lld  (spread %6lld) last cta %d\n", i, (int)v.size(), v[0], v[v.size() / 2], vmax, vmax - v[0], last);
       }
+    }
+    if (p.dbg_fine == 3) {
+      const unsigned long long* q = hbuf.data() + (size_t)c->n_sms * (MG_TRACE_SLOTS + 8);
+      fprintf(stderr, "  [sampler cta 0] ns:");
+      for (int i = 1; i < 6 && q[i]; ++i) fprintf(stderr, " +%lld", (long long)(q[i] - q[i - 1]));
+      fprintf(stderr, "  (entered -> loaded+penalty -> softmax -> filters -> min-p -> drawn)\n");
     }
     // whole-launch profile of the producer warp / consumer thread 0 (clock64 ticks)
     for (int j = 0; j < 3; ++j) {
@@ -928,6 +939,15 @@ static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int devic
   cudaMemset(c->st, 0, sizeof(ZbDevState));
   cudaEventCreate(&c->ev0);
   cudaEventCreate(&c->ev1);
+  for (auto& g : c->gen) {
+    cudaEventCreate(&g.e0);
+    cudaEventCreate(&g.e1);
+    cudaEventCreateWithFlags(&g.e2, cudaEventDisableTiming);
+    if (cudaMallocHost((void**)&g.h_st, sizeof(ZbDevState)) != cudaSuccess || cudaMallocHost((void**)&g.h_len, zb_ctx::kGenMaxB * 4) != cudaSuccess) {
+      zb_ctx_destroy(c);
+      return bad(ZB_ERR_NOMEM, "pinned host memory for the generation state snapshots");
+    }
+  }
   cudaStreamCreateWithFlags(&c->cap_stream, cudaStreamNonBlocking);
   *out = c;
   return ZB_OK;
@@ -945,6 +965,13 @@ int zb_ctx_destroy(zb_ctx* c) {
   if (c->dbg) cudaFree(c->dbg);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
+  for (auto& g : c->gen) {
+    if (g.e0) cudaEventDestroy(g.e0);
+    if (g.e1) cudaEventDestroy(g.e1);
+    if (g.e2) cudaEventDestroy(g.e2);
+    if (g.h_st) cudaFreeHost(g.h_st);
+    if (g.h_len) cudaFreeHost(g.h_len);
+  }
   if (c->cap_stream) cudaStreamDestroy(c->cap_stream);
   delete c;
   return ZB_OK;
@@ -1183,8 +1210,9 @@ int zb_gen_begin(zb_ctx* c, const void* d_prefix, int B, int Lc, int64_t* d_dela
   cudaStream_t s = (cudaStream_t)stream;
   ZB_CUDA(c->err, cudaSetDevice(c->device));
   const zb_config& g = c->cfg;
+  if (B > zb_ctx::kGenMaxB) return c->err.fail(ZB_ERR_ARG, "at most %d utterances per context", zb_ctx::kGenMaxB);
   c->B = B; c->L = L; c->delayed = (long long*)d_delayed;
-  c->ev_valid = false;
+  c->gen_head = c->gen_tail = 0; c->last_ms = -1.f;
 
   ZbDevState h;
   memset(&h, 0, sizeof(h));
@@ -1244,16 +1272,15 @@ int zb_gen_steps(zb_ctx* c, int n_steps, void* stream) {
   int rc = check_ready(c);
   if (rc) return rc;
   if (!c->delayed) return c->err.fail(ZB_ERR_STATE, "zb_gen_begin first");
+  if (c->gen_head - c->gen_tail >= zb_ctx::kGenSlots)
+    return c->err.fail(ZB_ERR_STATE, "%d zb_gen_steps calls in flight: zb_gen_poll first", zb_ctx::kGenSlots);
   cudaStream_t s = (cudaStream_t)stream;
   ZB_CUDA(c->err, cudaSetDevice(c->device));
+  zb_ctx::GenSlot& g = c->gen[c->gen_head % zb_ctx::kGenSlots];
+  ZB_CUDA(c->err, cudaEventRecord(g.e0, s));
   if (use_mega(c, 2 * c->B)) {
-    ZB_CUDA(c->err, cudaEventRecord(c->ev0, s));
     ZB_CUDA(c->err, launch_mega(c, MG_MODE_DECODE, n_steps, 2 * c->B, c->B, nullptr, nullptr, nullptr, 0, 0, s));
-    ZB_CUDA(c->err, cudaEventRecord(c->ev1, s));
-    c->ev_valid = true;
-    return ZB_OK;
-  }
-  if (c->opt_graph) {
+  } else if (c->opt_graph) {
     if (c->graph && (c->graph_B != c->B || c->graph_L != c->L || c->graph_delayed != c->delayed)) drop_graph(c);
     if (!c->graph) {
       cudaGraph_t graph = nullptr;
@@ -1271,17 +1298,19 @@ int zb_gen_steps(zb_ctx* c, int n_steps, void* stream) {
       cudaGraphDestroy(graph);
       if (e3 != cudaSuccess) { c->graph = nullptr; return c->err.fail(ZB_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(e3)); }
       c->graph_B = c->B; c->graph_L = c->L; c->graph_delayed = c->delayed;
+      ZB_CUDA(c->err, cudaEventRecord(g.e0, s));      // keep the capture / instantiation out of the timed span
     }
-    ZB_CUDA(c->err, cudaEventRecord(c->ev0, s));
     for (int i = 0; i < n_steps; ++i) ZB_CUDA(c->err, cudaGraphLaunch(c->graph, s));
-    ZB_CUDA(c->err, cudaEventRecord(c->ev1, s));
     c->launches += (int64_t)n_steps * c->graph_nodes;
   } else {
-    ZB_CUDA(c->err, cudaEventRecord(c->ev0, s));
     for (int i = 0; i < n_steps; ++i) ZB_CUDA(c->err, enqueue_decode_step(c, s));
-    ZB_CUDA(c->err, cudaEventRecord(c->ev1, s));
   }
-  c->ev_valid = true;
+  ZB_CUDA(c->err, cudaEventRecord(g.e1, s));
+  // snapshot of the loop state after this call, into pinned memory: zb_gen_poll reads it once e2 has fired
+  ZB_CUDA(c->err, cudaMemcpyAsync(g.h_st, c->st, sizeof(ZbDevState), cudaMemcpyDeviceToHost, s));
+  ZB_CUDA(c->err, cudaMemcpyAsync(g.h_len, c->out_len, (size_t)c->B * 4, cudaMemcpyDeviceToHost, s));
+  ZB_CUDA(c->err, cudaEventRecord(g.e2, s));
+  c->gen_head += 1;
   return ZB_OK;
 }
 
@@ -1290,6 +1319,18 @@ int zb_gen_poll(zb_ctx* c, int* done, int* col, int32_t* h_out_len, void* stream
   if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
   ZB_CUDA(c->err, cudaSetDevice(c->device));
+  if (c->gen_head > c->gen_tail) {
+    // state after the OLDEST zb_gen_steps call that has not been polled yet; later calls keep running meanwhile
+    zb_ctx::GenSlot& g = c->gen[c->gen_tail % zb_ctx::kGenSlots];
+    ZB_CUDA(c->err, cudaEventSynchronize(g.e2));
+    float ms = -1.f;
+    if (cudaEventElapsedTime(&ms, g.e0, g.e1) == cudaSuccess) c->last_ms = ms;
+    c->gen_tail += 1;
+    if (done) *done = g.h_st->done;
+    if (col) *col = g.h_st->col;
+    if (h_out_len) memcpy(h_out_len, g.h_len, (size_t)c->B * 4);
+    return ZB_OK;
+  }
   ZbDevState h;
   ZB_CUDA(c->err, cudaMemcpyAsync(&h, c->st, sizeof(h), cudaMemcpyDeviceToHost, s));
   if (h_out_len) ZB_CUDA(c->err, cudaMemcpyAsync(h_out_len, c->out_len, (size_t)c->B * 4, cudaMemcpyDeviceToHost, s));
@@ -1316,8 +1357,7 @@ int zb_update_frame(zb_ctx* c, int64_t* d_delayed, int B, int L, int col, const 
   up.st = c->st; up.delayed = (long long*)d_delayed; up.tokens = (const long long*)d_tokens; up.remaining = d_remaining;
   up.stopping = d_stopping; up.out_len = d_out_len; up.rope_pos = nullptr; up.rows = 0; up.n_q = c->cfg.n_codebooks;
   up.eos = c->cfg.eos_token_id; up.mask = c->cfg.masked_token_id;
-  int ub = B < 32 ? 32 : (B + 31) / 32 * 32;
-  if (ub > 1024) ub = 1024;
+  const int ub = B <= 8 ? 32 * B : 256;              // one warp per utterance
   k_update<<<1, ub, 0, s>>>(up);
   ZB_CUDA(c->err, cudaGetLastError());
   return ZB_OK;
@@ -1339,8 +1379,8 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "ll") c->opt_ll = value;
   else if (k == "att_single") c->opt_att_single = value;
   else if (k == "ring") c->opt_ring = value;
-  else if (k == "poll_all") c->opt_poll_all = value;
   else if (k == "psleep") c->opt_psleep = value;
+  else if (k == "evict") c->opt_evict = value;
   else if (k == "bt_min_rows") c->opt_bt_min_rows = value;
   else if (k == "attn_mma") c->opt_attn_mma = value;
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
@@ -1413,12 +1453,6 @@ int zb_bench_kernel(zb_ctx* c, const char* name, int iters, float* ms_out, void*
   return ZB_OK;
 }
 
-float zb_last_steps_ms(zb_ctx* c) {
-  if (!c || !c->ev_valid) return -1.f;
-  float ms = -1.f;
-  if (cudaEventSynchronize(c->ev1) != cudaSuccess) return -1.f;
-  if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) != cudaSuccess) return -1.f;
-  return ms;
-}
+float zb_last_steps_ms(zb_ctx* c) { return c ? c->last_ms : -1.f; }
 
 }  // extern "C"

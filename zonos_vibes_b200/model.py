@@ -211,11 +211,19 @@ class Zonos(nn.Module):
             stream = ctx.stream
             ctx.check(lib.zb_gen_begin(ctx.handle, prefix.data_ptr(), b, lc, delayed_codes.data_ptr(), length, offset0,
                                        float(cfg_scale), C.byref(sp), int(seed), 1 if compat_scatter else 0, stream))
-            step, aborted, total_ms = 0, False, 0.0
+            # Two zb_gen_steps calls are kept in flight: the host waits for call k (pinned snapshot of the loop state)
+            # while call k+1 already runs, so the device never idles between persistent-kernel launches.  A call issued
+            # after the utterances have finished returns at once (device-side done flag).
+            depth = 1 if callback is not None else 2
+            step, aborted, total_ms, issued, in_flight = 0, False, 0.0, 0, 0
             while True:
-                n = 1 if callback is not None else max(1, min(steps_per_poll, max_steps - step))
-                ctx.check(lib.zb_gen_steps(ctx.handle, n, stream))
+                while in_flight < depth and (issued < max_steps or in_flight == 0):
+                    n = 1 if callback is not None else max(1, min(steps_per_poll, max_steps - issued))
+                    ctx.check(lib.zb_gen_steps(ctx.handle, n, stream))
+                    issued += n
+                    in_flight += 1
                 ctx.check(lib.zb_gen_poll(ctx.handle, C.byref(done), C.byref(col), out_len, stream))
+                in_flight -= 1
                 total_ms += max(0.0, float(lib.zb_last_steps_ms(ctx.handle)))
                 new_step = col.value - offset0
                 if progress is not None:
@@ -228,6 +236,9 @@ class Zonos(nn.Module):
                         break
                 if done.value or step >= max_steps:
                     break
+            while in_flight > 0:                  # drain (the leftover call saw the done flag and did nothing)
+                ctx.check(lib.zb_gen_poll(ctx.handle, C.byref(done), C.byref(col), out_len, stream))
+                in_flight -= 1
         if progress is not None:
             progress.close()
         self.last_step_ms = total_ms / max(step, 1)
