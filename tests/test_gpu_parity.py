@@ -183,9 +183,10 @@ def test_greedy_stream_identical(golden, cuda, cname):
     m = make_model(cname, cuda)
     prefix = zo.synth_prefix_conditioning(CFGS[cname], 1, 6, 1).to(cuda)
     out = m.generate(prefix, max_new_tokens=48, sampling_params=dict(temperature=0), progress_bar=False)
-    assert out.dtype == torch.int64 and out.shape == (1, 9, 48)
+    assert out.dtype == torch.int64 and out.shape[:2] == (1, 9)
     first = _check_delayed(m.last_delayed_codes, golden[f"gen.{cname}.greedy.delayed"], golden[f"gen.{cname}.greedy.logits"], cname)
-    if first is None:
+    if first is None:                        # (after a coin flip the free-running stream may even reach EOS early)
+        assert out.shape == (1, 9, 48)
         assert torch.equal(out.cpu(), golden[f"gen.{cname}.greedy.codes"])       # incl. the masked_scatter_ tail quirk (A.6)
 
 

@@ -68,8 +68,7 @@ struct MegaParams {
   size_t kv_layer_elems;
   const int* page_table;       // [R][max_pages]
   int max_pages;
-  float *part_o, *part_ml;     // split-KV partials [R][Hkv][nsplit][G][Dh], [...][2]
-  int* att_counters;           // [R][Hkv] tickets (zero between launches)
+  unsigned long long* att_ll;  // split-KV partials as (fp32, epoch) words: [R][Hkv][MG_MAX_SPLIT][G * (Dh + 2)]
   int nsplit, min_chunk, single_ctx;
   int R, B;                    // activation rows (= 2B in the CFG modes) and utterances
   ZbDevState* st;
@@ -91,6 +90,7 @@ struct MegaParams {
   int stream_evict_first;      // 1: weight tiles are loaded with the L2 evict_first policy (A/B switch "evict")
   unsigned long long* dbg;     // optional trace: [grid][MG_TRACE_SLOTS] globaltimer stamps of step dbg_step (thread 0)
   int dbg_step;
+  int dbg_kind;                // stage-level trace (dbg_fine == 1): which phase kind of layer 1 is stamped (EPI_SWIGLU = fc1, EPI_QKV, EPI_RESID)
   int dbg_fine;                // trace variant: stage-level stamps of ONE fc1 phase (layer 1 of step dbg_step) instead of the per-phase timeline
 };
 #define MG_TRACE_SLOTS 64
@@ -109,6 +109,10 @@ __device__ __forceinline__ unsigned long long mg_globaltimer() {
     if (cx.afine && threadIdx.x == 0 && cx.trace_n < MG_TRACE_SLOTS) cx.trace_out[cx.trace_n++] = mg_globaltimer(); \
   } while (0)
 
+#define MG_LSTAMP()                                                                                        \
+  do {                                                                                                     \
+    if (cx.lfine && threadIdx.x == 0 && cx.trace_n < MG_TRACE_SLOTS) cx.trace_out[cx.trace_n++] = mg_globaltimer(); \
+  } while (0)
 #define MG_TSTAMP()                                                                                        \
   do {                                                                                                     \
     if (cx.tfine && threadIdx.x == 0 && cx.trace_n < MG_TRACE_SLOTS) cx.trace_out[cx.trace_n++] = mg_globaltimer(); \
@@ -210,6 +214,7 @@ struct MgCtx {
   bool trace;                // this step is being traced
   bool fine;                 // stage-level trace of one fc1 phase (MegaParams::dbg_fine == 1)
   bool afine;                // step-level trace of one attention phase (dbg_fine == 2, layer 1)
+  bool lfine;                // trace of one LayerNorm staging (dbg_fine == 4: LN2 of layer 1)
   bool tfine;                // trace of the step tail (dbg_fine == 3): final LN + heads, sampling, state machine, next embedding
   int trace_n;
   unsigned long long* trace_out;
@@ -439,90 +444,80 @@ __device__ __forceinline__ void mg_unpack8(const uint4& raw, float (&v)[8]) {
 
 // LayerNorm (F.layer_norm: biased variance, eps inside the sqrt, fp32 statistics, bf16 result) of rows r < R of src
 // into xs.  The affine parameters arrive through the ring (stage rows 0 / 1).  K <= 2048 (one uint4 per thread per row).
-// Three CTA barriers instead of five: every thread sums the 8 warp partials itself (same warp order, so the statistics
-// are bit-identical to the two-stage reduction of the per-op path), and the rows are walked by runtime loops.
+// ONE statistics pass: every thread accumulates sum and sum of squares of its 8 values straight from the registers the
+// loads land in, one warp reduction round, ONE CTA barrier, then every thread folds the 8 warp partials itself (warp
+// order: reproducible) and normalises.  The LayerNorm trace (--opt trace=7) of the two-pass version showed 1.7 us of
+// latency-bound scalar work (three barrier-separated passes over 2 x 2048 values) after the 0.9 us the data takes to
+// arrive.  var = E[x^2] - mean^2 in fp32: with K = 2048 its rounding error is ~1e-5 relative, 200x below the bf16
+// rounding of the result.
+__device__ __forceinline__ void mg_ln_row_stats(const uint4& raw, int r, int lane, int warp, float* red1, float* red2) {
+  float v[8];
+  mg_unpack8(raw, v);
+  float a = 0.f, q = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { a += v[j]; q = fmaf(v[j], v[j], q); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); q += __shfl_xor_sync(0xffffffffu, q, o); }
+  if (lane == 0) { red1[warp * 8 + r] = a; red2[warp * 8 + r] = q; }
+}
+
 __device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const bf16* src, int K, int R, float eps,
                                             const unsigned long long* ll = nullptr, unsigned ll_epoch = 0) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int e = tid * 8;
-  const bool active = e < K;
+  const bool active = e < K;                        // warp-uniform (K % 256 == 0)
   float* red1 = cx.red;             // [8 warps][8 rows] partial sums
-  float* red2 = cx.part;            // [8 warps][8 rows] partial sums of squared deviations (the GEMV partial buffer is idle here)
+  float* red2 = cx.part;            // [8 warps][8 rows] partial sums of squares (the GEMV partial buffer is idle here)
   const float fk = (float)K;
-  // pass 1: raw rows -> xs.  ALL rows are requested before the first one is used: one L2 round trip, not R.
-  if (ll != nullptr) {
-    // epoch-tagged source (x_ll): every 8-byte word is (bf16 pair, epoch).  Poll the words themselves until all of
-    // them carry this phase's epoch — this replaces "grid barrier, then load" (two dependent L2 round trips plus the
-    // barrier's own fence + atomic) by the load alone.  A thread only spins on its own 4 words per row.
-    for (int r0 = 0; r0 < R && active; r0 += 2) {          // two rows per round trip (R = 2 at batch 1: one round)
-      const bool two = r0 + 1 < R;
-      const unsigned long long* wp0 = ll + (size_t)r0 * (K >> 1) + (e >> 1);
-      const unsigned long long* wp1 = two ? wp0 + (K >> 1) : wp0;
-      unsigned long long w[8];
-      for (;;) {
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(wp0) : "memory");
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(wp0 + 2) : "memory");
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[4]), "=l"(w[5]) : "l"(wp1) : "memory");
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[6]), "=l"(w[7]) : "l"(wp1 + 2) : "memory");
-        bool ok = true;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) ok = ok && (unsigned)(w[i] >> 32) == ll_epoch;
-        if (ok) break;
-      }
-      *reinterpret_cast<uint4*>(xs + (size_t)r0 * ld + e) = make_uint4((unsigned)w[0], (unsigned)w[1], (unsigned)w[2], (unsigned)w[3]);
-      if (two) *reinterpret_cast<uint4*>(xs + (size_t)(r0 + 1) * ld + e) = make_uint4((unsigned)w[4], (unsigned)w[5], (unsigned)w[6], (unsigned)w[7]);
-    }
-  } else {
-    uint4 rawr[8];
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      rawr[r] = make_uint4(0, 0, 0, 0);
-      if (r < R && active) rawr[r] = mg_ldcg16(src + (size_t)r * K + e);
-    }
-#pragma unroll
-    for (int r = 0; r < 8; ++r)
-      if (r < R && active) *reinterpret_cast<uint4*>(xs + (size_t)r * ld + e) = rawr[r];
-  }
-  // row sums (each thread re-reads the 16 B it has just written)
+  const uint4 z4 = make_uint4(0, 0, 0, 0);
+  MG_LSTAMP();                                                      // L0: entered
+  // raw rows -> xs and the statistics partials, two rows per round trip
 #pragma unroll 1
-  for (int r = 0; r < R; ++r) {
-    float t = 0.f;
+  for (int r0 = 0; r0 < R; r0 += 2) {
+    const bool two = r0 + 1 < R;
+    uint4 raw0 = z4, raw1 = z4;
     if (active) {
-      float v[8];
-      mg_unpack8(*reinterpret_cast<const uint4*>(xs + (size_t)r * ld + e), v);
+      if (ll != nullptr) {
+        // epoch-tagged source (x_ll): every 8-byte word is (bf16 pair, epoch).  Poll the words themselves until all of
+        // them carry this phase's epoch - this replaces "grid barrier, then load" (two dependent L2 round trips plus the
+        // barrier's own fence + atomic) by the load alone.  A thread only spins on its own 4 words per row.
+        const unsigned long long* wp0 = ll + (size_t)r0 * (K >> 1) + (e >> 1);
+        const unsigned long long* wp1 = two ? wp0 + (K >> 1) : wp0;
+        unsigned long long w[8];
+        for (;;) {
+          asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(wp0) : "memory");
+          asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(wp0 + 2) : "memory");
+          asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[4]), "=l"(w[5]) : "l"(wp1) : "memory");
+          asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[6]), "=l"(w[7]) : "l"(wp1 + 2) : "memory");
+          bool ok = true;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) t += v[j];
+          for (int i = 0; i < 8; ++i) ok = ok && (unsigned)(w[i] >> 32) == ll_epoch;
+          if (ok) break;
+        }
+        raw0 = make_uint4((unsigned)w[0], (unsigned)w[1], (unsigned)w[2], (unsigned)w[3]);
+        raw1 = make_uint4((unsigned)w[4], (unsigned)w[5], (unsigned)w[6], (unsigned)w[7]);
+      } else {
+        raw0 = mg_ldcg16(src + (size_t)r0 * K + e);
+        if (two) raw1 = mg_ldcg16(src + (size_t)(r0 + 1) * K + e);
+      }
+      *reinterpret_cast<uint4*>(xs + (size_t)r0 * ld + e) = raw0;
+      if (two) *reinterpret_cast<uint4*>(xs + (size_t)(r0 + 1) * ld + e) = raw1;
     }
-    t = warp_sum(t);
-    if (lane == 0) red1[warp * 8 + r] = t;
+    mg_ln_row_stats(raw0, r0, lane, warp, red1, red2);
+    if (two) mg_ln_row_stats(raw1, r0 + 1, lane, warp, red1, red2);
   }
+  MG_LSTAMP();                                                      // L1: thread 0's own words arrived, partials written
   // affine parameters from the ring
   const uint32_t sp = mg_cons_wait_addr(cx);
-  uint4 wr = make_uint4(0, 0, 0, 0), br = make_uint4(0, 0, 0, 0);
+  uint4 wr = z4, br = z4;
   if (active) {
     wr = mg_lds128(sp + e * 2);
     br = mg_lds128(sp + MG_ROW_BYTES + e * 2);
   }
   mg_cons_release(cx);
+  MG_LSTAMP();                                                      // L2: affine parameters read
   SyncConsumers::sync();
-  // pass 2: variance around the mean (every thread sums the 8 warp partials itself, in warp order)
-#pragma unroll 1
-  for (int r = 0; r < R; ++r) {
-    float m = 0.f;
-#pragma unroll
-    for (int w = 0; w < MG_WARPS; ++w) m += red1[w * 8 + r];
-    const float mean = m / fk;
-    float t = 0.f;
-    if (active) {
-      float v[8];
-      mg_unpack8(*reinterpret_cast<const uint4*>(xs + (size_t)r * ld + e), v);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { const float dlt = v[j] - mean; t += dlt * dlt; }
-    }
-    t = warp_sum(t);
-    if (lane == 0) red2[warp * 8 + r] = t;
-  }
-  SyncConsumers::sync();
+  MG_LSTAMP();                                                      // L3: every thread's words arrived (CTA barrier)
   float g[8], bb[8];
   mg_unpack8(wr, g);
   mg_unpack8(br, bb);
@@ -531,7 +526,8 @@ __device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const b
     float m = 0.f, q = 0.f;
 #pragma unroll
     for (int w = 0; w < MG_WARPS; ++w) { m += red1[w * 8 + r]; q += red2[w * 8 + r]; }
-    const float mean = m / fk, rstd = rsqrtf(q / fk + eps);
+    const float mean = m / fk;
+    const float rstd = rsqrtf(fmaxf(q / fk - mean * mean, 0.f) + eps);
     if (active) {
       float v[8];
       mg_unpack8(*reinterpret_cast<const uint4*>(xs + (size_t)r * ld + e), v);
@@ -546,6 +542,7 @@ __device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const b
     }
   }
   SyncConsumers::sync();
+  MG_LSTAMP();                                                      // L5: normalised rows staged
 }
 
 // =================================================================================================================
@@ -658,7 +655,7 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
         for (int kc0 = 0; kc0 < K; kc0 += MG_KC) {
           const int kcs = min(MG_KC, K - kc0);
           const uint32_t st_addr = mg_cons_wait_addr(cx);
-          const bool fstamp = cx.fine && kind == EPI_SWIGLU && layer == 1 && threadIdx.x == 0 && cx.trace_n < 32;
+          const bool fstamp = cx.fine && kind == p.dbg_kind && layer == 1 && threadIdx.x == 0 && cx.trace_n < 32;
           if (fstamp) cx.trace_out[cx.trace_n++] = mg_globaltimer();        // stage data seen by warp 0
           if (PK) {
             // R <= 4: the WEIGHTS are the MMA's A operand.  A rows 0..7 = the 8 weight rows over the first half of the
@@ -732,6 +729,7 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
     float* pb = cx.part + (size_t)f * 2 * MG_WARPS * 64;
     if (ti >= 2) mg_bar_sync(MG_BAR_FREE + f, MG_HANDOFF);        // the epilogue warp is done with tile ti - 2
     ++ti;
+    if (cx.fine && kind == p.dbg_kind && layer == 1 && threadIdx.x == 0 && cx.trace_n < 32) cx.trace_out[cx.trace_n++] = mg_globaltimer();   // partial buffer free
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
       if (nt < NT) {
@@ -751,8 +749,10 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
     }
     __threadfence_block();
     mg_bar_arrive(MG_BAR_FULL + f, MG_HANDOFF);
+    if (cx.fine && kind == p.dbg_kind && layer == 1 && threadIdx.x == 0 && cx.trace_n < 32) cx.trace_out[cx.trace_n++] = mg_globaltimer();   // tile handed over
   }
   mg_bar_sync(MG_BAR_PHASE, MG_HANDOFF);     // every epilogue store of this phase has been issued (the grid barrier follows)
+  if (cx.fine && kind == p.dbg_kind && layer == 1 && threadIdx.x == 0 && cx.trace_n < 32) cx.trace_out[cx.trace_n++] = mg_globaltimer();     // phase done
   if (pf1) { cx.t_fc1 += clock64() - pt0; cx.t_fc1_full += cx.t_full - pfull0; }
 }
 
@@ -851,7 +851,7 @@ __device__ __forceinline__ void mg_att_token(const uint4& kraw, const uint4& vra
 }
 
 template <int G>
-__device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const bf16* kv_layer, int pos) {
+__device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const bf16* kv_layer, int pos, unsigned epoch) {
   const MgAttItem it = mg_att_item(p, pos);
   if (!it.mine) return;
   MG_ASTAMP();                                                      // a0: phase entered                               // CTA-uniform
@@ -934,89 +934,114 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
     }
     if (t == 0 && g < G) { s_m[warp * G + g] = m; s_l[warp * G + g] = l; }
   }
-  float* s_o = reinterpret_cast<float*>(cx.scratch);              // [MG_MAX_SPLIT >= 8][G][128]
+  float* s_o = reinterpret_cast<float*>(cx.scratch);              // [8 warps][G][128]
   float* s_m = s_o + MG_MAX_SPLIT * G * ZB_DH;                    // [8][G]
   float* s_l = s_m + MG_WARPS * G;                                // [8][G]
-  float* s_ml = s_l + MG_WARPS * G;                               // [32 * 8 * 2]
-  int* s_last = reinterpret_cast<int*>(s_ml + 32 * 8 * 2);
   SyncConsumers::sync();
-  const size_t pbase = (((size_t)row * p.Hkv + kvh) * nsplit + split) * G;
   const int nact = it.nact;
-#pragma unroll 1
-  for (int oi = tid; oi < G * ZB_DH; oi += MG_CONSUMERS) {
-    const int g = oi >> 7, dim = oi & (ZB_DH - 1);
+  // Split partials travel as epoch-tagged 8-byte words (fp32 value, epoch) like the residual stream (x_ll): the merging
+  // CTA polls the DATA.  The first version stored plain partials, took a ticket with an acq_rel atomic (a round trip,
+  // after a CTA barrier), and the last arriver then loaded all partials (another round trip) into shared memory and
+  // merged from there: 4.3 us from "partials stored" to "y stored" in the attention trace, on the critical path of the
+  // grid barrier that 100+ idle CTAs wait at.  Now: stores are fire-and-forget, the merger (the CTA of split 0) sees
+  // the last partial one round trip after it was stored and merges straight from the registers the polls land in.
+  const int wps = G * (ZB_DH + 2);                                // words per split: [G][128] o, then [G][2] (m, l)
+  unsigned long long* pair_ll = p.att_ll + ((size_t)row * p.Hkv + kvh) * MG_MAX_SPLIT * wps;
+  unsigned long long* my_ll = pair_ll + (size_t)split * wps;
+  // rescale factor of every (warp, head) once, by one thread each (the exp2f chain used to sit in every output's loop)
+  float* s_c = s_l + MG_WARPS * G;                                // [8][G]
+  if (tid < MG_WARPS * G) {
+    const int g = tid % G;
     float mn = -INFINITY;
 #pragma unroll
     for (int w = 0; w < MG_WARPS; ++w) mn = fmaxf(mn, s_m[w * G + g]);
-    float lt = 0.f, ot = 0.f;
-#pragma unroll
-    for (int w = 0; w < MG_WARPS; ++w) {
-      const float c = (s_m[w * G + g] == -INFINITY) ? 0.f : exp2f(s_m[w * G + g] - mn);
-      lt += s_l[w * G + g] * c;
-      ot += s_o[(w * G + g) * ZB_DH + dim] * c;
-    }
-    if (nact == 1) {                                              // the only split: this IS the attention output
-      p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + dim] = __float2bfloat16_rn(ot / lt);
-    } else {
-      p.part_o[(pbase + g) * ZB_DH + dim] = ot;
-      if (dim == 0) { p.part_ml[(pbase + g) * 2 + 0] = mn; p.part_ml[(pbase + g) * 2 + 1] = lt; }
-    }
-  }
-  MG_ASTAMP();                                                      // partials (or y) stored
-  if (nact == 1) return;                                          // CTA-uniform
-  // Ticket with ONE release/acquire by thread 0 after the CTA barrier (cumulativity makes every thread's partial stores
-  // visible before the ticket, exactly like the grid barrier).  The attention trace (--opt trace=3) showed 1.1-1.8 us
-  // spent in a __threadfence() executed by all 256 threads here, and again on the last arriver's side.
-  SyncConsumers::sync();
-  if (tid == 0) {
-    int ticket;
-    asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], 1;" : "=r"(ticket) : "l"(&p.att_counters[row * p.Hkv + kvh]) : "memory");
-    *s_last = (ticket == nact - 1);
-  }
-  SyncConsumers::sync();
-  MG_ASTAMP();                                                      // ticket taken
-  if (!*s_last) return;                                           // CTA-uniform
-  // ---- the last CTA of this (row, kv head) merges the split partials: ONE cooperative, coalesced L2 read of all of
-  // them into shared memory (a single round trip), then small runtime loops.
-  const size_t rbase = ((size_t)row * p.Hkv + kvh) * nsplit * G;
-  float* s_po = s_o;                                              // [nact][G][128]  (<= 16 x G x 128 floats, reuses s_o)
-  float* s_pml = s_ml;                                            // [nact][G][2]
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(p.part_o + rbase * ZB_DH);
-    const int n16 = nact * G * ZB_DH / 4;
-#pragma unroll 4
-    for (int i = tid; i < n16; i += MG_CONSUMERS) reinterpret_cast<uint4*>(s_po)[i] = __ldcg(src + i);
-#pragma unroll 1
-    for (int i = tid; i < nact * G * 2; i += MG_CONSUMERS) s_pml[i] = __ldcg(&p.part_ml[rbase * 2 + i]);
-  }
-  SyncConsumers::sync();
-  MG_ASTAMP();                                                      // last arriver: all partials staged
-  // rescale factor of every (split, head) once (the trace showed 1.4 us here when each of the 2 outputs per thread
-  // recomputed nact exp2f's in a serial loop); summation order over the splits is unchanged
-  float* s_c = s_ml + 256;                                          // [nact][G]
-  if (tid < nact * G) {
-    const int g = tid % G;
-    float mn = -INFINITY;
-#pragma unroll 1
-    for (int s2 = 0; s2 < nact; ++s2) mn = fmaxf(mn, s_pml[(s2 * G + g) * 2]);
-    const float ms = s_pml[tid * 2];
+    const float ms = s_m[tid];
     s_c[tid] = (ms == -INFINITY) ? 0.f : exp2f(ms - mn);
   }
   SyncConsumers::sync();
 #pragma unroll 1
   for (int oi = tid; oi < G * ZB_DH; oi += MG_CONSUMERS) {
     const int g = oi >> 7, dim = oi & (ZB_DH - 1);
-    float lt = 0.f, ot = 0.f;
-#pragma unroll 4
-    for (int s2 = 0; s2 < nact; ++s2) {
-      const float c = s_c[s2 * G + g];
-      lt += s_pml[(s2 * G + g) * 2 + 1] * c;
-      ot += s_po[(s2 * G + g) * ZB_DH + dim] * c;
+    float lt = 0.f, ot = 0.f, mn = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < MG_WARPS; ++w) {
+      const float c = s_c[w * G + g];
+      lt += s_l[w * G + g] * c;
+      ot += s_o[(w * G + g) * ZB_DH + dim] * c;
     }
-    p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + dim] = __float2bfloat16_rn(ot / lt);
+    if (dim == 0) {
+#pragma unroll
+      for (int w = 0; w < MG_WARPS; ++w) mn = fmaxf(mn, s_m[w * G + g]);
+    }
+    if (nact == 1) {                                              // the only split: this IS the attention output
+      p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + dim] = __float2bfloat16_rn(ot / lt);
+    } else {
+      const unsigned long long tag = (unsigned long long)epoch << 32;
+      asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(my_ll + oi), "l"(tag | __float_as_uint(ot)) : "memory");
+      if (dim == 0) {
+        asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(my_ll + G * ZB_DH + 2 * g), "l"(tag | __float_as_uint(mn)) : "memory");
+        asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(my_ll + G * ZB_DH + 2 * g + 1), "l"(tag | __float_as_uint(lt)) : "memory");
+      }
+    }
   }
-  if (tid == 0) p.att_counters[row * p.Hkv + kvh] = 0;
-  MG_ASTAMP();                                                      // last arriver: y stored
+  MG_ASTAMP();                                                      // partials (or y) stored
+  if (nact == 1) return;                                          // CTA-uniform
+  // ---- merge, spread over the nact CTAs of this (row, kv head): CTA `split` owns a balanced slice of the G * 64 output
+  // pairs and polls exactly the words it needs - (o[2 dp], o[2 dp + 1]) of its pairs from every split, and the (m, l)
+  // pairs of all (split, head) - about one 16-byte load per thread.  (One CTA pulling all 58 KB of partials through its
+  // own L2 port needs > 1 us for the transfer alone, and re-polling multiplies that: measured 3.5-5 us.)
+  const int npairs = G * (ZB_DH / 2);
+  const int lo = split * npairs / nact, cnt = (split + 1) * npairs / nact - lo;
+  const int items = cnt * nact;
+  float2* s_po = reinterpret_cast<float2*>(s_o + MG_WARPS * G * ZB_DH);       // [cnt][nact]  (upper half of the s_o region)
+  float2* s_pml = s_po + (MG_MAX_SPLIT * G * ZB_DH - MG_WARPS * G * ZB_DH) / 2 - MG_MAX_SPLIT * G;    // [nact][G] (m, l)
+#pragma unroll 1
+  for (int item = tid; item < items + nact * G; item += MG_CONSUMERS) {
+    const unsigned long long* wp;
+    float2* dst;
+    if (item < items) {
+      const int pl = item / nact, u = item - pl * nact, P = lo + pl;
+      wp = pair_ll + (size_t)u * wps + (P >> 6) * ZB_DH + 2 * (P & 63);
+      dst = s_po + item;
+    } else {
+      const int j = item - items, u = j / G, g = j - u * G;
+      wp = pair_ll + (size_t)u * wps + G * ZB_DH + 2 * g;
+      dst = s_pml + j;
+    }
+    unsigned long long w0, w1;
+    do {
+      asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(wp) : "memory");
+    } while ((unsigned)(w0 >> 32) != epoch || (unsigned)(w1 >> 32) != epoch);
+    *dst = make_float2(__uint_as_float((unsigned)w0), __uint_as_float((unsigned)w1));
+  }
+  SyncConsumers::sync();
+  MG_ASTAMP();                                                      // every partial word of this CTA's slice arrived
+  if (tid < nact * G) {                                           // (split, head): rescale factor and rescaled l, once
+    const int g = tid % G;
+    float mn = -INFINITY;
+#pragma unroll 1
+    for (int u = 0; u < nact; ++u) mn = fmaxf(mn, s_pml[u * G + g].x);
+    const float2 ml = s_pml[tid];
+    const float c = (ml.x == -INFINITY) ? 0.f : exp2f(ml.x - mn);
+    s_c[tid] = c;
+    s_c[MG_MAX_SPLIT * G + tid] = ml.y * c;
+  }
+  SyncConsumers::sync();
+#pragma unroll 1
+  for (int pl = tid; pl < cnt; pl += MG_CONSUMERS) {
+    const int P = lo + pl, g = P >> 6, dp = P & 63;
+    float lt = 0.f, o0 = 0.f, o1 = 0.f;
+#pragma unroll 2
+    for (int u = 0; u < nact; ++u) {
+      const float c = s_c[u * G + g];
+      const float2 o = s_po[pl * nact + u];
+      lt += s_c[MG_MAX_SPLIT * G + u * G + g];
+      o0 += o.x * c;
+      o1 += o.y * c;
+    }
+    *reinterpret_cast<__nv_bfloat162*>(p.y + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + 2 * dp) = __floats2bfloat162_rn(o0 / lt, o1 / lt);
+  }
+  MG_ASTAMP();                                                      // this CTA's slice of y stored
 }
 
 // =================================================================================================================
@@ -1095,7 +1120,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   volatile int* s_flags = reinterpret_cast<volatile int*>(bars + 16 * MG_MAX_STAGES);   // [0] stop, [1] consumer cursor, [2] misc, [3] step mailbox for the epilogue warp (KV position, -1 = stop)
   cx.stage = 0; cx.parity = 0; cx.tile_flip = 0;
   cx.prof = TR && p.dbg != nullptr; cx.t_full = 0; cx.t_fc1 = cx.t_fc1_full = cx.t_fc1_sync = 0;
-  cx.trace = false; cx.fine = false; cx.afine = false; cx.tfine = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
+  cx.trace = false; cx.fine = false; cx.afine = false; cx.tfine = false; cx.lfine = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
 
   const int tid = threadIdx.x, warp = tid >> 5;
   if (tid == 0) {
@@ -1141,7 +1166,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         }
         if (!__shfl_sync(0xffffffffu, go, 0)) break;
         const long long c2 = prof ? clock64() : 0;
-        if (prof && p.dbg_fine == 1 && lane == 0 && d.tag == ((uint32_t)MG_PH_FC1 | (1u << 8) | ((uint32_t)p.dbg_step << 16)) && n_fine < 32)
+        if (prof && p.dbg_fine == 1 && lane == 0 && d.tag == ((uint32_t)(p.dbg_kind == EPI_QKV ? MG_PH_QKV : p.dbg_kind == EPI_RESID ? MG_PH_OUT : MG_PH_FC1) | (1u << 8) | ((uint32_t)p.dbg_step << 16)) && n_fine < 32)
           p.dbg[(size_t)blockIdx.x * MG_TRACE_SLOTS + 32 + n_fine++] = mg_globaltimer();     // issue time of this fc1 stage
         if (d.src != nullptr) {
           const uint32_t dst = mg_smem_u32(cx.ring + (size_t)cx.stage * MG_STAGE_BYTES + d.dst_off);
@@ -1233,6 +1258,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
     cx.fine = TR && p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 1;
     const bool afine_step = TR && p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 2;
     cx.tfine = TR && p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 3;
+    const bool lfine_step = TR && p.dbg != nullptr && step == p.dbg_step && p.dbg_fine == 4;
     cx.trace_n = 0;
     MG_TSTAMP();                                                  // t0: step start
     MG_STAMP();                                                   // 0: step start
@@ -1296,7 +1322,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
           mg_grid_sync(p.bar_counter, bar_target);
           MG_STAMP();                                             // +2: barrier
           cx.afine = afine_step && l == 1;
-          mg_attention<G>(p, cx, kv_layer, pos);
+          mg_attention<G>(p, cx, kv_layer, pos, mg_ll_epoch(p, step, l, 0));
           cx.afine = false;
           MG_STAMP();                                             // +3: attention done
           mg_grid_sync(p.bar_counter, bar_target);
@@ -1317,7 +1343,9 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
             kind = heads_l ? EPI_HEADS : EPI_QKV; n_units = heads_l ? p.n_q * p.V / 2 : qkv_rows / 2;
             if (ll && l > 0) { src_ll = x_ll1; epoch = mg_ll_epoch(p, step, l - 1, 1); }
           }
+          cx.lfine = TR && lfine_step && l == 1 && ph == 2;
           mg_stage_ln(cx, xs, K + MG_XPAD, p.x, K, p.R, p.eps, src_ll, epoch);
+          cx.lfine = false;
         } else {
           K = ph == 1 ? p.q_size : p.F;
           kind = EPI_RESID; n_units = p.d / 2;

@@ -127,6 +127,7 @@ struct zb_ctx {
   bool mega_ok = false;
   unsigned* bar_counter = nullptr;
   unsigned long long* x_ll = nullptr;  // persistent kernel: epoch-tagged residual stream [2][8][d/2]
+  unsigned long long* att_ll = nullptr;   // persistent kernel: epoch-tagged split-KV partials [8 rows][Hkv][MG_MAX_SPLIT][G * (Dh + 2)]
   unsigned launch_seq = 0;             // persistent-kernel launches so far (epoch base of x_ll)
   int opt_ll = 1;                      // persistent kernel: poll x_ll instead of the grid barriers after out_proj / fc2
   int n_sms = ZB_NUM_SMS;
@@ -469,7 +470,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   p.eps = g.norm_eps; p.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
   p.x = c->x; p.q = c->q; p.y = c->y; p.h = c->h; p.logits = logits ? logits : c->logits;
   p.kv = c->kv; p.kv_layer_elems = c->kv_layer_elems; p.page_table = c->page_table; p.max_pages = c->max_pages;
-  p.part_o = c->part_o; p.part_ml = c->part_ml; p.att_counters = c->counters;
+  p.att_ll = c->att_ll;
   int ns = c->n_sms / (R * g.num_heads_kv);
   ns = ns < 1 ? 1 : (ns > c->nsplit ? c->nsplit : ns);
   if (ns > MG_MAX_SPLIT) ns = MG_MAX_SPLIT;
@@ -499,6 +500,10 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
 
   cudaError_t e = cudaMemsetAsync(c->bar_counter, 0, sizeof(unsigned), s);
   if (e != cudaSuccess) return e;
+  // tags of the split-KV partial words start from zero in every launch: a word that this launch has not written yet can
+  // never carry one of its epochs (launch numbers wrap after 4096 launches)
+  const size_t att_ll_bytes = (size_t)8 * g.num_heads_kv * MG_MAX_SPLIT * G * (ZB_DH + 2) * sizeof(unsigned long long);
+  if ((e = cudaMemsetAsync(c->att_ll, 0, att_ll_bytes, s)) != cudaSuccess) return e;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(c->n_sms);
   cfg.blockDim = dim3(MG_THREADS);
@@ -514,7 +519,9 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     const size_t nb = ((size_t)c->n_sms * (MG_TRACE_SLOTS + 8) + 16) * sizeof(unsigned long long);
     if (!c->dbg && (e = cudaMalloc(&c->dbg, nb)) != cudaSuccess) return e;
     cudaMemsetAsync(c->dbg, 0, nb, s);
-    p.dbg = c->dbg; p.dbg_step = n_steps / 2; p.dbg_fine = c->opt_trace == 2 ? 1 : (c->opt_trace == 3 ? 2 : (c->opt_trace == 4 ? 3 : 0));
+    p.dbg = c->dbg; p.dbg_step = n_steps / 2; // trace = 1 per-phase timeline | 2 / 5 / 6 stage level of fc1 / in_proj / out_proj (layer 1) | 3 attention | 4 step tail | 7 LN2 of layer 1
+    p.dbg_fine = (c->opt_trace == 2 || c->opt_trace == 5 || c->opt_trace == 6) ? 1 : c->opt_trace == 3 ? 2 : c->opt_trace == 4 ? 3 : c->opt_trace == 7 ? 4 : 0;
+    p.dbg_kind = c->opt_trace == 5 ? EPI_QKV : c->opt_trace == 6 ? EPI_RESID : EPI_SWIGLU;
     e = cudaLaunchKernelEx(&cfg, mega_kernel(G, true, mega_packed(g, R)), p);
     if (e != cudaSuccess) return e;
     std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8) + 16);
@@ -920,7 +927,9 @@ static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int devic
       return bad(ZB_ERR_NOMEM, std::string("barrier counter: ") + cudaGetErrorString(e));
     }
     const size_t ll_bytes = (size_t)2 * 8 * (c->cfg.d_model / 2) * sizeof(unsigned long long);
-    if ((e = cudaMalloc(&c->x_ll, ll_bytes)) != cudaSuccess || (e = cudaMemset(c->x_ll, 0, ll_bytes)) != cudaSuccess) {
+    const size_t att_ll_bytes = (size_t)8 * cfg->num_heads_kv * MG_MAX_SPLIT * (cfg->num_heads / cfg->num_heads_kv) * (ZB_DH + 2) * sizeof(unsigned long long);
+    if ((e = cudaMalloc(&c->x_ll, ll_bytes)) != cudaSuccess || (e = cudaMemset(c->x_ll, 0, ll_bytes)) != cudaSuccess ||
+        (e = cudaMalloc(&c->att_ll, att_ll_bytes)) != cudaSuccess || (e = cudaMemset(c->att_ll, 0, att_ll_bytes)) != cudaSuccess) {
       cudaFree(c->arena); delete c;
       return bad(ZB_ERR_NOMEM, std::string("x_ll: ") + cudaGetErrorString(e));
     }
@@ -962,6 +971,7 @@ int zb_ctx_destroy(zb_ctx* c) {
   if (c->st) cudaFree(c->st);
   if (c->bar_counter) cudaFree(c->bar_counter);
   if (c->x_ll) cudaFree(c->x_ll);
+  if (c->att_ll) cudaFree(c->att_ll);
   if (c->dbg) cudaFree(c->dbg);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
