@@ -43,6 +43,8 @@ struct zb_dac {
   int ew_k1 = 8;            // ... on k=1 layers
   int wide_cout = 768;      // layers with Cout >= this run on the one-tile-per-CTA kernel (impl 0)
   int mt2_min_waves = 8;    // 256-row tiles only when that still leaves this many tiles per SM
+  int max_group = 8;        // utterances decoded together: one launch per layer covers all their tiles (workspace = 5 x 49152 x T x group halves)
+  float conv2_bias_h = 0.f; // host copy of decoder.conv2.bias (read back once in zb_dac_finalize)
   ZbErr err;
   std::map<std::string, RawT> raw;
   bool finalized = false;
@@ -181,6 +183,21 @@ int make_map(zb_dac* d, CUtensorMap* m, const void* base, uint64_t inner, uint64
   return ZB_OK;
 }
 
+// activations of a group of utterances: [nb][T][C] fp16, as a 3-D map {C, T, nb}: rows outside [0, T) of an utterance are
+// zero-filled by TMA (the conv's zero padding), so a tile never reads its neighbour utterance
+int make_map_x(zb_dac* d, CUtensorMap* m, const void* base, uint64_t C, uint64_t T, uint64_t nb, uint32_t box_rows) {
+  cuuint64_t dims[3] = {C, T, nb};
+  cuuint64_t strides[2] = {C * 2, T * C * 2};
+  cuuint32_t box[3] = {TC_BK, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = d->encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return d->err.fail(ZB_ERR_CUDA, "cuTensorMapEncodeTiled (activations) failed: %d (C=%llu T=%llu nb=%llu box=%u)", (int)r,
+                                            (unsigned long long)C, (unsigned long long)T, (unsigned long long)nb, box_rows);
+  return ZB_OK;
+}
+
 int pick_n_tile(int Cout) {
   if (Cout % 256 == 0) return 256;
   if (Cout % 192 == 0) return 192;
@@ -190,7 +207,7 @@ int pick_n_tile(int Cout) {
   return 32;
 }
 
-int conv_tc(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half* residual, __half* out_raw, __half* out_act,
+int conv_tc(zb_dac* d, const ConvW& c, const __half* x, int nb, int T_in, const __half* residual, __half* out_raw, __half* out_act,
             const float* alpha_next, cudaStream_t s) {
   TcConvParams p;
   memset(&p, 0, sizeof(p));
@@ -210,10 +227,11 @@ int conv_tc(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half* 
   p.bias = c.bias; p.residual = residual; p.out_raw = out_raw; p.out_act = out_act; p.alpha_next = alpha_next;
   CUtensorMap mx, mw;
   int rc;
-  if ((rc = make_map(d, &mx, x, c.Cin, T_in, TC_BM))) return rc;
+  if ((rc = make_map_x(d, &mx, x, c.Cin, T_in, nb, TC_BM))) return rc;
   if ((rc = make_map(d, &mw, c.w_koi, c.Cin, (uint64_t)c.K * c.Cout, p.n_tile))) return rc;
   const size_t smem = 1024 + (size_t)stages * stage_bytes + 256 + TC_TAB_BYTES;
-  dim3 grid((p.m_rows + TC_BM - 1) / TC_BM, c.Cout / p.n_tile, c.stride > 1 ? c.stride : 1);
+  p.m_tiles = (p.m_rows + TC_BM - 1) / TC_BM;
+  dim3 grid(p.m_tiles * nb, c.Cout / p.n_tile, c.stride > 1 ? c.stride : 1);
   k_dac_conv_tc<<<grid, TC_THREADS, smem, s>>>(mx, mw, p);
   d->launches++;
   ZB_CUDA(d->err, cudaGetLastError());
@@ -222,7 +240,7 @@ int conv_tc(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half* 
 
 
 // second-generation persistent kernel (dac_tc2.cuh): window reuse across taps, 256-row tiles, double-buffered TMEM
-int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half* residual, __half* out_raw, __half* out_act,
+int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int nb, int T_in, const __half* residual, __half* out_raw, __half* out_act,
              const float* alpha_next, cudaStream_t s) {
   if (c.Cout > TC2_MAX_COUT) return d->err.fail(ZB_ERR_ARG, "conv_tc2: Cout %d > %d", c.Cout, TC2_MAX_COUT);
   TcConv2Params p;
@@ -238,7 +256,8 @@ int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half*
   p.phases = c.stride > 1 ? c.stride : 1;
   p.acc_cols = 128; p.acc_stages = 2;
   // 256-row tiles halve the weight traffic; keep 128-row tiles when there would be too few tiles to balance 148 SMs
-  const long tiles2 = (long)((p.m_rows + 2 * TC_BM - 1) / (2 * TC_BM)) * p.n_tiles * p.phases;
+  p.nb = nb;
+  const long tiles2 = (long)((p.m_rows + 2 * TC_BM - 1) / (2 * TC_BM)) * p.n_tiles * p.phases * nb;
   p.mt = tiles2 >= (long)d->mt2_min_waves * ZB_NUM_SMS ? 2 : 1;
   p.m_tiles = (p.m_rows + p.mt * TC_BM - 1) / (p.mt * TC_BM);
   p.lead = c.stride > 1 ? p.ntaps - 1 : c.pad;
@@ -257,10 +276,10 @@ int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half*
   p.bias = c.bias; p.residual = residual; p.out_raw = out_raw; p.out_act = out_act; p.alpha_next = alpha_next;
   CUtensorMap mx, mw;
   int rc;
-  if ((rc = make_map(d, &mx, x, c.Cin, T_in, p.box_rows))) return rc;
+  if ((rc = make_map_x(d, &mx, x, c.Cin, T_in, nb, p.box_rows))) return rc;
   if ((rc = make_map(d, &mw, c.w_koi, c.Cin, (uint64_t)c.K * c.Cout, p.n_tile))) return rc;
   const size_t smem = 1024 + (size_t)p.a_slots * p.a_bytes + (size_t)p.b_stages * b_bytes + 512 + TC2_TAB_BYTES;
-  const long tiles = (long)p.m_tiles * p.n_tiles * p.phases;
+  const long tiles = (long)p.m_tiles * p.n_tiles * p.phases * nb;
   const int grid = (int)(tiles < ZB_NUM_SMS ? tiles : ZB_NUM_SMS);
   if ((p.ntaps > 1 ? d->ew_multi : d->ew_k1) == 16) k_dac_conv_tc2<16><<<grid, 64 + 32 * 16, smem, s>>>(mx, mw, p);
   else k_dac_conv_tc2<8><<<grid, 64 + 32 * 8, smem, s>>>(mx, mw, p);
@@ -269,56 +288,56 @@ int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int T_in, const __half*
   return ZB_OK;
 }
 
-// `bufs` = the five fp16 activation buffers of 49152 * T halves each (the context workspace, or the static array of
-// zb_dac_decode_static); keep_dbg = copy intermediates for zb_dac_get_intermediate (allocates: context workspace only).
-int decode_one_tc(zb_dac* d, const long long* codes, float* wav, int T, cudaStream_t s, int impl, __half* const* bufs, bool keep_dbg) {
-  auto conv_tc = [&](zb_dac* dd, const ConvW& c, const __half* x, int T_in, const __half* residual, __half* out_raw, __half* out_act,
-                     const float* alpha_next, cudaStream_t st) {
-    // impl 0: per layer — the wide layers (Cout >= 768) run best on the N=256 one-tile-per-CTA kernel (two CTAs per SM),
+// One group of `nb` utterances: every layer is ONE launch whose tiles cover all of them (tile index = (utterance, time
+// tile, channel tile, phase)), so the tail of a layer is paid once per group instead of once per utterance, and the small
+// layers (conv1 at T = 2580: 120 tiles for 148 SMs) fill the machine.  `bufs` = the five fp16 activation buffers of
+// 49152 * T * nb halves each (the context workspace, or the static array of zb_dac_decode_static);
+// keep_dbg = copy intermediates of the group's LAST utterance for zb_dac_get_intermediate (allocates: context workspace only).
+int decode_group_tc(zb_dac* d, const long long* codes, float* wav, int nb, int T, cudaStream_t s, int impl, __half* const* bufs, bool keep_dbg) {
+  auto conv = [&](const ConvW& c, const __half* x, int T_in, const __half* residual, __half* out_raw, __half* out_act, const float* alpha_next) {
+    // impl 0: per layer - the wide layers (Cout >= 768) run best on the N=256 one-tile-per-CTA kernel (two CTAs per SM),
     // everything else on the persistent window-reuse kernel; impl 2 / 3 force one kernel everywhere (A/B runs)
     const bool v1 = impl == 2 || (impl == 0 && c.Cout >= d->wide_cout);
-    return v1 ? ::conv_tc(dd, c, x, T_in, residual, out_raw, out_act, alpha_next, st) : conv_tc2(dd, c, x, T_in, residual, out_raw, out_act, alpha_next, st);
+    return v1 ? conv_tc(d, c, x, nb, T_in, residual, out_raw, out_act, alpha_next, s) : conv_tc2(d, c, x, nb, T_in, residual, out_raw, out_act, alpha_next, s);
   };
   int rc;
   __half *A = bufs[0], *R = bufs[1], *Y = bufs[2], *A2 = bufs[3], *R2 = bufs[4];
   const bool keep = keep_dbg;
+  const size_t last = (size_t)(nb - 1);                          // intermediates are kept for the last utterance of the group
   // latent (raw, fp16) -> conv1 -> act = snake(., block0.snake1)
-  k_dac_latent<<<T, 256, 0, s>>>(codes, d->table, nullptr, R, T, kHidden, kNq, kCodes);
+  k_dac_latent<<<nb * T, 256, 0, s>>>(codes, d->table, nullptr, R, T, kHidden, kNq, kCodes);
   d->launches++;
-  if (keep && (rc = dbg_store_f16(d, "latent", R, T, kHidden, s))) return rc;
-  if ((rc = conv_tc(d, d->conv1, R, T, nullptr, keep ? R2 : nullptr, A, rawp(d, "decoder.block.0.snake1.alpha"), s))) return rc;
-  if (keep && (rc = dbg_store_f16(d, "conv1", R2, T, kDecoder, s))) return rc;
+  if (keep && (rc = dbg_store_f16(d, "latent", R + last * T * kHidden, T, kHidden, s))) return rc;
+  if ((rc = conv(d->conv1, R, T, nullptr, keep ? R2 : nullptr, A, rawp(d, "decoder.block.0.snake1.alpha")))) return rc;
+  if (keep && (rc = dbg_store_f16(d, "conv1", R2 + last * T * kDecoder, T, kDecoder, s))) return rc;
   int Tl = T;
   for (int j = 0; j < 4; ++j) {
     const std::string bp = "decoder.block." + std::to_string(j);
     // A (snaked) -> ConvT -> R (raw, residual of unit 1), A2 = snake(., ru1.snake1)
-    if ((rc = conv_tc(d, d->convt[j], A, Tl, nullptr, R, A2, rawp(d, bp + ".res_unit1.snake1.alpha"), s))) return rc;
+    if ((rc = conv(d->convt[j], A, Tl, nullptr, R, A2, rawp(d, bp + ".res_unit1.snake1.alpha")))) return rc;
     Tl *= kStrides[j];
     std::swap(A, A2);
     for (int u = 0; u < 3; ++u) {
       const std::string rp = bp + ".res_unit" + std::to_string(u + 1);
       // conv1 (k7, dilated): A -> Y = snake(., snake2)
-      if ((rc = conv_tc(d, d->ru1[j][u], A, Tl, nullptr, nullptr, Y, rawp(d, rp + ".snake2.alpha"), s))) return rc;
+      if ((rc = conv(d->ru1[j][u], A, Tl, nullptr, nullptr, Y, rawp(d, rp + ".snake2.alpha")))) return rc;
       // conv2 (k1) + residual R -> R2 (raw, only if a later unit needs it) and A2 = snake(., next alpha)
       std::string next_alpha;
       if (u < 2) next_alpha = bp + ".res_unit" + std::to_string(u + 2) + ".snake1.alpha";
       else if (j < 3) next_alpha = "decoder.block." + std::to_string(j + 1) + ".snake1.alpha";
       else next_alpha = "decoder.snake1.alpha";
       const bool need_raw = (u < 2) || keep;
-      if ((rc = conv_tc(d, d->ru2[j][u], Y, Tl, R, need_raw ? R2 : nullptr, A2, rawp(d, next_alpha), s))) return rc;
+      if ((rc = conv(d->ru2[j][u], Y, Tl, R, need_raw ? R2 : nullptr, A2, rawp(d, next_alpha)))) return rc;
       std::swap(A, A2);
       std::swap(R, R2);
     }
-    if (keep && (rc = dbg_store_f16(d, "block" + std::to_string(j), R, Tl, d->convt[j].Cout, s))) return rc;
+    if (keep && (rc = dbg_store_f16(d, "block" + std::to_string(j), R + last * Tl * d->convt[j].Cout, Tl, d->convt[j].Cout, s))) return rc;
   }
-  // final Conv1d(96 -> 1, k7) + tanh on the snaked activation
+  // final Conv1d(96 -> 1, k7) + tanh on the snaked activation (bias cached on the host at finalize: no sync here)
   const ConvW& c = d->conv2;
-  float bias_h = 0.f;
-  ZB_CUDA(d->err, cudaMemcpyAsync(&bias_h, c.bias, 4, cudaMemcpyDeviceToHost, s));
-  ZB_CUDA(d->err, cudaStreamSynchronize(s));
   {
     const size_t fsm = (size_t)(FC_TILE + c.K - 1) * ((c.Cin / 2) | 1) * 4 + (size_t)c.K * c.Cin * 4;
-    k_dac_final_conv<<<(Tl + FC_TILE - 1) / FC_TILE, FC_TILE, fsm, s>>>(A, c.w_kio, bias_h, wav, Tl, c.Cin, c.K, c.pad);
+    k_dac_final_conv<<<dim3((Tl + FC_TILE - 1) / FC_TILE, nb), FC_TILE, fsm, s>>>(A, c.w_kio, d->conv2_bias_h, wav, Tl, c.Cin, c.K, c.pad);
   }
   d->launches++;
   ZB_CUDA(d->err, cudaGetLastError());
@@ -435,6 +454,7 @@ int zb_dac_finalize(zb_dac* d, void* stream) {
     k_dac_repack<<<ZB_NUM_SMS * 4, 256, 0, s>>>(rawp(d, c->name + ".weight"), c->w_kio, c->w_koi, c->Cout, c->Cin, c->K, c->stride > 1 ? 1 : 0);
   }
   ZB_CUDA(d->err, cudaGetLastError());
+  ZB_CUDA(d->err, cudaMemcpyAsync(&d->conv2_bias_h, d->conv2.bias, 4, cudaMemcpyDeviceToHost, s));
   ZB_CUDA(d->err, cudaStreamSynchronize(s));
   // opt-in to large dynamic smem for the tensor-core kernel
   ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
@@ -451,12 +471,15 @@ int zb_dac_decode(zb_dac* d, const int64_t* d_codes, float* d_wav, int B, int T,
   if (B == 0 || T == 0) return ZB_OK;
   cudaStream_t s = (cudaStream_t)stream;
   ZB_CUDA(d->err, cudaSetDevice(d->device));
-  int rc = impl == 1 ? ensure_workspace_f32(d, T) : ensure_workspace(d, T);
+  const int group = impl == 1 ? 1 : (B < d->max_group ? B : (d->max_group < 1 ? 1 : d->max_group));
+  if ((long long)T * group > 0x7fffffffLL / 64) return d->err.fail(ZB_ERR_ARG, "T * group too large");
+  int rc = impl == 1 ? ensure_workspace_f32(d, T) : ensure_workspace(d, T * group);
   if (rc) return rc;
-  for (int b = 0; b < B; ++b) {
+  for (int b = 0; b < B; b += group) {
+    const int nb = B - b < group ? B - b : group;
     const long long* codes = reinterpret_cast<const long long*>(d_codes) + (size_t)b * kNq * T;
     float* wav = d_wav + (size_t)b * 512 * T;
-    rc = impl == 1 ? decode_one_simt(d, codes, wav, T, s) : decode_one_tc(d, codes, wav, T, s, impl, d->f16buf, d->keep != 0);
+    rc = impl == 1 ? decode_one_simt(d, codes, wav, T, s) : decode_group_tc(d, codes, wav, nb, T, s, impl, d->f16buf, d->keep != 0);
     if (rc) return rc;
   }
   return ZB_OK;
@@ -493,7 +516,7 @@ int zb_dac_decode_static(zb_dac* d, const int64_t* d_codes, float* d_wav, int B,
   for (int i = 0; i < 5; ++i) bufs[i] = g_dac_static_ptr[d->device] + (size_t)i * 49152 * ZB_DAC_STATIC_MAX_FRAMES;
   for (int b = 0; b < B; ++b) {
     const long long* codes = reinterpret_cast<const long long*>(d_codes) + (size_t)b * kNq * T;
-    int rc = decode_one_tc(d, codes, d_wav + (size_t)b * 512 * T, T, s, 0, bufs, false);
+    int rc = decode_group_tc(d, codes, d_wav + (size_t)b * 512 * T, 1, T, s, 0, bufs, false);
     if (rc) return rc;
   }
   return ZB_OK;
@@ -519,6 +542,7 @@ int zb_dac_set_option(zb_dac* d, const char* key, int value) {
   }
   if (k == "wide_cout") { d->wide_cout = value; return ZB_OK; }
   if (k == "mt2_min_waves") { d->mt2_min_waves = value; return ZB_OK; }
+  if (k == "max_group") { d->max_group = value < 1 ? 1 : value; return ZB_OK; }
   return d->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
 }
 

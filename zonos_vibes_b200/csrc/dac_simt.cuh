@@ -25,10 +25,13 @@ __global__ void k_dac_fold(const float* __restrict__ codebook /*[1024][8]*/, con
   }
 }
 
-// z[t][c] = sum_k table[k][codes[k][t]][c]        codes int64 [n_q][T] (one utterance), out fp32 and/or fp16
+// z[b][t][c] = sum_k table[k][codes[b][k][t]][c]        codes int64 [nb][n_q][T], out fp32 and/or fp16 [nb][T][C]; grid = nb * T
 __global__ void k_dac_latent(const long long* __restrict__ codes, const float* __restrict__ table, float* __restrict__ z32,
                              __half* __restrict__ z16, int T, int C, int nq, int ncode) {
-  const int t = blockIdx.x;
+  const int t = blockIdx.x % T;
+  codes += (size_t)(blockIdx.x / T) * nq * T;
+  if (z32) z32 += (size_t)(blockIdx.x / T) * T * C;
+  if (z16) z16 += (size_t)(blockIdx.x / T) * T * C;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float acc = 0.f;
     for (int k = 0; k < nq; ++k) {

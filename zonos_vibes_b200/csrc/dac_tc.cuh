@@ -36,6 +36,7 @@ struct TcConvParams {
   int n_tile;                // output channels per CTA (multiple of 32, <= 256)
   int tmem_cols;             // power of two >= n_tile
   int stages;
+  int m_tiles;               // 128-row tiles per utterance: grid.x = nb * m_tiles (utterance b = blockIdx.x / m_tiles)
   const float* bias;         // [Cout]
   const __half* residual;    // [T_out][Cout] or NULL
   __half* out_raw;           // [T_out][Cout] or NULL   (acc + bias + residual)
@@ -157,7 +158,8 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(tc_smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * TC_BM;
+  const int ub = blockIdx.x / p.m_tiles;                        // utterance: the activation map is 3-D {C, T, nb}
+  const int m0 = (blockIdx.x - ub * p.m_tiles) * TC_BM;
   const int n0 = blockIdx.y * p.n_tile;
   const int phase = blockIdx.z;
   const int num_kb = p.ntaps * p.kchunks;
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
         const uint32_t a_dst = base + (uint32_t)s * stage_bytes;
         const uint32_t b_dst = a_dst + TC_A_BYTES;
         mbar_expect_tx(full_bar(s), stage_bytes);
-        tma_load_2d(a_dst, &map_x, kc * TC_BK, m0 + row_off, full_bar(s));
+        tma_load_3d(a_dst, &map_x, kc * TC_BK, m0 + row_off, ub, full_bar(s));
         tma_load_2d(b_dst, &map_w, kc * TC_BK, w_row + n0, full_bar(s));
       }
     }
@@ -234,7 +236,8 @@ __global__ void __launch_bounds__(TC_THREADS) k_dac_conv_tc(const __grid_constan
     const bool odd = lane & 1;
     const int vA = __shfl_sync(0xffffffffu, (int)valid, lane & ~1), vB = __shfl_sync(0xffffffffu, (int)valid, lane | 1);
     const int orA = __shfl_sync(0xffffffffu, out_row, lane & ~1), orB = __shfl_sync(0xffffffffu, out_row, lane | 1);
-    const size_t rowA = (size_t)(vA ? orA : 0) * p.Cout + n0, rowB = (size_t)(vB ? orB : 0) * p.Cout + n0;
+    const size_t ubase = (size_t)ub * p.T_out;
+    const size_t rowA = (ubase + (size_t)(vA ? orA : 0)) * p.Cout + n0, rowB = (ubase + (size_t)(vB ? orB : 0)) * p.Cout + n0;
     const int chalf = (warp - 2) >> 2;                      // the two warps of a lane quarter alternate 32-column chunks
     for (int c0 = chalf * 32; c0 < p.n_tile; c0 += 64) {
       uint32_t v[32];
@@ -264,6 +267,8 @@ __global__ void __launch_bounds__(FC_TILE) k_dac_final_conv(const __half* __rest
   uint32_t* xs = reinterpret_cast<uint32_t*>(fc_smem);           // [FC_TILE + K - 1][ldw]
   float* ws = reinterpret_cast<float*>(xs + (size_t)(FC_TILE + K - 1) * ldw);   // [K][C]
   const int t0 = blockIdx.x * FC_TILE;
+  x += (size_t)blockIdx.y * T * C;                               // grid.y = utterance
+  out += (size_t)blockIdx.y * T;
   const int rows = FC_TILE + K - 1;
   const int wpr = C / 2;                                         // words per row
   for (int i = threadIdx.x; i < rows * wpr; i += FC_TILE) {

@@ -30,7 +30,8 @@ struct TcConv2Params {
   int m_rows;                // GEMM rows (conv: T; convT: T_in + 1)
   int T_out, Cout;
   int n_tile, n_tiles;       // output channels per tile (multiple of 32, <= 128 when acc_stages == 2)
-  int m_tiles, phases;       // tiles = m_tiles * n_tiles * phases
+  int m_tiles, phases;       // tiles per utterance = m_tiles * n_tiles * phases
+  int nb;                    // utterances in this launch: total tiles = nb * tiles per utterance, the activation map is 3-D {C, T, nb}
   int mt;                    // accumulators (128-row halves) per tile: 1 or 2
   int lead;                  // window row 0 = tile row 0 - lead  (conv: pad; convT: ntaps - 1)
   int box_rows, n_aload;     // the window is n_aload TMA boxes of box_rows rows (box_rows % 8 == 0)
@@ -73,7 +74,8 @@ __global__ void __launch_bounds__(64 + 32 * EW, 1) k_dac_conv_tc2(const __grid_c
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(tc2_smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int total_tiles = p.m_tiles * p.n_tiles * p.phases;
+  const int tiles_per_utt = p.m_tiles * p.n_tiles * p.phases;
+  const int total_tiles = p.nb * tiles_per_utt;
   const int tile_rows = p.mt * TC_BM;
 
   if (warp == 0 && lane == 0) {
@@ -110,7 +112,8 @@ __global__ void __launch_bounds__(64 + 32 * EW, 1) k_dac_conv_tc2(const __grid_c
       uint32_t a_par = 1, b_par = 1;
       const uint32_t a_tx = (uint32_t)(p.n_aload * p.box_rows) * 128u;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int mi = tile % p.m_tiles, rest = tile / p.m_tiles;
+        const int ub = tile / tiles_per_utt, tl = tile - ub * tiles_per_utt;
+        const int mi = tl % p.m_tiles, rest = tl / p.m_tiles;
         const int n0 = (rest % p.n_tiles) * p.n_tile, phase = rest / p.n_tiles;
         const int row0 = mi * tile_rows - p.lead;
         const int w_base = (p.stride > 1 ? phase : 0) * p.Cout + n0;
@@ -119,8 +122,8 @@ __global__ void __launch_bounds__(64 + 32 * EW, 1) k_dac_conv_tc2(const __grid_c
           mbar_wait(a_empty(slot), a_par);
           const uint32_t a_dst = a_base + (uint32_t)slot * (uint32_t)p.a_bytes;
           mbar_expect_tx(a_full(slot), a_tx);
-          tma_load_2d(a_dst, &map_x, kc * TC_BK, row0, a_full(slot));
-          if (p.n_aload == 2) tma_load_2d(a_dst + (uint32_t)p.box_rows * 128u, &map_x, kc * TC_BK, row0 + p.box_rows, a_full(slot));
+          tma_load_3d(a_dst, &map_x, kc * TC_BK, row0, ub, a_full(slot));
+          if (p.n_aload == 2) tma_load_3d(a_dst + (uint32_t)p.box_rows * 128u, &map_x, kc * TC_BK, row0 + p.box_rows, ub, a_full(slot));
           if (++slot == p.a_slots) { slot = 0; a_par ^= 1u; }
           int w_row = w_base;
           for (int tap = 0; tap < p.ntaps; ++tap, w_row += w_step) {
@@ -188,7 +191,8 @@ __global__ void __launch_bounds__(64 + 32 * EW, 1) k_dac_conv_tc2(const __grid_c
     int as = 0;
     uint32_t t_par = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int mi = tile % p.m_tiles, rest = tile / p.m_tiles;
+      const int ub = tile / tiles_per_utt, tl = tile - ub * tiles_per_utt;
+      const int mi = tl % p.m_tiles, rest = tl / p.m_tiles;
       const int n0 = (rest % p.n_tiles) * p.n_tile, phase = rest / p.n_tiles;
       const int m = mi * tile_rows + acc * TC_BM + lg * 32 + lane;
       const int out_row = p.stride > 1 ? m * p.stride + phase - p.pad : m;
@@ -196,7 +200,8 @@ __global__ void __launch_bounds__(64 + 32 * EW, 1) k_dac_conv_tc2(const __grid_c
       const bool odd = lane & 1;
       const int vA = __shfl_sync(0xffffffffu, (int)valid, lane & ~1), vB = __shfl_sync(0xffffffffu, (int)valid, lane | 1);
       const int orA = __shfl_sync(0xffffffffu, out_row, lane & ~1), orB = __shfl_sync(0xffffffffu, out_row, lane | 1);
-      const size_t rowA = (size_t)(vA ? orA : 0) * p.Cout + n0, rowB = (size_t)(vB ? orB : 0) * p.Cout + n0;
+      const size_t ubase = (size_t)ub * p.T_out;
+      const size_t rowA = (ubase + (size_t)(vA ? orA : 0)) * p.Cout + n0, rowB = (ubase + (size_t)(vB ? orB : 0)) * p.Cout + n0;
       // the warp's residual rows of the whole tile are requested before the accumulator wait
       uint4 res[NCH][4];
       if (p.residual) {
