@@ -28,6 +28,13 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FRAME_RATE = 44100 / 512          # 86.1328 frames per second of audio
+WORKLOAD = "Zonos-v0.1-transformer bf16 batch 1, 30 s audio (2580 frames), min-p 0.1, + DAC 44 kHz decode"
+
+
+def config_dict(args, dac_impl="tcgen05-fp16"):
+    """`config` of the JSON line: key-identical for the B200 arm and the reference arm."""
+    return {"workload": WORKLOAD, "frames": args.frames, "batch_per_gpu": args.batch,
+            "l2": "inputs exceed L2 (3.2 GB of weights streamed per decode step)", "options": list(args.opt), "dac_impl": dac_impl}
 LC = 24                           # synthetic conditioning length (SURVEY §8)
 FULL = dict(d_model=2048, n_layer=26, num_heads=16, num_heads_kv=4, ffn=8192)
 
@@ -41,6 +48,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=1, help="utterances per GPU")
     ap.add_argument("--frames", type=int, default=86 * 30)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the other BASELINE configs / GPU baseline / phase table after the headline")
     ap.add_argument("--dac-impl", type=int, default=0, help="0 = tcgen05 fp16 (default), 1 = SIMT fp32 cross-check path")
     ap.add_argument("--opt", action="append", default=[], help="native option key=value (pdl, l2_prefetch, graph)")
     return ap.parse_args()
@@ -312,23 +320,28 @@ def cpu_reference_sample(n_decode_steps=None, dac_frames=43, budget_s=12.0):
 
 def run_reference(args, world, rank):
     """--impl reference: the reference's CPU implementation of the path (oracle port; the reference is a Python
-    package that cannot travel to the GPU box), all host threads, bounded sample per step."""
+    package that cannot travel to the GPU box), all host threads.  One "step" here is a BOUNDED SAMPLE of the utterance
+    (prefill + 6 decode steps + a 22-frame DAC decode): `ms_per_step` is the time such a sample really took; `value` is the
+    audio-s/s that the sampled per-frame rates extrapolate to for the whole 2580-frame utterance (`extrapolated`)."""
     if rank != 0:
         return
-    vals = []
+    vals, walls = [], []
     for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
         r = cpu_reference_sample(n_decode_steps=6, dac_frames=22)
         if i >= args.warmup:
             vals.append(r)
+            walls.append(time.perf_counter() - t0)
     v = sum(x["audio_sec_per_sec"] for x in vals) / len(vals)
     ms = sum(x["ms_per_decode_step"] for x in vals) / len(vals)
-    sample = "full-size model B=1+CFG: prefill(25 tok) + 6 decode steps + DAC decode of 22 frames per step; per-frame rates extrapolated"
+    sample = ("full-size model B=1+CFG: weights + prefill(25 tok) + 6 decode steps + DAC decode of 22 frames per step; "
+              "per-frame rates extrapolated to 2580 frames")
     line = {
         "impl": "reference", "metric": "audio_sec_per_sec", "value": v, "unit": "audio-s/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": (args.frames / FRAME_RATE) / v * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": "Zonos-v0.1-transformer bf16 batch 1, 30 s audio (2580 frames), min-p 0.1, + DAC 44 kHz decode",
-                   "frames": args.frames, "batch_per_gpu": 1},
+        "warmup": args.warmup, "ms_per_step": sum(walls) / len(walls) * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "extrapolated": True,
+        "ms_per_utterance_extrapolated": (args.frames / FRAME_RATE) / v * 1e3,
+        "config": config_dict(args, dac_impl="oracle-fp32"),
         "decode_frames_per_s": sum(x["frames_per_s_decode"] for x in vals) / len(vals), "us_per_decode_step": ms * 1e3,
         "cpu_baseline": {"value": v, "unit": "audio-s/s", "cores": vals[0]["cores"], "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -401,18 +414,24 @@ def run_b200(args, world, rank, local):
     ms_e2e, frames_e2e, _, _ = timed(True)
     clocks = sampler.stop() if sampler else None
 
-    # isolated timing of the dominant kernel (fc1 GEMV: 67 MB of weights per launch) for the roofline object
-    import ctypes as C
-    ms_k = C.c_float(0)
-    iters = 26 * 8
-    ctx.check(ctx.lib.zb_bench_kernel(ctx.handle, b"fc1", 26, C.byref(ms_k), ctx.stream))       # warm-up
-    ctx.check(ctx.lib.zb_bench_kernel(ctx.handle, b"fc1", iters, C.byref(ms_k), ctx.stream))
-    fc1_bytes = 2 * FULL["ffn"] * FULL["d_model"] * 2
-    fc1_gbs = fc1_bytes * iters / (ms_k.value * 1e-3) / 1e9
-
     from zonos_vibes_b200.replicas import max_over_ranks
     ms_dev = max_over_ranks(ms_dev, dev)
     ms_e2e = max_over_ranks(ms_e2e, dev)
+    # ---- the other BASELINE configs, after (outside) the headline's timed region; every rank takes part in the sharded ones
+    extra = {}
+    if not args.no_extras and args.batch == 1 and not args.opt:
+        extra["b64"] = extra_b64(model, ctx, world, rank, dev, args.frames, per_gpu=False, total=64)
+        if world > 1:
+            extra["b64_per_gpu"] = extra_b64(model, ctx, world, rank, dev, args.frames, per_gpu=True, total=64 * world)
+        if rank == 0:
+            extra["dac_b32x2580"] = extra_dac(model, dev)
+            extra["phases_k_decode_mega"] = phase_table(model, ctx, dev)
+        extra["hybrid_b16"] = extra_hybrid(dev, world, rank)
+        if rank == 0 and world == 1:
+            try:
+                extra["gpu_baseline"] = gpu_baseline(dev)
+            except Exception as e:  # noqa: BLE001  (a baseline leg must not take the bench line down)
+                extra["gpu_baseline"] = {"unavailable": repr(e)[:200]}
     if rank != 0:
         return
     hbm_peak, _, peak_kind = measured_peaks()
@@ -430,25 +449,30 @@ def run_b200(args, world, rank, local):
     elif "mega=0" in args.opt:
         kernel_name = f"decode step, per-op path (one CUDA graph per step: {body})"
     else:
-        kernel_name = f"k_decode_mega<4> (persistent cooperative kernel, 64 decode steps per launch; bytes and time are per step: {body})"
+        kernel_name = f"k_decode_mega<4,false,true> (persistent cooperative kernel, 64 decode steps per launch; bytes and time are per step: {body})"
     line = {
         "metric": "audio_sec_per_sec", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
-        "config": {"workload": "Zonos-v0.1-transformer bf16 batch 1, 30 s audio (2580 frames), min-p 0.1, + DAC 44 kHz decode",
-                   "frames": T, "batch_per_gpu": B, "l2": "inputs exceed L2 (3.2 GB of weights streamed per decode step)",
-                   "options": args.opt, "dac_impl": "tcgen05-fp16" if args.dac_impl == 0 else "simt-fp32"},
+        "config": config_dict(args, "tcgen05-fp16" if args.dac_impl == 0 else "simt-fp32"),
         "decode_frames_per_s": B * world / (step_ms_dev * 1e-3), "us_per_decode_step": step_ms_dev * 1e3,
         "realtime_factor": value,
         "roofline": {"bound": "hbm", "kernel": kernel_name,
                      "achieved": step_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": step_gbs / hbm_peak, "frac_of_8TBs_nominal": step_gbs / 8000.0,
-                     "peak_kind": peak_kind, "traffic": ncu_traffic_per_step(args), "bytes_per_launch": step_bytes,
-                     "dominant_kernel": {"name": "k_gemv_mma<2,SWIGLU> (ln2+fc1+swiglu of the per-op path)", "achieved": fc1_gbs, "frac": fc1_gbs / hbm_peak,
-                                         "bytes_per_launch": fc1_bytes, "timed": "isolated, back to back over the 26 layers"}},
+                     "peak_kind": peak_kind, "traffic": ncu_traffic_per_step(args), "bytes_per_launch": step_bytes},
         "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": prefix_host.numel() * 2,
                 "d2h_bytes_per_step": wav_host.numel() * 4},
         "gpu_launches": int(launches), "clocks": clocks,
     }
+    if extra:
+        line["configs"] = {k: v for k, v in extra.items() if k != "gpu_baseline" and v is not None}
+        if "gpu_baseline" in extra:
+            line["gpu_baseline"] = extra["gpu_baseline"]
+            if "us_per_decode_step" in extra["gpu_baseline"]:
+                gb = line["gpu_baseline"]
+                gb["speedup_of_this_repo_vs_eager"] = gb["us_per_decode_step"] / (step_ms_dev * 1e3)
+                if gb.get("us_per_decode_step_cuda_graph_replay"):
+                    gb["speedup_of_this_repo_vs_graph_replay"] = gb["us_per_decode_step_cuda_graph_replay"] / (step_ms_dev * 1e3)
     if world == 1 and not args.no_cpu_baseline:
         r = cpu_reference_sample()
         line["cpu_baseline"] = {
@@ -457,6 +481,215 @@ def run_b200(args, world, rank, local):
                       f"DAC decode of {r['dac_frames_timed']} frames ({r['dac_frames_per_s']:.1f} frames/s); per-frame rates extrapolated to 2580 frames",
             "decode_frames_per_s": r["frames_per_s_decode"]}
     print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# the other BASELINE configs + same-box GPU baseline + per-phase table (all timed AFTER the headline's timed region)
+# ----------------------------------------------------------------------------------------------------------------
+def peaks_full():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), float(d["bf16_tflops"]), float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured"
+    return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+def extra_b64(model, ctx, world, rank, dev, T, per_gpu, total):
+    """BASELINE config 3: `total` utterances of T frames sharded over the ranks (replicas.generate_sharded: batched
+    tcgen05 decode path per rank + DAC + pinned-host gather).  Device events around the whole call, max over ranks."""
+    from zonos_vibes_b200.replicas import generate_sharded, max_over_ranks
+    g = torch.Generator(device="cpu").manual_seed(7)
+    prefixes = [torch.randn(2, LC, FULL["d_model"], generator=g).bfloat16() for _ in range(total)]
+    prefixes = [p.to(dev) for p in prefixes]
+    st = {}
+    barrier(world, dev)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    out = generate_sharded(model, prefixes, T, max_batch=64, seed=5, stats=st)
+    e1.record()
+    torch.cuda.synchronize()
+    barrier(world, dev)
+    ms = max_over_ranks(e0.elapsed_time(e1), dev)
+    step_ms = max_over_ranks(st["decode_step_ms"] or 0.0, dev)
+    if rank != 0:
+        return None
+    frames = sum(int(w.shape[-1]) // 512 for w in out)
+    b_rank = (total + world - 1) // world
+    n_dec = T + 8
+    mean_ctx = LC + 1 + n_dec / 2.0
+    step_bytes = ctx.lib.zb_weight_bytes(ctx.handle) + 106496 * b_rank * (mean_ctx + 1) + 36864 * b_rank
+    hbm, _, _, kind = peaks_full()
+    gbs = step_bytes / (step_ms * 1e-3) / 1e9
+    return {"utterances_total": total, "utterances_per_gpu": b_rank, "mode": "64 per GPU (weak)" if per_gpu else "64 total (strong)",
+            "frames": T, "ms": ms, "audio_sec_per_sec": frames / FRAME_RATE / (ms * 1e-3), "us_per_decode_step": step_ms * 1e3,
+            "decode_frames_per_s": total / (step_ms * 1e-3),
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm, "peak_kind": kind,
+                         "bytes_per_launch": step_bytes, "kernel": "decode step of the slowest rank, batched tcgen05 path (k_bt_gemm + finish kernels + k_attn_decode_mma)"}}
+
+
+def extra_dac(model, dev, B=32, T=2580, runs=3):
+    """BASELINE config 4: DAC decoder alone, 32 x 2580 frames -> waveform."""
+    codes = torch.randint(0, 1024, (B, 9, T), generator=torch.Generator().manual_seed(2)).to(dev)
+    model.autoencoder.decode(codes)
+    torch.cuda.synchronize()
+    ms = []
+    for _ in range(runs):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        model.autoencoder.decode(codes)
+        e1.record()
+        torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    m = sum(ms) / len(ms)
+    tf = 1.608302592e9 * B * T / (m * 1e-3) / 1e12
+    _, burst, sus, kind = peaks_full()
+    return {"batch": B, "frames": T, "ms": m, "ms_best": min(ms), "tflops": tf, "frames_per_s": B * T / (m * 1e-3),
+            "roofline": {"bound": "tensor", "achieved": tf, "peak": sus, "unit": "TFLOP/s", "frac": tf / sus, "frac_of_burst_peak": tf / burst,
+                         "peak_kind": kind + " bf16_tflops_sustained (a 0.2 s job under the power cap)", "flops_per_launch": 1.608302592e9 * B * T,
+                         "kernel": "k_dac_conv_tc / k_dac_conv_tc2<8> (tcgen05 implicit-GEMM convs, 30 layers)"}}
+
+
+def extra_hybrid(dev, world, rank, frames=96):
+    """BASELINE config 5: synthetic Zonos-v0.1-hybrid (Mamba2 + attention), 16 utterances over the ranks."""
+    import zonos_vibes_b200 as z
+    from zonos_vibes_b200.replicas import max_over_ranks
+    b = max(1, 16 // world)
+    model = z.Zonos.from_state_dict(z.ZonosConfig.from_dict(hybrid_config_dict()), random_hybrid_state_dict(dev), dev)
+    ctx = model._native()
+    prefix = torch.randn(2 * b, LC, FULL["d_model"], device=dev).bfloat16()
+    model.generate(prefix, max_new_tokens=8, batch_size=b, progress_bar=False, seed=1)
+    model.generate(prefix, max_new_tokens=frames, batch_size=b, progress_bar=False, seed=2)
+    step_ms = max_over_ranks(model.last_step_ms, dev)
+    wb = int(ctx.lib.zb_weight_bytes(ctx.handle))
+    n_attn, n_m = len(HYBRID["attn_layer_idx"]), HYBRID["n_layer"] - len(HYBRID["attn_layer_idx"])
+    di = HYBRID["expand"] * FULL["d_model"]
+    state_bytes = n_m * 2 * b * (2 * (di // HYBRID["headdim"]) * HYBRID["headdim"] * HYBRID["d_state"] * 4)      # ssm state read + write, 2 CFG rows
+    kv_bytes = 2 * b * n_attn * 2 * FULL["num_heads_kv"] * 128 * 2 * (LC + frames / 2)
+    groups = (2 * b + 7) // 8                                       # per-op path: weights re-streamed per group of 8 rows
+    step_bytes = wb * groups + state_bytes + kv_bytes
+    hbm, _, _, kind = peaks_full()
+    gbs = step_bytes / (step_ms * 1e-3) / 1e9
+    del model
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    return {"utterances_total": b * world, "utterances_per_gpu": b, "frames": frames, "us_per_decode_step": step_ms * 1e3,
+            "decode_frames_per_s": b * world / (step_ms * 1e-3), "audio_sec_per_sec": b * world / (step_ms * 1e-3) / FRAME_RATE,
+            "architecture": "synthetic: 46 layers, 5 attention + GatedMLP(8192), 41 Mamba2 (d_state 128, headdim 64, expand 2); dims unverified (SURVEY App. C)",
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm, "peak_kind": kind, "bytes_per_launch": step_bytes,
+                         "kernel": "per-op CUDA graph (k_gemv_mma + k_m2_conv / k_m2_ssm / k_m2_gated_norm + k_attn_decode_mma); bytes = weights x row groups + SSM state r/w + KV"}}
+
+
+def gpu_baseline(dev, steps=48, prefix_frames=1290):
+    """Secondary baseline: the reference ALGORITHM (oracle restatement of zonos/model.py + backbone/_torch.py,
+    plain torch ops) on this same B200 with stock torch kernels (cuBLAS GEMVs + SDPA, eager - the torch backbone of the
+    reference does not use CUDA graphs: model.py `can_use_cudagraphs` is true for the mamba-ssm backbone only), full-size
+    model, decode steps at ctx ~ 1300 incl. sampling.  Not the product path: oracle/ is imported here as a baseline only."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import zonos_oracle as zo
+    cfg = zo.OracleConfig(eos_token_id=1025)
+    sd = {k: v.to(dev) for k, v in zo.synth_state_dict(cfg, 0).items()}
+    prefix = zo.synth_prefix_conditioning(cfg, 1, LC, 1).to(dev)
+    codes = torch.randint(0, 1024, (1, 9, prefix_frames + steps + 16), generator=torch.Generator().manual_seed(3))
+    delayed = zo.apply_delay_pattern(codes, 1025).to(dev)
+    with torch.inference_mode(), torch.device(dev):         # factory functions inside the oracle default to the GPU
+        o = zo.OracleZonos(cfg, sd)
+        params = o.setup_cache(2, LC + delayed.shape[2] + 9)
+        o.freqs_cis = o.freqs_cis.to(dev)
+        for k in params.key_value_memory_dict:
+            params.key_value_memory_dict[k] = params.key_value_memory_dict[k].to(dev)
+        params.lengths_per_sample = params.lengths_per_sample.to(dev)
+        o.prefill(prefix, delayed[..., : prefix_frames + 1], params, 2.0)
+        n0 = LC + prefix_frames + 1
+        params.seqlen_offset += n0
+        params.lengths_per_sample[:] += n0
+
+        def step(s):
+            col = prefix_frames + 1 + s
+            logits = o.decode_one_token(delayed[..., col: col + 1], params, 2.0)
+            zo.sample_from_logits(logits, min_p=0.1, generated_tokens=delayed[..., : col + 1])
+            params.seqlen_offset += 1
+            params.lengths_per_sample[:] += 1
+
+        for s in range(8):
+            step(s)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for s in range(8, 8 + steps):
+            step(s)
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / steps
+        # the same step (fixed context) captured in a CUDA graph and replayed: the GPU time of the stock kernels without the
+        # eager host overhead (an upper bound on what graph capture could give the reference; the reference itself runs
+        # this backbone eagerly)
+        us_graph = None
+        try:
+            col = prefix_frames + 1 + 8 + steps
+            stream = torch.cuda.Stream()
+            stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(stream):
+                for _ in range(2):
+                    zo.sample_from_logits(o.decode_one_token(delayed[..., col: col + 1], params, 2.0), min_p=0.1, generated_tokens=delayed[..., : col + 1])
+            torch.cuda.current_stream().wait_stream(stream)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                zo.sample_from_logits(o.decode_one_token(delayed[..., col: col + 1], params, 2.0), min_p=0.1, generated_tokens=delayed[..., : col + 1])
+            for _ in range(3):
+                graph.replay()
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(steps):
+                graph.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            us_graph = e0.elapsed_time(e1) * 1e3 / steps
+        except Exception as e:  # noqa: BLE001
+            us_graph = None
+            graph_err = repr(e)[:160]
+    del o, sd, params
+    torch.cuda.empty_cache()
+    out = {"us_per_decode_step": us, "decode_frames_per_s": 1e6 / us, "steps_timed": steps, "ctx": [n0 + 8, n0 + 8 + steps],
+           "what": "reference algorithm (oracle port) with stock torch " + torch.__version__ + " CUDA kernels (cuBLAS + SDPA), eager like the "
+                   "reference's torch backbone, same B200, batch 1 + CFG, min-p sampling",
+           "us_per_decode_step_cuda_graph_replay": us_graph}
+    if us_graph is None:
+        out["cuda_graph_error"] = graph_err
+    return out
+
+
+def phase_table(model, ctx, dev, T=192):
+    """Per-phase breakdown of one decode step of k_decode_mega from one TRACED launch (slower instantiation with
+    %globaltimer stamps on CTA 0), outside every timed region: us and algorithmic bytes per phase, layers 1-2 averaged."""
+    import ctypes as C
+    ctx.set_option("trace", 1)
+    ctx.set_option("trace_quiet", 1)
+    try:
+        prefix = torch.randn(2, LC, FULL["d_model"], device=dev).bfloat16()
+        model.generate(prefix, max_new_tokens=T, batch_size=1, progress_bar=False, seed=3)
+        buf = (C.c_uint64 * 64)()
+        n = ctx.lib.zb_last_trace(ctx.handle, buf, 64)
+    finally:
+        ctx.set_option("trace", 0)
+        ctx.set_option("trace_quiet", 0)
+    names = ["ln1_stage", "in_proj", "grid_barrier", "attention", "grid_barrier", "y_stage", "out_proj", "ln2_stage", "fc1", "grid_barrier",
+             "h_stage", "fc2"]
+    if n < 2 + 3 * 12:
+        return None
+    t = [int(buf[i]) for i in range(n)]
+    d, f = FULL["d_model"], FULL["ffn"]
+    qkv = (FULL["num_heads"] + 2 * FULL["num_heads_kv"]) * 128
+    by = {"in_proj": qkv * d * 2, "out_proj": d * d * 2, "fc1": 2 * f * d * 2, "fc2": d * f * 2}
+    acc = {}
+    for layer in (1, 2):
+        base = 2 + 12 * layer
+        for j, nm in enumerate(names):
+            acc[nm] = acc.get(nm, 0.0) + (t[base + j] - t[base + j - 1]) / 2e3
+    rows = [{"phase": nm, "us": round(us, 2), "bytes": by.get(nm, 0), "gbs": round(by[nm] / us / 1e3, 1) if nm in by else None} for nm, us in acc.items()]
+    return {"per_layer_us": round(sum(acc.values()), 2), "phases": rows,
+            "note": "traced instantiation (about 5 % slower than the production kernel); grid_barrier sums the three barriers of a layer; stamps of CTA 0"}
 
 
 def main():

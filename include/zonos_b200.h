@@ -136,7 +136,9 @@ int  zb_decode_logits(zb_ctx* ctx, const int64_t* d_delayed, int B, int L, int c
  * zb_gen_steps: runs up to n_steps iterations of the loop model.py:276-307 entirely on the device
  *   (EOS wind-down and frame write-back included; no host sync inside).  compat_scatter=1 reproduces
  *   masked_scatter_'s sequential routing, 0 = positional.
- * zb_gen_poll: synchronises `stream` and returns loop state. */
+ * zb_gen_poll: returns the loop state after the OLDEST zb_gen_steps call that has not been polled yet (it waits for that
+ *   call only: up to 4 calls may be in flight, so the host can enqueue call k+1 before it waits for call k); with no call
+ *   in flight it synchronises `stream` and reads the current state. */
 int  zb_gen_begin(zb_ctx* ctx, const void* d_prefix, int B, int Lc, int64_t* d_delayed, int L, int prefix_cols,
                   float cfg_scale, const zb_sampling* sp, uint64_t seed, int compat_scatter, void* stream);
 int  zb_gen_steps(zb_ctx* ctx, int n_steps, void* stream);
@@ -185,8 +187,12 @@ int  zb_set_option(zb_ctx* ctx, const char* key, int value);   /* "pdl", "l2_pre
 /* isolated device timing of one kernel family ("in_proj", "attn", "out_proj", "fc1", "fc2"), `iters` launches cycling
  * over the layers, CUDA events on `stream`; total ms in *ms_out (synchronises).  Scratch outputs only. */
 int  zb_bench_kernel(zb_ctx* ctx, const char* name, int iters, float* ms_out, void* stream);
-/* device-timed (CUDA events on `stream`) duration of the last zb_gen_steps call, ms; <0 if none */
+/* device-timed (CUDA events on `stream`) duration of the zb_gen_steps call that the last zb_gen_poll returned, ms; <0 if none */
 float zb_last_steps_ms(zb_ctx* ctx);
+/* bench.py's per-phase table: with options "trace" = 1 and "trace_quiet" = 1 a persistent-kernel launch stamps
+ * %globaltimer (ns) at every phase boundary of one step on CTA 0; this copies those stamps (order documented in
+ * profiles/r02_summary.md) and returns how many there are.  Traced launches use a separate, slower instantiation. */
+int zb_last_trace(zb_ctx* ctx, uint64_t* out, int max_slots);
 
 #ifdef __cplusplus
 }

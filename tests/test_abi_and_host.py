@@ -179,3 +179,57 @@ def test_hybrid_rejects_fp32_residual_and_reads_rotary_cfg():
     import hybrid_oracle as ho
     d = ho.HYBRID_TINY.to_reference_dict()
     assert d["backbone"]["attn_cfg"]["rotary_emb_interleaved"] is False and d["backbone"]["attn_cfg"]["rotary_emb_dim"] == 128
+
+
+_SHARD_WORKER = r"""
+import sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+from zonos_vibes_b200.replicas import generate_sharded
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+
+class FakeDAC:
+    def decode(self, codes):                       # [B, 9, T] -> [B, 1, 512 T]
+        return codes.float().sum(1, keepdim=True).repeat_interleave(512, -1)
+
+class FakeModel:                                   # the interface generate_sharded drives (Zonos.generate / autoencoder.decode)
+    autoencoder, last_step_ms = FakeDAC(), 1.0
+    def generate(self, prefix, max_new_tokens, cfg_scale, batch_size, sampling_params, progress_bar, seed):
+        assert prefix.shape[0] == 2 * batch_size
+        ids = prefix[:batch_size, 0, 0].long()     # utterance id carried in the conditional row
+        assert torch.equal(prefix[batch_size:, 0, 0].long(), -ids - 1)      # cond rows first, then the uncond rows, same order
+        self.last_lengths = [max_new_tokens - int(i) % 3 for i in ids]
+        return ids[:, None, None].expand(batch_size, 9, max_new_tokens).clone()
+
+n = 7
+prefixes = []
+for i in range(n):
+    p = torch.zeros(2, 3 + i % 2, 4)
+    p[0, 0, 0], p[1, 0, 0] = i, -i - 1
+    prefixes.append(p)
+stats = {}
+out = generate_sharded(FakeModel(), prefixes, 10, max_batch=2, stats=stats)
+assert stats["frames"] == sum(10 - i % 3 for i in range(rank, n, world))
+if rank == 0:
+    assert len(out) == n
+    for i, w in enumerate(out):
+        assert tuple(w.shape) == (1, 512 * (10 - i % 3)) and float(w[0, 0]) == 9.0 * i, (i, w.shape)
+    print("SHARD_OK")
+else:
+    assert out is None
+dist.barrier()
+dist.destroy_process_group()
+"""
+
+
+def test_generate_sharded_gloo_world2(tmp_path):
+    """Config 3's multi-utterance driver: utterance i -> rank i mod world, batched per rank, gathered in
+    utterance order on rank 0, no data-path collective - with a stand-in model on CPU (the real one needs a B200)."""
+    script = tmp_path / "s.py"
+    script.write_text(_SHARD_WORKER)
+    r = subprocess.run(
+        [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+         "--master-port", "29541", str(script), ROOT],
+        capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "SHARD_OK" in r.stdout

@@ -74,6 +74,7 @@ SIGNATURES = {
     "zb_set_option": (_I, [_P, C.c_char_p, _I]),
     "zb_bench_kernel": (_I, [_P, C.c_char_p, _I, C.POINTER(_F), _P]),
     "zb_last_steps_ms": (_F, [_P]),
+    "zb_last_trace": (_I, [_P, _P, _I]),
 }
 
 _lib = None

@@ -140,6 +140,8 @@ struct zb_ctx {
   int opt_evict = 1;                   // persistent kernel: weight stream carries the L2 evict_first hint
   int opt_trace = 0;                   // debug: print a per-phase timeline of one step of every persistent launch
   unsigned long long* dbg = nullptr;
+  int opt_trace_quiet = 0;             // 1: traced launches keep their stamps for zb_last_trace instead of printing them
+  std::vector<unsigned long long> last_trace;   // %globaltimer stamps of CTA 0 in the traced step of the last traced launch
 };
 
 namespace {
@@ -527,6 +529,8 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
     std::vector<unsigned long long> hbuf((size_t)c->n_sms * (MG_TRACE_SLOTS + 8) + 16);
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
     cudaMemcpy(hbuf.data(), c->dbg, nb, cudaMemcpyDeviceToHost);
+    c->last_trace.assign(hbuf.begin(), hbuf.begin() + MG_TRACE_SLOTS);
+    if (c->opt_trace_quiet) return cudaSuccess;
     const int ctas[3] = {0, p.dbg_fine == 2 ? 5 : c->n_sms / 2, p.dbg_fine == 2 ? 41 : c->n_sms - 1};
     fprintf(stderr, "[mega trace] mode %d steps %d step %d: ns since step start (cta %d / %d / %d)\n", mode, n_steps, p.dbg_step, ctas[0], ctas[1], ctas[2]);
     for (int i = 0; i < MG_TRACE_SLOTS; ++i) {
@@ -1385,6 +1389,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "gemv") c->opt_gemv = value;
   else if (k == "mega") c->opt_mega = value;
   else if (k == "trace") c->opt_trace = value;
+  else if (k == "trace_quiet") c->opt_trace_quiet = value;
   else if (k == "att_chunk") c->opt_att_chunk = value;
   else if (k == "ll") c->opt_ll = value;
   else if (k == "att_single") c->opt_att_single = value;
@@ -1464,5 +1469,12 @@ int zb_bench_kernel(zb_ctx* c, const char* name, int iters, float* ms_out, void*
 }
 
 float zb_last_steps_ms(zb_ctx* c) { return c ? c->last_ms : -1.f; }
+
+int zb_last_trace(zb_ctx* c, uint64_t* out, int max_slots) {
+  if (!c || !out || max_slots <= 0) return 0;
+  int n = 0;
+  for (; n < (int)c->last_trace.size() && n < max_slots && c->last_trace[n] != 0; ++n) out[n] = c->last_trace[n];
+  return n;
+}
 
 }  // extern "C"
