@@ -569,6 +569,53 @@ def test_hybrid_backbone_plugin_forward(cuda):
     assert bool((err <= 2e-2 * want.abs() + 2e-2 * want.pow(2).mean().sqrt()).all()), (err.max(), want.pow(2).mean().sqrt())
 
 
+@pytest.mark.parametrize("S", [25, 600])
+def test_hybrid_chunked_scan_prefill(cuda, S):
+    """Row a8, prefill branch: the Mamba2 layers of a prefill run as the chunked SSD scan (k_m2_conv_seq +
+    k_m2_ssd_chunked, chunks of 64 tokens, state passed from chunk to chunk), attention layers stepped inside their
+    layer.  Against (1) the oracle's stepped recurrence, which tests/test_oracle_pinned.py pins to the transformers port
+    of mamba-ssm's chunked scan (Mamba2Mixer.torch_forward), and (2) this library's own token-by-token prefill
+    (option chunked_prefill=0): hidden states of the whole prefix AND of 4 decode steps after it (the recurrent state
+    and the KV cache the prefill leaves behind)."""
+    import hybrid_oracle as ho
+    import zonos_vibes_b200 as z
+    cfg = ho.HYBRID_TINY
+    zc = z.ZonosConfig.from_dict(cfg.to_reference_dict())
+    sd_full = ho.synth_hybrid_state_dict(cfg, 0)
+    bb = z.BACKBONES["b200"](zc.backbone).to(cuda, torch.bfloat16)
+    bb.load_state_dict({k[len("backbone."):]: v for k, v in sd_full.items()})
+    x = torch.randn(2, S + 4, cfg.d_model, generator=torch.Generator().manual_seed(12)).bfloat16()
+    oracle = ho.HybridOracleBackbone(cfg, sd_full)
+    oracle.allocate(2, S + 8)
+    want = oracle.forward(x).float()
+
+    def run(chunked):
+        kv = bb.allocate_inference_cache(2, S + 8)
+        bb.native().set_option("chunked_prefill", chunked)
+        params = z.InferenceParams(S + 8, 2, 0, 0, kv, torch.zeros(2, dtype=torch.int32, device=cuda))
+        got = [bb(x[:, :S].to(cuda), params)]
+        params.seqlen_offset += S
+        params.lengths_per_sample[:] += S
+        for t in range(S, S + 4):
+            got.append(bb(x[:, t:t + 1].to(cuda), params))
+            params.seqlen_offset += 1
+            params.lengths_per_sample[:] += 1
+        return torch.cat(got, dim=1).float().cpu()
+
+    try:
+        got = run(1)
+        stepped = run(0)
+    finally:
+        bb.native().set_option("chunked_prefill", 1)
+    assert got.shape == want.shape
+    rms = want.pow(2).mean().sqrt()
+    err = (got - want).abs()
+    assert bool((err <= 2e-2 * want.abs() + 2e-2 * rms).all()), (err.max(), rms)
+    err2 = (got - stepped).abs()
+    print(f"[chunked scan] S={S}: max |chunked - oracle| {err.max():.4f}, max |chunked - stepped| {err2.max():.4f} (rms {rms:.3f})")
+    assert bool((err2 <= 2e-2 * stepped.abs() + 2e-2 * rms).all()), err2.max()       # bf16 rounding flips cascade over 600 tokens
+
+
 def test_hybrid_generate_runs_and_is_deterministic(cuda):
     import hybrid_oracle as ho
     import zonos_vibes_b200 as z

@@ -43,6 +43,7 @@ struct zb_dac {
   int ew_k1 = 8;            // ... on k=1 layers
   int wide_cout = 768;      // layers with Cout >= this run on the one-tile-per-CTA kernel (impl 0)
   int mt2_min_waves = 8;    // 256-row tiles only when that still leaves this many tiles per SM
+  int k1_wide = 1;          // k = 1 layers: all output channels in one tile (A/B switch)
   int max_group = 8;        // utterances decoded together: one launch per layer covers all their tiles (workspace = 5 x 49152 x T x group halves)
   float conv2_bias_h = 0.f; // host copy of decoder.conv2.bias (read back once in zb_dac_finalize)
   ZbErr err;
@@ -252,20 +253,26 @@ int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int nb, int T_in, const
   p.m_rows = c.stride > 1 ? T_in + 1 : T_in;
   p.Cout = c.Cout;
   p.n_tile = c.Cout % 128 == 0 ? 128 : c.Cout % 96 == 0 ? 96 : c.Cout % 64 == 0 ? 64 : 32;
+  // k = 1 layers are pure streams (Y + residual in, raw + activated out; the weights are nothing): every output-channel
+  // tile re-reads the whole activation window, so they take ALL channels in one tile (up to 256 accumulator columns,
+  // 128-row tiles) - the ncu capture of the 192-channel k = 1 layer showed 846 MB read where 506 MB are needed
+  // (profiles/r02_summary.md).  384 channels: two tiles of 192 instead of three of 128.
+  const bool k1 = c.K == 1 && c.stride == 1 && d->k1_wide;
+  if (k1) p.n_tile = c.Cout <= 256 ? c.Cout : (c.Cout % 192 == 0 ? 192 : p.n_tile);
   p.n_tiles = c.Cout / p.n_tile;
   p.phases = c.stride > 1 ? c.stride : 1;
-  p.acc_cols = 128; p.acc_stages = 2;
+  p.acc_cols = k1 ? 256 : 128; p.acc_stages = 2;
   // 256-row tiles halve the weight traffic; keep 128-row tiles when there would be too few tiles to balance 148 SMs
   p.nb = nb;
   const long tiles2 = (long)((p.m_rows + 2 * TC_BM - 1) / (2 * TC_BM)) * p.n_tiles * p.phases * nb;
-  p.mt = tiles2 >= (long)d->mt2_min_waves * ZB_NUM_SMS ? 2 : 1;
+  p.mt = (!k1 && tiles2 >= (long)d->mt2_min_waves * ZB_NUM_SMS) ? 2 : 1;
   p.m_tiles = (p.m_rows + p.mt * TC_BM - 1) / (p.mt * TC_BM);
   p.lead = c.stride > 1 ? p.ntaps - 1 : c.pad;
   const int win_rows = p.mt * TC_BM + (c.stride > 1 ? p.ntaps - 1 : (c.K - 1) * c.dil);
   p.n_aload = win_rows > 256 ? 2 : 1;
   p.box_rows = (((win_rows + p.n_aload - 1) / p.n_aload) + 7) & ~7;
   p.a_bytes = p.n_aload * p.box_rows * 128;
-  p.a_slots = p.kchunks >= 3 ? 3 : 2;
+  p.a_slots = k1 ? TC2_MAX_A_SLOTS : (p.kchunks >= 3 ? 3 : 2);      // k = 1: bytes in flight are what bounds the stream
   const int b_bytes = p.n_tile * 128;
   const int budget = 227 * 1024 - 1024 - 512 - TC2_TAB_BYTES;
   if (p.a_slots * p.a_bytes + 4 * b_bytes > budget) p.a_slots = 2;
@@ -542,6 +549,7 @@ int zb_dac_set_option(zb_dac* d, const char* key, int value) {
   }
   if (k == "wide_cout") { d->wide_cout = value; return ZB_OK; }
   if (k == "mt2_min_waves") { d->mt2_min_waves = value; return ZB_OK; }
+  if (k == "k1_wide") { d->k1_wide = value; return ZB_OK; }
   if (k == "max_group") { d->max_group = value < 1 ? 1 : value; return ZB_OK; }
   return d->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
 }

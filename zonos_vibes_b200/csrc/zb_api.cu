@@ -108,6 +108,11 @@ struct zb_ctx {
   std::vector<LayerM> mlayers;
   int m_dinner = 0, m_nheads = 0, m_convdim = 0, m_dinproj = 0;
   float *m_conv_state = nullptr, *m_ssm_state = nullptr, *m_xbc = nullptr;
+  // layer-major prefill workspace of the hybrid backbone (token-major activations of the whole prefix, grown on demand)
+  bf16 *pf_x = nullptr, *pf_zx = nullptr, *pf_y = nullptr, *pf_yn = nullptr;
+  float* pf_xbc = nullptr;
+  int pf_M = 0;
+  int opt_chunked_prefill = 1;         // hybrid: prefill Mamba2 layers with the chunked SSD scan (0 = step token by token)
   bf16 *m_zx = nullptr, *m_y = nullptr, *m_ynorm = nullptr;
   // batched tcgen05 path (bt_kernels.cuh): rows >= opt_bt_min_rows
   typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -325,17 +330,13 @@ cudaError_t enqueue_mamba_layer(zb_ctx* c, int l, const std::vector<Pass>& passe
   return cudaSuccess;
 }
 
-// all transformer layers for the current token (x in c->x, positions in device state)
-cudaError_t enqueue_layers(zb_ctx* c, const std::vector<Pass>& passes, cudaStream_t s, bool heads_follow) {
+// one attention + GatedMLP layer for the current token (x in c->x, positions in device state)
+cudaError_t enqueue_attn_layer(zb_ctx* c, int l, const std::vector<Pass>& passes, cudaStream_t s, bool heads_follow) {
   const zb_config& g = c->cfg;
   const int d = g.d_model, H = g.num_heads, Hkv = g.num_heads_kv, F = g.ffn;
   const int q_size = H * ZB_DH, kv_size = Hkv * ZB_DH;
   cudaError_t e;
-  for (int l = 0; l < g.n_layer; ++l) {
-    if (c->is_mamba[l]) {
-      if ((e = enqueue_mamba_layer(c, l, passes, s)) != cudaSuccess) return e;
-      continue;
-    }
+  {
     const LayerW& w = c->layers[l];
     bf16* kv_layer = c->kv + (size_t)c->kv_slot[l] * c->kv_layer_elems;
     for (const Pass& ps : passes) {   // LN1 + in_proj + RoPE + KV append
@@ -381,6 +382,16 @@ cudaError_t enqueue_layers(zb_ctx* c, const std::vector<Pass>& passes, cudaStrea
       set_prefetch(c, p, nx);
       if ((e = launch_gemv(c, EPI_RESID, ps, p, s)) != cudaSuccess) return e;
     }
+  }
+  return cudaSuccess;
+}
+
+// all layers for the current token (x in c->x, positions in device state)
+cudaError_t enqueue_layers(zb_ctx* c, const std::vector<Pass>& passes, cudaStream_t s, bool heads_follow) {
+  cudaError_t e;
+  for (int l = 0; l < c->cfg.n_layer; ++l) {
+    e = c->is_mamba[l] ? enqueue_mamba_layer(c, l, passes, s) : enqueue_attn_layer(c, l, passes, s, heads_follow);
+    if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
 }
@@ -730,6 +741,101 @@ cudaError_t enqueue_bt_heads(zb_ctx* c, float* logits, cudaStream_t s) {
   return launch(c, k_bt_heads_finish, dim3(g.n_codebooks, c->rows / 2), dim3(256), 0, s, f);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// hybrid backbone: layer-major prefill of S tokens.  Mamba2 layers run in their SEQUENCE form (in_proj over all token
+// rows, depthwise conv over the sequence, chunked SSD scan, gated norm, out_proj); the attention layers (5 of 46 in the
+// benchmarked stack) are stepped token by token inside their layer.  Reference: mamba_ssm Mamba2.forward as wired by
+// zonos/backbone/_mamba_ssm.py:15-57.  Activations are token-major: row a = t * rows + r.
+// ---------------------------------------------------------------------------------------------------------------
+int ensure_prefill_ws(zb_ctx* c, int M) {
+  if (M <= c->pf_M) return ZB_OK;
+  ZB_CUDA(c->err, cudaDeviceSynchronize());
+  for (void* q : {(void*)c->pf_x, (void*)c->pf_zx, (void*)c->pf_y, (void*)c->pf_yn, (void*)c->pf_xbc}) if (q) cudaFree(q);
+  c->pf_x = c->pf_zx = c->pf_y = c->pf_yn = nullptr; c->pf_xbc = nullptr; c->pf_M = 0;
+  const size_t Mp = ((size_t)M + 7) / 8 * 8;
+  ZB_CUDA(c->err, cudaMalloc((void**)&c->pf_x, Mp * c->cfg.d_model * 2));
+  ZB_CUDA(c->err, cudaMalloc((void**)&c->pf_zx, Mp * c->m_dinproj * 2));
+  ZB_CUDA(c->err, cudaMalloc((void**)&c->pf_y, Mp * c->m_dinner * 2));
+  ZB_CUDA(c->err, cudaMalloc((void**)&c->pf_yn, Mp * c->m_dinner * 2));
+  ZB_CUDA(c->err, cudaMalloc((void**)&c->pf_xbc, Mp * c->m_convdim * 4));
+  ZB_CUDA(c->err, cudaMemset(c->pf_yn, 0, Mp * c->m_dinner * 2));
+  c->pf_M = M;
+  return ZB_OK;
+}
+
+int hybrid_prefill(zb_ctx* c, const bf16* d_in, bf16* d_out, int S, int pos0, const int* d_lengths, cudaStream_t s) {
+  const zb_config& g = c->cfg;
+  const int rows = c->rows, d = g.d_model, M = rows * S;
+  int rc = ensure_prefill_ws(c, M);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    ZB_CUDA(c->err, cudaFuncSetAttribute(k_m2_ssd_chunked, cudaFuncAttributeMaxDynamicSharedMemorySize, M2_SSD_SMEM));
+    attr_set = true;
+  }
+  const bool pdl = c->opt_pdl;
+  c->opt_pdl = 0;                                   // plain stream order between the sequence kernels
+  auto restore = [&](int r) { c->opt_pdl = pdl; return r; };
+  ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, pos0, d_lengths, 0));
+  k_m2_gather_tm<<<M, 256, 0, s>>>(d_in, c->pf_x, rows, S, d);
+  const std::vector<Pass> all = plain_passes(M), tok = plain_passes(rows);
+  for (int l = 0; l < g.n_layer; ++l) {
+    cudaError_t e = cudaSuccess;
+    if (c->is_mamba[l]) {
+      const LayerM& w = c->mlayers[l];
+      for (const Pass& ps : all) {                  // LN + in_proj over all token rows
+        GemvParams p = base_params(c, ps);
+        p.W = w.w_in; p.K = d; p.n_tasks = c->m_dinproj / 2; p.row0_mul = 2; p.row1_off = 1;
+        p.x = c->pf_x; p.ln_w = w.ln_w; p.ln_b = w.ln_b; p.out = c->pf_zx; p.out_stride = c->m_dinproj;
+        if ((e = launch_gemv(c, EPI_PLAIN, ps, p, s)) != cudaSuccess) break;
+      }
+      if (e != cudaSuccess) return restore(c->err.fail(ZB_ERR_CUDA, "hybrid prefill in_proj: %s", cudaGetErrorString(e)));
+      M2SeqParams q;
+      memset(&q, 0, sizeof(q));
+      q.zx = c->pf_zx; q.rows = rows; q.S = S; q.d_in_proj = c->m_dinproj; q.d_inner = c->m_dinner; q.conv_dim = c->m_convdim;
+      q.d_conv = c->hyb.d_conv; q.nheads = c->m_nheads; q.headdim = c->hyb.headdim; q.d_state = c->hyb.d_state; q.ngroups = c->hyb.ngroups;
+      q.conv_w = w.conv_w; q.conv_b = w.conv_b; q.dt_bias = w.dt_bias; q.A_log = w.A_log; q.D = w.D;
+      const int slot = c->kv_slot[l];
+      q.conv_state = c->m_conv_state + (size_t)slot * rows * c->m_convdim * c->hyb.d_conv;
+      q.ssm_state = c->m_ssm_state + (size_t)slot * rows * c->m_nheads * c->hyb.headdim * c->hyb.d_state;
+      q.xbc = c->pf_xbc; q.y = c->pf_y;
+      k_m2_conv_seq<<<dim3((c->m_convdim + 255) / 256, rows), 256, 0, s>>>(q);
+      k_m2_ssd_chunked<<<dim3(c->m_nheads, rows), 256, M2_SSD_SMEM, s>>>(q);
+      M2Params m;
+      memset(&m, 0, sizeof(m));
+      m.zx = c->pf_zx; m.d_in_proj = c->m_dinproj; m.d_inner = c->m_dinner; m.y = c->pf_y; m.ynorm = c->pf_yn; m.norm_w = w.norm_w;
+      m.eps = 1e-5f; m.st = c->st;
+      if ((e = launch(c, k_m2_gated_norm, dim3(M), dim3(256), 0, s, m)) != cudaSuccess)
+        return restore(c->err.fail(ZB_ERR_CUDA, "hybrid prefill gated norm: %s", cudaGetErrorString(e)));
+      c->launches += 3;
+      for (const Pass& ps : all) {                  // out_proj + residual
+        GemvParams p = base_params(c, ps);
+        p.W = w.w_out; p.K = c->m_dinner; p.n_tasks = d / 2; p.row0_mul = 2; p.row1_off = 1;
+        p.x = c->pf_yn; p.out = c->pf_x; p.out_stride = d;
+        if ((e = launch_gemv(c, EPI_RESID, ps, p, s)) != cudaSuccess) break;
+      }
+      if (e != cudaSuccess) return restore(c->err.fail(ZB_ERR_CUDA, "hybrid prefill out_proj: %s", cudaGetErrorString(e)));
+    } else {
+      for (int t = 0; t < S; ++t) {                 // attention + GatedMLP layer: token by token (KV position = pos0 + t)
+        if ((e = launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, pos0 + t, d_lengths, t)) != cudaSuccess) break;
+        if ((e = cudaMemcpyAsync(c->x, c->pf_x + (size_t)t * rows * d, (size_t)rows * d * 2, cudaMemcpyDeviceToDevice, s)) != cudaSuccess) break;
+        if ((e = enqueue_attn_layer(c, l, tok, s, false)) != cudaSuccess) break;
+        if ((e = cudaMemcpyAsync(c->pf_x + (size_t)t * rows * d, c->x, (size_t)rows * d * 2, cudaMemcpyDeviceToDevice, s)) != cudaSuccess) break;
+      }
+      if (e != cudaSuccess) return restore(c->err.fail(ZB_ERR_CUDA, "hybrid prefill attention layer: %s", cudaGetErrorString(e)));
+    }
+  }
+  if (d_out) {
+    for (int t = 0; t < S; ++t)
+      ZB_CUDA(c->err, launch(c, k_final_ln, dim3(rows), dim3(256), 0, s, (const bf16*)(c->pf_x + (size_t)t * rows * d), (const bf16*)c->normf_w,
+                             (const bf16*)c->normf_b, g.norm_eps, d_out, d, S, t));
+  }
+  // leave the device state positioned after the appended tokens
+  ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, pos0 + S, d_lengths, S));
+  ZB_CUDA(c->err, cudaGetLastError());
+  return restore(ZB_OK);
+}
+
 void drop_graph(zb_ctx* c) {
   if (c->graph) { cudaGraphExecDestroy(c->graph); c->graph = nullptr; }
   c->graph_nodes = 0;
@@ -976,6 +1082,7 @@ int zb_ctx_destroy(zb_ctx* c) {
   if (c->bar_counter) cudaFree(c->bar_counter);
   if (c->x_ll) cudaFree(c->x_ll);
   if (c->att_ll) cudaFree(c->att_ll);
+  for (void* q : {(void*)c->pf_x, (void*)c->pf_zx, (void*)c->pf_y, (void*)c->pf_yn, (void*)c->pf_xbc}) if (q) cudaFree(q);
   if (c->dbg) cudaFree(c->dbg);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
@@ -1114,6 +1221,8 @@ int zb_backbone_forward(zb_ctx* c, const void* d_in, void* d_out, int rows, int 
     ZB_CUDA(c->err, launch_mega(c, MG_MODE_HIDDEN, S, rows, 0, nullptr, d_in, d_out, S, 0, s));   // advances pos / rope_pos by S
     return ZB_OK;
   }
+  if (c->hybrid && S > 1 && c->opt_chunked_prefill && c->hyb.d_state == 128 && c->hyb.headdim == 64)
+    return hybrid_prefill(c, (const bf16*)d_in, (bf16*)d_out, S, seqlen_offset, (const int*)d_lengths, s);
   const std::vector<Pass> passes = plain_passes(rows);
   int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
   for (int t = 0; t < S; ++t) {
@@ -1253,11 +1362,15 @@ int zb_gen_begin(zb_ctx* c, const void* d_prefix, int B, int Lc, int64_t* d_dela
     // the prefix is exactly what a sequence of single-token steps computes.
     const std::vector<Pass> passes = cfg_passes(B);
     int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
-    for (int t = 0; t < Lc; ++t) {
-      ZB_CUDA(c->err, launch(c, k_load_hidden, dim3(2 * B), dim3(thr), 0, s, (const bf16*)d_prefix, c->x, g.d_model, Lc, t));
-      if (use_bt(c, 2 * B)) ZB_CUDA(c->err, enqueue_bt_layers(c, s));
-      else ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
-      ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
+    if (c->hybrid && Lc > 1 && c->opt_chunked_prefill && c->hyb.d_state == 128 && c->hyb.headdim == 64) {
+      if ((rc = hybrid_prefill(c, (const bf16*)d_prefix, nullptr, Lc, 0, nullptr, s))) return rc;      // leaves pos = rope_pos = Lc
+    } else {
+      for (int t = 0; t < Lc; ++t) {
+        ZB_CUDA(c->err, launch(c, k_load_hidden, dim3(2 * B), dim3(thr), 0, s, (const bf16*)d_prefix, c->x, g.d_model, Lc, t));
+        if (use_bt(c, 2 * B)) ZB_CUDA(c->err, enqueue_bt_layers(c, s));
+        else ZB_CUDA(c->err, enqueue_layers(c, passes, s, false));
+        ZB_CUDA(c->err, launch(c, k_advance, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, c->rows));
+      }
     }
     for (int j = 0; j + 1 < prefix_cols; ++j) {      // known audio-prefix columns: no sampling
       h.pos = Lc + j; h.col = j;
@@ -1396,6 +1509,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "ring") c->opt_ring = value;
   else if (k == "psleep") c->opt_psleep = value;
   else if (k == "evict") c->opt_evict = value;
+  else if (k == "chunked_prefill") c->opt_chunked_prefill = value;
   else if (k == "bt_min_rows") c->opt_bt_min_rows = value;
   else if (k == "attn_mma") c->opt_attn_mma = value;
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
