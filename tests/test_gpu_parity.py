@@ -376,17 +376,22 @@ def test_logit_error_is_bf16_noise_full_size(golden, golden_long, cuda):
     assert e_got <= 1.5 * e_ref + 1e-4, (e_got, e_ref)
 
 
-@pytest.mark.parametrize("ll", [1, 0])
+AP_PATHS = {"block_prefill": dict(), "forced_ll": dict(bt_prefill=0), "forced_barriers": dict(bt_prefill=0, ll=0)}
+
+
+@pytest.mark.parametrize("path", list(AP_PATHS))
 @pytest.mark.parametrize("p", [5, 300])
-def test_generate_with_audio_prefix(golden_long, cuda, p, ll):
-    """generate(audio_prefix_codes=...) (model.py:246-264): the known prefix columns run through the persistent kernel
-    in MG_MODE_FORCED.  Greedy stream against the reference's own generate with the same prefix; also run twice (a race
+def test_generate_with_audio_prefix(golden_long, cuda, p, path):
+    """generate(audio_prefix_codes=...) (model.py:246-264): the known prefix columns are embedded and prefilled as blocks
+    of token rows on the batched tcgen05 path (default), or run through the persistent kernel in MG_MODE_FORCED
+    (bt_prefill=0, with and without the epoch-tagged residual stream).  Greedy stream against the reference's own generate with the same prefix; also run twice (a race
     between CTA 0's embed-ahead and the other CTAs' fc2 epilogues would show up as run-to-run variation)."""
     m = make_model("small", cuda)
     prefix = zo.synth_prefix_conditioning(zo.SMALL_CONFIG, 1, 6, 1).to(cuda)
     apc = golden_long[f"prefix.p{p}.audio_prefix_codes"].to(cuda)
     want_d, want_l = golden_long[f"prefix.p{p}.delayed"], golden_long[f"prefix.p{p}.logits"]
-    with _options(m, ll=ll):
+    ll = path
+    with _options(m, **AP_PATHS[path]):
         out = m.generate(prefix, audio_prefix_codes=apc, max_new_tokens=24, sampling_params=dict(temperature=0), progress_bar=False)
         d1 = m.last_delayed_codes.clone()
         out2 = m.generate(prefix, audio_prefix_codes=apc, max_new_tokens=24, sampling_params=dict(temperature=0), progress_bar=False)
@@ -402,9 +407,10 @@ def test_generate_with_audio_prefix(golden_long, cuda, p, ll):
         assert_logits_close(got[s], want_l[s:s + 1], f"small audio prefix p={p} step {s}")
 
 
-def test_generate_with_long_audio_prefix_full_size(golden_long, cuda):
-    """Full-size model, audio prefix of 1290 frames through MG_MODE_FORCED (KV cache of 1 315 tokens built by the
-    persistent kernel's forced steps), then the prefill sample: codebook 0 of column p+1 is the argmax of the
+@pytest.mark.parametrize("path", ["block_prefill", "forced_ll"])
+def test_generate_with_long_audio_prefix_full_size(golden_long, cuda, path):
+    """Full-size model, audio prefix of 1290 frames (KV cache of 1 315 tokens built by the block prefill on the batched
+    tcgen05 path - 21 blocks of 64 tokens - or by the persistent kernel's forced steps), then the prefill sample: codebook 0 of column p+1 is the argmax of the
     reference's prefill logits wherever that argmax is outside the bf16 band; twice for reproducibility."""
     p = 1290
     m = make_model("full", cuda)
@@ -412,9 +418,10 @@ def test_generate_with_long_audio_prefix_full_size(golden_long, cuda):
     delayed = golden_long[f"long.p{p}.delayed"]
     apc = zo.revert_delay_pattern(delayed)[..., :p].to(cuda)
     outs = []
-    for _ in range(2):
-        m.generate(prefix, audio_prefix_codes=apc, max_new_tokens=8, sampling_params=dict(temperature=0), progress_bar=False)
-        outs.append(m.last_delayed_codes.clone().cpu())
+    with _options(m, **AP_PATHS[path]):
+        for _ in range(2):
+            m.generate(prefix, audio_prefix_codes=apc, max_new_tokens=8, sampling_params=dict(temperature=0), progress_bar=False)
+            outs.append(m.last_delayed_codes.clone().cpu())
     assert torch.equal(outs[0], outs[1]), "forced-prefix generation is not reproducible"
     assert torch.equal(outs[0][..., :p + 1], delayed[..., :p + 1])
     lg = golden_long[f"long.p{p}.logits"][0, 0]                  # prefill logits of codebook 0 (no bias, no penalty)
@@ -429,7 +436,7 @@ def test_generate_with_long_audio_prefix_full_size(golden_long, cuda):
 class _options:
     def __init__(self, model, **kw):
         self.ctx, self.kw = model._native(), kw
-        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=1)
+        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=1, bt_prefill=1)
 
     def __enter__(self):
         for k, v in self.kw.items():

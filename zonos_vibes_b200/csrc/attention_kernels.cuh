@@ -25,6 +25,8 @@ struct AttnParams {
   int* counters;            // [rows][Hkv], zero before launch; reset by the merging CTA
   const ZbDevState* st;
   float scale_log2;         // (1/sqrt(Dh)) * log2(e)
+  int vrows;                // 0: row = cache row, ctx = pos + 1.  > 0 (block prefill): activation row a is token a / vrows of cache
+                            // row a % vrows and attends positions [0, pos + a / vrows] - causal attention over the block
 };
 
 __device__ __forceinline__ void att_unpack8(const uint4& raw, float (&v)[8]) {
@@ -161,7 +163,8 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode(const AttnParams p)
   const int split = blockIdx.x, nsplit = gridDim.x, kvh = blockIdx.y, row = blockIdx.z;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int half = lane >> 4, l16 = lane & 15;
-  const int ctx = p.st->pos + 1;
+  const int crow = p.vrows ? row % p.vrows : row;
+  const int ctx = p.st->pos + 1 + (p.vrows ? row / p.vrows : 0);
   int chunk = (ctx + nsplit - 1) / nsplit;
   chunk = (chunk + 7) & ~7;
   const int t0 = split * chunk;
@@ -183,7 +186,7 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode(const AttnParams p)
     for (int j = 0; j < 8; ++j) acc[g][j] = 0.f;
   }
 
-  const int* pt = p.page_table + (size_t)row * p.max_pages;
+  const int* pt = p.page_table + (size_t)crow * p.max_pages;
   const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;             // elements between kv heads in a page
   const size_t kv_stride = (size_t)p.Hkv * head_stride;           // K -> V inside a page
   const size_t page_stride = 2 * kv_stride;
@@ -332,7 +335,8 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode_mma(const AttnParam
   const int split = blockIdx.x, nsplit = gridDim.x, kvh = blockIdx.y, row = blockIdx.z;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, t = lane & 3;
-  const int ctx = p.st->pos + 1;
+  const int crow = p.vrows ? row % p.vrows : row;
+  const int ctx = p.st->pos + 1 + (p.vrows ? row / p.vrows : 0);
   int chunk = (ctx + nsplit - 1) / nsplit;
   chunk = (chunk + 15) & ~15;                                     // 16-token groups never straddle a page (ZB_PAGE % 16 == 0)
   const int t0 = split * chunk;
@@ -349,7 +353,7 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode_mma(const AttnParam
 #pragma unroll
   for (int j = 0; j < 8; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
 
-  const int* pt = p.page_table + (size_t)row * p.max_pages;
+  const int* pt = p.page_table + (size_t)crow * p.max_pages;
   const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
   const size_t kv_stride = (size_t)p.Hkv * head_stride;
   const size_t page_stride = 2 * kv_stride;

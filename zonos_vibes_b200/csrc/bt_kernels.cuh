@@ -220,6 +220,7 @@ struct BtFinishParams {
   float* logits;             // [B][n_q][V]
   int n_q, V, eos, B;
   const ZbDevState* st;
+  int vrows;                 // > 0 (block prefill): activation row a = token a / vrows of cache row a % vrows, position pos + a / vrows
 };
 
 __device__ __forceinline__ float bt_split_sum(const float* partial, int splits, size_t split_stride, size_t off) {
@@ -307,10 +308,11 @@ __global__ void __launch_bounds__(256) k_bt_qkv_finish(const BtFinishParams p) {
   pdl_wait_prior_grid();
   if (p.st->done) return;
   const int row = blockIdx.x;
-  const int pos = p.st->pos;
+  const int crow = p.vrows ? row % p.vrows : row, tok = p.vrows ? row / p.vrows : 0;
+  const int pos = p.st->pos + tok;
   const size_t split_stride = (size_t)p.m_pad * p.N;
-  const int page = p.page_table[(size_t)row * p.max_pages + pos / ZB_PAGE];
-  const float* cs_row = p.rope + (size_t)p.rope_pos[row] * (ZB_DH / 2) * 2;
+  const int page = p.page_table[(size_t)crow * p.max_pages + pos / ZB_PAGE];
+  const float* cs_row = p.rope + (size_t)(p.rope_pos[crow] + tok) * (ZB_DH / 2) * 2;
   for (int n8 = threadIdx.x * 8; n8 < p.N; n8 += 2048) {
     float a[8];
     bt_split_sum8(p.partial, p.splits, split_stride, (size_t)row * p.N + n8, a);

@@ -353,6 +353,29 @@ __global__ void k_embed(const bf16* __restrict__ emb /*[n_q][vocab_rows][d]*/, c
   }
 }
 
+// Embedding of P known delayed-code columns at once (the audio prefix of model.py:246-255): out[b][j] = out[B + b][j] =
+// embed_codes(delayed[b, :, j]), out is [2B][P][d] like a prefix_conditioning block.  grid = (P, B).
+__global__ void k_embed_cols(const bf16* __restrict__ emb, const long long* __restrict__ delayed, bf16* __restrict__ out, int d, int n_q,
+                             int emb_rows, int B, int L, int P) {
+  const int j = blockIdx.x, b = blockIdx.y;
+  for (int e = threadIdx.x * 8; e < d; e += blockDim.x * 8) {
+    float acc[8];
+    for (int k = 0; k < n_q; ++k) {
+      long long id = delayed[((size_t)b * n_q + k) * L + j];
+      id = id < 0 ? 0 : (id >= emb_rows ? emb_rows - 1 : id);
+      const uint4 raw = *reinterpret_cast<const uint4*>(emb + ((size_t)k * emb_rows + id) * d + e);
+      const float v[8] = {bf16lo(raw.x), bf16hi(raw.x), bf16lo(raw.y), bf16hi(raw.y), bf16lo(raw.z), bf16hi(raw.z), bf16lo(raw.w), bf16hi(raw.w)};
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc[q] = k == 0 ? v[q] : bf16_round(acc[q] + v[q]);
+    }
+    __nv_bfloat162 o[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) o[q] = __floats2bfloat162_rn(acc[2 * q], acc[2 * q + 1]);
+    *reinterpret_cast<uint4*>(out + ((size_t)b * P + j) * d + e) = *reinterpret_cast<uint4*>(o);
+    *reinterpret_cast<uint4*>(out + ((size_t)(b + B) * P + j) * d + e) = *reinterpret_cast<uint4*>(o);
+  }
+}
+
 // x[r] <- src[r, s, :]  (prefill / plugin forward: feed given hidden states)
 __global__ void k_load_hidden(const bf16* __restrict__ src, bf16* __restrict__ x, int d, int S, int s) {
   pdl_launch_dependents();

@@ -332,3 +332,8 @@ __global__ void k_m2_gather_tm(const bf16* __restrict__ in, bf16* __restrict__ X
   for (int e = threadIdx.x * 8; e < d; e += blockDim.x * 8)
     *reinterpret_cast<uint4*>(X + (size_t)a * d + e) = *reinterpret_cast<const uint4*>(in + ((size_t)r * S + t) * d + e);
 }
+__global__ void k_bt_scatter_tm(const bf16* __restrict__ X, bf16* __restrict__ out, int rows, int S, int d) {
+  const int a = blockIdx.x, t = a / rows, r = a % rows;
+  for (int e = threadIdx.x * 8; e < d; e += blockDim.x * 8)
+    *reinterpret_cast<uint4*>(out + ((size_t)r * S + t) * d + e) = *reinterpret_cast<const uint4*>(X + (size_t)a * d + e);
+}

@@ -120,6 +120,10 @@ struct zb_ctx {
                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
   EncodeTiledFn encode = nullptr;
   int opt_bt_min_rows = 9;
+  int opt_bt_prefill = 1;              // transformer: prefill blocks of tokens as extra rows of the batched tcgen05 path
+  bf16* pf_embed = nullptr;            // block prefill of an audio prefix: embedded prefix columns [rows][P][d]
+  size_t pf_embed_elems = 0;
+  int bt_vM = 0, bt_vrows = 0;         // block prefill in progress: bt_vM activation rows = tokens x bt_vrows cache rows
   bool bt_ready = false;
   int bt_mpad = 0;
   bf16* bt_xn = nullptr;
@@ -662,10 +666,11 @@ cudaError_t bt_gemm(zb_ctx* c, const CUtensorMap& mx, const CUtensorMap& mw, int
   if (mode == BT_MODE_SWIGLU) { pl.splits = 1; pl.kb_per_split = pl.num_kb; }
   BtGemmParams p;
   memset(&p, 0, sizeof(p));
-  p.M = c->rows; p.N = N; p.num_kb = pl.num_kb; p.kb_per_split = pl.kb_per_split; p.mode = mode;
+  const int Mrows = c->bt_vM ? c->bt_vM : c->rows;
+  p.M = Mrows; p.N = N; p.num_kb = pl.num_kb; p.kb_per_split = pl.kb_per_split; p.mode = mode;
   p.partial = c->bt_partial; p.m_pad = c->bt_mpad; p.h = c->h; p.st = c->st;
   if (splits_out) *splits_out = pl.splits;
-  const dim3 grid(n_tiles, (c->rows + BT_BM - 1) / BT_BM, pl.splits);
+  const dim3 grid(n_tiles, (Mrows + BT_BM - 1) / BT_BM, pl.splits);
   return launch(c, k_bt_gemm, grid, dim3(BT_THREADS), (size_t)BT_SMEM_BYTES, s, mx, mw, p);
 }
 
@@ -678,6 +683,7 @@ BtFinishParams bt_finish_params(zb_ctx* c, int splits, int N) {
   f.q = c->q; f.page_table = c->page_table; f.max_pages = c->max_pages; f.Hkv = g.num_heads_kv;
   f.q_size = g.num_heads * ZB_DH; f.kv_size = g.num_heads_kv * ZB_DH; f.rope = c->rope; f.rope_pos = c->rope_pos;
   f.logits = c->logits; f.n_q = g.n_codebooks; f.V = g.vocab; f.eos = g.eos_token_id; f.B = c->rows / 2; f.st = c->st;
+  f.vrows = c->bt_vrows;
   return f;
 }
 
@@ -686,7 +692,7 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
   const zb_config& g = c->cfg;
   const int d = g.d_model, H = g.num_heads, Hkv = g.num_heads_kv, F = g.ffn;
   const int q_size = H * ZB_DH, qkv = (H + 2 * Hkv) * ZB_DH;
-  const int rows = c->rows;
+  const int rows = c->bt_vM ? c->bt_vM : c->rows;
   const size_t ln_smem = (size_t)d * 4;
   cudaError_t e;
   {
@@ -710,7 +716,9 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
       a.q = c->q; a.kv_layer = kv_layer; a.page_table = c->page_table; a.max_pages = c->max_pages;
       a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
       a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
-      if ((e = launch(c, attn_kernel(H / Hkv, c->opt_attn_mma != 0), dim3(c->nsplit, Hkv, rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
+      a.vrows = c->bt_vrows;
+      // block prefill: one split per (token row, kv head) - no partial buffers or tickets (they are sized for the cache rows)
+      if ((e = launch(c, attn_kernel(H / Hkv, c->opt_attn_mma != 0), dim3(c->bt_vM ? 1 : c->nsplit, Hkv, rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
     }
     if ((e = bt_gemm(c, c->bt_map_y, c->bt_map_out[l], d, q_size, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
     {
@@ -834,6 +842,33 @@ int hybrid_prefill(zb_ctx* c, const bf16* d_in, bf16* d_out, int S, int pos0, co
   ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, pos0 + S, d_lengths, S));
   ZB_CUDA(c->err, cudaGetLastError());
   return restore(ZB_OK);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// transformer: prefill of S tokens as BLOCKS of extra activation rows on the batched tcgen05 path.  A block of
+// Sc = rows_pad / rows tokens is M = Sc * rows activation rows (row a = token a / rows of cache row a % rows): the GEMMs
+// stream every weight once per block instead of once per token, k_bt_qkv_finish appends the K/V of all the block's tokens
+// at their own positions, and the decode attention kernel run with per-row context lengths IS causal attention over the
+// block.  Reference: Zonos._prefill -> one batched forward (model.py:181-196).  25 tokens: 27 ms -> ~1 ms.
+// ---------------------------------------------------------------------------------------------------------------
+int bt_prefill(zb_ctx* c, const bf16* d_in, bf16* d_out, int S, int pos0, const int* d_lengths, cudaStream_t s) {
+  const zb_config& g = c->cfg;
+  const int rows = c->rows, d = g.d_model;
+  const int Sc = c->bt_mpad / rows;                       // tokens per block
+  int thr = d / 8 < 1024 ? d / 8 : 1024;
+  for (int t0 = 0; t0 < S; t0 += Sc) {
+    const int n = S - t0 < Sc ? S - t0 : Sc, M = n * rows;
+    ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, pos0 + t0, d_lengths, t0));
+    k_m2_gather_tm<<<M, thr, 0, s>>>(d_in + (size_t)t0 * d, c->x, rows, S, d);      // x[t * rows + r] <- in[r][t0 + t]
+    c->bt_vM = M; c->bt_vrows = rows;
+    cudaError_t e = enqueue_bt_layers(c, s);             // leaves norm_f(x) in bt_xn
+    c->bt_vM = 0; c->bt_vrows = 0;
+    ZB_CUDA(c->err, e);
+    if (d_out) k_bt_scatter_tm<<<M, thr, 0, s>>>((const bf16*)c->bt_xn, d_out + (size_t)t0 * d, rows, S, d);
+  }
+  ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, pos0 + S, d_lengths, S));
+  ZB_CUDA(c->err, cudaGetLastError());
+  return ZB_OK;
 }
 
 void drop_graph(zb_ctx* c) {
@@ -1082,6 +1117,7 @@ int zb_ctx_destroy(zb_ctx* c) {
   if (c->bar_counter) cudaFree(c->bar_counter);
   if (c->x_ll) cudaFree(c->x_ll);
   if (c->att_ll) cudaFree(c->att_ll);
+  if (c->pf_embed) cudaFree(c->pf_embed);
   for (void* q : {(void*)c->pf_x, (void*)c->pf_zx, (void*)c->pf_y, (void*)c->pf_yn, (void*)c->pf_xbc}) if (q) cudaFree(q);
   if (c->dbg) cudaFree(c->dbg);
   if (c->ev0) cudaEventDestroy(c->ev0);
@@ -1216,6 +1252,8 @@ int zb_backbone_forward(zb_ctx* c, const void* d_in, void* d_out, int rows, int 
   cudaStream_t s = (cudaStream_t)stream;
   ZB_CUDA(c->err, cudaSetDevice(c->device));
   const zb_config& g = c->cfg;
+  if (S > 1 && c->opt_bt_prefill && c->bt_ready && !c->hybrid && rows <= c->bt_mpad)
+    return bt_prefill(c, (const bf16*)d_in, (bf16*)d_out, S, seqlen_offset, (const int*)d_lengths, s);
   if (use_mega(c, rows)) {
     ZB_CUDA(c->err, launch(c, k_set_pos, dim3(1), dim3(128), 0, s, c->st, c->rope_pos, rows, seqlen_offset, (const int*)d_lengths, 0));
     ZB_CUDA(c->err, launch_mega(c, MG_MODE_HIDDEN, S, rows, 0, nullptr, d_in, d_out, S, 0, s));   // advances pos / rope_pos by S
@@ -1349,7 +1387,28 @@ int zb_gen_begin(zb_ctx* c, const void* d_prefix, int B, int Lc, int64_t* d_dela
   ZB_CUDA(c->err, cudaStreamSynchronize(s));                          // `rem` is host-stack memory
 
   const bool mega = use_mega(c, 2 * B);
-  if (mega) {
+  const bool block_prefill = c->opt_bt_prefill && c->bt_ready && !c->hybrid && c->rows <= c->bt_mpad;
+  if (block_prefill) {
+    // prefill (model.py:181-196,253-264) as blocks of token rows on the batched tcgen05 path: the Lc conditioning tokens,
+    // then the embedded known audio-prefix columns - every weight is streamed once per block of tokens, not once per token
+    if (Lc > 1 || !mega) { if ((rc = bt_prefill(c, (const bf16*)d_prefix, nullptr, Lc, 0, nullptr, s))) return rc; }
+    else ZB_CUDA(c->err, launch_mega(c, MG_MODE_HIDDEN, Lc, 2 * B, B, nullptr, d_prefix, nullptr, Lc, 0, s));
+    const int P = prefix_cols - 1;
+    if (P > 0) {
+      const size_t need = (size_t)c->rows * P * g.d_model;
+      if (need > c->pf_embed_elems) {
+        ZB_CUDA(c->err, cudaStreamSynchronize(s));
+        if (c->pf_embed) cudaFree(c->pf_embed);
+        c->pf_embed = nullptr; c->pf_embed_elems = 0;
+        ZB_CUDA(c->err, cudaMalloc((void**)&c->pf_embed, need * 2));
+        c->pf_embed_elems = need;
+      }
+      int thr = g.d_model / 8 < 1024 ? g.d_model / 8 : 1024;
+      k_embed_cols<<<dim3(P, B), thr, 0, s>>>((const bf16*)c->emb, (const long long*)c->delayed, c->pf_embed, g.d_model, g.n_codebooks, g.vocab, B, L, P);
+      ZB_CUDA(c->err, cudaGetLastError());
+      if ((rc = bt_prefill(c, c->pf_embed, nullptr, P, Lc, nullptr, s))) return rc;
+    }
+  } else if (mega) {
     // prefill through the persistent kernel: Lc conditioning tokens, then the known audio-prefix columns
     ZB_CUDA(c->err, launch_mega(c, MG_MODE_HIDDEN, Lc, 2 * B, B, nullptr, d_prefix, nullptr, Lc, 0, s));
     if (prefix_cols > 1) {
@@ -1510,6 +1569,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "psleep") c->opt_psleep = value;
   else if (k == "evict") c->opt_evict = value;
   else if (k == "chunked_prefill") c->opt_chunked_prefill = value;
+  else if (k == "bt_prefill") c->opt_bt_prefill = value;
   else if (k == "bt_min_rows") c->opt_bt_min_rows = value;
   else if (k == "attn_mma") c->opt_attn_mma = value;
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
