@@ -9,6 +9,7 @@
 #include "dac_simt.cuh"
 #include "dac_tc.cuh"
 #include "dac_tc2.cuh"
+#include "dac_ru.cuh"
 
 namespace {
 
@@ -43,6 +44,7 @@ struct zb_dac {
   int ew_k1 = 8;            // ... on k=1 layers
   int wide_cout = 768;      // layers with Cout >= this run on the one-tile-per-CTA kernel (impl 0)
   int mt2_min_waves = 8;    // 256-row tiles only when that still leaves this many tiles per SM
+  int fuse_ru = 1;          // 96 / 192-channel ResidualUnits as ONE kernel (k7 -> snake -> k1 -> + residual, dac_ru.cuh)
   int k1_wide = 1;          // k = 1 layers: all output channels in one tile (A/B switch)
   int max_group = 8;        // utterances decoded together: one launch per layer covers all their tiles (workspace = 5 x 49152 x T x group halves)
   float conv2_bias_h = 0.f; // host copy of decoder.conv2.bias (read back once in zb_dac_finalize)
@@ -295,6 +297,46 @@ int conv_tc2(zb_dac* d, const ConvW& c, const __half* x, int nb, int T_in, const
   return ZB_OK;
 }
 
+// Fused ResidualUnit (dac_ru.cuh): x_act = snake1(x) [nb][T][C] in, x raw residual in, out raw (optional) + activated out.
+bool ru_fusable(const zb_dac* d, const ConvW& c1, const ConvW& c2) {
+  return d->fuse_ru && (c1.Cout == 96 || c1.Cout == 192) && c1.Cin == c1.Cout && c2.Cin == c1.Cout && c2.Cout == c1.Cout && c1.K == 7 && c2.K == 1 &&
+         c1.stride == 1 && c2.stride == 1;
+}
+int conv_ru(zb_dac* d, const ConvW& c1, const ConvW& c2, const __half* x_act, const __half* x_raw, int nb, int T, __half* out_raw, __half* out_act,
+            const float* alpha2, const float* alpha_next, cudaStream_t s) {
+  RuParams p;
+  memset(&p, 0, sizeof(p));
+  p.C = c1.Cout; p.mt = p.C == 96 ? 2 : 1; p.kchunks = (p.C + TC_BK - 1) / TC_BK;
+  p.dil = c1.dil; p.pad = c1.pad; p.T = T; p.nb = nb;
+  const int tile_rows = p.mt * TC_BM;
+  p.m_tiles = (T + tile_rows - 1) / tile_rows;
+  const int win_rows = tile_rows + (c1.K - 1) * c1.dil;
+  p.n_aload = win_rows > 256 ? 2 : 1;
+  p.box_rows = (((win_rows + p.n_aload - 1) / p.n_aload) + 7) & ~7;
+  p.a_bytes = p.n_aload * p.box_rows * 128;
+  p.a_slots = p.C == 96 ? 2 : 3;
+  const int b_bytes = p.C * 128, y_bytes = p.kchunks * tile_rows * 128;
+  const int budget = 227 * 1024 - 1024 - 512 - RU_TAB_BYTES - y_bytes - p.a_slots * p.a_bytes;
+  int bs = budget / b_bytes;
+  if (bs > RU_MAX_B_STAGES) bs = RU_MAX_B_STAGES;
+  if (bs < 3) return d->err.fail(ZB_ERR_ARG, "conv_ru: shared memory budget");
+  p.b_stages = bs;
+  p.bias1 = c1.bias; p.alpha2 = alpha2; p.bias2 = c2.bias; p.alpha_next = alpha_next;
+  p.residual = x_raw; p.out_raw = out_raw; p.out_act = out_act;
+  CUtensorMap mx, mw1, mw2;
+  int rc;
+  if ((rc = make_map_x(d, &mx, x_act, p.C, T, nb, p.box_rows))) return rc;
+  if ((rc = make_map(d, &mw1, c1.w_koi, p.C, (uint64_t)c1.K * p.C, p.C))) return rc;
+  if ((rc = make_map(d, &mw2, c2.w_koi, p.C, (uint64_t)p.C, RU_N2))) return rc;
+  const size_t smem = 1024 + (size_t)p.a_slots * p.a_bytes + (size_t)p.b_stages * b_bytes + (size_t)y_bytes + 512 + RU_TAB_BYTES;
+  const long tiles = (long)p.m_tiles * nb;
+  const int grid = (int)(tiles < ZB_NUM_SMS ? tiles : ZB_NUM_SMS);
+  k_dac_ru_fused<<<grid, RU_THREADS, smem, s>>>(mx, mw1, mw2, p);
+  d->launches++;
+  ZB_CUDA(d->err, cudaGetLastError());
+  return ZB_OK;
+}
+
 // One group of `nb` utterances: every layer is ONE launch whose tiles cover all of them (tile index = (utterance, time
 // tile, channel tile, phase)), so the tail of a layer is paid once per group instead of once per utterance, and the small
 // layers (conv1 at T = 2580: 120 tiles for 148 SMs) fill the machine.  `bufs` = the five fp16 activation buffers of
@@ -326,14 +368,22 @@ int decode_group_tc(zb_dac* d, const long long* codes, float* wav, int nb, int T
     std::swap(A, A2);
     for (int u = 0; u < 3; ++u) {
       const std::string rp = bp + ".res_unit" + std::to_string(u + 1);
-      // conv1 (k7, dilated): A -> Y = snake(., snake2)
-      if ((rc = conv(d->ru1[j][u], A, Tl, nullptr, nullptr, Y, rawp(d, rp + ".snake2.alpha")))) return rc;
       // conv2 (k1) + residual R -> R2 (raw, only if a later unit needs it) and A2 = snake(., next alpha)
       std::string next_alpha;
       if (u < 2) next_alpha = bp + ".res_unit" + std::to_string(u + 2) + ".snake1.alpha";
       else if (j < 3) next_alpha = "decoder.block." + std::to_string(j + 1) + ".snake1.alpha";
       else next_alpha = "decoder.snake1.alpha";
       const bool need_raw = (u < 2) || keep;
+      const bool fused = impl == 0 && ru_fusable(d, d->ru1[j][u], d->ru2[j][u]);
+      // conv1 (k7, dilated): A -> Y = snake(., snake2)
+      if (!fused && (rc = conv(d->ru1[j][u], A, Tl, nullptr, nullptr, Y, rawp(d, rp + ".snake2.alpha")))) return rc;
+      if (impl == 0 && ru_fusable(d, d->ru1[j][u], d->ru2[j][u])) {
+        // fused unit: A (activated) + R (raw residual) -> R2 (raw, if needed) and A2 = snake(., next alpha); Y stays on chip
+        if ((rc = conv_ru(d, d->ru1[j][u], d->ru2[j][u], A, R, nb, Tl, need_raw ? R2 : nullptr, A2, rawp(d, rp + ".snake2.alpha"), rawp(d, next_alpha), s))) return rc;
+        std::swap(A, A2);
+        std::swap(R, R2);
+        continue;
+      }
       if ((rc = conv(d->ru2[j][u], Y, Tl, R, need_raw ? R2 : nullptr, A2, rawp(d, next_alpha)))) return rc;
       std::swap(A, A2);
       std::swap(R, R2);
@@ -468,6 +518,7 @@ int zb_dac_finalize(zb_dac* d, void* stream) {
   ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc2<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_tc2<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_final_conv, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_ru_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   d->finalized = true;
   return ZB_OK;
 }
@@ -549,6 +600,7 @@ int zb_dac_set_option(zb_dac* d, const char* key, int value) {
   }
   if (k == "wide_cout") { d->wide_cout = value; return ZB_OK; }
   if (k == "mt2_min_waves") { d->mt2_min_waves = value; return ZB_OK; }
+  if (k == "fuse_ru") { d->fuse_ru = value; return ZB_OK; }
   if (k == "k1_wide") { d->k1_wide = value; return ZB_OK; }
   if (k == "max_group") { d->max_group = value < 1 ? 1 : value; return ZB_OK; }
   return d->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
