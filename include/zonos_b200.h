@@ -180,6 +180,21 @@ int  zb_dac_get_intermediate(zb_dac* dac, const char* name, float* d_out, int64_
 int  zb_dac_set_option(zb_dac* dac, const char* key, int value);      /* "keep_intermediates" */
 int64_t zb_dac_launch_count(const zb_dac* dac);
 
+/* ---- PrefixConditioner (zonos/conditioning.py) -------------------------------------------------------
+ * The four ops the reference's PrefixConditioner.forward (conditioning.py:297-313) is made of, on caller-owned bf16 device
+ * tensors; zonos_vibes_b200/conditioning.py composes them in the reference's order.  Text -> phoneme ids stays on the host.
+ *   zb_pc_fourier    FourierConditioner.apply_cond (conditioning.py:257-261): d_x fp32 [n, in_dim], weight bf16 [half, in_dim]
+ *                    -> bf16 [n, 2*half] = [cos | sin] of 2*pi*((x - min)/(max - min)) @ W^T
+ *   zb_pc_embed      nn.Embedding of EspeakPhonemeConditioner / IntegerConditioner (:230-236, :271-273): ids int64 [n]
+ *                    (id_offset = min_val is subtracted), table bf16 [table_rows, d] -> bf16 [n, d]
+ *   zb_pc_linear     nn.Linear (+ SiLU when silu != 0) of Conditioner.project (:24-35): in bf16 [n, K], w bf16 [N, K],
+ *                    b bf16 [N] or NULL -> bf16 [n, N]
+ *   zb_pc_layernorm  PrefixConditioner.norm (:301,313): bf16 [n, d] -> bf16 [n, d] */
+int  zb_pc_fourier(const float* d_x, const void* d_weight, float min_val, float max_val, void* d_out, int n, int in_dim, int half, void* stream);
+int  zb_pc_embed(const int64_t* d_ids, const void* d_table, void* d_out, int n, int d, int64_t id_offset, int64_t table_rows, void* stream);
+int  zb_pc_linear(const void* d_in, const void* d_w, const void* d_b, void* d_out, int n, int K, int N, int silu, void* stream);
+int  zb_pc_layernorm(const void* d_in, const void* d_w, const void* d_b, float eps, void* d_out, int n, int d, void* stream);
+
 /* ---- introspection used by bench.py (launch counting, roofline byte counts) ------------------- */
 int64_t zb_weight_bytes(const zb_ctx* ctx);            /* algorithmic weight bytes streamed per decode step */
 int64_t zb_launch_count(const zb_ctx* ctx);            /* kernels launched by this context so far (graph nodes count per replay) */

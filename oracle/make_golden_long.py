@@ -16,6 +16,7 @@ Sections
           model.py:246-264 (MG_MODE_FORCED here), delayed codes + per-step logits
   truth   fp32 evaluation of the full-size model on `full.delayed` of golden.pt (7 steps): the "truth" of
           test_logit_error_is_bf16_noise at full size
+  cond    the reference's PrefixConditioner (every conditioner type, d = 256, bf16) on fixed inputs: state_dict + outputs
   dac     DAC decode of 9 x 2580 codes (B = 1): six 32-frame windows of the waveform + per-frame mean |x| of all of it
 """
 from __future__ import annotations
@@ -129,11 +130,74 @@ def section_dac(g, ref):
     print(f"dac T={DAC_T}: {time.time() - t0:.0f} s", flush=True)
 
 
+COND_CONFIG = dict(projection="linear", conditioners=[
+    dict(type="EspeakPhonemeConditioner", name="espeak"),
+    dict(type="PassthroughConditioner", name="speaker", cond_dim=128, uncond_type="learned", projection="linear"),
+    dict(type="FourierConditioner", name="emotion", input_dim=8, uncond_type="learned"),
+    dict(type="FourierConditioner", name="fmax", min_val=0, max_val=24000, uncond_type="learned"),
+    dict(type="FourierConditioner", name="pitch_std", min_val=0, max_val=400, uncond_type="learned", projection="mlp"),
+    dict(type="FourierConditioner", name="speaking_rate", min_val=0, max_val=40, uncond_type="learned"),
+    dict(type="IntegerConditioner", name="language_id", min_val=-1, max_val=126, uncond_type="learned"),
+])
+
+
+@torch.inference_mode()
+def section_cond(g, ref):
+    """Row f1: the reference's own PrefixConditioner (conditioning.py:297-313) in bf16 on CPU, every conditioner type, with
+    the espeak phonemiser replaced by fixed phoneme strings (tokenised by the reference's tokenize_phonemes)."""
+    import zonos.conditioning as zc
+    d = 256
+    torch.manual_seed(11)
+    cfg = ref.config.PrefixConditionerConfig(**COND_CONFIG)
+    pc = zc.PrefixConditioner(cfg, d)
+    for prm in pc.parameters():                                  # exercise biases / learned uncond vectors / norm affine
+        if prm.dim() == 1:
+            prm.data = torch.randn_like(prm) * 0.2 + (1.0 if prm is pc.norm.weight else 0.0)
+    pc = pc.to(torch.bfloat16).eval()
+    phon = ["h@l'oU, w'3:ld!", "t'Est"]
+    zc.phonemize = lambda texts, languages: phon[: len(texts)]
+    ids, _ = zc.tokenize_phonemes(phon)
+    gen = torch.Generator().manual_seed(12)
+    # Conditioner.forward unpacks its input (`apply_cond(*inputs)`, conditioning.py:48): batched tensors go in as 1-tuples,
+    # while make_cond_dict's bare [1, 1, D] tensors (conditioning.py:396-400) unpack along the batch into one [1, D] row.
+    cond = {
+        "espeak": (["Hello, world!", "test"], ["en-us", "en-us"]),
+        "speaker": (torch.randn(2, 1, 128, generator=gen).bfloat16(),),
+        "emotion": (torch.rand(2, 1, 8, generator=gen),),
+        "fmax": (torch.tensor([[[22050.0]], [[24000.0]]]),),
+        "pitch_std": (torch.tensor([[[20.0]], [[145.5]]]),),
+        "speaking_rate": (torch.tensor([[[15.0]], [[31.0]]]),),
+        "language_id": (torch.tensor([[[24]], [[-1]]]),),
+    }
+    g["cond.config"] = COND_CONFIG
+    g["cond.state_dict"] = {k: v.clone() for k, v in pc.state_dict().items()}
+    g["cond.phoneme_ids"] = ids
+    g["cond.inputs"] = {k: v for k, v in cond.items() if k != "espeak"}
+    g["cond.out_full"] = pc(cond)
+    uncond = {k: cond[k] for k in ("espeak",)}                    # everything else falls back to the learned uncond vectors
+    g["cond.out_uncond"] = pc(uncond)
+    emo = torch.tensor([0.3077, 0.0256, 0.0256, 0.0256, 0.0256, 0.0256, 0.2564, 0.3077])
+    mcd = {                                                       # the shapes make_cond_dict produces, batch 1
+        "espeak": (["test"], ["en-us"]),
+        "speaker": torch.randn(1, 1, 128, generator=gen).bfloat16(),
+        "emotion": (emo / emo.sum()).view(1, 1, -1),
+        "fmax": torch.tensor(22050.0).view(1, 1, -1),
+        "pitch_std": torch.tensor(20.0).view(1, 1, -1),
+        "speaking_rate": torch.tensor(15.0).view(1, 1, -1),
+        "language_id": torch.tensor(24).view(1, 1, -1),
+    }
+    zc.phonemize = lambda texts, languages: phon[1:2]
+    g["cond.mcd_phoneme_ids"] = zc.tokenize_phonemes(phon[1:2])[0]
+    g["cond.mcd_inputs"] = {k: v for k, v in mcd.items() if k != "espeak"}
+    g["cond.out_mcd"] = pc(mcd)
+    print("cond:", tuple(g["cond.out_full"].shape), tuple(g["cond.out_uncond"].shape), tuple(g["cond.out_mcd"].shape), flush=True)
+
+
 def main():
-    want = set(sys.argv[1:]) or {"long", "prefix", "truth", "dac"}
+    want = set(sys.argv[1:]) or {"long", "prefix", "truth", "dac", "cond"}
     ref = load_reference()
     g = torch.load(OUT) if os.path.exists(OUT) else {}
-    for name, fn in (("prefix", section_prefix), ("dac", section_dac), ("truth", section_truth), ("long", section_long)):
+    for name, fn in (("cond", section_cond), ("prefix", section_prefix), ("dac", section_dac), ("truth", section_truth), ("long", section_long)):
         if name in want:
             fn(g, ref)
             torch.save(g, OUT)

@@ -233,3 +233,33 @@ def test_generate_sharded_gloo_world2(tmp_path):
         capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "SHARD_OK" in r.stdout
+
+
+def test_prefix_conditioner_mirror_keys_and_cond_dict():
+    """Row f1 host side: the conditioner mirror takes the reference's state_dict by key (frozen from the reference in
+    golden_long.pt `cond.state_dict`), make_cond_dict reproduces conditioning.py:331-405's keys / shapes, and the ops fail
+    loudly on CPU tensors (no fallback)."""
+    import zonos_vibes_b200 as z
+    from zonos_vibes_b200 import _lib
+    from zonos_vibes_b200.conditioning import make_cond_dict, supported_language_codes
+    g = torch.load(os.path.join(ROOT, "tests", "golden", "golden_long.pt"))
+    pc = z.PrefixConditioner(z.PrefixConditionerConfig(**g["cond.config"]), 256)
+    assert set(pc.state_dict()) == set(g["cond.state_dict"])
+    for k, v in pc.state_dict().items():
+        assert v.shape == g["cond.state_dict"][k].shape, k
+    assert pc.required_keys == {"espeak"}
+    with pytest.raises(ValueError, match="Missing required keys"):
+        pc({})
+    pc.load_state_dict(g["cond.state_dict"])
+    with pytest.raises(_lib.ZbError):
+        pc({"espeak": ("ids", g["cond.phoneme_ids"])})
+
+    cd = make_cond_dict(text="hi", language="en-us", device="cpu")
+    assert set(cd) == {"espeak", "speaker", "emotion", "fmax", "pitch_std", "speaking_rate", "language_id", "ctc_loss", "speaker_noised"}
+    assert cd["espeak"] == (["hi"], ["en-us"]) and cd["speaker"] is None
+    assert cd["emotion"].shape == (1, 1, 8) and abs(cd["emotion"].sum().item() - 1.0) < 1e-6
+    assert cd["language_id"].item() == 24 == supported_language_codes.index("en-us") and len(supported_language_codes) == 109
+    assert make_cond_dict(device="cpu", phoneme_ids=torch.zeros(1, 3, dtype=torch.int64))["espeak"][0] == "ids"
+    mcd = g["cond.mcd_inputs"]
+    for k in ("emotion", "fmax", "pitch_std", "speaking_rate", "language_id"):
+        assert cd[k].shape == mcd[k].shape and torch.allclose(cd[k].float(), mcd[k].float(), atol=1e-6), k

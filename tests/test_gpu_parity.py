@@ -727,3 +727,60 @@ def test_dac_batch32_equals_single_decodes(cuda):
     for b in (0, 13, 31):
         single = dac.decode(codes[b:b + 1].contiguous())
         assert torch.equal(wav[b:b + 1], single), b
+
+
+# ---- row f1: PrefixConditioner on the device -----------------------------------------------------------------------
+def _cond_inputs(d, cuda):
+    return {k: (tuple(t.to(cuda) for t in v) if isinstance(v, tuple) else v.to(cuda)) for k, v in d.items()}
+
+
+def test_prefix_conditioner_matches_reference(golden_long, cuda):
+    """zonos_vibes_b200.conditioning.PrefixConditioner (zb_pc_* kernels) against the reference's own PrefixConditioner run in
+    bf16 (oracle/make_golden_long.py `cond`): the reference state_dict loads by key, every conditioner type is exercised
+    (phoneme embedding, passthrough + linear, Fourier with none / mlp projection, integer embedding, learned uncond vectors,
+    prefix projection, LayerNorm).  Measured on B200: bit-identical on all three cases.  Bar: >= 99 % of the elements
+    bit-identical and none further than one bf16 ulp of the output range (the reference's CPU bf16 matmuls may accumulate in
+    a different order on another host)."""
+    from zonos_vibes_b200.conditioning import PrefixConditioner
+    from zonos_vibes_b200.config import PrefixConditionerConfig
+    pc = PrefixConditioner(PrefixConditionerConfig(**golden_long["cond.config"]), 256)
+    missing, unexpected = pc.load_state_dict(golden_long["cond.state_dict"], strict=True)
+    assert not missing and not unexpected
+    pc = pc.to(cuda, torch.bfloat16).eval()
+    full = dict(_cond_inputs(golden_long["cond.inputs"], cuda), espeak=("ids", golden_long["cond.phoneme_ids"]))
+    cases = [("full", full, golden_long["cond.out_full"]),
+             ("uncond", {"espeak": full["espeak"]}, golden_long["cond.out_uncond"]),
+             ("make_cond_dict shapes", dict(_cond_inputs(golden_long["cond.mcd_inputs"], cuda), espeak=("ids", golden_long["cond.mcd_phoneme_ids"])),
+              golden_long["cond.out_mcd"])]
+    with torch.inference_mode():
+        for what, cd, want in cases:
+            got = pc(cd)
+            assert got.shape == want.shape and got.dtype == torch.bfloat16, what
+            err = (got.float().cpu() - want.float()).abs()
+            tol = 2.0 ** -8 * want.float().abs().max().item()
+            frac_exact = (err == 0).float().mean().item()
+            print(f"[prefix conditioner {what}] max err {err.max().item():.4f} (tol {tol:.4f}), bit-identical {frac_exact:.3f}")
+            assert err.max().item() <= tol, what
+            assert frac_exact >= 0.99, what
+
+
+def test_prefix_conditioner_feeds_generate(golden_long, cuda):
+    """prepare_conditioning -> generate through a model built with a non-empty prefix_conditioner config (model.py:204-212)."""
+    import zonos_vibes_b200 as z
+    cfg = zo.TINY_CONFIG
+    rd = cfg.to_reference_dict()
+    assert cfg.d_model == 256
+    rd["prefix_conditioner"] = golden_long["cond.config"]
+    sd = dict(zo.synth_state_dict(cfg, 0))
+    sd.update({f"prefix_conditioner.{k}": v for k, v in golden_long["cond.state_dict"].items()})
+    m = z.Zonos.from_state_dict(z.ZonosConfig.from_dict(rd), sd, cuda)
+    assert isinstance(m.prefix_conditioner, z.PrefixConditioner)
+    cd = dict(_cond_inputs(golden_long["cond.mcd_inputs"], cuda), espeak=("ids", golden_long["cond.mcd_phoneme_ids"]))
+    with torch.inference_mode():
+        pre = m.prepare_conditioning(cd)
+    assert pre.shape == (2, 13, 256)
+    want = golden_long["cond.out_mcd"][0].float()               # row 0 = conditional; row 1 = espeak only + learned uncond vectors
+    assert (pre[0].float().cpu() - want).abs().max().item() <= 2 * 2.0 ** -8 * want.abs().max().item()
+    assert not torch.equal(pre[0], pre[1])
+    out = m.generate(pre, max_new_tokens=12, sampling_params=dict(temperature=0), progress_bar=False)
+    assert out.shape[:2] == (1, 9) and int(out.max()) < 1024

@@ -7,11 +7,12 @@ libzonos_b200.so (include/zonos_b200.h); there is no CPU fallback.
 from .autoencoder import DACAutoencoder
 from .backbone import BACKBONES, B200ZonosBackbone
 from .codebook_pattern import apply_delay_pattern, revert_delay_pattern
+from .conditioning import PrefixConditioner
 from .config import BackboneConfig, InferenceParams, PrefixConditionerConfig, ZonosConfig
 from .model import Zonos
 from .sampling import sample_from_logits
 
 __all__ = [
     "Zonos", "DACAutoencoder", "BACKBONES", "B200ZonosBackbone", "apply_delay_pattern", "revert_delay_pattern",
-    "sample_from_logits", "ZonosConfig", "BackboneConfig", "PrefixConditionerConfig", "InferenceParams",
+    "sample_from_logits", "ZonosConfig", "BackboneConfig", "PrefixConditionerConfig", "InferenceParams", "PrefixConditioner",
 ]

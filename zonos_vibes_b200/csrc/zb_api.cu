@@ -14,6 +14,7 @@
 #include "hybrid_kernels.cuh"
 #include "mega_kernel.cuh"
 #include "sample_kernels.cuh"
+#include "prefix_kernels.cuh"
 
 int ZbErr::fail(int code, const char* fmt, ...) {
   char buf[1024];
@@ -1547,6 +1548,32 @@ int zb_update_frame(zb_ctx* c, int64_t* d_delayed, int B, int L, int col, const 
   k_update<<<1, ub, 0, s>>>(up);
   ZB_CUDA(c->err, cudaGetLastError());
   return ZB_OK;
+}
+
+// ---- PrefixConditioner building blocks: stateless, caller-owned tensors ------------------------------------
+int zb_pc_fourier(const float* d_x, const void* d_weight, float min_val, float max_val, void* d_out, int n, int in_dim, int half, void* stream) {
+  if (!d_x || !d_weight || !d_out || n < 0 || in_dim <= 0 || half <= 0) return ZB_ERR_ARG;
+  if (n == 0) return ZB_OK;
+  k_pc_fourier<<<n, 128, 0, (cudaStream_t)stream>>>(d_x, (const bf16*)d_weight, min_val, max_val, (bf16*)d_out, in_dim, half);
+  return cudaGetLastError() == cudaSuccess ? ZB_OK : ZB_ERR_CUDA;
+}
+int zb_pc_embed(const int64_t* d_ids, const void* d_table, void* d_out, int n, int d, int64_t id_offset, int64_t table_rows, void* stream) {
+  if (!d_ids || !d_table || !d_out || n < 0 || d <= 0 || d % 8 != 0 || table_rows <= 0) return ZB_ERR_ARG;
+  if (n == 0) return ZB_OK;
+  k_pc_embed<<<n, 128, 0, (cudaStream_t)stream>>>((const long long*)d_ids, (const bf16*)d_table, (bf16*)d_out, d, (long long)id_offset, (long long)table_rows);
+  return cudaGetLastError() == cudaSuccess ? ZB_OK : ZB_ERR_CUDA;
+}
+int zb_pc_linear(const void* d_in, const void* d_w, const void* d_b, void* d_out, int n, int K, int N, int silu, void* stream) {
+  if (!d_in || !d_w || !d_out || n < 0 || K <= 0 || K % 8 != 0 || N <= 0) return ZB_ERR_ARG;
+  if (n == 0) return ZB_OK;
+  k_pc_linear<<<(N + 7) / 8, 256, 0, (cudaStream_t)stream>>>((const bf16*)d_in, (const bf16*)d_w, (const bf16*)d_b, (bf16*)d_out, n, K, N, silu);
+  return cudaGetLastError() == cudaSuccess ? ZB_OK : ZB_ERR_CUDA;
+}
+int zb_pc_layernorm(const void* d_in, const void* d_w, const void* d_b, float eps, void* d_out, int n, int d, void* stream) {
+  if (!d_in || !d_w || !d_b || !d_out || n < 0 || d <= 0) return ZB_ERR_ARG;
+  if (n == 0) return ZB_OK;
+  k_pc_layernorm<<<n, 256, 0, (cudaStream_t)stream>>>((const bf16*)d_in, (const bf16*)d_w, (const bf16*)d_b, eps, (bf16*)d_out, d);
+  return cudaGetLastError() == cudaSuccess ? ZB_OK : ZB_ERR_CUDA;
 }
 
 int64_t zb_weight_bytes(const zb_ctx* c) { return c ? c->step_weight_bytes : 0; }

@@ -36,8 +36,12 @@ class Zonos(nn.Module):
         self.autoencoder = autoencoder            # not an nn.Module, like the reference (model.py:30)
         self.backbone = backbone_cls(config.backbone)
         self.backbone.eos_token_id, self.backbone.masked_token_id = config.eos_token_id, config.masked_token_id
-        # The conditioner is outside the accelerated path: any module with the reference's
-        # PrefixConditioner interface (conditioning.py:297-313) can be plugged in.
+        # the device-side mirror of the reference's PrefixConditioner (conditioning.py) is built whenever the
+        # config lists conditioners, so a checkpoint's `prefix_conditioner.*` entries load; any module with the same
+        # interface (conditioning.py:297-313) can be passed in instead.
+        if prefix_conditioner is None and config.prefix_conditioner.conditioners:
+            from .conditioning import PrefixConditioner
+            prefix_conditioner = PrefixConditioner(config.prefix_conditioner, dim)
         self.prefix_conditioner = prefix_conditioner
         self.spk_clone_model = None
         self.embeddings = nn.ModuleList([nn.Embedding(1026, dim) for _ in range(N_CODEBOOKS)])
@@ -55,8 +59,8 @@ class Zonos(nn.Module):
     @classmethod
     def from_state_dict(cls, config: ZonosConfig, state_dict: dict, device="cuda", dac_state_dict: dict | None = None,
                         prefix_conditioner: nn.Module | None = None) -> "Zonos":
-        """Build from a reference state_dict (SURVEY App. B keys); extra keys (prefix_conditioner.*) are ignored
-        unless a conditioner module is supplied."""
+        """Build from a reference state_dict (SURVEY App. B keys).  `prefix_conditioner.*` entries load into the conditioner
+        (built from config.prefix_conditioner, or the module supplied) and may be absent from a backbone-only state_dict."""
         dac = DACAutoencoder(dac_state_dict, device) if dac_state_dict is not None else None
         model = cls(config, autoencoder=dac, prefix_conditioner=prefix_conditioner).to(device, torch.bfloat16)
         own = model.state_dict()
