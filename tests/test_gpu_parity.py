@@ -338,7 +338,7 @@ def golden_long():
     return torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_long.pt"))
 
 
-LONG_PATHS = {"persistent": {}, "persistent_grid_barriers": dict(ll=0), "per_op_graph": dict(mega=0),
+LONG_PATHS = {"persistent": {}, "persistent_grid_barriers": dict(ll=0), "persistent_ll2": dict(ll=2), "per_op_graph": dict(mega=0),
               "batched_tcgen05": dict(mega=0, bt_min_rows=2)}
 
 
@@ -436,7 +436,7 @@ def test_generate_with_long_audio_prefix_full_size(golden_long, cuda, path):
 class _options:
     def __init__(self, model, **kw):
         self.ctx, self.kw = model._native(), kw
-        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=1, bt_prefill=1)
+        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=3, bt_prefill=1)
 
     def __enter__(self):
         for k, v in self.kw.items():
@@ -474,9 +474,11 @@ def test_teacher_forced_logits_full_size_other_paths(golden, cuda, path):
 
 @pytest.mark.parametrize("cname", ["tiny", "full"])
 def test_persistent_kernel_epoch_tagged_stream_equals_grid_barriers(golden, cuda, cname):
-    """The persistent kernel hands the residual stream from out_proj / fc2 to the next LayerNorm either through grid
-    barriers (ll=0) or as epoch-tagged words that the readers poll (ll=1, default).  Only the synchronisation differs:
-    the logits must be bit-identical, step after step, over several launches (the epoch changes with every launch)."""
+    """The persistent kernel passes activations between phases either through grid barriers (ll=0) or as epoch-tagged words
+    that the readers poll: ll=1 the residual stream (out_proj / fc2 -> next LayerNorm), ll=2 also q / k / v and the attention
+    output (no barrier around the attention), ll=3 (default) also the SwiGLU output (no barrier inside the layer stack, and
+    the MMA warps no longer wait for their epilogue warp between phases).  Only the synchronisation differs: the logits must
+    be bit-identical, step after step, over several launches (the epoch changes with every launch)."""
     m = make_model(cname, cuda)
     cfg = CFGS[cname] if cname in CFGS else zo.FULL_CONFIG
     if cname == "full":
@@ -485,11 +487,28 @@ def test_persistent_kernel_epoch_tagged_stream_equals_grid_barriers(golden, cuda
         prefix, delayed, n = zo.synth_prefix_conditioning(cfg, 1, 6, 1), golden[f"gen.{cname}.greedy.delayed"], 40
     with _options(m, ll=0):
         want = m.compute_logits_teacher_forced(prefix, delayed, n).float().cpu()
-    for _ in range(2):
-        got = m.compute_logits_teacher_forced(prefix, delayed, n).float().cpu()
-        assert torch.equal(torch.isfinite(got), torch.isfinite(want))
-        fin = torch.isfinite(want)
-        assert torch.equal(got[fin], want[fin]), f"{cname}: epoch-tagged path differs from the grid-barrier path"
+    fin = torch.isfinite(want)
+    for ll in (3, 3, 2, 1):
+        with _options(m, ll=ll):
+            got = m.compute_logits_teacher_forced(prefix, delayed, n).float().cpu()
+        assert torch.equal(torch.isfinite(got), fin)
+        assert torch.equal(got[fin], want[fin]), f"{cname}: epoch-tagged path ll={ll} differs from the grid-barrier path"
+
+
+def test_persistent_kernel_dependency_modes_bit_identical_long_context(golden_long, cuda):
+    """The same at ctx 1 315..1 323 of the full-size model, where the attention runs 11 KV splits per (row, kv head) and the
+    tagged q / k / v, split partials, y and h words all cross CTAs."""
+    m = make_model("full", cuda)
+    prefix = zo.synth_prefix_conditioning(zo.FULL_CONFIG, 1, 24, 1)
+    delayed = golden_long["long.p1290.delayed"]
+    with _options(m, ll=0):
+        want = m.compute_logits_teacher_forced(prefix, delayed, 8, skip=1290).float().cpu()
+    fin = torch.isfinite(want)
+    for ll in (3, 2, 1, 3):
+        with _options(m, ll=ll):
+            got = m.compute_logits_teacher_forced(prefix, delayed, 8, skip=1290).float().cpu()
+        assert torch.equal(torch.isfinite(got), fin)
+        assert torch.equal(got[fin], want[fin]), f"ll={ll} differs from the grid-barrier path at long context"
 
 
 @pytest.mark.parametrize("path", list(PATHS))

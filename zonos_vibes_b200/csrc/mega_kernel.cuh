@@ -33,8 +33,8 @@
 #define MG_EPI_WARP 9
 #define MG_HANDOFF 288               // threads on the tile hand-off barriers: the 8 MMA warps + the epilogue warp
 // named barriers: 0 __syncthreads, 1 SyncConsumers (8 MMA warps), 2/3 partial buffer 0/1 full, 4/5 partial buffer 0/1 free,
-// 6 GEMV phase done, 7 step start
-enum { MG_BAR_FULL = 2, MG_BAR_FREE = 4, MG_BAR_PHASE = 6, MG_BAR_STEP = 7 };
+// 7 step start
+enum { MG_BAR_FULL = 2, MG_BAR_FREE = 4, MG_BAR_STEP = 7 };
 #define MG_WARPS 8
 #define MG_KC 2048                   // weight columns per ring stage (4 KB per row copy)
 #define MG_ROW_BYTES (MG_KC * 2 + 64)   // stage row stride: +64 B => 8 rows x 16 B quarter-warp reads hit 32 distinct banks
@@ -78,7 +78,11 @@ struct MegaParams {
   int *remaining, *stopping, *out_len;
   unsigned* bar_counter;       // grid barrier (zero at launch)
   unsigned long long* x_ll;    // [2][8][d/2] residual stream as (bf16 pair, epoch) 8-byte words: data that carries its own 'ready' flag
-  int use_ll;                  // 1: LayerNorm staging polls x_ll and the grid barriers after out_proj / fc2 are skipped
+  unsigned long long* qkv_ll;  // [8][(q_size + 2 kv_size)/2]: this step's q, k, v rows of the current layer, tagged the same way
+  unsigned long long* y_ll;    // [8][q_size/2]: attention output
+  unsigned long long* h_ll;    // [8][F/2]: SwiGLU output
+  int use_ll;                  // 1: LayerNorm staging polls x_ll and the grid barriers after out_proj / fc2 are skipped;
+                               // 2: q / k / v and y travel tagged too: no grid barrier around the attention; 3: and h: no barrier in the layer
   unsigned epoch_base;         // launch number << 20: epochs never repeat while an x_ll word can still be around
   int mode, n_steps;
   const bf16* hidden_in;       // MG_MODE_HIDDEN: x <- hidden_in[r, t0 + i, :], row stride hidden_S tokens
@@ -87,6 +91,8 @@ struct MegaParams {
   int n_stages;                // ring stages
   unsigned producer_sleep_ns;  // producer back-off between polls of a full ring (0 = hot spin)
   int scratch_bytes;           // activation staging / attention / sampling scratch
+  int chain;                   // use_ll >= 3: 1 = the MMA warps do not wait for their epilogue warp between the phases of the layer stack
+                               // (measured SLOWER, 918 -> 969 us per step: the pollers' loads delay the epilogue warp's stores; default 0)
   int stream_evict_first;      // 1: weight tiles are loaded with the L2 evict_first policy (A/B switch "evict")
   unsigned long long* dbg;     // optional trace: [grid][MG_TRACE_SLOTS] globaltimer stamps of step dbg_step (thread 0)
   int dbg_step;
@@ -176,6 +182,33 @@ __device__ __forceinline__ uint4 mg_lds128(uint32_t addr) {
 __device__ __forceinline__ uint4 mg_ldcg16(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
 __device__ __forceinline__ int mg_ld_volatile(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
 
+// N groups of 8 consecutive bf16 (= 4 tagged words (bf16 pair, epoch) each) from an epoch-tagged buffer: all loads of a
+// round are in flight together; the round is repeated until every word carries `epoch`.
+template <int N>
+__device__ __forceinline__ void mg_ll_load(const unsigned long long* const (&wp)[N], unsigned epoch, uint4 (&out)[N]) {
+  // (Re-reading only the groups that are still incomplete keeps every group's registers alive around the loop: with the
+  // 168 registers a thread of this 10-warp CTA can have, that version spilled ~1 KB per thread.)
+  unsigned long long w[N][4];
+  for (;;) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[i][0]), "=l"(w[i][1]) : "l"(wp[i]) : "memory");
+      asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[i][2]), "=l"(w[i][3]) : "l"(wp[i] + 2) : "memory");
+    }
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < N; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ok = ok && (unsigned)(w[i][j] >> 32) == epoch;
+    if (ok) break;
+  }
+#pragma unroll
+  for (int i = 0; i < N; ++i) out[i] = make_uint4((unsigned)w[i][0], (unsigned)w[i][1], (unsigned)w[i][2], (unsigned)w[i][3]);
+}
+__device__ __forceinline__ void mg_ll_store(unsigned long long* wp, unsigned epoch, unsigned pair_bits) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(wp), "l"(((unsigned long long)epoch << 32) | (unsigned long long)pair_bits) : "memory");
+}
+
 // ---- grid barrier over the consumer threads of all CTAs -----------------------------------------------------------
 __device__ __forceinline__ void mg_grid_sync(unsigned* counter, unsigned& target) {
   SyncConsumers::sync();
@@ -202,14 +235,14 @@ struct MgCtx {
   uint32_t ring_addr;        // the same, as a shared-space address
   unsigned char* scratch;    // activation staging etc.
   float* part;               // [2][2][8 warps][8 r][8 n]
-  float* red;                // [64]
+  float* red;                // [160]: LayerNorm partials [2][8 warps][8 rows] + 32 spare
   float* s_rope;             // [8][128]: (cos, sin) rows of this step's positions
   float* s_xown;             // [8][MG_OWN]: this CTA's columns of the residual stream
   int* s_page;               // [8]: KV page of the current position per row
   uint32_t full0, empty0;    // smem addresses of the barrier arrays
   int n_stages;
   int stage, parity;         // ring cursor of this role
-  int tile_flip;             // partial-buffer parity (consumers)
+  int tile_seq;              // tiles handed to the epilogue warp since the last drain (partial buffer = tile_seq & 1); both roles count
   bool prof;                 // debug profile on
   bool trace;                // this step is being traced
   bool fine;                 // stage-level trace of one fc1 phase (MegaParams::dbg_fine == 1)
@@ -307,7 +340,7 @@ __device__ __forceinline__ void mg_phase_weights(const MegaParams& p, int l, int
   switch (ph) {
     case MG_PH_QKV: W = mg_lw(p.l0.w_in, p.layer_stride, l); K = p.d; n_units = (p.q_size + 2 * p.kv_size) / 2; break;
     case MG_PH_OUT: W = mg_lw(p.l0.w_out, p.layer_stride, l); K = p.q_size; n_units = p.d / 2; break;
-    case MG_PH_FC1: W = mg_lw(p.l0.w_fc1, p.layer_stride, l); K = p.d; n_units = p.F; gate_off = p.F; NT = 2; UNIT = 1; break;
+    case MG_PH_FC1: W = mg_lw(p.l0.w_fc1, p.layer_stride, l); K = p.d; n_units = p.F / 2; gate_off = p.F; NT = 2; break;
     case MG_PH_FC2: W = mg_lw(p.l0.w_fc2, p.layer_stride, l); K = p.F; n_units = p.d / 2; break;
     default: W = p.heads; K = p.d; n_units = p.n_q * p.V / 2; break;      // MG_PH_HEADS
   }
@@ -437,6 +470,46 @@ __device__ __forceinline__ void mg_stage_copy(bf16* xs, int ld, const bf16* src,
   SyncConsumers::sync();
 }
 
+// the same from an epoch-tagged buffer [R][K/2] words: the poll IS the cross-CTA dependency (no grid barrier before it)
+__device__ __forceinline__ void mg_stage_ll(bf16* xs, int ld, const unsigned long long* ll, int K, int R, unsigned epoch) {
+  const int tid = threadIdx.x;
+  const int e0 = tid * 8;
+  if (K <= MG_CONSUMERS * 8) {                                      // y: one column group, two rows per round trip
+    if (e0 < K) {
+#pragma unroll 1
+      for (int r0 = 0; r0 < R; r0 += 2) {
+        const bool r2 = r0 + 1 < R;
+        const unsigned long long* w00 = ll + (size_t)r0 * (K >> 1) + (e0 >> 1);
+        const unsigned long long* const wp[2] = {w00, r2 ? w00 + (K >> 1) : w00};
+        uint4 v[2];
+        mg_ll_load<2>(wp, epoch, v);
+        *reinterpret_cast<uint4*>(xs + (size_t)r0 * ld + e0) = v[0];
+        if (r2) *reinterpret_cast<uint4*>(xs + (size_t)(r0 + 1) * ld + e0) = v[1];
+      }
+    }
+  } else {                                                          // h: K % 4096 == 0, two column groups x two rows per
+#pragma unroll 1                                                    //    round trip (8 groups in flight spill: 168-register cap)
+    for (int e = e0; e < K; e += MG_CONSUMERS * 8 * 2) {
+#pragma unroll 1
+      for (int r0 = 0; r0 < R; r0 += 2) {
+        const bool r2 = r0 + 1 < R;
+        const unsigned long long* w00 = ll + (size_t)r0 * (K >> 1) + (e >> 1);
+        const unsigned long long* w01 = w00 + MG_CONSUMERS * 4;
+        const unsigned long long* const wp[4] = {w00, w01, r2 ? w00 + (K >> 1) : w00, r2 ? w01 + (K >> 1) : w01};
+        uint4 v[4];
+        mg_ll_load<4>(wp, epoch, v);
+        *reinterpret_cast<uint4*>(xs + (size_t)r0 * ld + e) = v[0];
+        *reinterpret_cast<uint4*>(xs + (size_t)r0 * ld + e + MG_CONSUMERS * 8) = v[1];
+        if (r2) {
+          *reinterpret_cast<uint4*>(xs + (size_t)(r0 + 1) * ld + e) = v[2];
+          *reinterpret_cast<uint4*>(xs + (size_t)(r0 + 1) * ld + e + MG_CONSUMERS * 8) = v[3];
+        }
+      }
+    }
+  }
+  SyncConsumers::sync();
+}
+
 __device__ __forceinline__ void mg_unpack8(const uint4& raw, float (&v)[8]) {
   v[0] = bf16lo(raw.x); v[1] = bf16hi(raw.x); v[2] = bf16lo(raw.y); v[3] = bf16hi(raw.y);
   v[4] = bf16lo(raw.z); v[5] = bf16hi(raw.z); v[6] = bf16lo(raw.w); v[7] = bf16hi(raw.w);
@@ -467,7 +540,8 @@ __device__ __forceinline__ void mg_stage_ln(MgCtx& cx, bf16* xs, int ld, const b
   const int e = tid * 8;
   const bool active = e < K;                        // warp-uniform (K % 256 == 0)
   float* red1 = cx.red;             // [8 warps][8 rows] partial sums
-  float* red2 = cx.part;            // [8 warps][8 rows] partial sums of squares (the GEMV partial buffer is idle here)
+  float* red2 = cx.red + 64;        // [8 warps][8 rows] partial sums of squares (NOT the GEMV partial buffer: with use_ll >= 3
+                                    // the epilogue warp may still be reducing the previous phase's last tiles)
   const float fk = (float)K;
   const uint4 z4 = make_uint4(0, 0, 0, 0);
   MG_LSTAMP();                                                      // L0: entered
@@ -580,14 +654,16 @@ __device__ __forceinline__ void mg_epi_resid(const MgCtx& cx, const MgEpi& e, in
 __device__ __forceinline__ void mg_epi_qkv(const MegaParams& p, const MgCtx& cx, const MgEpi& e, int a, int n0, float s0, float s1) {
   const float v0 = bf16_round(s0), v1 = bf16_round(s1);
   const int pos = e.pos;
+  __nv_bfloat162 ob;
   if (n0 < p.q_size + p.kv_size) {
     const int i = (n0 % ZB_DH) >> 1;
     const float2 cs = *reinterpret_cast<const float2*>(cx.s_rope + a * (ZB_DH) + i * 2);
     const float o0 = __fsub_rn(__fmul_rn(v0, cs.x), __fmul_rn(v1, cs.y));
     const float o1 = __fadd_rn(__fmul_rn(v1, cs.x), __fmul_rn(v0, cs.y));
     const __nv_bfloat162 o = __floats2bfloat162_rn(o0, o1);
+    ob = o;
     if (n0 < p.q_size) {
-      *reinterpret_cast<__nv_bfloat162*>(e.out + (size_t)a * e.out_stride + n0) = o;
+      if (e.ll == nullptr) *reinterpret_cast<__nv_bfloat162*>(e.out + (size_t)a * e.out_stride + n0) = o;
     } else {
       const int m = n0 - p.q_size;
       const int page = cx.s_page[a];
@@ -598,8 +674,11 @@ __device__ __forceinline__ void mg_epi_qkv(const MegaParams& p, const MgCtx& cx,
     const int m = n0 - p.q_size - p.kv_size;
     const int page = cx.s_page[a];
     bf16* dst = e.kv_layer + ((((size_t)page * 2 + 1) * p.Hkv + m / ZB_DH) * ZB_PAGE + pos % ZB_PAGE) * ZB_DH + m % ZB_DH;
-    *reinterpret_cast<__nv_bfloat162*>(dst) = __floats2bfloat162_rn(v0, v1);
+    ob = __floats2bfloat162_rn(v0, v1);
+    *reinterpret_cast<__nv_bfloat162*>(dst) = ob;
   }
+  // use_ll >= 2: the attention of THIS step polls q and the fresh k / v row from here (the cache rows above are for later steps)
+  if (e.ll != nullptr) mg_ll_store(e.ll + (size_t)a * ((p.q_size + 2 * p.kv_size) >> 1) + (n0 >> 1), e.ll_epoch, *reinterpret_cast<const unsigned*>(&ob));
 }
 
 __device__ __forceinline__ void mg_epi_heads(const MegaParams& p, const MgEpi& e, int b, int n0, float c0, float c1, float u0, float u1) {
@@ -626,9 +705,9 @@ __device__ __forceinline__ void mg_epi_heads(const MegaParams& p, const MgEpi& e
 // host checks both); only ONE of the two MMA loop variants exists in a given instantiation (code size: see k_decode_mega).
 template <bool PK>
 __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, const bf16* xs, int ld, int K, int n_units, int gate_off,
-                                           int kind, int layer) {
+                                           int kind, int layer, bool drain) {
   const int NT = kind == EPI_SWIGLU ? 2 : 1;
-  const int UNIT = kind == EPI_SWIGLU ? 1 : 2;
+  const int UNIT = 2;                            // every phase deals rows in pairs (bf16 pairs are the store / tag granularity)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, t = lane & 3;
   const int R = p.R;
@@ -638,7 +717,6 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
   const uint32_t xs_addr = mg_smem_u32(xs);
   const bool pf1 = cx.prof && kind == EPI_SWIGLU && threadIdx.x == 0;
   const long long pt0 = pf1 ? clock64() : 0, pfull0 = cx.t_full;
-  int ti = 0;                                    // tile counter of this phase (partial buffer = ti & 1)
   for (int n0 = lo; n0 < hi; n0 += 8) {
     const int cnt = min(8, hi - n0);
     // FOUR independent accumulator sets per tile: HMMA results chain through the accumulator, and one chain of 16
@@ -725,10 +803,10 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
     // (partial store, CTA barrier, 8-warp reduce, SwiGLU on warp 0) against 2 x 0.35 us of MMA work: the GEMV phases were
     // bound by that serial tail, not by HBM.  Here the MMA warps only store their partials and arrive on a named
     // barrier; warp 9 reduces and runs the epilogue while they are already in the next tile.
-    const int f = ti & 1;
+    const int f = cx.tile_seq & 1;
     float* pb = cx.part + (size_t)f * 2 * MG_WARPS * 64;
-    if (ti >= 2) mg_bar_sync(MG_BAR_FREE + f, MG_HANDOFF);        // the epilogue warp is done with tile ti - 2
-    ++ti;
+    if (cx.tile_seq >= 2) mg_bar_sync(MG_BAR_FREE + f, MG_HANDOFF);        // the epilogue warp is done with tile tile_seq - 2
+    ++cx.tile_seq;
     if (cx.fine && kind == p.dbg_kind && layer == 1 && threadIdx.x == 0 && cx.trace_n < 32) cx.trace_out[cx.trace_n++] = mg_globaltimer();   // partial buffer free
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
@@ -751,38 +829,48 @@ __device__ __forceinline__ void mg_gemv_phase(const MegaParams& p, MgCtx& cx, co
     mg_bar_arrive(MG_BAR_FULL + f, MG_HANDOFF);
     if (cx.fine && kind == p.dbg_kind && layer == 1 && threadIdx.x == 0 && cx.trace_n < 32) cx.trace_out[cx.trace_n++] = mg_globaltimer();   // tile handed over
   }
-  mg_bar_sync(MG_BAR_PHASE, MG_HANDOFF);     // every epilogue store of this phase has been issued (the grid barrier follows)
+  // Drain: wait until the epilogue warp has issued every store of the (up to two) tiles still in flight - needed where a
+  // grid barrier publishes plain stores.  Where the phase's output travels epoch-tagged (use_ll >= 3: every phase of the
+  // layer stack) nobody waits: the MMA warps go straight on to the next phase's staging and the tile counter runs on.
+  if (drain) {
+    if (cx.tile_seq >= 2) mg_bar_sync(MG_BAR_FREE + (cx.tile_seq & 1), MG_HANDOFF);
+    if (cx.tile_seq >= 1) mg_bar_sync(MG_BAR_FREE + ((cx.tile_seq - 1) & 1), MG_HANDOFF);
+    cx.tile_seq = 0;
+  }
   if (cx.fine && kind == p.dbg_kind && layer == 1 && threadIdx.x == 0 && cx.trace_n < 32) cx.trace_out[cx.trace_n++] = mg_globaltimer();     // phase done
   if (pf1) { cx.t_fc1 += clock64() - pt0; cx.t_fc1_full += cx.t_full - pfull0; }
 }
 
 // The epilogue warp's side of one GEMV phase: per tile, wait for the 8 MMA warps' partials, reduce them in warp order
 // (fixed summation order: reproducible tokens) and run the fused epilogue; same arithmetic as gm_epilogue_* in gemv_mma.cuh.
-__device__ __forceinline__ void mg_gemv_epi(const MegaParams& p, const MgCtx& cx, int n_units, int kind, const MgEpi& epi) {
-  const int UNIT = kind == EPI_SWIGLU ? 1 : 2;
+__device__ __forceinline__ void mg_gemv_epi(const MegaParams& p, MgCtx& cx, int n_units, int kind, const MgEpi& epi, bool drain) {
+  const int UNIT = 2;
   const int lane = threadIdx.x & 31;
   const int R = p.R;
   int lo, hi;
   mg_range(n_units, lo, hi);
   lo *= UNIT; hi *= UNIT;
-  const int n_tiles = (hi - lo + 7) >> 3;
-  int ti = 0;
-  for (int n0 = lo; n0 < hi; n0 += 8, ++ti) {
+  for (int n0 = lo; n0 < hi; n0 += 8) {
     const int cnt = min(8, hi - n0);
-    const int f = ti & 1;
+    const int f = cx.tile_seq & 1;
+    ++cx.tile_seq;
     const float* pb = cx.part + (size_t)f * 2 * MG_WARPS * 64;
     mg_bar_sync(MG_BAR_FULL + f, MG_HANDOFF);
     if (kind == EPI_SWIGLU) {
-      for (int i = lane; i < R * 8; i += 32) {
-        const int r = i >> 3, n = i & 7;
+      for (int i0 = 0; i0 < R * 8; i0 += 32) {                      // all 32 lanes run every trip (the shuffle below)
+        const int i = i0 + lane;
+        const int r = i >> 3, n = i & 7;                            // r < 8 always: in bounds of the partial buffer
         float yv = 0.f, gt = 0.f;
 #pragma unroll
         for (int w = 0; w < MG_WARPS; ++w) { yv += pb[((0 * MG_WARPS + w) * 8 + r) * 8 + n]; gt += pb[((1 * MG_WARPS + w) * 8 + r) * 8 + n]; }
-        if (n < cnt) {
-          yv = bf16_round(yv);
-          gt = bf16_round(gt);
-          const float sg = bf16_round(gt / (1.0f + expf(-gt)));
-          epi.out[(size_t)r * epi.out_stride + n0 + n] = __float2bfloat16_rn(yv * sg);
+        yv = bf16_round(yv);
+        gt = bf16_round(gt);
+        const float sg = bf16_round(gt / (1.0f + expf(-gt)));
+        const float hv = yv * sg, ho = __shfl_xor_sync(0xffffffffu, hv, 1);
+        if (r < R && n < cnt && !(n & 1)) {                                     // n0 and cnt are even
+          const __nv_bfloat162 o2 = __floats2bfloat162_rn(hv, ho);
+          if (epi.ll != nullptr) mg_ll_store(epi.ll + (((size_t)r * epi.out_stride + n0 + n) >> 1), epi.ll_epoch, *reinterpret_cast<const unsigned*>(&o2));
+          else *reinterpret_cast<__nv_bfloat162*>(epi.out + (size_t)r * epi.out_stride + n0 + n) = o2;
         }
       }
     } else if (kind == EPI_HEADS) {
@@ -810,12 +898,10 @@ __device__ __forceinline__ void mg_gemv_epi(const MegaParams& p, const MgCtx& cx
       }
     }
     __syncwarp();
-    if (ti + 2 < n_tiles) {                      // the MMA warps wait for this buffer again only before tile ti + 2
-      __threadfence_block();
-      mg_bar_arrive(MG_BAR_FREE + f, MG_HANDOFF);
-    }
+    __threadfence_block();
+    mg_bar_arrive(MG_BAR_FREE + f, MG_HANDOFF);   // consumed by the MMA warps before tile + 2, or by their drain
   }
-  mg_bar_sync(MG_BAR_PHASE, MG_HANDOFF);
+  if (drain) cx.tile_seq = 0;
 }
 
 // =================================================================================================================
@@ -851,7 +937,7 @@ __device__ __forceinline__ void mg_att_token(const uint4& kraw, const uint4& vra
 }
 
 template <int G>
-__device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const bf16* kv_layer, int pos, unsigned epoch) {
+__device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, const bf16* kv_layer, int pos, unsigned epoch, bool tagged) {
   const MgAttItem it = mg_att_item(p, pos);
   if (!it.mine) return;
   MG_ASTAMP();                                                      // a0: phase entered                               // CTA-uniform
@@ -868,20 +954,44 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
   uint32_t qa[8][2];
   {
     uint4 qw[4];
-#pragma unroll
-    for (int s = 0; s < 4; ++s)
-      qw[s] = g < G ? mg_ldcg16(p.q + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + 32 * s + 8 * t) : z4;
     AttFrag fn;                                         // the fresh row is token 0 of a one-token group
-    if (has_new && warp == 0) {
-      const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
-      const size_t kv_stride = (size_t)p.Hkv * head_stride;
-      const bf16* kp = kv_layer + (size_t)cx.s_page[row] * 2 * kv_stride + (size_t)kvh * head_stride + (size_t)(pos % ZB_PAGE) * ZB_DH;
+    if (tagged) {
+      // use_ll >= 2: q and the fresh k / v row are polled from the in_proj epilogues' tagged words - no grid barrier
+      // between in_proj and here.  Lanes without a fragment of their own poll lane 0's words (always valid addresses).
+      const unsigned long long* qrow = p.qkv_ll + (size_t)row * ((p.q_size + 2 * p.kv_size) >> 1);
+      const unsigned long long* qb = qrow + (((size_t)(kvh * G + (g < G ? g : 0)) * ZB_DH + 8 * t) >> 1);
+      const unsigned long long* const wq[4] = {qb, qb + 16, qb + 32, qb + 48};
+      mg_ll_load<4>(wq, epoch, qw);
+      if (g >= G) { qw[0] = z4; qw[1] = z4; qw[2] = z4; qw[3] = z4; }
+      if (has_new && warp == 0) {
+        const unsigned long long* kb = qrow + ((p.q_size + (size_t)kvh * ZB_DH + 8 * t) >> 1);
+        const unsigned long long* vb = qrow + ((p.q_size + p.kv_size + (size_t)kvh * ZB_DH + 16 * g) >> 1);
+        const unsigned long long* const wf[6] = {kb, kb + 16, kb + 32, kb + 48, vb, vb + 4};
+        uint4 f6[6];
+        mg_ll_load<6>(wf, epoch, f6);
 #pragma unroll
-      for (int s = 0; s < 4; ++s) { fn.k[0][s] = g == 0 ? mg_ldcg16(kp + 32 * s + 8 * t) : z4; fn.k[1][s] = z4; }
+        for (int s = 0; s < 4; ++s) { fn.k[0][s] = g == 0 ? f6[s] : z4; fn.k[1][s] = z4; }
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        fn.v[0][h] = t == 0 ? mg_ldcg16(kp + kv_stride + 16 * g + 8 * h) : z4;
-        fn.v[1][h] = z4; fn.v[2][h] = z4; fn.v[3][h] = z4;
+        for (int h = 0; h < 2; ++h) {
+          fn.v[0][h] = t == 0 ? f6[4 + h] : z4;
+          fn.v[1][h] = z4; fn.v[2][h] = z4; fn.v[3][h] = z4;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int s = 0; s < 4; ++s)
+        qw[s] = g < G ? mg_ldcg16(p.q + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + 32 * s + 8 * t) : z4;
+      if (has_new && warp == 0) {
+        const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
+        const size_t kv_stride = (size_t)p.Hkv * head_stride;
+        const bf16* kp = kv_layer + (size_t)cx.s_page[row] * 2 * kv_stride + (size_t)kvh * head_stride + (size_t)(pos % ZB_PAGE) * ZB_DH;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) { fn.k[0][s] = g == 0 ? mg_ldcg16(kp + 32 * s + 8 * t) : z4; fn.k[1][s] = z4; }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          fn.v[0][h] = t == 0 ? mg_ldcg16(kp + kv_stride + 16 * g + 8 * h) : z4;
+          fn.v[1][h] = z4; fn.v[2][h] = z4; fn.v[3][h] = z4;
+        }
       }
     }
 #pragma unroll
@@ -974,7 +1084,14 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
       for (int w = 0; w < MG_WARPS; ++w) mn = fmaxf(mn, s_m[w * G + g]);
     }
     if (nact == 1) {                                              // the only split: this IS the attention output
-      p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + dim] = __float2bfloat16_rn(ot / lt);
+      const float yv = ot / lt;
+      if (tagged) {                                               // (pair, epoch) words: the even lane stores both values
+        const float yo = __shfl_xor_sync(0xffffffffu, yv, 1);
+        const __nv_bfloat162 o2 = __floats2bfloat162_rn(yv, yo);
+        if (!(dim & 1)) mg_ll_store(p.y_ll + (((size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + dim) >> 1), epoch, *reinterpret_cast<const unsigned*>(&o2));
+      } else {
+        p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + dim] = __float2bfloat16_rn(yv);
+      }
     } else {
       const unsigned long long tag = (unsigned long long)epoch << 32;
       asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(my_ll + oi), "l"(tag | __float_as_uint(ot)) : "memory");
@@ -1039,7 +1156,10 @@ __device__ __forceinline__ void mg_attention(const MegaParams& p, MgCtx& cx, con
       o0 += o.x * c;
       o1 += o.y * c;
     }
-    *reinterpret_cast<__nv_bfloat162*>(p.y + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + 2 * dp) = __floats2bfloat162_rn(o0 / lt, o1 / lt);
+    const __nv_bfloat162 o2 = __floats2bfloat162_rn(o0 / lt, o1 / lt);
+    const size_t yi = (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + 2 * dp;
+    if (tagged) mg_ll_store(p.y_ll + (yi >> 1), epoch, *reinterpret_cast<const unsigned*>(&o2));
+    else *reinterpret_cast<__nv_bfloat162*>(p.y + yi) = o2;
   }
   MG_ASTAMP();                                                      // this CTA's slice of y stored
 }
@@ -1111,14 +1231,14 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
   cx.scratch = cx.ring + (size_t)p.n_stages * MG_STAGE_BYTES;
   cx.part = reinterpret_cast<float*>(cx.scratch + p.scratch_bytes);
   cx.red = cx.part + 2 * 2 * MG_WARPS * 64;
-  cx.s_rope = cx.red + 96;
+  cx.s_rope = cx.red + 160;
   cx.s_xown = cx.s_rope + 8 * ZB_DH;
   cx.s_page = reinterpret_cast<int*>(cx.s_xown + 8 * MG_OWN);
   unsigned char* bars = reinterpret_cast<unsigned char*>(cx.s_page + 16);
   cx.full0 = mg_smem_u32(bars);
   cx.empty0 = cx.full0 + 8u * MG_MAX_STAGES;
   volatile int* s_flags = reinterpret_cast<volatile int*>(bars + 16 * MG_MAX_STAGES);   // [0] stop, [1] consumer cursor, [2] misc, [3] step mailbox for the epilogue warp (KV position, -1 = stop)
-  cx.stage = 0; cx.parity = 0; cx.tile_flip = 0;
+  cx.stage = 0; cx.parity = 0; cx.tile_seq = 0;
   cx.prof = TR && p.dbg != nullptr; cx.t_full = 0; cx.t_fc1 = cx.t_fc1_full = cx.t_fc1_sync = 0;
   cx.trace = false; cx.fine = false; cx.afine = false; cx.tfine = false; cx.lfine = false; cx.trace_n = 0; cx.trace_out = p.dbg ? p.dbg + (size_t)blockIdx.x * MG_TRACE_SLOTS : nullptr;
 
@@ -1223,13 +1343,19 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
 #pragma unroll 1
         for (int ph = 0; ph < n_ph; ++ph) {
           int n_units, kind;
-          if (ph == 0) { kind = heads_l ? EPI_HEADS : EPI_QKV; n_units = heads_l ? p.n_q * p.V / 2 : qkv_rows / 2; epi.out = p.q; epi.out_stride = p.q_size; }
-          else if (ph == 2) { kind = EPI_SWIGLU; n_units = p.F; epi.out = p.h; epi.out_stride = p.F; }
+          if (ph == 0) {
+            kind = heads_l ? EPI_HEADS : EPI_QKV; n_units = heads_l ? p.n_q * p.V / 2 : qkv_rows / 2; epi.out = p.q; epi.out_stride = p.q_size;
+            epi.ll = p.use_ll >= 2 ? p.qkv_ll : nullptr; epi.ll_epoch = mg_ll_epoch(p, step, l, 0);
+          }
+          else if (ph == 2) {
+            kind = EPI_SWIGLU; n_units = p.F / 2; epi.out = p.h; epi.out_stride = p.F;
+            epi.ll = p.use_ll >= 3 ? p.h_ll : nullptr; epi.ll_epoch = mg_ll_epoch(p, step, l, 0);
+          }
           else {
             kind = EPI_RESID; n_units = p.d / 2; epi.out = p.x; epi.out_stride = p.d;
             epi.ll = p.x_ll + (ph == 3 ? (size_t)8 * (p.d >> 1) : 0); epi.ll_epoch = mg_ll_epoch(p, step, l, ph == 3);
           }
-          mg_gemv_epi(p, cx, n_units, kind, epi);
+          mg_gemv_epi(p, cx, n_units, kind, epi, !(p.use_ll >= 3 && p.chain) || heads_l || (!with_heads && l == p.n_layer - 1 && ph == 3));
         }
       }
     }
@@ -1295,7 +1421,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       if (own_lo + i < own_hi) cx.s_xown[r * MG_OWN + i] = __bfloat162float(__ldcg(p.x + (size_t)r * p.d + own_lo + i));
     }
 
-    const bool ll = p.use_ll != 0;
+    const bool ll = p.use_ll != 0, ll2 = p.use_ll >= 2, ll3 = p.use_ll >= 3;
     const unsigned long long* x_ll1 = p.x_ll + (size_t)8 * (p.d >> 1);      // fc2's half of x_ll
     // Layer loop with ONE call site each for the LayerNorm staging, the plain staging, the attention and the GEMV phase
     // (layer n_layer = final LN + heads).  The first version had every phase inlined separately (5 GEMV phases, 8
@@ -1319,16 +1445,22 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
       for (int ph = 0; ph < n_ph; ++ph) {
         // ---- cross-CTA dependencies of this phase
         if (ph == 1) {
-          mg_grid_sync(p.bar_counter, bar_target);
+          // use_ll >= 2: q / k / v and y carry their own epoch tags (qkv_ll, y_ll), so neither barrier is needed: the
+          // CTAs with an attention item poll the in_proj outputs, everyone polls y in the staging below.  Overwriting a
+          // tagged buffer in layer l + 1 is safe without a barrier because every phase consumes ALL of the previous
+          // phase's output: a CTA that reaches phase n + 2 has seen every CTA finish phase n + 1, i.e. finish reading
+          // phase n's output (the epoch of a word is only ever polled for, never waited past).
+          if (!ll2) mg_grid_sync(p.bar_counter, bar_target);
           MG_STAMP();                                             // +2: barrier
           cx.afine = afine_step && l == 1;
-          mg_attention<G>(p, cx, kv_layer, pos, mg_ll_epoch(p, step, l, 0));
+          mg_attention<G>(p, cx, kv_layer, pos, mg_ll_epoch(p, step, l, 0), ll2);
           cx.afine = false;
           MG_STAMP();                                             // +3: attention done
-          mg_grid_sync(p.bar_counter, bar_target);
+          if (!ll2) mg_grid_sync(p.bar_counter, bar_target);
           MG_STAMP();                                             // +4: barrier
-        } else if (ph == 3 || (!ll && (ph == 2 || l > 0))) {
-          // fc1 -> fc2 always meets at a barrier; out_proj -> LN2 and fc2 -> next LN1 only without the epoch-tagged stream
+        } else if ((ph == 3 && !ll3) || (!ll && (ph == 2 || l > 0))) {
+          // fc1 -> fc2 meets at a barrier unless h travels tagged (use_ll >= 3); out_proj -> LN2 and fc2 -> next LN1 only
+          // without the epoch-tagged stream
           mg_grid_sync(p.bar_counter, bar_target);
           MG_STAMP();
         }
@@ -1338,7 +1470,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
           K = p.d;
           const unsigned long long* src_ll = nullptr;
           unsigned epoch = 0;
-          if (ph == 2) { kind = EPI_SWIGLU; n_units = p.F; gate_off = p.F; if (ll) { src_ll = p.x_ll; epoch = mg_ll_epoch(p, step, l, 0); } }
+          if (ph == 2) { kind = EPI_SWIGLU; n_units = p.F / 2; gate_off = p.F; if (ll) { src_ll = p.x_ll; epoch = mg_ll_epoch(p, step, l, 0); } }
           else {
             kind = heads_l ? EPI_HEADS : EPI_QKV; n_units = heads_l ? p.n_q * p.V / 2 : qkv_rows / 2;
             if (ll && l > 0) { src_ll = x_ll1; epoch = mg_ll_epoch(p, step, l - 1, 1); }
@@ -1349,11 +1481,12 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         } else {
           K = ph == 1 ? p.q_size : p.F;
           kind = EPI_RESID; n_units = p.d / 2;
-          mg_stage_copy(xs, K + MG_XPAD, ph == 1 ? p.y : p.h, K, p.R);
+          if (ph == 1 ? ll2 : ll3) mg_stage_ll(xs, K + MG_XPAD, ph == 1 ? p.y_ll : p.h_ll, K, p.R, mg_ll_epoch(p, step, l, 0));
+          else mg_stage_copy(xs, K + MG_XPAD, ph == 1 ? p.y : p.h, K, p.R);
         }
         MG_STAMP();                                               // activations staged
         if (heads_l) MG_TSTAMP();                                 // t2: final LN staged
-        mg_gemv_phase<PK>(p, cx, xs, K + MG_XPAD, K, n_units, gate_off, kind, l);
+        mg_gemv_phase<PK>(p, cx, xs, K + MG_XPAD, K, n_units, gate_off, kind, l, !(ll3 && p.chain) || heads_l || (!with_heads && l == p.n_layer - 1 && ph == 3));
         MG_STAMP();                                               // GEMV phase done
       }
     }

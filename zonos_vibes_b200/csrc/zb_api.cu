@@ -138,8 +138,12 @@ struct zb_ctx {
   unsigned* bar_counter = nullptr;
   unsigned long long* x_ll = nullptr;  // persistent kernel: epoch-tagged residual stream [2][8][d/2]
   unsigned long long* att_ll = nullptr;   // persistent kernel: epoch-tagged split-KV partials [8 rows][Hkv][MG_MAX_SPLIT][G * (Dh + 2)]
+  unsigned long long *qkv_ll = nullptr, *y_ll = nullptr, *h_ll = nullptr;   // tagged q/k/v, attention output, SwiGLU output (same allocation as x_ll)
+  size_t ll_bytes = 0;                 // size of that allocation
+  int opt_chain = 0;                   // persistent kernel, ll = 3: MMA warps run on into the next phase without waiting for their epilogue warp
   unsigned launch_seq = 0;             // persistent-kernel launches so far (epoch base of x_ll)
-  int opt_ll = 1;                      // persistent kernel: poll x_ll instead of the grid barriers after out_proj / fc2
+  int opt_ll = 3;                      // persistent kernel: 1 = poll x_ll instead of the grid barriers after out_proj / fc2; 2 = also q/k/v and y
+                                       // (no barrier around the attention); 0 = grid barriers everywhere
   int n_sms = ZB_NUM_SMS;
   int smem_optin = 0;
   int opt_mega = 1;
@@ -496,8 +500,9 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   p.R = R; p.B = B; p.st = c->st; p.rope_pos = c->rope_pos; p.delayed = c->delayed; p.tokens = c->tokens;
   p.remaining = c->remaining; p.stopping = c->stopping; p.out_len = c->out_len; p.bar_counter = c->bar_counter;
   p.mode = mode; p.n_steps = n_steps;
-  p.x_ll = c->x_ll;
-  p.use_ll = c->opt_ll && n_steps < 8192 && R <= 4;     // R > 4: the polling loader needs > 2 round trips, the barrier is cheaper
+  p.x_ll = c->x_ll; p.qkv_ll = c->qkv_ll; p.y_ll = c->y_ll; p.h_ll = c->h_ll;
+  p.use_ll = (n_steps < 8192 && R <= 4) ? c->opt_ll : 0;     // R > 4: the polling loader needs > 2 round trips, the barrier is cheaper
+  if (p.use_ll >= 3 && g.ffn > 2048 && g.ffn % 4096 != 0) p.use_ll = 2;      // mg_stage_ll's wide variant walks 4096 columns per round
   p.epoch_base = ((++c->launch_seq) & 0xfffu) << 20;    // epochs of different launches never coincide
   p.hidden_in = (const bf16*)hidden_in; p.hidden_out = (bf16*)hidden_out; p.hidden_S = hidden_S; p.hidden_t0 = hidden_t0;
   // shared memory plan: [ring][scratch][partials 8 KB][red 256 B][barriers][flags]
@@ -508,20 +513,19 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
   if (att > scratch) scratch = att;
   if ((size_t)SMP_SMEM_BYTES > scratch) scratch = SMP_SMEM_BYTES;
   scratch = align_up(scratch, 128);
-  const size_t fixed = 2 * 2 * MG_WARPS * 64 * 4 + 96 * 4 + 8 * ZB_DH * 4 + 8 * MG_OWN * 4 + 64 + 16 * MG_MAX_STAGES + 64;
+  const size_t fixed = 2 * 2 * MG_WARPS * 64 * 4 + 160 * 4 + 8 * ZB_DH * 4 + 8 * MG_OWN * 4 + 64 + 16 * MG_MAX_STAGES + 64;
   int stages = (int)(((size_t)c->smem_optin - scratch - fixed) / MG_STAGE_BYTES);
   if (stages > MG_MAX_STAGES) stages = MG_MAX_STAGES;
   if (c->opt_ring > 0 && stages > c->opt_ring) stages = c->opt_ring;
   if (stages < 2) return cudaErrorInvalidConfiguration;
-  p.n_stages = stages; p.scratch_bytes = (int)scratch; p.producer_sleep_ns = (unsigned)c->opt_psleep; p.stream_evict_first = c->opt_evict;
+  p.n_stages = stages; p.scratch_bytes = (int)scratch; p.producer_sleep_ns = (unsigned)c->opt_psleep; p.stream_evict_first = c->opt_evict; p.chain = c->opt_chain;
   const size_t smem = (size_t)stages * MG_STAGE_BYTES + scratch + fixed;
 
   cudaError_t e = cudaMemsetAsync(c->bar_counter, 0, sizeof(unsigned), s);
   if (e != cudaSuccess) return e;
-  // tags of the split-KV partial words start from zero in every launch: a word that this launch has not written yet can
+  // the tags of every epoch-tagged word start from zero in every launch: a word that this launch has not written yet can
   // never carry one of its epochs (launch numbers wrap after 4096 launches)
-  const size_t att_ll_bytes = (size_t)8 * g.num_heads_kv * MG_MAX_SPLIT * G * (ZB_DH + 2) * sizeof(unsigned long long);
-  if ((e = cudaMemsetAsync(c->att_ll, 0, att_ll_bytes, s)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(c->x_ll, 0, c->ll_bytes, s)) != cudaSuccess) return e;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(c->n_sms);
   cfg.blockDim = dim3(MG_THREADS);
@@ -1072,13 +1076,17 @@ static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int devic
       cudaFree(c->arena); delete c;
       return bad(ZB_ERR_NOMEM, std::string("barrier counter: ") + cudaGetErrorString(e));
     }
-    const size_t ll_bytes = (size_t)2 * 8 * (c->cfg.d_model / 2) * sizeof(unsigned long long);
-    const size_t att_ll_bytes = (size_t)8 * cfg->num_heads_kv * MG_MAX_SPLIT * (cfg->num_heads / cfg->num_heads_kv) * (ZB_DH + 2) * sizeof(unsigned long long);
-    if ((e = cudaMalloc(&c->x_ll, ll_bytes)) != cudaSuccess || (e = cudaMemset(c->x_ll, 0, ll_bytes)) != cudaSuccess ||
-        (e = cudaMalloc(&c->att_ll, att_ll_bytes)) != cudaSuccess || (e = cudaMemset(c->att_ll, 0, att_ll_bytes)) != cudaSuccess) {
+    // every epoch-tagged buffer of the persistent kernel in ONE allocation (zeroed at the start of every launch):
+    // [x_ll 2 x 8 x d/2][qkv_ll 8 x (q + 2 kv)/2][y_ll 8 x q/2][h_ll 8 x F/2][att_ll 8 x Hkv x MAX_SPLIT x G (Dh + 2)] words
+    const size_t w_x = (size_t)2 * 8 * (cfg->d_model / 2), w_qkv = (size_t)8 * ((cfg->num_heads + 2 * cfg->num_heads_kv) * ZB_DH / 2);
+    const size_t w_y = (size_t)8 * (cfg->num_heads * ZB_DH / 2), w_h = (size_t)8 * (cfg->ffn / 2);
+    const size_t w_att = (size_t)8 * cfg->num_heads_kv * MG_MAX_SPLIT * (cfg->num_heads / cfg->num_heads_kv) * (ZB_DH + 2);
+    c->ll_bytes = (w_x + w_qkv + w_y + w_h + w_att) * sizeof(unsigned long long);
+    if ((e = cudaMalloc(&c->x_ll, c->ll_bytes)) != cudaSuccess || (e = cudaMemset(c->x_ll, 0, c->ll_bytes)) != cudaSuccess) {
       cudaFree(c->arena); delete c;
       return bad(ZB_ERR_NOMEM, std::string("x_ll: ") + cudaGetErrorString(e));
     }
+    c->qkv_ll = c->x_ll + w_x; c->y_ll = c->qkv_ll + w_qkv; c->h_ll = c->y_ll + w_y; c->att_ll = c->h_ll + w_h;
   }
   if ((e = cudaFuncSetAttribute(k_bt_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM_BYTES)) != cudaSuccess) {
     cudaFree(c->arena); delete c;
@@ -1117,7 +1125,6 @@ int zb_ctx_destroy(zb_ctx* c) {
   if (c->st) cudaFree(c->st);
   if (c->bar_counter) cudaFree(c->bar_counter);
   if (c->x_ll) cudaFree(c->x_ll);
-  if (c->att_ll) cudaFree(c->att_ll);
   if (c->pf_embed) cudaFree(c->pf_embed);
   for (void* q : {(void*)c->pf_x, (void*)c->pf_zx, (void*)c->pf_y, (void*)c->pf_yn, (void*)c->pf_xbc}) if (q) cudaFree(q);
   if (c->dbg) cudaFree(c->dbg);
@@ -1591,6 +1598,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "trace_quiet") c->opt_trace_quiet = value;
   else if (k == "att_chunk") c->opt_att_chunk = value;
   else if (k == "ll") c->opt_ll = value;
+  else if (k == "chain") c->opt_chain = value;
   else if (k == "att_single") c->opt_att_single = value;
   else if (k == "ring") c->opt_ring = value;
   else if (k == "psleep") c->opt_psleep = value;
