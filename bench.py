@@ -254,11 +254,11 @@ def random_dac_state_dict(dev, seed=2):
 # ----------------------------------------------------------------------------------------------------------------
 def ncu_traffic_per_step(args):
     """dram__bytes_read.sum + dram__bytes_write.sum of the persistent decode kernel, per decode step, from the committed
-    `ncu --set full` capture (profiles/r01_traffic.json); None when the run is not the configuration that was captured."""
+    `ncu --set full` capture (profiles/r02_traffic.json); None when the run is not the configuration that was captured."""
     if args.batch != 1 or "mega=0" in args.opt:
         return None
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
             return float(json.load(f)["dram_bytes_per_step"])
     except Exception:
         return None
@@ -425,7 +425,7 @@ def run_b200(args, world, rank, local):
             extra["b64_per_gpu"] = extra_b64(model, ctx, world, rank, dev, args.frames, per_gpu=True, total=64 * world)
         if rank == 0:
             extra["dac_b32x2580"] = extra_dac(model, dev)
-            extra["phases_k_decode_mega"] = phase_table(model, ctx, dev)
+            extra["phases_k_decode_mega"] = phase_table(model, ctx, dev, args)
         extra["hybrid_b16"] = extra_hybrid(dev, world, rank)
         if rank == 0 and world == 1:
             try:
@@ -660,36 +660,46 @@ def gpu_baseline(dev, steps=48, prefix_frames=1290):
     return out
 
 
-def phase_table(model, ctx, dev, T=192):
+def phase_table(model, ctx, dev, args, T=128, ctx_len=1290):
     """Per-phase breakdown of one decode step of k_decode_mega from one TRACED launch (slower instantiation with
-    %globaltimer stamps on CTA 0), outside every timed region: us and algorithmic bytes per phase, layers 1-2 averaged."""
+    %globaltimer stamps on CTA 0), outside every timed region, at the mean context of the headline workload (a conditioning
+    prefix of `ctx_len` tokens): us and algorithmic bytes per phase, layers 1-2 averaged."""
     import ctypes as C
     ctx.set_option("trace", 1)
     ctx.set_option("trace_quiet", 1)
     try:
-        prefix = torch.randn(2, LC, FULL["d_model"], device=dev).bfloat16()
+        prefix = torch.randn(2, ctx_len, FULL["d_model"], device=dev).bfloat16()
         model.generate(prefix, max_new_tokens=T, batch_size=1, progress_bar=False, seed=3)
         buf = (C.c_uint64 * 64)()
         n = ctx.lib.zb_last_trace(ctx.handle, buf, 64)
     finally:
         ctx.set_option("trace", 0)
         ctx.set_option("trace_quiet", 0)
-    names = ["ln1_stage", "in_proj", "grid_barrier", "attention", "grid_barrier", "y_stage", "out_proj", "ln2_stage", "fc1", "grid_barrier",
-             "h_stage", "fc2"]
-    if n < 2 + 3 * 12:
+    # stamp order per layer (mega_kernel.cuh, MG_STAMP): dependencies that are grid barriers in the ll < 2 / ll < 3 modes are
+    # polls of epoch-tagged words inside the following staging in the default mode (ll = 3), where their slots are ~0
+    ll = 3
+    for kv in args.opt:
+        if kv.startswith("ll="):
+            ll = int(kv[3:])
+    names = ["ln1_stage", "in_proj", "dep_in_proj_to_attention", "attention", "dep_attention_to_out_proj", "y_stage", "out_proj", "ln2_stage", "fc1"]
+    names += (["dep_fc1_to_fc2"] if ll < 3 else []) + ["h_stage", "fc2"]
+    per = len(names)
+    if n < 2 + 3 * per:
         return None
     t = [int(buf[i]) for i in range(n)]
     d, f = FULL["d_model"], FULL["ffn"]
     qkv = (FULL["num_heads"] + 2 * FULL["num_heads_kv"]) * 128
-    by = {"in_proj": qkv * d * 2, "out_proj": d * d * 2, "fc1": 2 * f * d * 2, "fc2": d * f * 2}
+    by = {"in_proj": qkv * d * 2, "out_proj": d * d * 2, "fc1": 2 * f * d * 2, "fc2": d * f * 2,
+          "attention": 2 * FULL["num_heads_kv"] * 2 * 128 * 2 * (ctx_len + T // 2)}
     acc = {}
     for layer in (1, 2):
-        base = 2 + 12 * layer
+        base = 2 + per * layer
         for j, nm in enumerate(names):
             acc[nm] = acc.get(nm, 0.0) + (t[base + j] - t[base + j - 1]) / 2e3
-    rows = [{"phase": nm, "us": round(us, 2), "bytes": by.get(nm, 0), "gbs": round(by[nm] / us / 1e3, 1) if nm in by else None} for nm, us in acc.items()]
-    return {"per_layer_us": round(sum(acc.values()), 2), "phases": rows,
-            "note": "traced instantiation (about 5 % slower than the production kernel); grid_barrier sums the three barriers of a layer; stamps of CTA 0"}
+    rows = [{"phase": nm, "us": round(us, 2), "bytes": by.get(nm, 0), "gbs": round(by[nm] / us / 1e3, 1) if nm in by and us > 0 else None} for nm, us in acc.items()]
+    return {"per_layer_us": round(sum(acc.values()), 2), "ctx": ctx_len + T // 2, "dependency_mode_ll": ll, "phases": rows,
+            "note": "traced instantiation (a few % slower than the production kernel); stamps of CTA 0; *_stage = polling the previous phase's "
+                    "epoch-tagged output + LayerNorm where there is one; dep_* = grid barriers (zero when the data carries the dependency)"}
 
 
 def main():

@@ -151,7 +151,7 @@ def test_bench_reports_ncu_traffic_only_for_the_captured_configuration():
     sys.path.insert(0, root)
     bench = importlib.import_module("bench")
     t = bench.ncu_traffic_per_step(argparse.Namespace(batch=1, opt=[]))
-    with open(os.path.join(root, "profiles", "r01_traffic.json")) as f:
+    with open(os.path.join(root, "profiles", "r02_traffic.json")) as f:
         rec = json.load(f)
     assert t == float(rec["dram_bytes_per_step"])
     # traffic must be close to (and not below) the algorithmic bytes: every weight byte read once per step
