@@ -566,8 +566,7 @@ def extra_hybrid(dev, world, rank, frames=96):
     di = HYBRID["expand"] * FULL["d_model"]
     state_bytes = n_m * 2 * b * (2 * (di // HYBRID["headdim"]) * HYBRID["headdim"] * HYBRID["d_state"] * 4)      # ssm state read + write, 2 CFG rows
     kv_bytes = 2 * b * n_attn * 2 * FULL["num_heads_kv"] * 128 * 2 * (LC + frames / 2)
-    groups = (2 * b + 7) // 8                                       # per-op path: weights re-streamed per group of 8 rows
-    step_bytes = wb * groups + state_bytes + kv_bytes
+    step_bytes = wb + state_bytes + kv_bytes                        # algorithmic: every weight byte once per step (batched tcgen05 path, >= 9 rows)
     hbm, _, _, kind = peaks_full()
     gbs = step_bytes / (step_ms * 1e-3) / 1e9
     del model
@@ -578,7 +577,7 @@ def extra_hybrid(dev, world, rank, frames=96):
             "decode_frames_per_s": b * world / (step_ms * 1e-3), "audio_sec_per_sec": b * world / (step_ms * 1e-3) / FRAME_RATE,
             "architecture": "synthetic: 46 layers, 5 attention + GatedMLP(8192), 41 Mamba2 (d_state 128, headdim 64, expand 2); dims unverified (SURVEY App. C)",
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm, "peak_kind": kind, "bytes_per_launch": step_bytes,
-                         "kernel": "per-op CUDA graph (k_gemv_mma + k_m2_conv / k_m2_ssm / k_m2_gated_norm + k_attn_decode_mma); bytes = weights x row groups + SSM state r/w + KV"}}
+                         "kernel": "batched tcgen05 path (k_bt_gemm + finish kernels for the Mamba2 / attention projections, k_m2_conv / k_m2_ssm / k_m2_gated_norm, k_attn_decode_mma), one CUDA graph per step; bytes = weights once + SSM state read + write (fp32) + KV"}}
 
 
 def gpu_baseline(dev, steps=48, prefix_frames=1290):

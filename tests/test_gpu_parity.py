@@ -563,10 +563,13 @@ def test_backbone_plugin_forward(golden, cuda, cname):
 
 
 # ------------------------------------------------------------------------------------------------ hybrid (Mamba2) backbone
-def test_hybrid_backbone_plugin_forward(cuda):
+@pytest.mark.parametrize("path", ["per_op_graph", "batched_tcgen05", "batched_tcgen05_stepped_prefill"])
+def test_hybrid_backbone_plugin_forward(cuda, path):
     """Row a8: MambaSSMZonosBackbone (zonos/backbone/_mamba_ssm.py:8-57) through the plugin API against
     oracle/hybrid_oracle.py (whose Mamba2 mixer is pinned to the transformers port of mamba-ssm on CPU): a prefill of 8
-    tokens, then 4 single-token decode calls; 2 rows."""
+    tokens, then 4 single-token decode calls; 2 rows.  `batched_tcgen05`: the decode steps run the Mamba2 and attention
+    projections on the batched tcgen05 path (what >= 9 rows use: weights streamed once for all rows); with
+    `_stepped_prefill` the 8 prefill tokens go through it too, one by one."""
     import hybrid_oracle as ho
     import zonos_vibes_b200 as z
     cfg = ho.HYBRID_TINY
@@ -576,6 +579,8 @@ def test_hybrid_backbone_plugin_forward(cuda):
     bb.load_state_dict({k[len("backbone."):]: v for k, v in sd_full.items()})
     kv = bb.allocate_inference_cache(2, 32)
     assert set(kv) == set(range(cfg.n_layer))
+    bb.native().set_option("bt_min_rows", 9 if path == "per_op_graph" else 2)
+    bb.native().set_option("chunked_prefill", 0 if path.endswith("stepped_prefill") else 1)
     params = z.InferenceParams(32, 2, 0, 0, kv, torch.zeros(2, dtype=torch.int32, device=cuda))
     x = torch.randn(2, 12, cfg.d_model, generator=torch.Generator().manual_seed(11)).bfloat16()
     oracle = ho.HybridOracleBackbone(cfg, sd_full)

@@ -341,6 +341,23 @@ __global__ void __launch_bounds__(256) k_bt_qkv_finish(const BtFinishParams p) {
   }
 }
 
+// plain finish (hybrid backbone, Mamba2 in_proj): out[row][n] = bf16(sum of the split partials).  grid = rows, block = 256.
+__global__ void __launch_bounds__(256) k_bt_plain_finish(const BtFinishParams p, bf16* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+  if (p.st->done) return;
+  const int row = blockIdx.x;
+  const size_t split_stride = (size_t)p.m_pad * p.N;
+  for (int n8 = threadIdx.x * 8; n8 < p.N; n8 += 2048) {           // N % 8 == 0 (checked by the host)
+    float a[8];
+    bt_split_sum8(p.partial, p.splits, split_stride, (size_t)row * p.N + n8, a);
+    __nv_bfloat162 o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = __floats2bfloat162_rn(a[2 * j], a[2 * j + 1]);
+    *reinterpret_cast<uint4*>(out + (size_t)row * p.N + n8) = *reinterpret_cast<uint4*>(o);
+  }
+}
+
 // heads finish: bf16 round, fp32 CFG mix of rows b (cond) and B+b (uncond), pad / EOS masks (model.py:111-115,266-267,280).
 // grid = (n_q, B), block = 256.
 __global__ void __launch_bounds__(256) k_bt_heads_finish(const BtFinishParams p) {

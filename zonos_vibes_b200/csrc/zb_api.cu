@@ -129,7 +129,7 @@ struct zb_ctx {
   int bt_mpad = 0;
   bf16* bt_xn = nullptr;
   float* bt_partial = nullptr;
-  CUtensorMap bt_map_xn{}, bt_map_y{}, bt_map_h{}, bt_map_heads{};
+  CUtensorMap bt_map_xn{}, bt_map_y{}, bt_map_h{}, bt_map_heads{}, bt_map_yn{};   // yn: gated-norm output of a Mamba2 layer (hybrid)
   std::vector<CUtensorMap> bt_map_in, bt_map_out, bt_map_fc1, bt_map_fc2;
   // persistent decode kernel (mega_kernel.cuh)
   MegaLayer mega_l0{};
@@ -604,7 +604,7 @@ cudaError_t launch_mega(zb_ctx* c, int mode, int n_steps, int R, int B, float* l
 // ---------------------------------------------------------------------------------------------------------------
 // batched tcgen05 path
 // ---------------------------------------------------------------------------------------------------------------
-bool use_bt(const zb_ctx* c, int rows) { return c->bt_ready && !c->hybrid && rows >= c->opt_bt_min_rows && !(use_mega(c, rows)); }
+bool use_bt(const zb_ctx* c, int rows) { return c->bt_ready && rows >= c->opt_bt_min_rows && !(use_mega(c, rows)); }
 
 int bt_make_map(zb_ctx* c, CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows, uint32_t box_rows) {
   cuuint64_t dims[2] = {inner, rows};
@@ -637,13 +637,15 @@ BtPlan bt_plan(const zb_ctx* c, int n_tiles, int K) {
 int bt_setup(zb_ctx* c, int rows_pad) {
   const zb_config& g = c->cfg;
   c->bt_ready = false;
-  if (!c->encode || c->hybrid) return ZB_OK;                                   // driver without cuTensorMapEncodeTiled: per-op path only
+  if (!c->encode) return ZB_OK;                                                // driver without cuTensorMapEncodeTiled: per-op path only
   const int d = g.d_model, F = g.ffn, q_size = g.num_heads * ZB_DH, qkv = (g.num_heads + 2 * g.num_heads_kv) * ZB_DH;
   if (d % BT_BK || F % BT_BK || q_size % BT_BK || F % 64) return ZB_OK;
   if (d < BT_BN || qkv < BT_BN || F < 64) return ZB_OK;
+  if (c->hybrid && (c->m_dinner % BT_BK || c->m_dinproj % 8 || c->m_dinproj < BT_BN)) return ZB_OK;
   c->bt_mpad = rows_pad;
   int maxN = qkv > d ? qkv : d;
   if (g.n_codebooks * g.vocab > maxN) maxN = g.n_codebooks * g.vocab;
+  if (c->hybrid && c->m_dinproj > maxN) maxN = c->m_dinproj;
   ZB_CUDA(c->err, cudaMalloc((void**)&c->bt_xn, (size_t)rows_pad * d * 2));
   ZB_CUDA(c->err, cudaMemset(c->bt_xn, 0, (size_t)rows_pad * d * 2));
   ZB_CUDA(c->err, cudaMalloc((void**)&c->bt_partial, (size_t)8 * rows_pad * maxN * 4));
@@ -651,9 +653,16 @@ int bt_setup(zb_ctx* c, int rows_pad) {
   if ((rc = bt_make_map(c, &c->bt_map_xn, c->bt_xn, d, rows_pad, BT_BM))) return rc;
   if ((rc = bt_make_map(c, &c->bt_map_y, c->y, q_size, rows_pad, BT_BM))) return rc;
   if ((rc = bt_make_map(c, &c->bt_map_h, c->h, F, rows_pad, BT_BM))) return rc;
+  if (c->hybrid && c->n_mamba > 0 && (rc = bt_make_map(c, &c->bt_map_yn, c->m_ynorm, c->m_dinner, rows_pad, BT_BM))) return rc;
   const int nl = g.n_layer;
   c->bt_map_in.resize(nl); c->bt_map_out.resize(nl); c->bt_map_fc1.resize(nl); c->bt_map_fc2.resize(nl);
   for (int l = 0; l < nl; ++l) {
+    if (c->hybrid && c->is_mamba[l]) {                     // Mamba2 layer: in_proj [d_in_proj][d], out_proj [d][d_inner]
+      const LayerM& m = c->mlayers[l];
+      if ((rc = bt_make_map(c, &c->bt_map_in[l], m.w_in, d, c->m_dinproj, BT_BN))) return rc;
+      if ((rc = bt_make_map(c, &c->bt_map_out[l], m.w_out, c->m_dinner, d, BT_BN))) return rc;
+      continue;
+    }
     const LayerW& w = c->layers[l];
     if ((rc = bt_make_map(c, &c->bt_map_in[l], w.w_in, d, qkv, BT_BN))) return rc;
     if ((rc = bt_make_map(c, &c->bt_map_out[l], w.w_out, q_size, d, BT_BN))) return rc;
@@ -692,6 +701,47 @@ BtFinishParams bt_finish_params(zb_ctx* c, int splits, int N) {
   return f;
 }
 
+// LayerNorm that feeds layer l's first projection (l == n_layer: norm_f): a Mamba2 block's norm, or an attention block's norm1
+static void bt_ln_of(const zb_ctx* c, int l, const bf16*& w, const bf16*& b) {
+  if (l >= c->cfg.n_layer) { w = c->normf_w; b = c->normf_b; }
+  else if (c->hybrid && c->is_mamba[l]) { w = c->mlayers[l].ln_w; b = c->mlayers[l].ln_b; }
+  else { w = c->layers[l].ln1_w; b = c->layers[l].ln1_b; }
+}
+
+// One Mamba2 layer of the hybrid backbone on the batched path: in_proj and out_proj stream their weights ONCE for all rows
+// (the per-op path re-streams them per group of 8 rows); conv / SSM step / gated norm are the decode-step kernels.
+cudaError_t enqueue_bt_mamba_layer(zb_ctx* c, int l, cudaStream_t s) {
+  const zb_config& g = c->cfg;
+  const LayerM& w = c->mlayers[l];
+  const int d = g.d_model, rows = c->rows;
+  cudaError_t e;
+  int splits = 1;
+  if ((e = bt_gemm(c, c->bt_map_xn, c->bt_map_in[l], c->m_dinproj, d, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
+  {
+    BtFinishParams f = bt_finish_params(c, splits, c->m_dinproj);
+    if ((e = launch(c, k_bt_plain_finish, dim3(rows), dim3(256), 0, s, f, c->m_zx)) != cudaSuccess) return e;
+  }
+  M2Params m;
+  memset(&m, 0, sizeof(m));
+  m.zx = c->m_zx; m.d_in_proj = c->m_dinproj; m.d_inner = c->m_dinner; m.conv_dim = c->m_convdim; m.d_conv = c->hyb.d_conv;
+  m.nheads = c->m_nheads; m.headdim = c->hyb.headdim; m.d_state = c->hyb.d_state; m.ngroups = c->hyb.ngroups;
+  m.conv_w = w.conv_w; m.conv_b = w.conv_b; m.dt_bias = w.dt_bias; m.A_log = w.A_log; m.D = w.D; m.norm_w = w.norm_w;
+  const int slot = c->kv_slot[l];
+  m.conv_state = c->m_conv_state + (size_t)slot * rows * c->m_convdim * c->hyb.d_conv;
+  m.ssm_state = c->m_ssm_state + (size_t)slot * rows * c->m_nheads * c->hyb.headdim * c->hyb.d_state;
+  m.xbc = c->m_xbc; m.y = c->m_y; m.ynorm = c->m_ynorm; m.eps = 1e-5f; m.st = c->st;
+  if ((e = launch(c, k_m2_conv, dim3((c->m_convdim + 255) / 256, rows), dim3(256), 0, s, m)) != cudaSuccess) return e;
+  if ((e = launch(c, k_m2_ssm, dim3(c->m_nheads, rows), dim3(256), 0, s, m)) != cudaSuccess) return e;
+  if ((e = launch(c, k_m2_gated_norm, dim3(rows), dim3(256), 0, s, m)) != cudaSuccess) return e;
+  if ((e = bt_gemm(c, c->bt_map_yn, c->bt_map_out[l], d, c->m_dinner, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
+  {
+    BtFinishParams f = bt_finish_params(c, splits, d);
+    bt_ln_of(c, l + 1, f.ln_w, f.ln_b);
+    if ((e = launch(c, k_bt_resid_ln, dim3(rows), dim3(256), (size_t)d * 4, s, f)) != cudaSuccess) return e;
+  }
+  return cudaSuccess;
+}
+
 // x holds the layer-0 input.  Runs LN1(0) + all layers; leaves norm_f(x) in bt_xn.
 cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
   const zb_config& g = c->cfg;
@@ -702,10 +752,15 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
   cudaError_t e;
   {
     BtFinishParams f = bt_finish_params(c, 0, d);
-    f.partial = nullptr; f.ln_w = c->layers[0].ln1_w; f.ln_b = c->layers[0].ln1_b;
+    f.partial = nullptr;
+    bt_ln_of(c, 0, f.ln_w, f.ln_b);
     if ((e = launch(c, k_bt_resid_ln, dim3(rows), dim3(256), ln_smem, s, f)) != cudaSuccess) return e;
   }
   for (int l = 0; l < g.n_layer; ++l) {
+    if (c->hybrid && c->is_mamba[l]) {
+      if ((e = enqueue_bt_mamba_layer(c, l, s)) != cudaSuccess) return e;
+      continue;
+    }
     const LayerW& w = c->layers[l];
     bf16* kv_layer = c->kv + (size_t)c->kv_slot[l] * c->kv_layer_elems;
     int splits = 1;
@@ -735,8 +790,7 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
     if ((e = bt_gemm(c, c->bt_map_h, c->bt_map_fc2[l], d, F, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
     {
       BtFinishParams f = bt_finish_params(c, splits, d);
-      if (l + 1 < g.n_layer) { f.ln_w = c->layers[l + 1].ln1_w; f.ln_b = c->layers[l + 1].ln1_b; }
-      else { f.ln_w = c->normf_w; f.ln_b = c->normf_b; }
+      bt_ln_of(c, l + 1, f.ln_w, f.ln_b);
       if ((e = launch(c, k_bt_resid_ln, dim3(rows), dim3(256), ln_smem, s, f)) != cudaSuccess) return e;
     }
   }
