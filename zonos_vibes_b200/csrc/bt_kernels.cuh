@@ -33,6 +33,8 @@
 enum { BT_MODE_PARTIAL = 0, BT_MODE_SWIGLU = 1 };
 
 struct BtGemmParams {
+  int cs;                // cluster size along the weight-tile dimension (1, 2 or 4): the CTAs of a cluster share the activation
+                         // tile, every CTA loads 1 / cs of it and multicasts it to all of them (the launch carries the cluster attribute)
   int M;                 // real activation rows
   int N;                 // weight rows (PARTIAL) or ffn size F (SWIGLU: value rows [0,F), gate rows [F,2F))
   int num_kb;            // K / 64
@@ -44,8 +46,22 @@ struct BtGemmParams {
   const ZbDevState* st;  // done flag
 };
 
-// grid = (n_tiles, m_tiles, splits); block = 192; dyn smem = BT_SMEM_BYTES
-__global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm(const __grid_constant__ CUtensorMap map_x,
+__device__ __forceinline__ void bt_tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint16_t mask) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%2, %3}], [%4], %5;" ::"r"(dst),
+               "l"(map), "r"(c0), "r"(c1), "r"(bar), "h"(mask)
+               : "memory");
+}
+__device__ __forceinline__ void bt_commit_mc(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void bt_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// grid = (n_tiles, m_tiles, splits); block = 192; dyn smem = BT_SMEM_BYTES.  map_xs: the activations again with a box of
+// BT_BM / cs rows (the slice one CTA of a cluster loads and multicasts); unused when cs == 1.
+__global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_xs,
                                                            const __grid_constant__ CUtensorMap map_w, const BtGemmParams p) {
   extern __shared__ unsigned char bt_smem_raw[];
   const uint32_t raw = smem_u32(bt_smem_raw);
@@ -66,16 +82,24 @@ __global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm(const __grid_constant
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
-    for (int s = 0; s < BT_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    // a stage is free again when the MMAs of ALL CTAs of the cluster have read it (every CTA multicasts into every CTA)
+    for (int s = 0; s < BT_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), (uint32_t)p.cs); }
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  const int cs = p.cs;
+  uint32_t crank = 0;
+  if (cs > 1) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+  const uint16_t cmask = (uint16_t)((1u << cs) - 1u);
+  const int a_rows = BT_BM / cs;                                  // rows of the activation tile this CTA loads
+  const uint32_t a_off = crank * (uint32_t)(a_rows * BT_BK * 2);  // ... and where they land in every CTA's stage
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(128u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
+  if (cs > 1) bt_cluster_sync();                                  // every CTA's barriers exist before a peer's multicast signals them
   tc_fence_after();
   const uint32_t tmem_d = *tmem_slot_ptr;
 
@@ -97,14 +121,18 @@ __global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm(const __grid_constant
         }
       }
       pdl_wait_prior_grid();
-      for (int i = 0; i < pre; ++i) tma_load_2d(base + (uint32_t)i * BT_STAGE_BYTES, &map_x, (kb0 + i) * BT_BK, m0, full_bar(i));
+      for (int i = 0; i < pre; ++i) {
+        if (cs > 1) bt_tma_load_2d_mc(base + (uint32_t)i * BT_STAGE_BYTES + a_off, &map_xs, (kb0 + i) * BT_BK, m0 + (int)crank * a_rows, full_bar(i), cmask);
+        else tma_load_2d(base + (uint32_t)i * BT_STAGE_BYTES, &map_x, (kb0 + i) * BT_BK, m0, full_bar(i));
+      }
       for (int i = pre; i < nkb; ++i) {
         const int s = i % BT_STAGES;
         mbar_wait(empty_bar(s), ((i / BT_STAGES) - 1) & 1);
         const uint32_t a_dst = base + (uint32_t)s * BT_STAGE_BYTES;
         const uint32_t b_dst = a_dst + BT_A_BYTES;
         mbar_expect_tx(full_bar(s), BT_STAGE_BYTES);
-        tma_load_2d(a_dst, &map_x, (kb0 + i) * BT_BK, m0, full_bar(s));
+        if (cs > 1) bt_tma_load_2d_mc(a_dst + a_off, &map_xs, (kb0 + i) * BT_BK, m0 + (int)crank * a_rows, full_bar(s), cmask);
+        else tma_load_2d(a_dst, &map_x, (kb0 + i) * BT_BK, m0, full_bar(s));
         if (swiglu) {
           tma_load_2d(b_dst, &map_w, (kb0 + i) * BT_BK, n_tile * 64, full_bar(s));
           tma_load_2d(b_dst + BT_B_BYTES / 2, &map_w, (kb0 + i) * BT_BK, p.N + n_tile * 64, full_bar(s));
@@ -127,7 +155,8 @@ __global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm(const __grid_constant
 #pragma unroll
         for (int k = 0; k < BT_BK / 16; ++k)
           tc_mma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (i | k) != 0);
-        tc_commit(empty_bar(s));
+        if (cs > 1) bt_commit_mc(empty_bar(s), cmask);
+        else tc_commit(empty_bar(s));
       }
       tc_commit(tmem_full_bar);
     }
@@ -193,6 +222,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm(const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (cs > 1) bt_cluster_sync();                                  // no CTA leaves while a peer may still multicast into it / arrive on its barriers
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(128u) : "memory");
   }

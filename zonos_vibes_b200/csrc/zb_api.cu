@@ -130,6 +130,11 @@ struct zb_ctx {
   bf16* bt_xn = nullptr;
   float* bt_partial = nullptr;
   CUtensorMap bt_map_xn{}, bt_map_y{}, bt_map_h{}, bt_map_heads{}, bt_map_yn{};   // yn: gated-norm output of a Mamba2 layer (hybrid)
+  CUtensorMap bt_maps_xn{}, bt_maps_y{}, bt_maps_h{}, bt_maps_yn{};                // the same activations with a box of 128 / bt_cs rows (cluster multicast slices)
+  int bt_cs = 1;                       // cluster size the slice maps were built for
+  int opt_bt_cluster = 1;              // batched path: CTAs per cluster sharing (multicasting) the activation tile: 1, 2 or 4.  Measured
+                                       // at batch 64: 1 837 / 1 891 / 2 060 us per step for 1 / 2 / 4 - the GEMMs are bound by what is delivered INTO the
+                                       // SMs (weights + activation tile per CTA), which multicast does not reduce; off by default
   std::vector<CUtensorMap> bt_map_in, bt_map_out, bt_map_fc1, bt_map_fc2;
   // persistent decode kernel (mega_kernel.cuh)
   MegaLayer mega_l0{};
@@ -654,6 +659,11 @@ int bt_setup(zb_ctx* c, int rows_pad) {
   if ((rc = bt_make_map(c, &c->bt_map_y, c->y, q_size, rows_pad, BT_BM))) return rc;
   if ((rc = bt_make_map(c, &c->bt_map_h, c->h, F, rows_pad, BT_BM))) return rc;
   if (c->hybrid && c->n_mamba > 0 && (rc = bt_make_map(c, &c->bt_map_yn, c->m_ynorm, c->m_dinner, rows_pad, BT_BM))) return rc;
+  c->bt_cs = c->opt_bt_cluster;
+  if ((rc = bt_make_map(c, &c->bt_maps_xn, c->bt_xn, d, rows_pad, BT_BM / c->bt_cs))) return rc;
+  if ((rc = bt_make_map(c, &c->bt_maps_y, c->y, q_size, rows_pad, BT_BM / c->bt_cs))) return rc;
+  if ((rc = bt_make_map(c, &c->bt_maps_h, c->h, F, rows_pad, BT_BM / c->bt_cs))) return rc;
+  if (c->hybrid && c->n_mamba > 0 && (rc = bt_make_map(c, &c->bt_maps_yn, c->m_ynorm, c->m_dinner, rows_pad, BT_BM / c->bt_cs))) return rc;
   const int nl = g.n_layer;
   c->bt_map_in.resize(nl); c->bt_map_out.resize(nl); c->bt_map_fc1.resize(nl); c->bt_map_fc2.resize(nl);
   for (int l = 0; l < nl; ++l) {
@@ -684,8 +694,32 @@ cudaError_t bt_gemm(zb_ctx* c, const CUtensorMap& mx, const CUtensorMap& mw, int
   p.M = Mrows; p.N = N; p.num_kb = pl.num_kb; p.kb_per_split = pl.kb_per_split; p.mode = mode;
   p.partial = c->bt_partial; p.m_pad = c->bt_mpad; p.h = c->h; p.st = c->st;
   if (splits_out) *splits_out = pl.splits;
-  const dim3 grid(n_tiles, (Mrows + BT_BM - 1) / BT_BM, pl.splits);
-  return launch(c, k_bt_gemm, grid, dim3(BT_THREADS), (size_t)BT_SMEM_BYTES, s, mx, mw, p);
+  // the activation tile is shared by the CTAs of a cluster (multicast): the slice map that goes with the full-tile map
+  const int cs = c->bt_cs;
+  const CUtensorMap* mxs = &mx == &c->bt_map_xn ? &c->bt_maps_xn : &mx == &c->bt_map_y ? &c->bt_maps_y : &mx == &c->bt_map_h ? &c->bt_maps_h : &c->bt_maps_yn;
+  p.cs = cs;
+  const int gx = (n_tiles + cs - 1) / cs * cs;        // padding CTAs load out-of-range (zero) weight rows and store nothing
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(gx, (Mrows + BT_BM - 1) / BT_BM, pl.splits);
+  cfg.blockDim = dim3(BT_THREADS);
+  cfg.dynamicSmemBytes = (size_t)BT_SMEM_BYTES;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (c->opt_pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (cs > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = cs; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
+  if (c->counting) c->launches += 1;
+  return cudaLaunchKernelEx(&cfg, k_bt_gemm, mx, *mxs, mw, p);
 }
 
 BtFinishParams bt_finish_params(zb_ctx* c, int splits, int N) {
@@ -1653,6 +1687,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "att_chunk") c->opt_att_chunk = value;
   else if (k == "ll") c->opt_ll = value;
   else if (k == "chain") c->opt_chain = value;
+  else if (k == "bt_cluster") c->opt_bt_cluster = (value == 2 || value == 4) ? value : 1;
   else if (k == "att_single") c->opt_att_single = value;
   else if (k == "ring") c->opt_ring = value;
   else if (k == "psleep") c->opt_psleep = value;
