@@ -263,3 +263,16 @@ def test_prefix_conditioner_mirror_keys_and_cond_dict():
     mcd = g["cond.mcd_inputs"]
     for k in ("emotion", "fmax", "pitch_std", "speaking_rate", "language_id"):
         assert cd[k].shape == mcd[k].shape and torch.allclose(cd[k].float(), mcd[k].float(), atol=1e-6), k
+
+
+def test_library_staleness_is_by_content(tmp_path, monkeypatch):
+    """_lib.load() rebuilds a library that was built from other sources: staleness is a content hash of csrc/ +
+    the header recorded next to the .so, so a copied tree (the GPU box's snapshot) with new timestamps stays current."""
+    from zonos_vibes_b200 import build
+    assert os.path.exists(build.LIB) and not build._stale()
+    fake = tmp_path / "stamp"
+    fake.write_text("0" * 64 + "\n")
+    monkeypatch.setattr(build, "STAMP", str(fake))
+    assert build._stale()
+    fake.write_text(build._source_hash() + "\n")
+    assert not build._stale()

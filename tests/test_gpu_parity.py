@@ -436,7 +436,7 @@ def test_generate_with_long_audio_prefix_full_size(golden_long, cuda, path):
 class _options:
     def __init__(self, model, **kw):
         self.ctx, self.kw = model._native(), kw
-        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=3, bt_prefill=1)
+        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=3, bt_prefill=1, bt_cluster=1)
 
     def __enter__(self):
         for k, v in self.kw.items():
@@ -447,7 +447,8 @@ class _options:
             self.ctx.set_option(k, self.defaults[k])
 
 
-PATHS = {"per_op_graph": dict(mega=0), "batched_tcgen05": dict(mega=0, bt_min_rows=2)}
+PATHS = {"per_op_graph": dict(mega=0), "batched_tcgen05": dict(mega=0, bt_min_rows=2),
+         "batched_tcgen05_cluster2": dict(mega=0, bt_min_rows=2, bt_cluster=2)}     # activation tile multicast across CTA pairs
 
 
 @pytest.mark.parametrize("path", list(PATHS))

@@ -93,13 +93,18 @@ def load() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        from . import build as _build
+    from . import build as _build
+    if _build._stale():
+        # missing, or built from other sources than the ones next to it (content hash, build.py): rebuild when nvcc is
+        # there; a stale library without a compiler is used as it is, loudly
         try:
             _build.build()
         except Exception as e:  # noqa: BLE001
-            raise ZbError(
-                f"libzonos_b200.so is missing and could not be built ({e}); the B200 path has no fallback") from e
+            if not os.path.exists(LIB_PATH):
+                raise ZbError(
+                    f"libzonos_b200.so is missing and could not be built ({e}); the B200 path has no fallback") from e
+            import warnings
+            warnings.warn(f"libzonos_b200.so does not match csrc/ and could not be rebuilt ({e}); using it as it is")
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)          # AttributeError if the ABI lost a symbol

@@ -16,12 +16,34 @@ NVCC_FLAGS = [
 ]
 
 
+STAMP = LIB + ".src.sha256"      # hash of the sources the library was built from (travels with the .so; both git-ignored)
+
+
+def _source_hash() -> str:
+    import hashlib
+    h = hashlib.sha256()
+    deps = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h")))
+    deps.append(os.path.join(HERE, "..", "include", "zonos_b200.h"))
+    for p in deps:
+        h.update(os.path.basename(p).encode())
+        with open(p, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
 def _stale() -> bool:
-    if not os.path.exists(LIB):
+    """True when the library is missing or was built from other sources.  By content, not mtime: a copy of the tree (the GPU
+    box gets a snapshot) keeps the library current whatever happened to the timestamps."""
+    if not os.path.exists(LIB) or not os.path.exists(STAMP):
         return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "zonos_b200.h")]
-    return any(os.path.getmtime(p) > t for p in deps)
+    with open(STAMP) as f:
+        return f.read().strip() != _source_hash()
+
+
+def stamp() -> None:
+    """Record the current sources as what LIB was built from (after a manual nvcc build)."""
+    with open(STAMP, "w") as f:
+        f.write(_source_hash() + "\n")
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -49,8 +71,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}")
+    stamp()
     return LIB
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--stamp" in sys.argv:
+        stamp()
+        print("stamped", STAMP)
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -639,6 +639,19 @@ BtPlan bt_plan(const zb_ctx* c, int n_tiles, int K) {
   return pl;
 }
 
+// the activation maps again with a box of 128 / cluster-size rows: the slice one CTA of a cluster loads and multicasts
+int bt_make_slices(zb_ctx* c) {
+  const zb_config& g = c->cfg;
+  const int rows_pad = c->bt_mpad, box = BT_BM / c->opt_bt_cluster;
+  int rc;
+  c->bt_cs = c->opt_bt_cluster;
+  if ((rc = bt_make_map(c, &c->bt_maps_xn, c->bt_xn, g.d_model, rows_pad, box))) return rc;
+  if ((rc = bt_make_map(c, &c->bt_maps_y, c->y, g.num_heads * ZB_DH, rows_pad, box))) return rc;
+  if ((rc = bt_make_map(c, &c->bt_maps_h, c->h, g.ffn, rows_pad, box))) return rc;
+  if (c->hybrid && c->n_mamba > 0 && (rc = bt_make_map(c, &c->bt_maps_yn, c->m_ynorm, c->m_dinner, rows_pad, box))) return rc;
+  return ZB_OK;
+}
+
 int bt_setup(zb_ctx* c, int rows_pad) {
   const zb_config& g = c->cfg;
   c->bt_ready = false;
@@ -659,11 +672,7 @@ int bt_setup(zb_ctx* c, int rows_pad) {
   if ((rc = bt_make_map(c, &c->bt_map_y, c->y, q_size, rows_pad, BT_BM))) return rc;
   if ((rc = bt_make_map(c, &c->bt_map_h, c->h, F, rows_pad, BT_BM))) return rc;
   if (c->hybrid && c->n_mamba > 0 && (rc = bt_make_map(c, &c->bt_map_yn, c->m_ynorm, c->m_dinner, rows_pad, BT_BM))) return rc;
-  c->bt_cs = c->opt_bt_cluster;
-  if ((rc = bt_make_map(c, &c->bt_maps_xn, c->bt_xn, d, rows_pad, BT_BM / c->bt_cs))) return rc;
-  if ((rc = bt_make_map(c, &c->bt_maps_y, c->y, q_size, rows_pad, BT_BM / c->bt_cs))) return rc;
-  if ((rc = bt_make_map(c, &c->bt_maps_h, c->h, F, rows_pad, BT_BM / c->bt_cs))) return rc;
-  if (c->hybrid && c->n_mamba > 0 && (rc = bt_make_map(c, &c->bt_maps_yn, c->m_ynorm, c->m_dinner, rows_pad, BT_BM / c->bt_cs))) return rc;
+  if ((rc = bt_make_slices(c))) return rc;
   const int nl = g.n_layer;
   c->bt_map_in.resize(nl); c->bt_map_out.resize(nl); c->bt_map_fc1.resize(nl); c->bt_map_fc2.resize(nl);
   for (int l = 0; l < nl; ++l) {
@@ -1687,7 +1696,10 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "att_chunk") c->opt_att_chunk = value;
   else if (k == "ll") c->opt_ll = value;
   else if (k == "chain") c->opt_chain = value;
-  else if (k == "bt_cluster") c->opt_bt_cluster = (value == 2 || value == 4) ? value : 1;
+  else if (k == "bt_cluster") {
+    c->opt_bt_cluster = (value == 2 || value == 4) ? value : 1;
+    if (c->bt_ready) { int rc = bt_make_slices(c); if (rc) return rc; }
+  }
   else if (k == "att_single") c->opt_att_single = value;
   else if (k == "ring") c->opt_ring = value;
   else if (k == "psleep") c->opt_psleep = value;
