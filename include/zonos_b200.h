@@ -180,6 +180,11 @@ int  zb_dac_get_intermediate(zb_dac* dac, const char* name, float* d_out, int64_
 int  zb_dac_set_option(zb_dac* dac, const char* key, int value);      /* "keep_intermediates" */
 int64_t zb_dac_launch_count(const zb_dac* dac);
 
+/* ---- serving shell (server.py:142-147) -----------------------------------------------------------------
+ * fp32 waveform -> 16-bit PCM exactly as the reference's /tts handler does it on the host with numpy:
+ * clip to [-1, 1], multiply by 32767, convert to int16 with truncation toward zero.  NaN -> 0.  n samples, device pointers. */
+int  zb_wav_to_pcm16(const float* d_wav, int16_t* d_pcm, int64_t n, void* stream);
+
 /* ---- PrefixConditioner (zonos/conditioning.py) -------------------------------------------------------
  * The four ops the reference's PrefixConditioner.forward (conditioning.py:297-313) is made of, on caller-owned bf16 device
  * tensors; zonos_vibes_b200/conditioning.py composes them in the reference's order.  Text -> phoneme ids stays on the host.

@@ -276,3 +276,60 @@ def test_library_staleness_is_by_content(tmp_path, monkeypatch):
     assert build._stale()
     fake.write_text(build._source_hash() + "\n")
     assert not build._stale()
+
+
+def test_serving_shell_batches_and_wav_container():
+    """Row f2 host side: the batching engine groups compatible requests (same conditioning length and sampling parameters) into
+    one generate call of at most max_batch utterances, keeps arrival order, and resolves every future; the WAV container is
+    byte-identical to scipy.io.wavfile.write on int16 mono (server.py:149-152); tts_request keeps the reference's validation."""
+    import io
+    import numpy as np
+    import scipy.io.wavfile
+    from zonos_vibes_b200 import serving
+
+    pcm = torch.randint(-32768, 32767, (5000,), dtype=torch.int16)
+    buf = io.BytesIO()
+    scipy.io.wavfile.write(buf, 44100, pcm.numpy())
+    assert serving.wav_bytes(pcm, 44100) == buf.getvalue()
+
+    class FakeModel:
+        autoencoder = None
+        device = torch.device("cpu")
+
+        def __init__(self):
+            self.calls = []
+
+        def generate(self, prefix, max_new_tokens, cfg_scale, batch_size, sampling_params, progress_bar, seed):
+            assert prefix.shape[0] == 2 * batch_size
+            self.calls.append((batch_size, prefix.shape[1], max_new_tokens))
+            # utterance i's codes carry its conditional row's first value, so that routing can be checked
+            ids = prefix[:batch_size, 0, 0].to(torch.int64)
+            self.last_lengths = [3 + int(i) % 2 for i in ids]
+            return ids.view(-1, 1, 1).expand(batch_size, 9, 5).contiguous()
+
+    m = FakeModel()
+    eng = serving.BatchingEngine(m, max_batch=4, max_wait_ms=200.0)
+    futs = []
+    for i in range(6):                                   # six requests with Lc = 7, two with Lc = 9, one with other sampling
+        futs.append(eng.submit(torch.full((2, 7, 8), float(i)), 10))
+    for i in range(6, 8):
+        futs.append(eng.submit(torch.full((2, 9, 8), float(i)), 10))
+    futs.append(eng.submit(torch.full((2, 7, 8), 8.0), 10, sampling_params=dict(min_p=0.1)))
+    res = [f.result(timeout=30) for f in futs]
+    eng.close()
+    for i, r in enumerate(res):
+        assert r.codes.shape == (9, 3 + i % 2) and int(r.codes[0, 0]) == i and r.pcm is None
+    assert sorted(eng.batches) == [1, 2, 2, 4] and max(c[0] for c in m.calls) == 4
+    assert [r.batch_size for r in res[:4]] == [4, 4, 4, 4]
+    with pytest.raises(ValueError):
+        eng.submit(torch.zeros(3, 7, 8))
+
+    eng2 = serving.BatchingEngine(m, max_batch=2, max_wait_ms=1.0)
+    spk = lambda p: (_ for _ in ()).throw(FileNotFoundError(p))     # noqa: E731
+    assert serving.tts_request(eng2, None, spk)[0] == 400
+    assert serving.tts_request(eng2, {"speaker_audio_path": "a", "speaking_rate": 1}, spk) == (400, {"error": "Missing 'text' parameter"})
+    assert serving.tts_request(eng2, {"text": "t", "speaking_rate": 1}, spk)[1] == {"error": "Missing 'speaker_audio_path' parameter"}
+    assert serving.tts_request(eng2, {"text": "t", "speaker_audio_path": "a"}, spk)[1] == {"error": "Missing 'speaking_rate' parameter"}
+    assert serving.tts_request(eng2, {"text": "t", "speaker_audio_path": "a", "speaking_rate": "x"}, spk)[1] == {"error": "'speaking_rate' must be a number"}
+    assert serving.tts_request(eng2, {"text": "t", "speaker_audio_path": "missing.wav", "speaking_rate": 15}, spk)[0] == 404
+    eng2.close()

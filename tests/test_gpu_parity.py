@@ -809,3 +809,37 @@ def test_prefix_conditioner_feeds_generate(golden_long, cuda):
     assert not torch.equal(pre[0], pre[1])
     out = m.generate(pre, max_new_tokens=12, sampling_params=dict(temperature=0), progress_bar=False)
     assert out.shape[:2] == (1, 9) and int(out.max()) < 1024
+
+
+# ---- row f2: serving shell ---------------------------------------------------------------------------------------------
+def test_pcm16_bit_exact(cuda):
+    """zb_wav_to_pcm16 against the numpy expression of the reference's /tts handler (server.py:142-147), incl. out-of-range,
+    boundary and tiny values: bit-exact."""
+    import numpy as np
+    from zonos_vibes_b200 import serving
+    g = torch.Generator().manual_seed(5)
+    wav = torch.randn(1, 1, 512 * 37, generator=g) * 0.7
+    wav[0, 0, :8] = torch.tensor([1.0, -1.0, 1.5, -2.0, 0.0, 1e-6, -1e-6, 0.99999])
+    want = (np.clip(wav.numpy(), -1.0, 1.0) * 32767).astype(np.int16)
+    got = serving.pcm16(wav.to(cuda))
+    assert got.dtype == torch.int16 and got.shape == wav.shape
+    assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_batching_engine_equals_single_requests(golden, cuda):
+    """Requests served together by the BatchingEngine (one batched generate on the tcgen05 path) give each client the greedy
+    stream and length it gets when served alone (reference semantics: one request at a time, server.py:120-130)."""
+    from zonos_vibes_b200 import serving
+    m = make_model("tiny", cuda)
+    prefixes = [zo.synth_prefix_conditioning(zo.TINY_CONFIG, 1, 6, 10 + i).to(cuda) for i in range(5)]
+    # both on the batched tcgen05 path (a row's arithmetic there does not depend on how many rows share the step), so the
+    # comparison is exact; batch-1 on the persistent kernel differs by bf16 rounding order (covered with its tolerance above)
+    with _options(m, mega=0, bt_min_rows=2):
+        alone = [m.generate(p, max_new_tokens=24, sampling_params=dict(temperature=0), progress_bar=False) for p in prefixes]
+        eng = serving.BatchingEngine(m, max_batch=8, max_wait_ms=500.0)
+        futs = [eng.submit(p, 24, sampling_params=dict(temperature=0)) for p in prefixes]
+        res = [f.result(timeout=120) for f in futs]
+        eng.close()
+    assert eng.batches == [5]
+    for r, a in zip(res, alone):
+        assert r.batch_size == 5 and torch.equal(r.codes.cpu(), a[0].cpu())

@@ -11,8 +11,9 @@ from .conditioning import PrefixConditioner
 from .config import BackboneConfig, InferenceParams, PrefixConditionerConfig, ZonosConfig
 from .model import Zonos
 from .sampling import sample_from_logits
+from .serving import BatchingEngine
 
 __all__ = [
     "Zonos", "DACAutoencoder", "BACKBONES", "B200ZonosBackbone", "apply_delay_pattern", "revert_delay_pattern",
-    "sample_from_logits", "ZonosConfig", "BackboneConfig", "PrefixConditionerConfig", "InferenceParams", "PrefixConditioner",
+    "sample_from_logits", "ZonosConfig", "BackboneConfig", "PrefixConditionerConfig", "InferenceParams", "PrefixConditioner", "BatchingEngine",
 ]

@@ -429,3 +429,12 @@ __global__ void k_advance(ZbDevState* st, int* rope_pos, int R) {
   if (threadIdx.x == 0) st->pos += 1;
   for (int r = threadIdx.x; r < R; r += blockDim.x) rope_pos[r] += 1;
 }
+
+// server.py:142-147: np.clip(wav, -1, 1) * 32767 -> astype(int16) (C cast: truncation toward zero)
+__global__ void k_wav_to_pcm16(const float* __restrict__ wav, short* __restrict__ pcm, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float v = wav[i];
+    v = v != v ? 0.f : fminf(fmaxf(v, -1.0f), 1.0f);
+    pcm[i] = (short)(int)(__fmul_rn(v, 32767.0f));
+  }
+}

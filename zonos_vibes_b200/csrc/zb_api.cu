@@ -1386,6 +1386,15 @@ int zb_backbone_forward(zb_ctx* c, const void* d_in, void* d_out, int rows, int 
   return ZB_OK;
 }
 
+int zb_wav_to_pcm16(const float* d_wav, int16_t* d_pcm, int64_t n, void* stream) {
+  if (n < 0 || (n > 0 && (!d_wav || !d_pcm))) return ZB_ERR_ARG;
+  if (n == 0) return ZB_OK;
+  long long blocks = (n + 255) / 256;
+  if (blocks > ZB_NUM_SMS * 8) blocks = ZB_NUM_SMS * 8;
+  k_wav_to_pcm16<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_wav, (short*)d_pcm, (long long)n);
+  return cudaGetLastError() == cudaSuccess ? ZB_OK : ZB_ERR_CUDA;
+}
+
 int zb_delay_apply(const int64_t* d_codes, int64_t* d_out, int B, int n_q, int T, int64_t mask_token, void* stream) {
   if (B < 0 || n_q <= 0 || T < 0) return ZB_ERR_ARG;
   const size_t n = (size_t)B * n_q * (T + n_q);
