@@ -174,6 +174,12 @@ int  zb_dac_decode(zb_dac* dac, const int64_t* d_codes, float* d_wav, int B, int
  * zb_dac contexts on the same device) RACE on it - serialise them.  Same inputs / outputs as zb_dac_decode. */
 #define ZB_DAC_STATIC_MAX_FRAMES 48
 int  zb_dac_decode_static(zb_dac* dac, const int64_t* d_codes, float* d_wav, int B, int T, void* stream);
+/* SURVEY §8 row f3 - DACAutoencoder.encode (zonos/autoencoder.py:22-23 -> HF DacModel.encode: DacEncoder + DacResidualVectorQuantizer,
+ * modeling_dac.py): d_wav fp32 [B][1][S] at 44.1 kHz, S a multiple of 512 (the reference's preprocess pads, autoencoder.py:17-20)
+ * -> d_codes int64 [B][9][S / 512].  fp32 arithmetic like the reference (no autocast on encode).  Needs the encoder tensors
+ * ("encoder.*" and "quantizer.quantizers.K.in_proj.*", set with zb_dac_set_tensor before zb_dac_finalize); a context that was
+ * given the decoder tensors only returns ZB_ERR_STATE here and decodes as before. */
+int  zb_dac_encode(zb_dac* dac, const float* d_wav, int64_t* d_codes, int B, int64_t S, void* stream);
 /* debug/parity: copy an intermediate of the last decode ("latent", "conv1", "block0".."block3") as fp32
  * [B, C, T_l] (reference layout) into d_out; returns ZB_ERR_ARG if the name is unknown. */
 int  zb_dac_get_intermediate(zb_dac* dac, const char* name, float* d_out, int64_t numel, void* stream);

@@ -135,3 +135,97 @@ def load_into_hf(sd: dict):
         full[k] = v
     m.load_state_dict(full)
     return m
+
+
+# ---- encoder side: DACAutoencoder.encode, zonos/autoencoder.py:22-23 ------------------------------------
+ENCODER_HIDDEN = 64               # DacConfig.encoder_hidden_size
+DOWNSAMPLING = (2, 4, 8, 8)       # DacConfig.downsampling_ratios
+
+
+def synth_dac_encoder_state_dict(seed: int = 3) -> dict:
+    """Deterministic random encoder + quantizer in_proj weights under HF `DacModel` keys; same scale rules as
+    synth_dac_state_dict (activations stay O(1) through the 29 conv layers)."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    sd: dict = {}
+
+    def conv(prefix, cout, cin, k, gain=1.0):
+        b = gain * math.sqrt(3.0 / (cin * k))
+        sd[prefix + ".weight"] = (torch.rand((cout, cin, k), generator=g) * 2 - 1) * b
+        sd[prefix + ".bias"] = 0.05 * torch.randn(cout, generator=g)
+
+    def snake(prefix, c):
+        sd[prefix + ".alpha"] = 0.5 + torch.rand(1, c, 1, generator=g)
+
+    conv("encoder.conv1", ENCODER_HIDDEN, 1, 7, gain=3.0)
+    c = ENCODER_HIDDEN
+    for j, s in enumerate(DOWNSAMPLING):
+        p = f"encoder.block.{j}"
+        for u in (1, 2, 3):
+            r = f"{p}.res_unit{u}"
+            snake(r + ".snake1", c)
+            conv(r + ".conv1", c, c, 7, gain=0.7)
+            snake(r + ".snake2", c)
+            conv(r + ".conv2", c, c, 1, gain=0.5)
+        snake(p + ".snake1", c)
+        conv(p + ".conv1", 2 * c, c, 2 * s)
+        c *= 2
+    snake("encoder.snake1", c)
+    conv("encoder.conv2", HIDDEN, c, 3)
+    for k in range(N_CODEBOOKS):
+        conv(f"quantizer.quantizers.{k}.in_proj", CODEBOOK_DIM, HIDDEN, 1)
+    return sd
+
+
+def encoder_forward(sd: dict, wav: torch.Tensor) -> torch.Tensor:
+    """modeling_dac.py DacEncoder.forward / DacEncoderBlock.forward: wav [B, 1, S] -> latents [B, 1024, S / 512]."""
+    x = F.conv1d(wav, sd["encoder.conv1.weight"], sd["encoder.conv1.bias"], padding=3)
+    for j, s in enumerate(DOWNSAMPLING):
+        p = f"encoder.block.{j}"
+        for u, dil in zip((1, 2, 3), DILATIONS):
+            x = residual_unit(sd, f"{p}.res_unit{u}", x, dil)
+        x = snake1d(x, sd[p + ".snake1.alpha"])
+        x = F.conv1d(x, sd[p + ".conv1.weight"], sd[p + ".conv1.bias"], stride=s, padding=math.ceil(s / 2))
+    x = snake1d(x, sd["encoder.snake1.alpha"])
+    return F.conv1d(x, sd["encoder.conv2.weight"], sd["encoder.conv2.bias"], padding=1)
+
+
+def rvq_encode(sd: dict, z: torch.Tensor):
+    """DacResidualVectorQuantizer.forward (eval) + DacVectorQuantize.decode_latents: latents [B, 1024, T] ->
+    (codes int64 [B, 9, T], gap fp32 [B, 9, T] = best distance minus runner-up: how close each decision was)."""
+    residual = z
+    codes, gaps = [], []
+    for k in range(N_CODEBOOKS):
+        q = f"quantizer.quantizers.{k}"
+        proj = F.conv1d(residual, sd[q + ".in_proj.weight"], sd[q + ".in_proj.bias"])          # [B, 8, T]
+        b, dcb, t = proj.shape
+        enc = F.normalize(proj.permute(0, 2, 1).reshape(b * t, dcb))
+        cb = F.normalize(sd[q + ".codebook.weight"])
+        dist = -(enc.pow(2).sum(1, keepdim=True) - 2 * enc @ cb.t()) + cb.pow(2).sum(1, keepdim=True).t()
+        top2 = dist.topk(2, dim=1)
+        idx = dist.max(1)[1].reshape(b, t)
+        codes.append(idx)
+        gaps.append((top2.values[:, 0] - top2.values[:, 1]).reshape(b, t))
+        quant = F.embedding(idx, sd[q + ".codebook.weight"]).transpose(1, 2)
+        residual = residual - F.conv1d(quant, sd[q + ".out_proj.weight"], sd[q + ".out_proj.bias"])
+    return torch.stack(codes, 1), torch.stack(gaps, 1)
+
+
+@torch.inference_mode()
+def dac_encode(sd: dict, wav: torch.Tensor, with_gaps: bool = False):
+    """zonos/autoencoder.py:22-23 on CPU: wav fp32 [B, 1, S] (S % 512 == 0) -> codes int64 [B, 9, S / 512]."""
+    codes, gaps = rvq_encode(sd, encoder_forward(sd, wav.float()))
+    return (codes, gaps) if with_gaps else codes
+
+
+def synth_waveform(batch: int, frames: int, seed: int = 7) -> torch.Tensor:
+    """Audio-like test input [B, 1, 512 * frames]: a few partials with slow amplitude modulation + a little noise, |x| < 0.6."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    n = HOP * frames
+    t = torch.arange(n, dtype=torch.float32) / SAMPLING_RATE
+    out = []
+    for _ in range(batch):
+        f0 = 90.0 + 200.0 * torch.rand(1, generator=g).item()
+        x = sum((0.3 / (h + 1)) * torch.sin(2 * math.pi * f0 * (h + 1) * t + 6.28 * torch.rand(1, generator=g).item()) for h in range(5))
+        x = x * (0.6 + 0.4 * torch.sin(2 * math.pi * 3.1 * t)) + 0.02 * torch.randn(n, generator=g)
+        out.append(x)
+    return torch.stack(out).unsqueeze(1)

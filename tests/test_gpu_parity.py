@@ -843,3 +843,41 @@ def test_batching_engine_equals_single_requests(golden, cuda):
     assert eng.batches == [5]
     for r, a in zip(res, alone):
         assert r.batch_size == 5 and torch.equal(r.codes.cpu(), a[0].cpu())
+
+
+# ---- row f3: DAC encoder + residual vector quantiser -----------------------------------------------------------------
+def test_dac_encode_matches_oracle(cuda):
+    """DACAutoencoder.encode (zb_dac_encode: fp32 SIMT encoder + RVQ argmax kernel) against oracle/dac_oracle.py dac_encode,
+    which tests/test_oracle_pinned.py pins to transformers' DacModel.encode.  Integer output: codes must be IDENTICAL, except
+    that a frame may leave the oracle's path at a decision the oracle itself marks as a near-tie (best minus runner-up
+    distance < 1e-3, the fp32 summation-order noise of 29 conv layers); after such a frame-level fork the deeper codebooks
+    of that frame are unconstrained.  Also: >= 99 % of all codes identical; B = 2; 37 frames (not a multiple of any tile)."""
+    import zonos_vibes_b200 as z
+    sd = dict(do.synth_dac_state_dict(2))
+    sd.update(do.synth_dac_encoder_state_dict(3))
+    auto = z.DACAutoencoder(sd, cuda)
+    wav = do.synth_waveform(2, 37, 7)
+    want, gaps = do.dac_encode(sd, wav, with_gaps=True)
+    got = auto.encode(wav.to(cuda)).cpu()
+    assert got.shape == want.shape == (2, 9, 37) and got.dtype == torch.int64
+    forks = 0
+    for b in range(2):
+        for t in range(37):
+            for k in range(9):
+                if got[b, k, t] != want[b, k, t]:
+                    assert gaps[b, k, t] < 1e-3, f"codes differ at b={b} k={k} t={t} where the oracle's decision was clear (gap {gaps[b, k, t]:.3e})"
+                    forks += 1
+                    break
+    frac = (got == want).float().mean().item()
+    print(f"[dac encode] identical codes {frac:.4f}, near-tie forks {forks}")
+    assert frac >= 0.99
+    # the preprocess / encode / decode chain of the reference's audio-prefix path (gradio_interface.py:153-159) runs end to end
+    pre = auto.preprocess(torch.randn(1, 1, 30000), 32000)
+    assert pre.shape[-1] % 512 == 0
+    codes = auto.encode(pre.to(cuda))
+    assert auto.decode(codes).shape == (1, 1, pre.shape[-1])
+    with pytest.raises(Exception):
+        auto.encode(torch.zeros(1, 1, 1000, device=cuda))          # not a multiple of 512
+    dec_only = z.DACAutoencoder(do.synth_dac_state_dict(2), cuda)
+    with pytest.raises(Exception, match="encoder tensors"):
+        dec_only.encode(wav[:1].to(cuda))

@@ -181,3 +181,19 @@ def test_long_fixture_shapes(golden_long):
         assert golden_long[f"long.p{p}.delayed"].shape == (1, 9, p + 12 + 9)
         assert bool(torch.isfinite(golden_long[f"long.p{p}.logits"][..., :1024]).all())
     assert golden_long["full.truth_logits"].shape == (7, 9, 1026)
+
+
+def test_dac_encode_oracle_matches_hf_model():
+    """Row f3 pin: the encoder + RVQ restatement (oracle/dac_oracle.py dac_encode) against the installed transformers
+    DacModel.encode (what zonos/autoencoder.py:22-23 calls) on the same synthetic weights and waveform: codes identical."""
+    import dac_oracle as do
+    sd = dict(do.synth_dac_state_dict(2))
+    sd.update(do.synth_dac_encoder_state_dict(3))
+    wav = do.synth_waveform(2, 20, 7)
+    codes, gaps = do.dac_encode(sd, wav, with_gaps=True)
+    assert codes.shape == (2, 9, 20) and codes.dtype == torch.int64 and int(codes.min()) >= 0 and int(codes.max()) < 1024
+    m = do.load_into_hf(sd)
+    with torch.inference_mode():
+        ref = m.encode(wav).audio_codes
+    assert torch.equal(ref, codes)
+    assert bool((gaps >= 0).all())

@@ -1,4 +1,5 @@
-"""DAC 44 kHz codec, decode side — mirror of the reference's zonos/autoencoder.py:8-27 `DACAutoencoder`."""
+"""DAC 44 kHz codec — mirror of the reference's zonos/autoencoder.py:8-27 `DACAutoencoder` (decode: the hot path; preprocess /
+encode: SURVEY §8 row f3, the audio-prefix input side)."""
 from __future__ import annotations
 
 import ctypes as C
@@ -35,10 +36,8 @@ class DACAutoencoder:
         with torch.cuda.device(self.device):
             stream = torch.cuda.current_stream(self.device)
             for name, t in state_dict.items():
-                if not (name.startswith("decoder.") or name.startswith("quantizer.")):
-                    continue
-                if ".in_proj." in name:
-                    continue           # encoder-side projection of the quantizer: not on the decode path
+                if not (name.startswith("decoder.") or name.startswith("quantizer.") or name.startswith("encoder.")):
+                    continue           # (encoder.* and quantizer.*.in_proj.* are optional: without them encode() raises)
                 t = t.detach().to(self.device, torch.float32).contiguous()
                 self._check(self.lib.zb_dac_set_tensor(self.handle, name.encode(), t.data_ptr(), t.numel(), stream.cuda_stream))
                 stream.synchronize()
@@ -62,11 +61,27 @@ class DACAutoencoder:
     def set_option(self, key: str, value: int) -> None:
         self._check(self.lib.zb_dac_set_option(self.handle, key.encode(), int(value)))
 
-    def preprocess(self, wav, sr):
-        raise NotImplementedError("audio-prefix encode path is outside the accelerated hot path (SURVEY §8 f3)")
+    def preprocess(self, wav: torch.Tensor, sr: int) -> torch.Tensor:
+        """autoencoder.py:17-20: resample to 44.1 kHz (torchaudio, like the reference) and zero-pad on the right to a multiple of 512."""
+        import math
 
-    def encode(self, wav):
-        raise NotImplementedError("audio-prefix encode path is outside the accelerated hot path (SURVEY §8 f3)")
+        import torchaudio
+        wav = torchaudio.functional.resample(wav, sr, 44_100)
+        right_pad = math.ceil(wav.shape[-1] / 512) * 512 - wav.shape[-1]
+        return torch.nn.functional.pad(wav, (0, right_pad))
+
+    @torch.inference_mode()
+    def encode(self, wav: torch.Tensor) -> torch.Tensor:
+        """wav fp32 [B, 1, S] (S % 512 == 0, see preprocess) -> codes int64 [B, 9, S / 512]   (autoencoder.py:22-23)."""
+        if wav.dim() != 3 or wav.shape[1] != 1:
+            raise _lib.ZbError(f"expected a waveform of shape [B, 1, S], got {tuple(wav.shape)}")
+        wav = wav.to(self.device, torch.float32).contiguous()
+        b, _, n = wav.shape
+        codes = torch.empty((b, self.num_codebooks, n // self.hop_length), dtype=torch.int64, device=self.device)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.zb_dac_encode(self.handle, wav.data_ptr(), codes.data_ptr(), b, n,
+                                               torch.cuda.current_stream(self.device).cuda_stream))
+        return codes
 
     @torch.inference_mode()
     def decode(self, codes: torch.Tensor) -> torch.Tensor:

@@ -1,4 +1,5 @@
-// C ABI of libzonos_b200.so — DAC 44 kHz decoder side (DACAutoencoder.decode, zonos/autoencoder.py:25-27).
+// C ABI of libzonos_b200.so — DAC 44 kHz codec: decoder (DACAutoencoder.decode, zonos/autoencoder.py:25-27) and, as the
+// optional row f3, encoder + residual vector quantiser (DACAutoencoder.encode, autoencoder.py:22-23).
 #include <stdarg.h>
 #include <string.h>
 
@@ -16,6 +17,8 @@ namespace {
 constexpr int kNq = 9, kCodes = 1024, kCodeDim = 8, kHidden = 1024, kDecoder = 1536;
 constexpr int kStrides[4] = {8, 8, 4, 2};
 constexpr int kDil[3] = {1, 3, 9};
+constexpr int kEncHidden = 64;
+constexpr int kEncStrides[4] = {2, 4, 8, 8};      // DacConfig.downsampling_ratios
 
 struct RawT {
   float* ptr = nullptr;
@@ -63,6 +66,11 @@ struct zb_dac {
   std::map<std::string, std::pair<float*, int64_t>> dbg;   // fp32 [C][T_l] copies (keep=1)
   EncodeTiledFn encode = nullptr;
   int64_t launches = 0;
+  // ---- encoder side (optional: zb_dac_encode needs every "encoder.*" / "*.in_proj.*" tensor; decode does not) ----
+  std::map<std::string, RawT> raw_enc;
+  bool enc_ready = false;
+  ConvW e_conv1, e_conv2, e_down[4], e_ru1[4][3], e_ru2[4][3];
+  const float** q_ptrs = nullptr;   // device: [5][9] pointers (in_proj w, in_proj b, codebook, out_proj w, out_proj b)
 };
 
 static std::string g_dac_create_error;
@@ -82,6 +90,19 @@ void declare_conv(zb_dac* d, ConvW& c, const std::string& name, int Cin, int Cou
   c.pad = stride > 1 ? (stride + 1) / 2 : ((K - 1) * dil) / 2;
   declare(d, name + ".weight", (int64_t)Cin * Cout * K);
   declare(d, name + ".bias", Cout);
+}
+
+void declare_enc(zb_dac* d, const std::string& n, int64_t numel) {
+  RawT t;
+  t.numel = numel;
+  d->raw_enc[n] = t;
+}
+// encoder conv: stride > 1 here means a strided (down-sampling) Conv1d with K = 2 * stride, pad = ceil(stride / 2)
+void declare_conv_enc(zb_dac* d, ConvW& c, const std::string& name, int Cin, int Cout, int K, int dil, int stride) {
+  c.name = name; c.Cin = Cin; c.Cout = Cout; c.K = K; c.dil = dil; c.stride = stride;
+  c.pad = stride > 1 ? (stride + 1) / 2 : ((K - 1) * dil) / 2;
+  declare_enc(d, name + ".weight", (int64_t)Cin * Cout * K);
+  declare_enc(d, name + ".bias", Cout);
 }
 
 int dbg_store_f32(zb_dac* d, const std::string& name, const float* x_tc, int T, int C, cudaStream_t s) {
@@ -445,6 +466,31 @@ int zb_dac_create(int device, zb_dac** out) {
   }
   declare(d, "decoder.snake1.alpha", C);
   declare_conv(d, d->conv2, "decoder.conv2", C, 1, 7, 1, 1);
+  {
+    // encoder (DacEncoder): conv1 1 -> 64 k7; 4 x [3 ResidualUnits(C), Snake, Conv1d C -> 2C k 2s stride s]; Snake; conv2 1024 -> 1024 k3
+    for (int k = 0; k < kNq; ++k) {
+      const std::string q = "quantizer.quantizers." + std::to_string(k);
+      declare_enc(d, q + ".in_proj.weight", (int64_t)kCodeDim * kHidden);
+      declare_enc(d, q + ".in_proj.bias", kCodeDim);
+    }
+    declare_conv_enc(d, d->e_conv1, "encoder.conv1", 1, kEncHidden, 7, 1, 1);
+    int Ce = kEncHidden;
+    for (int j = 0; j < 4; ++j) {
+      const std::string bp = "encoder.block." + std::to_string(j);
+      for (int u = 0; u < 3; ++u) {
+        const std::string rp = bp + ".res_unit" + std::to_string(u + 1);
+        declare_enc(d, rp + ".snake1.alpha", Ce);
+        declare_conv_enc(d, d->e_ru1[j][u], rp + ".conv1", Ce, Ce, 7, kDil[u], 1);
+        declare_enc(d, rp + ".snake2.alpha", Ce);
+        declare_conv_enc(d, d->e_ru2[j][u], rp + ".conv2", Ce, Ce, 1, 1, 1);
+      }
+      declare_enc(d, bp + ".snake1.alpha", Ce);
+      declare_conv_enc(d, d->e_down[j], bp + ".conv1", Ce, 2 * Ce, 2 * kEncStrides[j], 1, kEncStrides[j]);
+      Ce *= 2;
+    }
+    declare_enc(d, "encoder.snake1.alpha", Ce);
+    declare_conv_enc(d, d->e_conv2, "encoder.conv2", Ce, kHidden, 3, 1, 1);
+  }
   // driver entry point for tensor-map encoding (no -lcuda link dependency)
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult qres;
@@ -468,7 +514,11 @@ int zb_dac_destroy(zb_dac* d) {
   if (d->table) cudaFree(d->table);
   std::vector<ConvW*> all = {&d->conv1, &d->conv2};
   for (int j = 0; j < 4; ++j) { all.push_back(&d->convt[j]); for (int u = 0; u < 3; ++u) { all.push_back(&d->ru1[j][u]); all.push_back(&d->ru2[j][u]); } }
+  all.push_back(&d->e_conv1); all.push_back(&d->e_conv2);
+  for (int j = 0; j < 4; ++j) { all.push_back(&d->e_down[j]); for (int u = 0; u < 3; ++u) { all.push_back(&d->e_ru1[j][u]); all.push_back(&d->e_ru2[j][u]); } }
   for (ConvW* c : all) { if (c->w_kio) cudaFree(c->w_kio); if (c->w_koi) cudaFree(c->w_koi); }
+  for (auto& kv : d->raw_enc) if (kv.second.ptr) cudaFree(kv.second.ptr);
+  if (d->q_ptrs) cudaFree(d->q_ptrs);
   for (auto& p : d->f32buf) if (p) cudaFree(p);
   for (auto& p : d->f16buf) if (p) cudaFree(p);
   delete d;
@@ -478,7 +528,10 @@ int zb_dac_destroy(zb_dac* d) {
 int zb_dac_set_tensor(zb_dac* d, const char* name, const float* d_ptr, int64_t numel, void* stream) {
   if (!d || !name || !d_ptr) return ZB_ERR_ARG;
   auto it = d->raw.find(name);
-  if (it == d->raw.end()) return d->err.fail(ZB_ERR_ARG, "unknown DAC tensor '%s'", name);
+  if (it == d->raw.end()) {
+    it = d->raw_enc.find(name);
+    if (it == d->raw_enc.end()) return d->err.fail(ZB_ERR_ARG, "unknown DAC tensor '%s'", name);
+  }
   RawT& t = it->second;
   if (numel != t.numel) return d->err.fail(ZB_ERR_ARG, "DAC tensor '%s': numel %lld, expected %lld", name, (long long)numel, (long long)t.numel);
   ZB_CUDA(d->err, cudaSetDevice(d->device));
@@ -510,6 +563,37 @@ int zb_dac_finalize(zb_dac* d, void* stream) {
     c->bias = d->raw[c->name + ".bias"].ptr;
     k_dac_repack<<<ZB_NUM_SMS * 4, 256, 0, s>>>(rawp(d, c->name + ".weight"), c->w_kio, c->w_koi, c->Cout, c->Cin, c->K, c->stride > 1 ? 1 : 0);
   }
+  // encoder side: only when every one of its tensors was provided (a decode-only user never sets them)
+  d->enc_ready = false;
+  {
+    bool all_enc = true;
+    for (auto& kv : d->raw_enc) all_enc = all_enc && kv.second.provided;
+    if (all_enc) {
+      std::vector<ConvW*> enc = {&d->e_conv1, &d->e_conv2};
+      for (int j = 0; j < 4; ++j) { enc.push_back(&d->e_down[j]); for (int u = 0; u < 3; ++u) { enc.push_back(&d->e_ru1[j][u]); enc.push_back(&d->e_ru2[j][u]); } }
+      for (ConvW* c : enc) {
+        const size_t n = (size_t)c->Cin * c->Cout * c->K;
+        if (!c->w_kio) ZB_CUDA(d->err, cudaMalloc((void**)&c->w_kio, n * 4));
+        if (!c->w_koi) ZB_CUDA(d->err, cudaMalloc((void**)&c->w_koi, n * 2));
+        c->bias = d->raw_enc[c->name + ".bias"].ptr;
+        k_dac_repack<<<ZB_NUM_SMS * 4, 256, 0, s>>>(d->raw_enc[c->name + ".weight"].ptr, c->w_kio, c->w_koi, c->Cout, c->Cin, c->K, 0);
+      }
+      const float* h[5 * kNq];
+      for (int k = 0; k < kNq; ++k) {
+        const std::string q = "quantizer.quantizers." + std::to_string(k);
+        h[0 * kNq + k] = d->raw_enc[q + ".in_proj.weight"].ptr;
+        h[1 * kNq + k] = d->raw_enc[q + ".in_proj.bias"].ptr;
+        h[2 * kNq + k] = rawp(d, q + ".codebook.weight");
+        h[3 * kNq + k] = rawp(d, q + ".out_proj.weight");
+        h[4 * kNq + k] = rawp(d, q + ".out_proj.bias");
+      }
+      if (!d->q_ptrs) ZB_CUDA(d->err, cudaMalloc((void**)&d->q_ptrs, sizeof(h)));
+      ZB_CUDA(d->err, cudaMemcpyAsync(d->q_ptrs, h, sizeof(h), cudaMemcpyHostToDevice, s));
+      ZB_CUDA(d->err, cudaStreamSynchronize(s));          // `h` is a stack array
+      ZB_CUDA(d->err, cudaFuncSetAttribute(k_dac_conv_down_simt, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      d->enc_ready = true;
+    }
+  }
   ZB_CUDA(d->err, cudaGetLastError());
   ZB_CUDA(d->err, cudaMemcpyAsync(&d->conv2_bias_h, d->conv2.bias, 4, cudaMemcpyDeviceToHost, s));
   ZB_CUDA(d->err, cudaStreamSynchronize(s));
@@ -539,6 +623,60 @@ int zb_dac_decode(zb_dac* d, const int64_t* d_codes, float* d_wav, int B, int T,
     float* wav = d_wav + (size_t)b * 512 * T;
     rc = impl == 1 ? decode_one_simt(d, codes, wav, T, s) : decode_group_tc(d, codes, wav, nb, T, s, impl, d->f16buf, d->keep != 0);
     if (rc) return rc;
+  }
+  return ZB_OK;
+}
+
+// ---- encoder + residual vector quantiser (row f3): wav fp32 [B][1][S], S % 512 == 0 -> codes int64 [B][9][S / 512] --------
+namespace {
+int conv_down_simt(zb_dac* d, const ConvW& c, const float* x, int T_in, const float* alpha, float* out, cudaStream_t s) {
+  ConvSimtParams p;
+  memset(&p, 0, sizeof(p));
+  p.x = x; p.w = c.w_kio; p.bias = c.bias; p.alpha = alpha; p.out = out;
+  p.T_in = T_in; p.T_out = T_in / c.stride; p.Cin = c.Cin; p.Cout = c.Cout; p.K = c.K; p.dil = 1; p.pad = c.pad; p.stride = c.stride;
+  const size_t smem = (size_t)(7 * c.stride + c.K) * c.Cin * sizeof(float);
+  dim3 grid((p.T_out + 7) / 8, (c.Cout + 127) / 128);
+  k_dac_conv_down_simt<<<grid, 128, smem, s>>>(p);
+  d->launches++;
+  ZB_CUDA(d->err, cudaGetLastError());
+  return ZB_OK;
+}
+const float* rawe(zb_dac* d, const std::string& n) { return d->raw_enc[n].ptr; }
+}  // namespace
+
+int zb_dac_encode(zb_dac* d, const float* d_wav, int64_t* d_codes, int B, int64_t S, void* stream) {
+  if (!d || B < 0 || S < 0 || (B > 0 && S > 0 && (!d_wav || !d_codes))) return ZB_ERR_ARG;
+  if (!d->finalized) return d->err.fail(ZB_ERR_STATE, "zb_dac_finalize first");
+  if (!d->enc_ready) return d->err.fail(ZB_ERR_STATE, "zb_dac_encode: the encoder tensors (encoder.*, quantizer.quantizers.*.in_proj.*) were not provided");
+  if (S % 512) return d->err.fail(ZB_ERR_ARG, "zb_dac_encode: %lld samples is not a multiple of the hop length 512 (autoencoder.py:17-20 pads)", (long long)S);
+  if (B == 0 || S == 0) return ZB_OK;
+  if (S / 512 > 0x7fffffffLL / 49152) return d->err.fail(ZB_ERR_ARG, "zb_dac_encode: utterance too long");
+  cudaStream_t s = (cudaStream_t)stream;
+  ZB_CUDA(d->err, cudaSetDevice(d->device));
+  const int T = (int)(S / 512);
+  int rc = ensure_workspace_f32(d, T);
+  if (rc) return rc;
+  for (int b = 0; b < B; ++b) {
+    float *a = d->f32buf[0], *o = d->f32buf[1], *y = d->f32buf[2];
+    int Tl = (int)S;
+    if ((rc = conv_simt(d, d->e_conv1, d_wav + (size_t)b * S, Tl, nullptr, nullptr, a, 0, s))) return rc;     // [S][1] -> [S][64]
+    for (int j = 0; j < 4; ++j) {
+      const std::string bp = "encoder.block." + std::to_string(j);
+      for (int u = 0; u < 3; ++u) {
+        const std::string rp = bp + ".res_unit" + std::to_string(u + 1);
+        if ((rc = conv_simt(d, d->e_ru1[j][u], a, Tl, rawe(d, rp + ".snake1.alpha"), nullptr, y, 0, s))) return rc;
+        if ((rc = conv_simt(d, d->e_ru2[j][u], y, Tl, rawe(d, rp + ".snake2.alpha"), a, o, 0, s))) return rc;
+        std::swap(a, o);
+      }
+      if ((rc = conv_down_simt(d, d->e_down[j], a, Tl, rawe(d, bp + ".snake1.alpha"), o, s))) return rc;
+      Tl /= kEncStrides[j];
+      std::swap(a, o);
+    }
+    if ((rc = conv_simt(d, d->e_conv2, a, Tl, rawe(d, "encoder.snake1.alpha"), nullptr, o, 0, s))) return rc;   // [T][1024] latents
+    k_dac_rvq_encode<<<T, 256, 0, s>>>(o, d->q_ptrs, d->q_ptrs + kNq, d->q_ptrs + 2 * kNq, d->q_ptrs + 3 * kNq, d->q_ptrs + 4 * kNq,
+                                       reinterpret_cast<long long*>(d_codes) + (size_t)b * kNq * T, T, kHidden, kNq, kCodes);
+    d->launches++;
+    ZB_CUDA(d->err, cudaGetLastError());
   }
   return ZB_OK;
 }

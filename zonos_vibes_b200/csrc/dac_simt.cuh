@@ -194,3 +194,121 @@ __global__ void k_dac_to_channel_major(const float* __restrict__ x, float* __res
     out[(size_t)c * T + t] = x[i];
   }
 }
+
+// =================================================================================================================
+// DAC encoder side (modeling_dac.py DacEncoder / DacEncoderBlock / DacVectorQuantize /
+// DacResidualVectorQuantizer, driven by autoencoder.py:22-23).  fp32 like the reference's encode (no autocast there).
+// The residual units reuse k_dac_conv_simt; these are the two ops the decoder does not have.
+// =================================================================================================================
+
+// Strided Conv1d of an encoder block: K = 2 * stride, padding = ceil(stride / 2), T_out = T_in / stride; snake on the input.
+// out[t][co] = b[co] + sum_j sum_ci snake(x[t * s - pad + j][ci]) w[j][ci][co].   grid = (ceil(T_out / 8), ceil(Cout / 128)),
+// block = 128 (one output channel per thread, 8 output steps per block; the input window of the block is staged in smem).
+__global__ void __launch_bounds__(128) k_dac_conv_down_simt(const ConvSimtParams p) {
+  extern __shared__ float dn_xs[];                       // [rows][Cin], rows = 7 * s + K
+  const int s = p.stride, t0 = blockIdx.x * 8, co = blockIdx.y * 128 + threadIdx.x;
+  const int rows = 7 * s + p.K;
+  for (int i = threadIdx.x; i < rows * p.Cin; i += 128) {
+    const int r = i / p.Cin, ci = i - r * p.Cin;
+    const int t = t0 * s - p.pad + r;
+    float v = 0.f;
+    if (t >= 0 && t < p.T_in) {
+      v = p.x[(size_t)t * p.Cin + ci];
+      if (p.alpha) v = snake_f(v, p.alpha[ci]);
+    }
+    dn_xs[i] = v;
+  }
+  __syncthreads();
+  if (co >= p.Cout) return;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  for (int j = 0; j < p.K; ++j) {
+    const float* wj = p.w + (size_t)j * p.Cin * p.Cout + co;
+    for (int ci = 0; ci < p.Cin; ++ci) {
+      const float w = wj[(size_t)ci * p.Cout];
+#pragma unroll
+      for (int tt = 0; tt < 8; ++tt) acc[tt] = fmaf(dn_xs[(tt * s + j) * p.Cin + ci], w, acc[tt]);
+    }
+  }
+  const float b = p.bias[co];
+#pragma unroll
+  for (int tt = 0; tt < 8; ++tt)
+    if (t0 + tt < p.T_out) p.out[(size_t)(t0 + tt) * p.Cout + co] = acc[tt] + b;
+}
+
+// Residual vector quantisation of one latent frame (DacResidualVectorQuantizer.forward in eval mode + DacVectorQuantize.
+// decode_latents): for k = 0..n_q-1: e = in_proj_k(residual) [8]; both e and the codebook rows L2-normalised (F.normalize,
+// eps 1e-12); dist = -(|e|^2 - 2 e.c) + |c|^2; code = argmax (first maximum); residual -= out_proj_k(codebook_k[code]).
+// z: [T][C] time-major latents (C = 1024), codes: int64 [n_q][T].  grid = T, block = 256.
+__global__ void __launch_bounds__(256) k_dac_rvq_encode(const float* __restrict__ z, const float* const* __restrict__ in_w /*[n_q] -> [8][C]*/,
+                                                        const float* const* __restrict__ in_b, const float* const* __restrict__ codebook /*[1024][8]*/,
+                                                        const float* const* __restrict__ out_w /*[C][8]*/, const float* const* __restrict__ out_b,
+                                                        long long* __restrict__ codes, int T, int C, int n_q, int n_codes) {
+  __shared__ float res[1024];
+  __shared__ float e[8], en[8];
+  __shared__ float red_v[8];
+  __shared__ int red_i[8];
+  __shared__ int best;
+  const int t = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int c = tid; c < C; c += 256) res[c] = z[(size_t)t * C + c];
+  __syncthreads();
+  for (int k = 0; k < n_q; ++k) {
+    // in_proj: warp w computes e[w] (8 warps = 8 code dims)
+    {
+      const float* w = in_w[k] + (size_t)warp * C;
+      float a = 0.f;
+      for (int c = lane; c < C; c += 32) a = fmaf(w[c], res[c], a);
+      for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+      if (lane == 0) e[warp] = a + in_b[k][warp];
+    }
+    __syncthreads();
+    if (tid == 0) {
+      float n2 = 0.f;
+      for (int j = 0; j < 8; ++j) n2 += e[j] * e[j];
+      const float inv = 1.0f / fmaxf(sqrtf(n2), 1e-12f);
+      for (int j = 0; j < 8; ++j) en[j] = e[j] * inv;
+    }
+    __syncthreads();
+    float l2 = 0.f;
+    for (int j = 0; j < 8; ++j) l2 += en[j] * en[j];
+    float bv = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int n = tid; n < n_codes; n += 256) {
+      const float* cb = codebook[k] + (size_t)n * 8;
+      float c2 = 0.f;
+      for (int j = 0; j < 8; ++j) c2 += cb[j] * cb[j];
+      const float inv = 1.0f / fmaxf(sqrtf(c2), 1e-12f);
+      float dot = 0.f, cn2 = 0.f;
+      for (int j = 0; j < 8; ++j) { const float cj = cb[j] * inv; dot = fmaf(en[j], cj, dot); cn2 += cj * cj; }
+      const float dist = -(l2 - 2.0f * dot) + cn2;
+      if (dist > bv) { bv = dist; bi = n; }               // n ascending per thread: the first maximum is kept
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    if (lane == 0) { red_v[warp] = bv; red_i[warp] = bi; }
+    __syncthreads();
+    if (tid == 0) {
+      float v = red_v[0];
+      int i = red_i[0];
+      for (int w = 1; w < 8; ++w)
+        if (red_v[w] > v || (red_v[w] == v && red_i[w] < i)) { v = red_v[w]; i = red_i[w]; }
+      best = i;
+      codes[(size_t)k * T + t] = i;
+    }
+    __syncthreads();
+    {
+      const float* cb = codebook[k] + (size_t)best * 8;    // the UN-normalised embedding goes through out_proj
+      for (int c = tid; c < C; c += 256) {
+        const float* w = out_w[k] + (size_t)c * 8;
+        float a = out_b[k][c];
+        for (int j = 0; j < 8; ++j) a = fmaf(w[j], cb[j], a);
+        res[c] -= a;
+      }
+    }
+    __syncthreads();
+  }
+}
