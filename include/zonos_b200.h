@@ -191,6 +191,23 @@ int64_t zb_dac_launch_count(const zb_dac* dac);
  * clip to [-1, 1], multiply by 32767, convert to int16 with truncation toward zero.  NaN -> 0.  n samples, device pointers. */
 int  zb_wav_to_pcm16(const float* d_wav, int16_t* d_pcm, int64_t n, void* stream);
 
+/* ---- speaker-embedding network (zonos/speaker_cloning.py) ------------------------------------------------
+ * Op-level entry points on caller-owned fp32 device tensors (NCHW, contiguous); zonos_vibes_b200/speaker_cloning.py composes
+ * them in the reference's order (ResNet293_based.forward, :217-224).  BatchNorm is eval-mode and arrives folded:
+ * scale = weight / sqrt(running_var + eps), shift = bias - running_mean * scale.
+ *   zb_spk_conv2d          nn.Conv2d(bias=False) 3x3 pad 1 (stride 1 | 2) or 1x1 pad 0 (the downsample branch) + folded
+ *                          BatchNorm2d + optional ReLU (:69-81, :169-170): x [B, Cin, H, W], w [Cout, Cin, k, k] -> [B, Cout, Ho, Wo]
+ *   zb_spk_simam_add_relu  SimAMBasicBlock tail (:86-97): out = relu(x * sigmoid(d / (4 (v + lambda)) + 0.5) + shortcut) per (b, c) plane
+ *   zb_spk_asp             attentive statistics pooling (:38-61): x [B, C, T]; attention Conv1d(C, hidden, 1) -> ReLU -> BatchNorm1d
+ *                          (folded) -> Conv1d(hidden, C, 1) -> softmax over T; out [B, 2 C] = [mean | std]; d_hidden = scratch [B, hidden, T]
+ *   zb_spk_linear          nn.Linear (the bottleneck :212 and the LDA projection :400-402): x [B, in] -> [B, out], bias may be NULL */
+int  zb_spk_conv2d(const float* d_x, const float* d_w, const float* d_scale, const float* d_shift, float* d_out, int B, int Cin, int H, int W,
+                   int Cout, int ksize, int stride, int relu, void* stream);
+int  zb_spk_simam_add_relu(const float* d_x, const float* d_shortcut, float* d_out, int B, int C, int H, int W, float lambda_p, void* stream);
+int  zb_spk_asp(const float* d_x, const float* d_w1, const float* d_b1, const float* d_bn_scale, const float* d_bn_shift, const float* d_w2,
+                const float* d_b2, float* d_hidden, float* d_out, int B, int C, int T, int hidden, void* stream);
+int  zb_spk_linear(const float* d_x, const float* d_w, const float* d_bias, float* d_out, int B, int in_features, int out_features, void* stream);
+
 /* ---- PrefixConditioner (zonos/conditioning.py) -------------------------------------------------------
  * The four ops the reference's PrefixConditioner.forward (conditioning.py:297-313) is made of, on caller-owned bf16 device
  * tensors; zonos_vibes_b200/conditioning.py composes them in the reference's order.  Text -> phoneme ids stays on the host.

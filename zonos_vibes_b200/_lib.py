@@ -70,6 +70,10 @@ SIGNATURES = {
     "zb_dac_set_option": (_I, [_P, C.c_char_p, _I]),
     "zb_dac_launch_count": (_I64, [_P]),
     "zb_dac_encode": (_I, [_P, _P, _P, _I, _I64, _P]),
+    "zb_spk_conv2d": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _P]),
+    "zb_spk_simam_add_relu": (_I, [_P, _P, _P, _I, _I, _I, _I, _F, _P]),
+    "zb_spk_asp": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "zb_spk_linear": (_I, [_P, _P, _P, _P, _I, _I, _I, _P]),
     "zb_wav_to_pcm16": (_I, [_P, _P, _I64, _P]),
     "zb_pc_fourier": (_I, [_P, _P, _F, _F, _P, _I, _I, _I, _P]),
     "zb_pc_embed": (_I, [_P, _P, _P, _I, _I, _I64, _I64, _P]),
