@@ -333,3 +333,20 @@ def test_serving_shell_batches_and_wav_container():
     assert serving.tts_request(eng2, {"text": "t", "speaker_audio_path": "a", "speaking_rate": "x"}, spk)[1] == {"error": "'speaking_rate' must be a number"}
     assert serving.tts_request(eng2, {"text": "t", "speaker_audio_path": "missing.wav", "speaking_rate": 15}, spk)[0] == 404
     eng2.close()
+
+
+def test_speaker_mirror_state_dict_keys():
+    """Row f4 host side: the mirror module takes the reference's ResNet293_SimAM_ASP state_dict by key (the oracle's synthetic
+    state_dict has exactly the keys of the reference's ResNet293_based, see oracle/make_golden_spk.py) and refuses CPU tensors."""
+    import speaker_oracle as so
+    from zonos_vibes_b200 import _lib, speaker_cloning as sc
+    m = sc.ResNet293_based(num_blocks=(2, 2, 3, 1))
+    sd = so.synth_speaker_state_dict(5, (2, 2, 3, 1))
+    assert set(m.state_dict()) == set(sd)
+    for k, v in m.state_dict().items():
+        assert v.shape == sd[k].shape, k
+    m.load_state_dict(sd)
+    with pytest.raises(_lib.ZbError):
+        m.forward_features(so.synth_features(1, 16, 8))
+    full = sc.ResNet293_based()
+    assert sum(len(layer) for layer in (full.front.layer1, full.front.layer2, full.front.layer3, full.front.layer4)) == 97

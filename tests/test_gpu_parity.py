@@ -881,3 +881,52 @@ def test_dac_encode_matches_oracle(cuda):
     dec_only = z.DACAutoencoder(do.synth_dac_state_dict(2), cuda)
     with pytest.raises(Exception, match="encoder tensors"):
         dec_only.encode(wav[:1].to(cuda))
+
+
+# ---- row f4: speaker-embedding network ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,num_blocks,frames", [("shallow", (2, 2, 3, 1), 101), ("full", (10, 20, 64, 3), 48)])
+def test_speaker_embedding_matches_oracle(cuda, name, num_blocks, frames):
+    """zonos_vibes_b200.speaker_cloning.ResNet293_based (zb_spk_* fp32 kernels: 3x3 / 1x1 conv + folded BatchNorm, SimAM gate +
+    residual + ReLU, attentive statistics pooling, bottleneck, LDA) against oracle/speaker_oracle.py, which
+    tests/test_oracle_pinned.py pins to the reference's own classes.  fp32 on both sides; tolerance 1e-3 of the output's max
+    (summation order over up to 190 residual blocks)."""
+    import speaker_oracle as so
+    from zonos_vibes_b200 import speaker_cloning as sc
+    sd = so.synth_speaker_state_dict(5, num_blocks)
+    lda_sd = so.synth_lda_state_dict(6)
+    feats = so.synth_features(2, frames, 8)
+    want_emb, want_lda = so.embedding_from_features(sd, feats, num_blocks, lda_sd)
+    m = sc.ResNet293_based(num_blocks=None if name == "full" else num_blocks)
+    m.load_state_dict(sd)
+    m = m.to(cuda).eval()
+    lda = torch.nn.Linear(256, 128)
+    lda.load_state_dict(lda_sd)
+    lda = lda.to(cuda)
+    with torch.inference_mode():
+        emb = m.forward_features(feats.to(cuda))
+        proj = sc._linear(emb, lda)
+    for what, got, want in (("embedding", emb, want_emb), ("lda", proj, want_lda)):
+        err = (got.cpu() - want).abs().max().item()
+        print(f"[speaker {name}] {what}: max abs err {err:.3e} (max |want| {want.abs().max().item():.3f})")
+        assert got.shape == want.shape and err <= 1e-3 * want.abs().max().item(), what
+
+
+def test_speaker_embedding_from_waveform(cuda):
+    """The whole `ResNet293_based.forward` (speaker_cloning.py:217-224) from a waveform: torchaudio log-mel front end on the
+    device (the same library call as the reference's), then the native network, against front end + oracle on the CPU."""
+    import speaker_oracle as so
+    from zonos_vibes_b200 import speaker_cloning as sc
+    nb = (2, 2, 3, 1)
+    sd = so.synth_speaker_state_dict(5, nb)
+    wav = do.synth_waveform(1, 40, 9)[0, :, ::3].contiguous() * 0.5          # [1, 6827]: ~0.43 s at 16 kHz
+    feat_cpu = sc.logFbankCal()
+    with torch.inference_mode():
+        want = so.embedding_from_features(sd, feat_cpu(wav), nb)
+    m = sc.ResNet293_based(num_blocks=nb, featCal=None)
+    m.load_state_dict(sd)
+    m.featCal = sc.logFbankCal()
+    m = m.to(cuda).eval()
+    got = m(wav.to(cuda))
+    err = (got.cpu() - want).abs().max().item()
+    print(f"[speaker from waveform] max abs err {err:.3e} (max |want| {want.abs().max().item():.3f})")
+    assert err <= 5e-3 * want.abs().max().item()

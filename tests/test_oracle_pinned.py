@@ -197,3 +197,18 @@ def test_dac_encode_oracle_matches_hf_model():
         ref = m.encode(wav).audio_codes
     assert torch.equal(ref, codes)
     assert bool((gaps >= 0).all())
+
+
+@pytest.mark.parametrize("name", ["shallow", "full"])
+def test_speaker_embedding_oracle_golden(name):
+    """Row f4 pin: oracle/speaker_oracle.py against vectors frozen from the reference's own ResNet293_based + LDA classes
+    (oracle/make_golden_spk.py, full depth 10 + 20 + 64 + 3 SimAM blocks and a shallow stack)."""
+    import os
+    import speaker_oracle as so
+    g = torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_spk.pt"))
+    nb = g[f"{name}.num_blocks"]
+    sd = so.synth_speaker_state_dict(5, nb)
+    emb, lda = so.embedding_from_features(sd, so.synth_features(2, g[f"{name}.frames"], 8), nb, so.synth_lda_state_dict(6))
+    for got, want in ((emb, g[f"{name}.embedding"]), (lda, g[f"{name}.lda"])):
+        assert got.shape == want.shape
+        assert (got - want).abs().max().item() <= 1e-4 * want.abs().max().item()

@@ -123,6 +123,16 @@ class Zonos(nn.Module):
         lengths = torch.zeros((batch_size,), dtype=torch.int32, device=self.device)
         return InferenceParams(max_seqlen, batch_size, 0, 0, kv, lengths)
 
+    def make_speaker_embedding(self, wav: torch.Tensor, sr: int) -> torch.Tensor:
+        """model.py:90-95: speaker embedding of an audio clip ([1, 1, 128] bf16) from the ResNet293-SimAM-ASP + LDA network
+        (zonos_vibes_b200/speaker_cloning.py).  The checkpoints come from the hub like the reference's, or
+        assign `model.spk_clone_model = SpeakerEmbeddingLDA(device, spk_model_path=..., lda_spk_model_path=...)` first."""
+        if self.spk_clone_model is None:
+            from .speaker_cloning import SpeakerEmbeddingLDA
+            self.spk_clone_model = SpeakerEmbeddingLDA(str(self.device))
+        _, spk_embedding = self.spk_clone_model(wav.to(self.spk_clone_model.device), sr)
+        return spk_embedding.unsqueeze(0).bfloat16()
+
     def prepare_conditioning(self, cond_dict: dict, uncond_dict: dict | None = None) -> torch.Tensor:
         """model.py:204-212."""
         if self.prefix_conditioner is None:
