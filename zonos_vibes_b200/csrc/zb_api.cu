@@ -1019,6 +1019,7 @@ static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int devic
       return bad(ZB_ERR_ARG, "hybrid: d_state must be 128, ngroups 1, d_conv in [2,8]");
     if ((hyb->expand * cfg->d_model) % hyb->headdim != 0 || (hyb->expand * cfg->d_model) % 256 != 0)
       return bad(ZB_ERR_ARG, "hybrid: d_inner must be a multiple of headdim and of 256");
+    if (hyb->expand * cfg->d_model > 8192) return bad(ZB_ERR_ARG, "hybrid: d_inner above 8192 is not supported (k_m2_gated_norm keeps a row in registers)");
     if (hyb->n_attn_layers < 0 || hyb->n_attn_layers > 64) return bad(ZB_ERR_ARG, "hybrid: at most 64 attention layers");
     const int dinp = 2 * hyb->expand * cfg->d_model + 2 * hyb->d_state + hyb->expand * cfg->d_model / hyb->headdim;
     if (dinp % 8 != 0) return bad(ZB_ERR_ARG, "hybrid: in_proj rows must be a multiple of 8");
