@@ -332,7 +332,7 @@ __global__ void __launch_bounds__(256) k_bt_resid_ln(const BtFinishParams p) {
 }
 
 // in_proj finish: bf16 round, interleaved-pair RoPE in fp32 on q and k (_torch.py:18-30), q -> q buffer, k/v -> paged cache
-// at the current position (_torch.py:33-49).  grid = rows, block = 256.
+// at the current position (_torch.py:33-49).  grid = (rows, ceil(N / 2048)), block = 256.
 __global__ void __launch_bounds__(256) k_bt_qkv_finish(const BtFinishParams p) {
   pdl_launch_dependents();
   pdl_wait_prior_grid();
@@ -343,7 +343,7 @@ __global__ void __launch_bounds__(256) k_bt_qkv_finish(const BtFinishParams p) {
   const size_t split_stride = (size_t)p.m_pad * p.N;
   const int page = p.page_table[(size_t)crow * p.max_pages + pos / ZB_PAGE];
   const float* cs_row = p.rope + (size_t)(p.rope_pos[crow] + tok) * (ZB_DH / 2) * 2;
-  for (int n8 = threadIdx.x * 8; n8 < p.N; n8 += 2048) {
+  for (int n8 = blockIdx.y * 2048 + threadIdx.x * 8; n8 < p.N; n8 += 2048 * gridDim.y) {     // grid.y = ceil(N / 2048): one trip per thread
     float a[8];
     bt_split_sum8(p.partial, p.splits, split_stride, (size_t)row * p.N + n8, a);
     __nv_bfloat162 o[4];
@@ -371,14 +371,14 @@ __global__ void __launch_bounds__(256) k_bt_qkv_finish(const BtFinishParams p) {
   }
 }
 
-// plain finish (hybrid backbone, Mamba2 in_proj): out[row][n] = bf16(sum of the split partials).  grid = rows, block = 256.
+// plain finish (hybrid backbone, Mamba2 in_proj): out[row][n] = bf16(sum of the split partials).  grid = (rows, ceil(N / 2048)), block = 256.
 __global__ void __launch_bounds__(256) k_bt_plain_finish(const BtFinishParams p, bf16* __restrict__ out) {
   pdl_launch_dependents();
   pdl_wait_prior_grid();
   if (p.st->done) return;
   const int row = blockIdx.x;
   const size_t split_stride = (size_t)p.m_pad * p.N;
-  for (int n8 = threadIdx.x * 8; n8 < p.N; n8 += 2048) {           // N % 8 == 0 (checked by the host)
+  for (int n8 = blockIdx.y * 2048 + threadIdx.x * 8; n8 < p.N; n8 += 2048 * gridDim.y) {   // N % 8 == 0 (checked by the host)
     float a[8];
     bt_split_sum8(p.partial, p.splits, split_stride, (size_t)row * p.N + n8, a);
     __nv_bfloat162 o[4];

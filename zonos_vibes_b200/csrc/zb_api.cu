@@ -762,7 +762,7 @@ cudaError_t enqueue_bt_mamba_layer(zb_ctx* c, int l, cudaStream_t s) {
   if ((e = bt_gemm(c, c->bt_map_xn, c->bt_map_in[l], c->m_dinproj, d, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
   {
     BtFinishParams f = bt_finish_params(c, splits, c->m_dinproj);
-    if ((e = launch(c, k_bt_plain_finish, dim3(rows), dim3(256), 0, s, f, c->m_zx)) != cudaSuccess) return e;
+    if ((e = launch(c, k_bt_plain_finish, dim3(rows, (c->m_dinproj + 2047) / 2048), dim3(256), 0, s, f, c->m_zx)) != cudaSuccess) return e;
   }
   M2Params m;
   memset(&m, 0, sizeof(m));
@@ -811,7 +811,7 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
     {
       BtFinishParams f = bt_finish_params(c, splits, qkv);
       f.kv_layer = kv_layer;
-      if ((e = launch(c, k_bt_qkv_finish, dim3(rows), dim3(256), 0, s, f)) != cudaSuccess) return e;
+      if ((e = launch(c, k_bt_qkv_finish, dim3(rows, (qkv + 2047) / 2048), dim3(256), 0, s, f)) != cudaSuccess) return e;
     }
     {
       AttnParams a;
