@@ -212,5 +212,31 @@ int main() {
       fflush(stdout);
     }
   }
+  // ---- how much can ONE SM take in?  The same ring on fewer CTAs: if the per-SM rate stays at total / 148 the limit is the SM's
+  // own ingest path, if it rises the limit is the fabric / memory in aggregate (decides whether fatter tiles on fewer CTAs can
+  // pay for the batched GEMMs, whose per-CTA traffic is weights + activation tile).
+  for (int grid : {148, 74, 37, 16, 4, 1}) {
+    for (int l2 = 0; l2 < 2; ++l2) {
+      P p;
+      p.src = buf; p.per_cta = total / 148; p.n_stages = 5; p.rows = 8; p.row_bytes = 4096; p.row_stride = 4160;
+      p.src_row_stride = 4096; p.mode = 0; p.poll_all = 0; p.direct = 0; p.sink = sink; p.wrap_iters = l2 ? 8 : 0; p.n_iter = l2 ? 4096 : 0;
+      const size_t smem = (size_t)5 * 8 * 4160 + 16 * 5 + 64;
+      float best = 1e30f;
+      for (int rep = 0; rep < 3; ++rep) {
+        CK(cudaEventRecord(e0));
+        k_ring<<<grid, 288, smem>>>(p);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        CK(cudaGetLastError());
+        float ms;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (ms < best) best = ms;
+      }
+      const double bytes = l2 ? (double)grid * 4096 * 32768 : (double)grid * (double)(total / 148);
+      printf("grid %3d CTAs, source %s: %8.3f ms  %8.1f GB/s total  %7.1f GB/s per SM\n", grid, l2 ? "L2 (8 stages per CTA)" : "HBM", best,
+             bytes / (best * 1e-3) / 1e9, bytes / (best * 1e-3) / 1e9 / grid);
+      fflush(stdout);
+    }
+  }
   return 0;
 }
