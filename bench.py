@@ -525,7 +525,7 @@ def extra_b64(model, ctx, world, rank, dev, T, per_gpu, total):
             "frames": T, "ms": ms, "audio_sec_per_sec": frames / FRAME_RATE / (ms * 1e-3), "us_per_decode_step": step_ms * 1e3,
             "decode_frames_per_s": total / (step_ms * 1e-3),
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm, "peak_kind": kind,
-                         "bytes_per_launch": step_bytes, "kernel": "decode step of the slowest rank, batched tcgen05 path (k_bt_gemm + finish kernels + k_attn_decode_mma)"}}
+                         "bytes_per_launch": step_bytes, "kernel": "decode step of the slowest rank, batched tcgen05 path (k_bt_gemm + finish kernels + k_attn_decode_tma)"}}
 
 
 def extra_dac(model, dev, B=32, T=2580, runs=3):
@@ -577,7 +577,7 @@ def extra_hybrid(dev, world, rank, frames=96):
             "decode_frames_per_s": b * world / (step_ms * 1e-3), "audio_sec_per_sec": b * world / (step_ms * 1e-3) / FRAME_RATE,
             "architecture": "synthetic: 46 layers, 5 attention + GatedMLP(8192), 41 Mamba2 (d_state 128, headdim 64, expand 2); dims unverified (SURVEY App. C)",
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm, "peak_kind": kind, "bytes_per_launch": step_bytes,
-                         "kernel": "batched tcgen05 path (k_bt_gemm + finish kernels for the Mamba2 / attention projections, k_m2_conv / k_m2_ssm / k_m2_gated_norm, k_attn_decode_mma), one CUDA graph per step; bytes = weights once + SSM state read + write (fp32) + KV"}}
+                         "kernel": "batched tcgen05 path (k_bt_gemm + finish kernels for the Mamba2 / attention projections, k_m2_conv / k_m2_ssm / k_m2_gated_norm, k_attn_decode_tma), one CUDA graph per step; bytes = weights once + SSM state read + write (fp32) + KV"}}
 
 
 def gpu_baseline(dev, steps=48, prefix_frames=1290):

@@ -339,7 +339,7 @@ def golden_long():
 
 
 LONG_PATHS = {"persistent": {}, "persistent_grid_barriers": dict(ll=0), "persistent_ll2": dict(ll=2), "per_op_graph": dict(mega=0),
-              "batched_tcgen05": dict(mega=0, bt_min_rows=2)}
+              "batched_tcgen05": dict(mega=0, bt_min_rows=2), "batched_tcgen05_ldg_attn": dict(mega=0, bt_min_rows=2, attn_tma=0)}
 
 
 @pytest.mark.parametrize("path", list(LONG_PATHS))
@@ -376,7 +376,8 @@ def test_logit_error_is_bf16_noise_full_size(golden, golden_long, cuda):
     assert e_got <= 1.5 * e_ref + 1e-4, (e_got, e_ref)
 
 
-AP_PATHS = {"block_prefill": dict(), "forced_ll": dict(bt_prefill=0), "forced_barriers": dict(bt_prefill=0, ll=0)}
+AP_PATHS = {"block_prefill": dict(), "forced_ll": dict(bt_prefill=0), "forced_barriers": dict(bt_prefill=0, ll=0),
+            "block_prefill_ldg_attn": dict(attn_tma=0)}
 
 
 @pytest.mark.parametrize("path", list(AP_PATHS))
@@ -436,7 +437,7 @@ def test_generate_with_long_audio_prefix_full_size(golden_long, cuda, path):
 class _options:
     def __init__(self, model, **kw):
         self.ctx, self.kw = model._native(), kw
-        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=3, bt_prefill=1, bt_cluster=1)
+        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=3, bt_prefill=1, bt_cluster=1, attn_tma=1)
 
     def __enter__(self):
         for k, v in self.kw.items():
@@ -448,7 +449,21 @@ class _options:
 
 
 PATHS = {"per_op_graph": dict(mega=0), "batched_tcgen05": dict(mega=0, bt_min_rows=2),
-         "batched_tcgen05_cluster2": dict(mega=0, bt_min_rows=2, bt_cluster=2)}     # activation tile multicast across CTA pairs
+         "batched_tcgen05_cluster2": dict(mega=0, bt_min_rows=2, bt_cluster=2),     # activation tile multicast across CTA pairs
+         "batched_tcgen05_ldg_attn": dict(mega=0, bt_min_rows=2, attn_tma=0)}       # K / V fragments by ld.global instead of the cp.async.bulk ring
+
+
+def test_batched_attention_tma_staging_is_bit_identical(golden_long, cuda):
+    """k_attn_decode_tma gives every warp the same 16-token groups in the same order as k_attn_decode_mma, so the batched
+    path's logits must not change by one bit when K / V arrive through the shared-memory ring (ctx 1315: 11 pages, a
+    partial last stage, stages that straddle a page boundary)."""
+    m = make_model("full", cuda)
+    prefix = zo.synth_prefix_conditioning(zo.FULL_CONFIG, 1, 24, 1)
+    got = []
+    for tma in (0, 1, 2):
+        with _options(m, mega=0, bt_min_rows=2, attn_tma=tma):
+            got.append(m.compute_logits_teacher_forced(prefix, golden_long["long.p1290.delayed"], 8, skip=1290).clone())
+    assert torch.equal(got[0], got[1]) and torch.equal(got[0], got[2])
 
 
 @pytest.mark.parametrize("path", list(PATHS))
@@ -523,7 +538,8 @@ def test_greedy_stream_other_paths(golden, cuda, path):
         assert torch.equal(out.cpu(), golden["gen.tiny.greedy.codes"])
 
 
-def test_batched_tcgen05_equals_independent_runs(golden, cuda):
+@pytest.mark.parametrize("attn", ["ldg", "tma", "tma_early_release"])
+def test_batched_tcgen05_equals_independent_runs(golden, cuda, attn):
     """Batch semantics = B independent batch-1 runs: 6 utterances (12 rows -> batched tcgen05 path by
     default) teacher-forced on the same codes must give, per utterance, the logits of its own batch-1 run."""
     m = make_model("small", cuda)
@@ -533,7 +549,9 @@ def test_batched_tcgen05_equals_independent_runs(golden, cuda):
     delayed1 = golden["gen.small.greedy.delayed"]
     singles = [m.compute_logits_teacher_forced(x, delayed1, 12) for x in ps]                    # persistent kernel, rows = 2
     batch_prefix = torch.cat([torch.cat([x[:1] for x in ps]), torch.cat([x[1:] for x in ps])])
-    got = m.compute_logits_teacher_forced(batch_prefix, delayed1.expand(nb, -1, -1).contiguous(), 12)   # rows = 12
+    opts = {"ldg": dict(attn_tma=0), "tma": {}, "tma_early_release": dict(attn_tma=2)}[attn]
+    with _options(m, **opts):
+        got = m.compute_logits_teacher_forced(batch_prefix, delayed1.expand(nb, -1, -1).contiguous(), 12)   # rows = 12
     for i in range(nb):
         for s in range(13):
             assert_logits_close(got[s, i:i + 1], singles[i][s], f"utterance {i} step {s}")

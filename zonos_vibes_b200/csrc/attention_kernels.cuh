@@ -85,14 +85,17 @@ __device__ __forceinline__ void att_tokens4(const uint4 (&kraw)[4], const uint4 
 
 // Cross-warp merge of the per-warp online-softmax states in shared memory, then (nsplit > 1) the ticketed merge of the
 // split partials by the last CTA of the (row, kv-head).  Shared by the SIMT and the mma.sync kernels.
+// `split` of `nparts` ticket holders writes partial slot `split` of the (row, kv head)'s `stride` slots; the last ticket merges
+// the first `nact` slots.
 template <int G>
-__device__ __forceinline__ void att_finish(const AttnParams& p, int row, int kvh, int split, int nsplit, int ctx, int chunk,
-                                           float (*s_o)[G][ZB_DH], float (*s_m)[G], float (*s_l)[G]) {
+__device__ __forceinline__ void att_finish_parts(const AttnParams& p, int row, int kvh, int split, int stride, int nparts, int nact,
+                                                 float (*s_o)[G][ZB_DH], float (*s_m)[G], float (*s_l)[G]) {
   __shared__ int s_last;
   const int tid = threadIdx.x;
+  const int nsplit = nparts;
   __syncthreads();
   // thread `tid` owns dim tid (ATT_THREADS == ZB_DH)
-  const size_t pbase = (((size_t)row * p.Hkv + kvh) * nsplit + split) * G;
+  const size_t pbase = (((size_t)row * p.Hkv + kvh) * stride + split) * G;
 #pragma unroll
   for (int g = 0; g < G; ++g) {
     float mn = -INFINITY;
@@ -126,8 +129,7 @@ __device__ __forceinline__ void att_finish(const AttnParams& p, int row, int kvh
   // staged in shared memory with one parallel load; the partial outputs are then read 8 splits at a time so the L2
   // round trips overlap instead of serialising (the first version of this loop cost 26 us per launch, r01 launch list).
   __shared__ float s_ml[32 * 8 * 2];
-  const int nact = min(nsplit, (ctx + chunk - 1) / chunk);
-  const size_t rbase = ((size_t)row * p.Hkv + kvh) * nsplit * G;
+  const size_t rbase = ((size_t)row * p.Hkv + kvh) * stride * G;
   for (int i = tid; i < nact * G * 2; i += ATT_THREADS) s_ml[i] = __ldcg(&p.part_ml[rbase * 2 + i]);
   __syncthreads();
 #pragma unroll
@@ -152,6 +154,11 @@ __device__ __forceinline__ void att_finish(const AttnParams& p, int row, int kvh
     p.y[(size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + tid] = __float2bfloat16_rn(ot / lt);
   }
   if (tid == 0) p.counters[row * p.Hkv + kvh] = 0;
+}
+template <int G>
+__device__ __forceinline__ void att_finish(const AttnParams& p, int row, int kvh, int split, int nsplit, int ctx, int chunk,
+                                           float (*s_o)[G][ZB_DH], float (*s_m)[G], float (*s_l)[G]) {
+  att_finish_parts<G>(p, row, kvh, split, nsplit, nsplit, min(nsplit, (ctx + chunk - 1) / chunk), s_o, s_m, s_l);
 }
 
 template <int G>
@@ -393,6 +400,141 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode_mma(const AttnParam
 
   __shared__ float s_o[ATT_WARPS][G][ZB_DH];
   __shared__ float s_m[ATT_WARPS][G], s_l[ATT_WARPS][G];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int d = 16 * g + 2 * j;
+    if (2 * t < G) { s_o[warp][2 * t][d] = o[j][0]; s_o[warp][2 * t][d + 1] = o[j][2]; }
+    if (2 * t + 1 < G) { s_o[warp][2 * t + 1][d] = o[j][1]; s_o[warp][2 * t + 1][d + 1] = o[j][3]; }
+  }
+  if (t == 0 && g < G) { s_m[warp][g] = m; s_l[warp][g] = l; }
+  att_finish<G>(p, row, kvh, split, nsplit, ctx, chunk, s_o, s_m, s_l);
+}
+
+// =====================================================================================================================
+// k_attn_decode_tma: the same split-KV attention with K / V brought in by the TMA engine (cp.async.bulk, 64 tokens =
+// 16 KB of K + 16 KB of V per stage, ring of ATT_TMA_STAGES stages with full mbarriers) instead of per-lane ld.global.
+// Why: scripts/ring_bench.cu measures ~50 GB/s per SM for bulk copies against ~38 GB/s per SM for the ld.global path; at
+// batch 64 the ld.global kernel sits at 5.45 TB/s = 36.8 GB/s per SM (profiles/r02_summary.md), i.e. on that ceiling.
+// One warp = one 16-token group of a stage (4 warps = the 4 groups); fragments come from shared memory in the mma.sync
+// layout of att_group16.  A stage never straddles more than one page boundary (ZB_PAGE = 128, stages of 64 tokens): at
+// most two copies per tensor per stage.
+// =====================================================================================================================
+#define ATT_TMA_TOK 64
+#define ATT_TMA_STAGE_BYTES (2 * ATT_TMA_TOK * ZB_DH * 2)       // 32 KB
+#define ATT_TMA_STAGES 3    // 3 stages = 96 KB = 2 CTAs per SM.  Measured at batch 64, ctx 1 300 (profiles/r02_attn_tma_ab.txt): 2 stages
+                            // (3 CTAs per SM) 3 675 us per decode step, 4 stages (1 CTA per SM) 3 987, 3 stages 3 152-3 230
+#define ATT_TMA_SMEM (ATT_TMA_STAGES * ATT_TMA_STAGE_BYTES + 64)
+
+__device__ __forceinline__ uint32_t att_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ bool att_mbar_try(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ uint4 att_lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+
+template <int G, bool EARLY>
+__global__ void __launch_bounds__(ATT_THREADS) k_attn_decode_tma(const AttnParams p) {
+  extern __shared__ __align__(128) unsigned char att_ring[];
+  pdl_launch_dependents();
+  pdl_wait_prior_grid();
+  if (p.st->done) return;
+
+  const int split = blockIdx.x, nsplit = gridDim.x, kvh = blockIdx.y, row = blockIdx.z;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int crow = p.vrows ? row % p.vrows : row;
+  const int ctx = p.st->pos + 1 + (p.vrows ? row / p.vrows : 0);
+  int chunk = (ctx + nsplit - 1) / nsplit;
+  chunk = (chunk + 15) & ~15;
+  const int t0 = split * chunk;
+  const int t1 = min(ctx, t0 + chunk);
+  const int n_st = t1 > t0 ? (t1 - t0 + ATT_TMA_TOK - 1) / ATT_TMA_TOK : 0;
+
+  const uint32_t ring = att_smem_u32(att_ring);
+  const uint32_t bar0 = ring + ATT_TMA_STAGES * ATT_TMA_STAGE_BYTES;
+  const int* pt = p.page_table + (size_t)crow * p.max_pages;
+  const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
+  const size_t kv_stride = (size_t)p.Hkv * head_stride;
+  const size_t page_stride = 2 * kv_stride;
+
+  // thread 0 is the producer: one stage = K rows [0, 16 KB) and V rows [16 KB, 32 KB) of tokens [ts, ts + n)
+  auto issue = [&](int si) {
+    const int slot = si % ATT_TMA_STAGES;
+    const int ts = t0 + si * ATT_TMA_TOK;
+    const int n = min(ATT_TMA_TOK, t1 - ts);
+    const uint32_t bar = bar0 + 8u * slot, dst = ring + (uint32_t)slot * ATT_TMA_STAGE_BYTES;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(n * ZB_DH * 2 * 2)) : "memory");
+    const int n1 = min(n, ZB_PAGE - ts % ZB_PAGE);                 // tokens before the page boundary
+    for (int run = 0; run < 2; ++run) {
+      const int tb = run == 0 ? ts : ts + n1, nn = run == 0 ? n1 : n - n1;
+      if (nn <= 0) continue;
+      const bf16* src = p.kv_layer + (size_t)pt[tb / ZB_PAGE] * page_stride + (size_t)kvh * head_stride + (size_t)(tb % ZB_PAGE) * ZB_DH;
+      const uint32_t off = (uint32_t)(tb - ts) * ZB_DH * 2;
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst + off), "l"(src),
+                   "r"((uint32_t)(nn * ZB_DH * 2)), "r"(bar) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst + ATT_TMA_TOK * ZB_DH * 2 + off),
+                   "l"(src + kv_stride), "r"((uint32_t)(nn * ZB_DH * 2)), "r"(bar) : "memory");
+    }
+  };
+  if (tid == 0) {
+    for (int s = 0; s < ATT_TMA_STAGES; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar0 + 8u * s), "r"(1u) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async;" ::: "memory");             // this step's K / V rows were written by ordinary stores of the previous kernel
+    for (int si = 0; si < min(n_st, ATT_TMA_STAGES); ++si) issue(si);
+  }
+
+  uint32_t qa[8][2];
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    uint4 w = make_uint4(0, 0, 0, 0);
+    if (g < G) w = *reinterpret_cast<const uint4*>(p.q + (size_t)row * p.H * ZB_DH + (size_t)(kvh * G + g) * ZB_DH + 32 * s + 8 * t);
+    qa[2 * s][0] = w.x; qa[2 * s][1] = w.y; qa[2 * s + 1][0] = w.z; qa[2 * s + 1][1] = w.w;
+  }
+  float m = -INFINITY, l = 0.f, o[8][4];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { o[j][0] = 0.f; o[j][1] = 0.f; o[j][2] = 0.f; o[j][3] = 0.f; }
+  __syncthreads();                                                  // barriers initialised before anyone polls them
+
+  const uint4 z4 = make_uint4(0, 0, 0, 0);
+  for (int si = 0; si < n_st; ++si) {
+    const int slot = si % ATT_TMA_STAGES;
+    const int ts = t0 + si * ATT_TMA_TOK;
+    const int n = min(ATT_TMA_TOK, t1 - ts);
+    if (lane == 0) { while (!att_mbar_try(bar0 + 8u * slot, (uint32_t)((si / ATT_TMA_STAGES) & 1))) {} }
+    __syncwarp();
+    const int tl = 16 * warp;                                       // this warp's 16-token group of the stage
+    AttFrag f;
+    if (tl < n) {
+      const uint32_t sp = ring + (uint32_t)slot * ATT_TMA_STAGE_BYTES;
+#pragma unroll
+      for (int nn = 0; nn < 2; ++nn) {
+        const int tok = tl + 8 * nn + g;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) f.k[nn][s] = tok < n ? att_lds128(sp + tok * (ZB_DH * 2) + (32 * s + 8 * t) * 2) : z4;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int tok = tl + 2 * t + (u & 1) + 8 * (u >> 1);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) f.v[u][h] = tok < n ? att_lds128(sp + ATT_TMA_TOK * ZB_DH * 2 + tok * (ZB_DH * 2) + (16 * g + 8 * h) * 2) : z4;
+      }
+    }
+    // EARLY: the slot is handed back as soon as the fragments are in registers; otherwise after the group's math
+    if (!EARLY && tl < n) att_group16<G>(f, ts + tl, t1, qa, m, l, o, p.scale_log2, lane);
+    __syncthreads();                                                // every warp has its fragments out of the slot
+    if (tid == 0 && si + ATT_TMA_STAGES < n_st) issue(si + ATT_TMA_STAGES);
+    if (EARLY && tl < n) att_group16<G>(f, ts + tl, t1, qa, m, l, o, p.scale_log2, lane);
+  }
+
+  // every stage has been consumed (the loop ends on a __syncthreads): the ring is free to hold the per-warp states
+  float (*s_o)[G][ZB_DH] = reinterpret_cast<float (*)[G][ZB_DH]>(att_ring);
+  float (*s_m)[G] = reinterpret_cast<float (*)[G]>(att_ring + sizeof(float) * ATT_WARPS * G * ZB_DH);
+  float (*s_l)[G] = s_m + ATT_WARPS;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int d = 16 * g + 2 * j;

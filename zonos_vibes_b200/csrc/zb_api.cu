@@ -89,6 +89,9 @@ struct zb_ctx {
   // options
   int opt_pdl = 1, opt_l2_prefetch_mb = 0, opt_graph = 1, opt_gemv = 1;
   int opt_attn_mma = 1;     // 1: mma.sync attention kernel, 0: SIMT (A/B and cross-check)
+  int opt_nsplit = 0;       // > 0: KV splits of the multi-kernel / batched attention (default: 4 CTAs per SM worth), read by zb_kv_alloc
+  int opt_attn_tma = 1;     // batched path: 0 = K/V fragments by ld.global (k_attn_decode_mma), 1 = K/V staged through shared memory by cp.async.bulk (k_attn_decode_tma); 2 = same, ring slot
+                            // released before the group's math
   int64_t launches = 0;
   bool counting = true;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;     // zb_bench_kernel
@@ -241,6 +244,15 @@ size_t gemv_mma_smem(int R, int K, int epi) {
 size_t gemv_smem(int R, int K) { return (size_t)R * K * sizeof(bf16) + (size_t)(GEMV_THREADS / 32) * R * sizeof(float); }
 
 typedef void (*AttnKernel)(const AttnParams);
+AttnKernel attn_tma_kernel(int G, bool early) {
+  switch (G) {
+    case 1: return early ? k_attn_decode_tma<1, true> : k_attn_decode_tma<1, false>;
+    case 2: return early ? k_attn_decode_tma<2, true> : k_attn_decode_tma<2, false>;
+    case 4: return early ? k_attn_decode_tma<4, true> : k_attn_decode_tma<4, false>;
+    case 8: return early ? k_attn_decode_tma<8, true> : k_attn_decode_tma<8, false>;
+  }
+  return nullptr;
+}
 AttnKernel attn_kernel(int G, bool mma = true) {
   switch (G) {
     case 1: return mma ? k_attn_decode_mma<1> : k_attn_decode<1>;
@@ -821,6 +833,9 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
       a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
       a.vrows = c->bt_vrows;
       // block prefill: one split per (token row, kv head) - no partial buffers or tickets (they are sized for the cache rows)
+      if (c->opt_attn_tma) {
+        if ((e = launch(c, attn_tma_kernel(H / Hkv, c->opt_attn_tma == 2), dim3(c->bt_vM ? 1 : c->nsplit, Hkv, rows), dim3(ATT_THREADS), ATT_TMA_SMEM, s, a)) != cudaSuccess) return e;
+      } else
       if ((e = launch(c, attn_kernel(H / Hkv, c->opt_attn_mma != 0), dim3(c->bt_vM ? 1 : c->nsplit, Hkv, rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
     }
     if ((e = bt_gemm(c, c->bt_map_y, c->bt_map_out[l], d, q_size, BT_MODE_PARTIAL, &splits, s)) != cudaSuccess) return e;
@@ -1150,6 +1165,12 @@ static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int devic
   c->n_sms = prop.multiProcessorCount;
   c->smem_optin = max_smem;
   for (int G2 = 1; G2 <= 8; G2 *= 2)
+    if ((e = cudaFuncSetAttribute(attn_tma_kernel(G2, false), cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_TMA_SMEM)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(attn_tma_kernel(G2, true), cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_TMA_SMEM)) != cudaSuccess) {
+      cudaFree(c->arena); delete c;
+      return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute(attn): ") + cudaGetErrorString(e));
+    }
+  for (int G2 = 1; G2 <= 8; G2 *= 2)
     if ((e = cudaFuncSetAttribute(mega_kernel(G2, false, false), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(mega_kernel(G2, false, true), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(mega_kernel(G2, true, false), cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)) != cudaSuccess ||
@@ -1280,6 +1301,7 @@ int zb_kv_alloc(zb_ctx* c, int rows, int max_seqlen) {
   c->kv_layer_elems = total_pages * 2 * g.num_heads_kv * ZB_PAGE * ZB_DH;
   int ns = (4 * ZB_NUM_SMS) / (rows * g.num_heads_kv);
   ns = ns < 1 ? 1 : (ns > 32 ? 32 : ns);
+  if (c->opt_nsplit > 0) ns = c->opt_nsplit > 32 ? 32 : c->opt_nsplit;
   c->nsplit = ns;
   const int G = g.num_heads / g.num_heads_kv;
   const int rows_pad = (rows + 127) / 128 * 128;       // activation matrices are TMA operands of 128-row tiles (bt path)
@@ -1718,6 +1740,8 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "bt_prefill") c->opt_bt_prefill = value;
   else if (k == "bt_min_rows") c->opt_bt_min_rows = value;
   else if (k == "attn_mma") c->opt_attn_mma = value;
+  else if (k == "attn_tma") c->opt_attn_tma = value;
+  else if (k == "nsplit") c->opt_nsplit = value;
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
   drop_graph(c);
   return ZB_OK;
