@@ -339,7 +339,9 @@ def golden_long():
 
 
 LONG_PATHS = {"persistent": {}, "persistent_grid_barriers": dict(ll=0), "persistent_ll2": dict(ll=2), "per_op_graph": dict(mega=0),
-              "batched_tcgen05": dict(mega=0, bt_min_rows=2), "batched_tcgen05_ldg_attn": dict(mega=0, bt_min_rows=2, attn_tma=0)}
+              "batched_tcgen05": dict(mega=0, bt_min_rows=2), "batched_tcgen05_tma_attn": dict(mega=0, bt_min_rows=2, attn_tma=2),
+              "batched_tcgen05_single_cta": dict(mega=0, bt_min_rows=2, bt_cta2=0),
+              "batched_tcgen05_cta_pairs_fc1": dict(mega=0, bt_min_rows=2, bt_cta2=3)}
 
 
 @pytest.mark.parametrize("path", list(LONG_PATHS))
@@ -377,7 +379,7 @@ def test_logit_error_is_bf16_noise_full_size(golden, golden_long, cuda):
 
 
 AP_PATHS = {"block_prefill": dict(), "forced_ll": dict(bt_prefill=0), "forced_barriers": dict(bt_prefill=0, ll=0),
-            "block_prefill_ldg_attn": dict(attn_tma=0)}
+            "block_prefill_tma_attn": dict(attn_tma=2)}
 
 
 @pytest.mark.parametrize("path", list(AP_PATHS))
@@ -437,7 +439,7 @@ def test_generate_with_long_audio_prefix_full_size(golden_long, cuda, path):
 class _options:
     def __init__(self, model, **kw):
         self.ctx, self.kw = model._native(), kw
-        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=3, bt_prefill=1, bt_cluster=1, attn_tma=1)
+        self.defaults = dict(mega=1, bt_min_rows=9, graph=1, gemv=1, ll=3, bt_prefill=1, bt_cluster=1, attn_tma=1, bt_cta2=1)
 
     def __enter__(self):
         for k, v in self.kw.items():
@@ -449,8 +451,10 @@ class _options:
 
 
 PATHS = {"per_op_graph": dict(mega=0), "batched_tcgen05": dict(mega=0, bt_min_rows=2),
-         "batched_tcgen05_cluster2": dict(mega=0, bt_min_rows=2, bt_cluster=2),     # activation tile multicast across CTA pairs
-         "batched_tcgen05_ldg_attn": dict(mega=0, bt_min_rows=2, attn_tma=0)}       # K / V fragments by ld.global instead of the cp.async.bulk ring
+         "batched_tcgen05_cluster2": dict(mega=0, bt_min_rows=2, bt_cluster=2, bt_cta2=0),     # activation tile multicast across CTA pairs
+         "batched_tcgen05_tma_attn": dict(mega=0, bt_min_rows=2, attn_tma=2),       # K / V staged by cp.async.bulk (the default from 64 rows up)
+         "batched_tcgen05_single_cta": dict(mega=0, bt_min_rows=2, bt_cta2=0),      # k_bt_gemm for every GEMM (default: k_bt_gemm2 = CTA pairs for the split-K GEMMs)
+         "batched_tcgen05_cta_pairs_fc1": dict(mega=0, bt_min_rows=2, bt_cta2=3)}   # k_bt_gemm2 (tcgen05.mma.cta_group::2, weights as the M operand) for fc1 too
 
 
 def test_batched_attention_tma_staging_is_bit_identical(golden_long, cuda):
@@ -460,7 +464,7 @@ def test_batched_attention_tma_staging_is_bit_identical(golden_long, cuda):
     m = make_model("full", cuda)
     prefix = zo.synth_prefix_conditioning(zo.FULL_CONFIG, 1, 24, 1)
     got = []
-    for tma in (0, 1, 2):
+    for tma in (0, 2, 3):
         with _options(m, mega=0, bt_min_rows=2, attn_tma=tma):
             got.append(m.compute_logits_teacher_forced(prefix, golden_long["long.p1290.delayed"], 8, skip=1290).clone())
     assert torch.equal(got[0], got[1]) and torch.equal(got[0], got[2])
@@ -549,7 +553,7 @@ def test_batched_tcgen05_equals_independent_runs(golden, cuda, attn):
     delayed1 = golden["gen.small.greedy.delayed"]
     singles = [m.compute_logits_teacher_forced(x, delayed1, 12) for x in ps]                    # persistent kernel, rows = 2
     batch_prefix = torch.cat([torch.cat([x[:1] for x in ps]), torch.cat([x[1:] for x in ps])])
-    opts = {"ldg": dict(attn_tma=0), "tma": {}, "tma_early_release": dict(attn_tma=2)}[attn]
+    opts = {"ldg": dict(attn_tma=0), "tma": dict(attn_tma=2), "tma_early_release": dict(attn_tma=3)}[attn]
     with _options(m, **opts):
         got = m.compute_logits_teacher_forced(batch_prefix, delayed1.expand(nb, -1, -1).contiguous(), 12)   # rows = 12
     for i in range(nb):

@@ -229,6 +229,215 @@ __global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm(const __grid_constant
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// k_bt_gemm2: the same contraction on CTA PAIRS (tcgen05.mma.cta_group::2, M = 256).  What bounds k_bt_gemm at batch 64 is
+// the bytes delivered into each SM (profiles/r02_summary.md section 3): every CTA pulls its 128-row weight tile AND the whole
+// 128-row activation tile.  Here the roles are swapped - the WEIGHTS are the M operand (128 rows per CTA, 256 per pair, each
+// CTA loads only its own), the ACTIVATIONS the N operand (N = 128 rows, split between the pair: each CTA loads 64) - so a
+// CTA ingests 16 + 8 KB per k-block instead of 16 + 16.  The accumulator comes out transposed (TMEM lane = weight row,
+// column = activation row); the epilogues store it into the same [rows][N] layouts as k_bt_gemm.
+//   grid = (weight tiles padded to even, activation tiles, splits), cluster (2, 1, 1); rank 0 of a pair issues the MMAs, both
+//   CTAs' TMA loads complete on rank 0's full barrier, the commits are multicast to both CTAs' empty / accumulator barriers.
+// SWIGLU: the CTA's 128 weight rows are, per TMEM lane quarter, 16 value rows then the 16 gate rows of the same ffn columns
+// (one 4-D TMA box over fc1 viewed as [16-column group][value | gate][16 rows][K]): a warp pairs value and gate with one
+// shuffle per two activation rows, every lane evaluates one SwiGLU, and the tile leaves through shared memory as 16-byte
+// row segments.
+// ---------------------------------------------------------------------------------------------------------------
+#define BT2_A_BYTES (128 * BT_BK * 2)       // 16 KB: this CTA's weight rows
+#define BT2_B_BYTES (64 * BT_BK * 2)        // 8 KB: this CTA's half of the activation rows
+#define BT2_STAGE_BYTES (BT2_A_BYTES + BT2_B_BYTES)
+#define BT2_STAGES 8
+#define BT2_SMEM_BYTES (1024 + BT2_STAGES * BT2_STAGE_BYTES + 256)
+
+__device__ __forceinline__ void bt2_tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t leader_bar) {
+  asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+               "l"(map), "r"(c0), "r"(c1), "r"(leader_bar)
+               : "memory");
+}
+__device__ __forceinline__ void bt2_tma_load_4d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint32_t leader_bar) {
+  asm volatile("cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];" ::"r"(dst),
+               "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(leader_bar)
+               : "memory");
+}
+// Execution barrier of the pair without the release fence (barrier.cluster.arrive.release is a MEMBAR.ALL.GPU: at the end of
+// the kernel it would wait for every epilogue store to become visible device-wide).  Barrier initialisation is published by
+// fence.mbarrier_init.release.cluster; nothing else is communicated through memory across this barrier.
+__device__ __forceinline__ void bt2_pair_sync() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void bt2_commit(uint32_t bar) {         // arrives on `bar` of both CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void bt2_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// map_xh: the activations with a box of {64 k, 64 rows}; map_w: the weights with a box of {64 k, 128 rows}, or (SWIGLU) fc1 as
+// the 4-D tensor {K, 16 rows, value | gate, F / 16 groups} with a box of {64 k, 16, 2, 4}
+__global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm2(const __grid_constant__ CUtensorMap map_xh, const __grid_constant__ CUtensorMap map_w,
+                                                            const BtGemmParams p) {
+  extern __shared__ unsigned char bt_smem_raw[];
+  const uint32_t raw = smem_u32(bt_smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t bar_base = base + BT2_STAGES * BT2_STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * (uint32_t)s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (uint32_t)(BT2_STAGES + s); };
+  const uint32_t tmem_full_bar = bar_base + 8u * (uint32_t)(2 * BT2_STAGES);
+  const uint32_t tmem_slot = tmem_full_bar + 8u;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(bt_smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tile = blockIdx.x, m0 = blockIdx.y * BT_BM, split = blockIdx.z;
+  const int kb0 = split * p.kb_per_split;
+  const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+  const int nkb = kb1 - kb0;
+  uint32_t crank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+  const bool leader = crank == 0;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_xh) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+    for (int s = 0; s < BT2_STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(128u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  bt2_pair_sync();                                              // the peer's barriers and accumulator exist before anything signals them
+  tc_fence_after();
+  const uint32_t tmem_d = *tmem_slot_ptr;
+
+  pdl_launch_dependents();
+  const bool swiglu = p.mode == BT_MODE_SWIGLU;
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer (both CTAs).  Every load of the pair completes on the LEADER's full barrier: the address of the
+      // same barrier in the even CTA of the pair is this CTA's address with the peer bit cleared.
+      auto lfull = [&](int s) { return full_bar(s) & 0xFEFFFFFFu; };
+      auto load_w = [&](int i, int s) {
+        const uint32_t a_dst = base + (uint32_t)s * BT2_STAGE_BYTES;
+        if (swiglu) {
+          bt2_tma_load_4d(a_dst, &map_w, (kb0 + i) * BT_BK, 0, 0, n_tile * 4, lfull(s));
+        } else {
+          bt2_tma_load_2d(a_dst, &map_w, (kb0 + i) * BT_BK, n_tile * 128, lfull(s));
+        }
+      };
+      auto load_x = [&](int i, int s) {
+        bt2_tma_load_2d(base + (uint32_t)s * BT2_STAGE_BYTES + BT2_A_BYTES, &map_xh, (kb0 + i) * BT_BK, m0 + (int)crank * 64, lfull(s));
+      };
+      const int pre = nkb < BT2_STAGES ? nkb : BT2_STAGES;
+      for (int i = 0; i < pre; ++i) {                              // weights do not depend on the previous kernel
+        if (leader) mbar_expect_tx(full_bar(i), 2 * BT2_STAGE_BYTES);
+        load_w(i, i);
+      }
+      pdl_wait_prior_grid();
+      for (int i = 0; i < pre; ++i) load_x(i, i);
+      for (int i = pre; i < nkb; ++i) {
+        const int s = i % BT2_STAGES;
+        mbar_wait(empty_bar(s), ((i / BT2_STAGES) - 1) & 1);
+        if (leader) mbar_expect_tx(full_bar(s), 2 * BT2_STAGE_BYTES);
+        load_x(i, s);
+        load_w(i, s);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0 && leader) {
+      uint32_t idesc = 0;                                         // kind::f16: D = F32, A = B = BF16, K-major, M = 256 (pair), N = 128
+      idesc |= 1u << 4; idesc |= 1u << 7; idesc |= 1u << 10; idesc |= (uint32_t)(128 >> 3) << 17; idesc |= (uint32_t)(256 >> 4) << 24;
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % BT2_STAGES;
+        mbar_wait(full_bar(s), (i / BT2_STAGES) & 1);
+        tc_fence_after();
+        const uint32_t a_addr = base + (uint32_t)s * BT2_STAGE_BYTES;
+        const uint64_t adesc = umma_desc_sw128(a_addr);
+        const uint64_t bdesc = umma_desc_sw128(a_addr + BT2_A_BYTES);
+#pragma unroll
+        for (int k = 0; k < BT_BK / 16; ++k)
+          bt2_mma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (i | k) != 0);
+        bt2_commit(empty_bar(s));
+      }
+      bt2_commit(tmem_full_bar);
+    }
+    __syncwarp();
+  } else {
+    // ===== epilogue: warp w owns TMEM lanes [32*(w%4), +32) = weight rows of this CTA; columns = activation rows
+    const int lg = warp & 3;
+    const int mcols = min(BT_BM, (p.M - m0 + 31) & ~31);          // accumulator columns that are real activation rows (in 32s)
+    if (nkb > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    if (swiglu) {
+      // fc1 -> y * silu(gate), all three rounded to bf16 like the reference's bf16 tensors (_torch.py:150-152)
+      // lanes 0..15 of the quarter hold value rows, lanes 16..31 the gate rows of the same 16 ffn columns.  For activation rows
+      // (e, e + 1): the value lane keeps y[e] and receives g[e], the gate lane keeps g[e + 1] and receives y[e + 1].
+      const int BT2_HROW = 160;                                                  // bytes per staged row: 64 bf16 + pad (bank spread, 16 B aligned)
+      unsigned char* s_h = bt_smem_raw + (base - raw);                           // [128 activation rows][BT2_HROW]; the stages are drained
+      const bool gate_lane = lane >= 16;
+      const int jc = lg * 16 + (lane & 15);                                      // ffn column of the tile
+      for (int c0 = 0; c0 < mcols; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+        for (int e = 0; e < 32; e += 2) {
+          const uint32_t got = __shfl_xor_sync(0xffffffffu, gate_lane ? v[e] : v[e + 1], 16);
+          const float y = bf16_round(__uint_as_float(gate_lane ? got : v[e]));
+          const float gt = bf16_round(__uint_as_float(gate_lane ? v[e + 1] : got));
+          const float sg = bf16_round(gt / (1.0f + expf(-gt)));
+          *reinterpret_cast<bf16*>(s_h + (size_t)(c0 + e + (gate_lane ? 1 : 0)) * BT2_HROW + jc * 2) = __float2bfloat16_rn(y * sg);
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      {
+        const int t = threadIdx.x - 64;                                          // 0..127 over the four epilogue warps
+        const int seg = t & 7;                                                   // 16-byte segment of a 128-byte row
+        if (n_tile * 64 + seg * 8 < p.N) {
+#pragma unroll 4
+          for (int r = t >> 3; r < mcols; r += 16) {
+            const int m = m0 + r;
+            if (m < p.M) *reinterpret_cast<uint4*>(p.h + (size_t)m * p.N + n_tile * 64 + seg * 8) = *reinterpret_cast<const uint4*>(s_h + (size_t)r * BT2_HROW + seg * 16);
+          }
+        }
+      }
+    } else {
+      const int n = n_tile * 128 + lg * 32 + lane;
+      for (int c0 = 0; c0 < mcols; c0 += 32) {
+        uint32_t v[32];
+        if (nkb > 0) {
+          tmem_ld32(tmem_d + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, v);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 32; ++e) v[e] = 0u;
+        }
+        float* dst = p.partial + ((size_t)split * p.m_pad + m0 + c0) * p.N + n;
+#pragma unroll
+        for (int e = 0; e < 32; ++e)
+          if (m0 + c0 + e < p.M && n < p.N) dst[(size_t)e * p.N] = __uint_as_float(v[e]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  bt2_pair_sync();                                              // the leader's MMAs read the peer's shared memory and write its accumulator
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(128u) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // finish kernels: fixed-order split sums + the epilogues that need whole rows
 // ---------------------------------------------------------------------------------------------------------------
 struct BtFinishParams {

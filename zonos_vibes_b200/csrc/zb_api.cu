@@ -90,8 +90,9 @@ struct zb_ctx {
   int opt_pdl = 1, opt_l2_prefetch_mb = 0, opt_graph = 1, opt_gemv = 1;
   int opt_attn_mma = 1;     // 1: mma.sync attention kernel, 0: SIMT (A/B and cross-check)
   int opt_nsplit = 0;       // > 0: KV splits of the multi-kernel / batched attention (default: 4 CTAs per SM worth), read by zb_kv_alloc
-  int opt_attn_tma = 1;     // batched path: 0 = K/V fragments by ld.global (k_attn_decode_mma), 1 = K/V staged through shared memory by cp.async.bulk (k_attn_decode_tma); 2 = same, ring slot
-                            // released before the group's math
+  int opt_attn_tma = 1;     // batched path: K/V staged through shared memory by cp.async.bulk (k_attn_decode_tma) instead of ld.global fragments
+                            // (k_attn_decode_mma).  0 = never, 1 = when rows >= 64 (measured: batch 64 -9 %, batch 32 -3 %, batch 16 +-0 at
+                            // ctx 1 300; hybrid batch 16 at short context +2 %), 2 = always, 3 = always, ring slot released before the math
   int64_t launches = 0;
   bool counting = true;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;     // zb_bench_kernel
@@ -135,10 +136,15 @@ struct zb_ctx {
   CUtensorMap bt_map_xn{}, bt_map_y{}, bt_map_h{}, bt_map_heads{}, bt_map_yn{};   // yn: gated-norm output of a Mamba2 layer (hybrid)
   CUtensorMap bt_maps_xn{}, bt_maps_y{}, bt_maps_h{}, bt_maps_yn{};                // the same activations with a box of 128 / bt_cs rows (cluster multicast slices)
   int bt_cs = 1;                       // cluster size the slice maps were built for
+  CUtensorMap bt_map2_xn{}, bt_map2_y{}, bt_map2_h{}, bt_map2_yn{};                // ... with a box of 64 rows: the half of the N operand one CTA of a pair loads (k_bt_gemm2)
+  int opt_bt_cta2 = 1;                 // batched path, k_bt_gemm2 (CTA pairs, tcgen05.mma.cta_group::2, weights as the M operand): bit 0 = the
+                                       // split-K GEMMs (default: 1 817 -> 1 667 us per batch-64 step at short context), bit 1 = fc1
+                                       // (SwiGLU epilogue; measured slower than k_bt_gemm: 1 854, profiles/r02_bt_cta2_ab.txt)
   int opt_bt_cluster = 1;              // batched path: CTAs per cluster sharing (multicasting) the activation tile: 1, 2 or 4.  Measured
                                        // at batch 64: 1 837 / 1 891 / 2 060 us per step for 1 / 2 / 4 - the GEMMs are bound by what is delivered INTO the
                                        // SMs (weights + activation tile per CTA), which multicast does not reduce; off by default
   std::vector<CUtensorMap> bt_map_in, bt_map_out, bt_map_fc1, bt_map_fc2;
+  std::vector<CUtensorMap> bt_map_fc1p;                                             // fc1 as value / gate row pairs (k_bt_gemm2)
   // persistent decode kernel (mega_kernel.cuh)
   MegaLayer mega_l0{};
   long long mega_layer_stride = 0;
@@ -636,6 +642,20 @@ int bt_make_map(zb_ctx* c, CUtensorMap* m, const void* base, uint64_t inner, uin
   return ZB_OK;
 }
 
+// fc1 [2F][K] as {K, 16 rows, value | gate, F / 16 groups}: one box {64 k, 16, 2, 4} is a 128-row tile in which every 32-row
+// quarter is 16 value rows followed by the gate rows of the same ffn columns (k_bt_gemm2's SwiGLU epilogue)
+int bt_make_map_fc1_pairs(zb_ctx* c, CUtensorMap* m, const void* base, uint64_t K, uint64_t F) {
+  cuuint64_t dims[4] = {K, 16, 2, F / 16};
+  cuuint64_t strides[3] = {K * 2, F * K * 2, 16 * K * 2};
+  cuuint32_t box[4] = {BT_BK, 16, 2, 4};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = c->encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return c->err.fail(ZB_ERR_CUDA, "cuTensorMapEncodeTiled (fc1 pairs) failed: %d", (int)r);
+  return ZB_OK;
+}
+
 struct BtPlan { int n_tiles, splits, kb_per_split, num_kb; };
 BtPlan bt_plan(const zb_ctx* c, int n_tiles, int K) {
   BtPlan pl;
@@ -685,8 +705,12 @@ int bt_setup(zb_ctx* c, int rows_pad) {
   if ((rc = bt_make_map(c, &c->bt_map_h, c->h, F, rows_pad, BT_BM))) return rc;
   if (c->hybrid && c->n_mamba > 0 && (rc = bt_make_map(c, &c->bt_map_yn, c->m_ynorm, c->m_dinner, rows_pad, BT_BM))) return rc;
   if ((rc = bt_make_slices(c))) return rc;
+  if ((rc = bt_make_map(c, &c->bt_map2_xn, c->bt_xn, d, rows_pad, 64))) return rc;
+  if ((rc = bt_make_map(c, &c->bt_map2_y, c->y, q_size, rows_pad, 64))) return rc;
+  if ((rc = bt_make_map(c, &c->bt_map2_h, c->h, F, rows_pad, 64))) return rc;
+  if (c->hybrid && c->n_mamba > 0 && (rc = bt_make_map(c, &c->bt_map2_yn, c->m_ynorm, c->m_dinner, rows_pad, 64))) return rc;
   const int nl = g.n_layer;
-  c->bt_map_in.resize(nl); c->bt_map_out.resize(nl); c->bt_map_fc1.resize(nl); c->bt_map_fc2.resize(nl);
+  c->bt_map_in.resize(nl); c->bt_map_out.resize(nl); c->bt_map_fc1.resize(nl); c->bt_map_fc2.resize(nl); c->bt_map_fc1p.resize(nl);
   for (int l = 0; l < nl; ++l) {
     if (c->hybrid && c->is_mamba[l]) {                     // Mamba2 layer: in_proj [d_in_proj][d], out_proj [d][d_inner]
       const LayerM& m = c->mlayers[l];
@@ -699,6 +723,7 @@ int bt_setup(zb_ctx* c, int rows_pad) {
     if ((rc = bt_make_map(c, &c->bt_map_out[l], w.w_out, q_size, d, BT_BN))) return rc;
     if ((rc = bt_make_map(c, &c->bt_map_fc1[l], w.w_fc1, d, 2 * F, 64))) return rc;       // value box + gate box per tile
     if ((rc = bt_make_map(c, &c->bt_map_fc2[l], w.w_fc2, F, d, BT_BN))) return rc;
+    if ((rc = bt_make_map_fc1_pairs(c, &c->bt_map_fc1p[l], w.w_fc1, d, F))) return rc;
   }
   if ((rc = bt_make_map(c, &c->bt_map_heads, c->heads, d, (uint64_t)g.n_codebooks * g.vocab, BT_BN))) return rc;
   c->bt_ready = true;
@@ -719,6 +744,31 @@ cudaError_t bt_gemm(zb_ctx* c, const CUtensorMap& mx, const CUtensorMap& mw, int
   const int cs = c->bt_cs;
   const CUtensorMap* mxs = &mx == &c->bt_map_xn ? &c->bt_maps_xn : &mx == &c->bt_map_y ? &c->bt_maps_y : &mx == &c->bt_map_h ? &c->bt_maps_h : &c->bt_maps_yn;
   p.cs = cs;
+  if (c->opt_bt_cta2 & (mode == BT_MODE_SWIGLU ? 2 : 1)) {
+    const CUtensorMap* mxh = &mx == &c->bt_map_xn ? &c->bt_map2_xn : &mx == &c->bt_map_y ? &c->bt_map2_y : &mx == &c->bt_map_h ? &c->bt_map2_h : &c->bt_map2_yn;
+    p.cs = 2;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((n_tiles + 1) / 2 * 2, (Mrows + BT_BM - 1) / BT_BM, pl.splits);   // a padding CTA loads zero weight rows and stores nothing
+    cfg.blockDim = dim3(BT_THREADS);
+    cfg.dynamicSmemBytes = (size_t)BT2_SMEM_BYTES;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (c->opt_pdl) {
+      attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    ++na;
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    if (c->counting) c->launches += 1;
+    // fc1: the map that interleaves value and gate rows, found by the layer index of the map the caller passed
+    const CUtensorMap& mw2 = mode == BT_MODE_SWIGLU ? c->bt_map_fc1p[&mw - c->bt_map_fc1.data()] : mw;
+    return cudaLaunchKernelEx(&cfg, k_bt_gemm2, *mxh, mw2, p);
+  }
   const int gx = (n_tiles + cs - 1) / cs * cs;        // padding CTAs load out-of-range (zero) weight rows and store nothing
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(gx, (Mrows + BT_BM - 1) / BT_BM, pl.splits);
@@ -833,8 +883,8 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
       a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
       a.vrows = c->bt_vrows;
       // block prefill: one split per (token row, kv head) - no partial buffers or tickets (they are sized for the cache rows)
-      if (c->opt_attn_tma) {
-        if ((e = launch(c, attn_tma_kernel(H / Hkv, c->opt_attn_tma == 2), dim3(c->bt_vM ? 1 : c->nsplit, Hkv, rows), dim3(ATT_THREADS), ATT_TMA_SMEM, s, a)) != cudaSuccess) return e;
+      if (c->opt_attn_tma >= 2 || (c->opt_attn_tma == 1 && c->rows >= 64)) {
+        if ((e = launch(c, attn_tma_kernel(H / Hkv, c->opt_attn_tma == 3), dim3(c->bt_vM ? 1 : c->nsplit, Hkv, rows), dim3(ATT_THREADS), ATT_TMA_SMEM, s, a)) != cudaSuccess) return e;
       } else
       if ((e = launch(c, attn_kernel(H / Hkv, c->opt_attn_mma != 0), dim3(c->bt_vM ? 1 : c->nsplit, Hkv, rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
     }
@@ -1207,7 +1257,8 @@ static int ctx_create_impl(const zb_config* cfg, const zb_hybrid* hyb, int devic
     }
     c->qkv_ll = c->x_ll + w_x; c->y_ll = c->qkv_ll + w_qkv; c->h_ll = c->y_ll + w_y; c->att_ll = c->h_ll + w_h;
   }
-  if ((e = cudaFuncSetAttribute(k_bt_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM_BYTES)) != cudaSuccess) {
+  if ((e = cudaFuncSetAttribute(k_bt_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM_BYTES)) != cudaSuccess ||
+      (e = cudaFuncSetAttribute(k_bt_gemm2, cudaFuncAttributeMaxDynamicSharedMemorySize, BT2_SMEM_BYTES)) != cudaSuccess) {
     cudaFree(c->arena); delete c;
     return bad(ZB_ERR_CUDA, std::string("cudaFuncSetAttribute(bt): ") + cudaGetErrorString(e));
   }
@@ -1741,6 +1792,7 @@ int zb_set_option(zb_ctx* c, const char* key, int value) {
   else if (k == "bt_min_rows") c->opt_bt_min_rows = value;
   else if (k == "attn_mma") c->opt_attn_mma = value;
   else if (k == "attn_tma") c->opt_attn_tma = value;
+  else if (k == "bt_cta2") c->opt_bt_cta2 = value;
   else if (k == "nsplit") c->opt_nsplit = value;
   else return c->err.fail(ZB_ERR_ARG, "unknown option '%s'", key);
   drop_graph(c);
