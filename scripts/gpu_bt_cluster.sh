@@ -1,7 +1,8 @@
 #!/bin/bash
-# Batched tcgen05 path: activation tile multicast across a cluster of 1 / 2 / 4 CTAs; parity subset first (under a timeout).
+# fc1 (the one GEMM left on k_bt_gemm) with the activation tile multicast across clusters of 2 / 4 / 8 CTAs; batch 64, short context
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_parity.py -q -m gpu -x -k "batched or other_paths or long_context or audio_prefix or hybrid or plugin" 2>&1 | tail -4
-for cs in 1 2 4; do
-  timeout 200 python scripts/profile_decode.py --frames 48 --runs 2 --batch 64 --prefix-len 24 --opt bt_cluster=$cs 2>&1 | tail -1
-done | tee gpurun_out/bt_cluster_ab.log
+{
+for o in "bt_cluster=1" "bt_cluster=2" "bt_cluster=4" "bt_cluster=8" "bt_cluster=1"; do
+  echo "== $o"; timeout -s KILL 300 python scripts/profile_decode.py --batch 64 --frames 48 --runs 2 --prefix-len 24 --opt $o 2>&1 | tail -1
+done
+} | tee gpurun_out/bt_cluster8_ab.txt
