@@ -328,6 +328,23 @@ def test_batch_is_independent_batch1_runs(golden, cuda):
 
 
 
+@pytest.mark.parametrize("nb", [3, 6])
+def test_batch_block_prefill_several_row_tiles(golden, cuda, nb):
+    """Prefill of a batch: nb utterances x 40 conditioning tokens = 240 / 480 activation rows per block = two / four 128-row tiles
+    per weight tile (k_bt_gemm / k_bt_gemm2 grid.y > 1, causal attention over 40 positions of 2 nb cache rows).  The prefill logits
+    (step 0) and 8 teacher-forced steps of every utterance must be those of its own batch-1 run (one row tile)."""
+    m = make_model("small", cuda)
+    cfg = zo.SMALL_CONFIG
+    ps = [zo.synth_prefix_conditioning(cfg, 1, 40, 20 + i) for i in range(nb)]
+    delayed1 = golden["gen.small.greedy.delayed"]
+    singles = [m.compute_logits_teacher_forced(x, delayed1, 8) for x in ps]
+    batch_prefix = torch.cat([torch.cat([x[:1] for x in ps]), torch.cat([x[1:] for x in ps])])
+    got = m.compute_logits_teacher_forced(batch_prefix, delayed1.expand(nb, -1, -1).contiguous(), 8)
+    for i in range(nb):
+        for s in range(9):
+            assert_logits_close(got[s, i:i + 1], singles[i][s], f"utterance {i} step {s}")
+
+
 # ------------------------------------------------------------------------------------------------ long context / full size
 # The benched workload runs to ctx 2 613; these fixtures (oracle/make_golden_long.py, frozen from the imported reference)
 # put the comparison where the persistent kernel splits the KV range over 14-16 CTAs per (row, kv head), merges the

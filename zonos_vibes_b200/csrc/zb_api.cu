@@ -1355,7 +1355,14 @@ int zb_kv_alloc(zb_ctx* c, int rows, int max_seqlen) {
   if (c->opt_nsplit > 0) ns = c->opt_nsplit > 32 ? 32 : c->opt_nsplit;
   c->nsplit = ns;
   const int G = g.num_heads / g.num_heads_kv;
-  const int rows_pad = (rows + 127) / 128 * 128;       // activation matrices are TMA operands of 128-row tiles (bt path)
+  int rows_pad = (rows + 127) / 128 * 128;             // activation matrices are TMA operands of 128-row tiles (bt path)
+  if (!c->hybrid) {
+    // block prefill (bt_prefill) turns rows_pad / rows token positions into one pass over the weights: room for 64 positions,
+    // at most 1 024 activation rows (8 M tiles per weight tile; batch 64: 8 positions per pass instead of 1)
+    int want = rows * 64 > 1024 ? 1024 : rows * 64;
+    want = (want + 127) / 128 * 128;
+    if (want > rows_pad) rows_pad = want;
+  }
 #define ZB_ALLOC(ptr, bytes) ZB_CUDA(c->err, cudaMalloc((void**)&(ptr), (bytes)))
   const size_t n_kv_layers = c->n_attn > 0 ? c->n_attn : 1;
   ZB_ALLOC(c->kv, c->kv_layer_elems * n_kv_layers * sizeof(bf16));
