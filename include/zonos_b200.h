@@ -226,7 +226,18 @@ int  zb_pc_layernorm(const void* d_in, const void* d_w, const void* d_b, float e
 /* ---- introspection used by bench.py (launch counting, roofline byte counts) ------------------- */
 int64_t zb_weight_bytes(const zb_ctx* ctx);            /* algorithmic weight bytes streamed per decode step */
 int64_t zb_launch_count(const zb_ctx* ctx);            /* kernels launched by this context so far (graph nodes count per replay) */
-int  zb_set_option(zb_ctx* ctx, const char* key, int value);   /* "pdl", "l2_prefetch", "graph": tuning switches */
+/* Tuning / cross-check switches (defaults in parentheses; every combination is parity-tested in tests/test_gpu_parity.py):
+ *   which path:   "mega" (1) persistent kernel for <= 8 rows; "bt_min_rows" (9) batched tcgen05 path from this many rows;
+ *                 "graph" (1) one CUDA graph per step on the per-op / batched paths; "gemv" (1) mma.sync GEMVs on the per-op path;
+ *                 "bt_prefill" (1) prefill as blocks of rows on the batched path; "chunked_prefill" (1) hybrid chunked SSD scan
+ *   persistent:   "ll" (3) which activations travel as epoch-tagged words (0 = grid barriers ... 3 = all); "chain" (0);
+ *                 "att_chunk", "att_single", "ring", "psleep", "evict", "l2_prefetch", "pdl" (1)
+ *   batched:      "bt_cta2" (1) bit 0: split-K GEMMs on CTA pairs (k_bt_gemm2), bit 1: fc1 too; "bt_cluster" (1) 2 / 4 = activation
+ *                 tile multicast across a cluster (k_bt_gemm); "attn_tma" (1) 0 = ld.global attention, 1 = TMA-staged K/V from 64 rows,
+ *                 2 = always, 3 = always with early slot release; "attn_mma" (1) 0 = SIMT attention; "nsplit" (0 = auto) KV splits
+ *   debug:        "trace", "trace_quiet" (see zb_last_trace)
+ * Unknown keys return ZB_ERR_ARG. */
+int  zb_set_option(zb_ctx* ctx, const char* key, int value);
 /* isolated device timing of one kernel family ("in_proj", "attn", "out_proj", "fc1", "fc2"), `iters` launches cycling
  * over the layers, CUDA events on `stream`; total ms in *ms_out (synchronises).  Scratch outputs only. */
 int  zb_bench_kernel(zb_ctx* ctx, const char* name, int iters, float* ms_out, void* stream);
