@@ -657,10 +657,12 @@ int bt_make_map_fc1_pairs(zb_ctx* c, CUtensorMap* m, const void* base, uint64_t 
 }
 
 struct BtPlan { int n_tiles, splits, kb_per_split, num_kb; };
-BtPlan bt_plan(const zb_ctx* c, int n_tiles, int K) {
+// split K only as far as the weight tiles x activation-row tiles leave SMs idle (a prefill block of 1 024 rows has 8 row tiles:
+// no split, no partial traffic; a decode step has one)
+BtPlan bt_plan(const zb_ctx* c, int n_tiles, int K, int m_tiles) {
   BtPlan pl;
   pl.n_tiles = n_tiles; pl.num_kb = K / BT_BK;
-  int s = c->n_sms / n_tiles;
+  int s = c->n_sms / (n_tiles * m_tiles);
   if (s < 1) s = 1;
   int max_s = pl.num_kb / 4;                       // at least 4 k-blocks (32 KB of weights) per CTA
   if (max_s < 1) max_s = 1;
@@ -732,11 +734,11 @@ int bt_setup(zb_ctx* c, int rows_pad) {
 
 cudaError_t bt_gemm(zb_ctx* c, const CUtensorMap& mx, const CUtensorMap& mw, int N, int K, int mode, int* splits_out, cudaStream_t s) {
   const int n_tiles = mode == BT_MODE_SWIGLU ? (N + 63) / 64 : (N + BT_BN - 1) / BT_BN;
-  BtPlan pl = bt_plan(c, n_tiles, K);
+  const int Mrows = c->bt_vM ? c->bt_vM : c->rows;
+  BtPlan pl = bt_plan(c, n_tiles, K, (Mrows + BT_BM - 1) / BT_BM);
   if (mode == BT_MODE_SWIGLU) { pl.splits = 1; pl.kb_per_split = pl.num_kb; }
   BtGemmParams p;
   memset(&p, 0, sizeof(p));
-  const int Mrows = c->bt_vM ? c->bt_vM : c->rows;
   p.M = Mrows; p.N = N; p.num_kb = pl.num_kb; p.kb_per_split = pl.kb_per_split; p.mode = mode;
   p.partial = c->bt_partial; p.m_pad = c->bt_mpad; p.h = c->h; p.st = c->st;
   if (splits_out) *splits_out = pl.splits;
