@@ -577,6 +577,33 @@ def test_batched_tcgen05_equals_independent_runs(golden, cuda, attn):
         for s in range(13):
             assert_logits_close(got[s, i:i + 1], singles[i][s], f"utterance {i} step {s}")
 
+# ------------------------------------------------------------------------------------------------ GQA group sizes
+# The fixtures cover G = num_heads / num_heads_kv = 2 (tiny, small) and 4 (full size).  The attention kernels are also instantiated for
+# G = 1 (no grouping) and G = 8 (the most query heads one kv head can feed through the n8 dimension of the PV product): those
+# instantiations are checked here against the oracle evaluated on the spot (two small layers: seconds on the CPU).
+GQA_CONFIGS = {"G1": zo.OracleConfig(d_model=256, n_layer=2, num_heads=2, num_heads_kv=2, attn_mlp_d_intermediate=512),
+               "G8": zo.OracleConfig(d_model=1024, n_layer=2, num_heads=8, num_heads_kv=1, attn_mlp_d_intermediate=1024)}
+GQA_PATHS = {"persistent": {}, "per_op_graph": dict(mega=0), "batched_tcgen05_tma_attn": dict(mega=0, bt_min_rows=2, attn_tma=2),
+             "batched_tcgen05_ldg_attn": dict(mega=0, bt_min_rows=2, attn_tma=0)}
+
+
+@pytest.mark.parametrize("gname", list(GQA_CONFIGS))
+def test_gqa_group_sizes_1_and_8_against_oracle(cuda, gname):
+    import zonos_vibes_b200 as z
+    cfg = GQA_CONFIGS[gname]
+    sd = zo.synth_state_dict(cfg, 3)
+    prefix = zo.synth_prefix_conditioning(cfg, 1, 70, 2)          # 71 + 12 tokens of context: two KV stages of 64 tokens, a partial one
+    codes = torch.randint(0, 1024, (1, 9, 24), generator=torch.Generator().manual_seed(5))
+    delayed = zo.apply_delay_pattern(codes, cfg.masked_token_id)
+    want = zo.OracleZonos(cfg, sd).teacher_forced_logits(prefix, delayed, 12)
+    m = z.Zonos.from_state_dict(z.ZonosConfig.from_dict(cfg.to_reference_dict()), sd, cuda)
+    for path, opts in GQA_PATHS.items():
+        with _options(m, **opts):
+            got = m.compute_logits_teacher_forced(prefix, delayed, 12)
+        for s in range(13):
+            assert_logits_close(got[s], want[s:s + 1], f"{gname} {path} step {s}")
+
+
 # ------------------------------------------------------------------------------------------------ plugin boundary
 @pytest.mark.parametrize("cname", ["tiny", "small"])
 def test_backbone_plugin_forward(golden, cuda, cname):
