@@ -99,6 +99,18 @@ def load() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
+    override = os.environ.get("ZB_LIB")
+    if override:
+        # a library built some other way (scripts/build_checked.sh: the -DZB_BOUNDS build with index assertions); same ABI checks
+        lib = C.CDLL(override)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        if lib.zb_abi_version() != 1:
+            raise ZbError(f"{override}: ABI version mismatch")
+        _lib = lib
+        return lib
     from . import build as _build
     if _build._stale():
         # missing, or built from other sources than the ones next to it (content hash, build.py): rebuild when nvcc is

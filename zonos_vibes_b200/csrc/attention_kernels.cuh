@@ -25,6 +25,7 @@ struct AttnParams {
   int* counters;            // [rows][Hkv], zero before launch; reset by the merging CTA
   const ZbDevState* st;
   float scale_log2;         // (1/sqrt(Dh)) * log2(e)
+  int total_pages;          // pages of one layer's cache (checked build: bound of every page-table entry)
   int vrows;                // 0: row = cache row, ctx = pos + 1.  > 0 (block prefill): activation row a is token a / vrows of cache
                             // row a % vrows and attends positions [0, pos + a / vrows] - causal attention over the block
 };
@@ -208,7 +209,9 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode(const AttnParams p)
       kr[i] = make_uint4(0, 0, 0, 0);
       vr[i] = make_uint4(0, 0, 0, 0);
       if (vl[i]) {
+        ZB_ASSERT(t / ZB_PAGE < p.max_pages);
         const int page = pt[t / ZB_PAGE];
+        ZB_ASSERT(page >= 0 && page < p.total_pages);
         const bf16* kp = p.kv_layer + (size_t)page * page_stride + (size_t)kvh * head_stride + (size_t)(t % ZB_PAGE) * ZB_DH + l16 * 8;
         kr[i] = ldg_stream(kp);
         vr[i] = ldg_stream(kp + kv_stride);
@@ -365,7 +368,9 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode_mma(const AttnParam
   const size_t kv_stride = (size_t)p.Hkv * head_stride;
   const size_t page_stride = 2 * kv_stride;
   auto load_group = [&](int tb, AttFrag& f) {
+    ZB_ASSERT(tb / ZB_PAGE < p.max_pages);
     const int page = pt[tb / ZB_PAGE];
+    ZB_ASSERT(page >= 0 && page < p.total_pages);
     const bf16* kbase = p.kv_layer + (size_t)page * page_stride + (size_t)kvh * head_stride + (size_t)(tb % ZB_PAGE) * ZB_DH;
     const uint4 z = make_uint4(0, 0, 0, 0);
 #pragma unroll
@@ -473,6 +478,8 @@ __global__ void __launch_bounds__(ATT_THREADS) k_attn_decode_tma(const AttnParam
     for (int run = 0; run < 2; ++run) {
       const int tb = run == 0 ? ts : ts + n1, nn = run == 0 ? n1 : n - n1;
       if (nn <= 0) continue;
+      ZB_ASSERT(tb / ZB_PAGE < p.max_pages && pt[tb / ZB_PAGE] >= 0 && pt[tb / ZB_PAGE] < p.total_pages);
+      ZB_ASSERT(tb % ZB_PAGE + nn <= ZB_PAGE && (tb - ts) + nn <= ATT_TMA_TOK && slot < ATT_TMA_STAGES);
       const bf16* src = p.kv_layer + (size_t)pt[tb / ZB_PAGE] * page_stride + (size_t)kvh * head_stride + (size_t)(tb % ZB_PAGE) * ZB_DH;
       const uint32_t off = (uint32_t)(tb - ts) * ZB_DH * 2;
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst + off), "l"(src),

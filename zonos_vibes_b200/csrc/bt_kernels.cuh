@@ -44,6 +44,7 @@ struct BtGemmParams {
   int m_pad;
   bf16* h;               // SWIGLU: [rows][F] bf16
   const ZbDevState* st;  // done flag
+  size_t partial_elems;  // floats allocated behind `partial` (checked build)
 };
 
 __device__ __forceinline__ void bt_tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint16_t mask) {
@@ -199,6 +200,8 @@ __global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm(const __grid_constant
       }
     } else {
       float* dst_row = p.partial + ((size_t)split * p.m_pad + m) * p.N + (size_t)n_tile * BT_BN;
+      ZB_ASSERT(!valid || ((size_t)split * p.m_pad + m) * p.N + min(p.N, (n_tile + 1) * BT_BN) <= p.partial_elems);
+      ZB_ASSERT(m < p.m_pad || !valid);
       for (int c0 = 0; c0 < BT_BN; c0 += 32) {
         uint32_t v[32];
         if (nkb > 0) {
@@ -397,6 +400,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm2(const __grid_constan
           const float y = bf16_round(__uint_as_float(gate_lane ? got : v[e]));
           const float gt = bf16_round(__uint_as_float(gate_lane ? v[e + 1] : got));
           const float sg = bf16_round(gt / (1.0f + expf(-gt)));
+          ZB_ASSERT((size_t)(c0 + e + 1) * BT2_HROW + jc * 2 + 2 <= (size_t)BT2_STAGE_BYTES);
           *reinterpret_cast<bf16*>(s_h + (size_t)(c0 + e + (gate_lane ? 1 : 0)) * BT2_HROW + jc * 2) = __float2bfloat16_rn(y * sg);
         }
       }
@@ -423,6 +427,8 @@ __global__ void __launch_bounds__(BT_THREADS, 1) k_bt_gemm2(const __grid_constan
           for (int e = 0; e < 32; ++e) v[e] = 0u;
         }
         float* dst = p.partial + ((size_t)split * p.m_pad + m0 + c0) * p.N + n;
+        ZB_ASSERT(n >= p.N || m0 + c0 >= p.M || ((size_t)split * p.m_pad + min(p.M, m0 + c0 + 32) - 1) * p.N + n < p.partial_elems);
+        ZB_ASSERT(p.M <= p.m_pad);
 #pragma unroll
         for (int e = 0; e < 32; ++e)
           if (m0 + c0 + e < p.M && n < p.N) dst[(size_t)e * p.N] = __uint_as_float(v[e]);
@@ -460,6 +466,7 @@ struct BtFinishParams {
   int n_q, V, eos, B;
   const ZbDevState* st;
   int vrows;                 // > 0 (block prefill): activation row a = token a / vrows of cache row a % vrows, position pos + a / vrows
+  int total_pages;           // pages of one layer's cache (checked build)
 };
 
 __device__ __forceinline__ float bt_split_sum(const float* partial, int splits, size_t split_stride, size_t off) {
@@ -550,7 +557,9 @@ __global__ void __launch_bounds__(256) k_bt_qkv_finish(const BtFinishParams p) {
   const int crow = p.vrows ? row % p.vrows : row, tok = p.vrows ? row / p.vrows : 0;
   const int pos = p.st->pos + tok;
   const size_t split_stride = (size_t)p.m_pad * p.N;
+  ZB_ASSERT(pos >= 0 && pos / ZB_PAGE < p.max_pages && row < p.m_pad);
   const int page = p.page_table[(size_t)crow * p.max_pages + pos / ZB_PAGE];
+  ZB_ASSERT(page >= 0 && page < p.total_pages);
   const float* cs_row = p.rope + (size_t)(p.rope_pos[crow] + tok) * (ZB_DH / 2) * 2;
   for (int n8 = blockIdx.y * 2048 + threadIdx.x * 8; n8 < p.N; n8 += 2048 * gridDim.y) {     // grid.y = ceil(N / 2048): one trip per thread
     float a[8];

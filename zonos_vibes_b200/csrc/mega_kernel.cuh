@@ -388,6 +388,8 @@ __device__ __forceinline__ bool mg_sched_next(MgSched& s, const MegaParams& p, M
           int page = __shfl_sync(0xffffffffu, s.my_page, (tb / ZB_PAGE) & 31);
           if (lane < 4 && nn > 0) {
             if (p.max_pages > 32) page = p.page_table[(size_t)it.row * p.max_pages + tb / ZB_PAGE];
+            ZB_ASSERT(tb / ZB_PAGE < p.max_pages && page >= 0 && (size_t)(page + 1) * 2 * p.Hkv * ZB_PAGE * ZB_DH <= (size_t)p.kv_layer_elems);
+            ZB_ASSERT(tb % ZB_PAGE + nn <= ZB_PAGE && (tb - ts) + nn <= MG_KV_TOK);
             const size_t head_stride = (size_t)ZB_PAGE * ZB_DH;
             const size_t kv_stride = (size_t)p.Hkv * head_stride;
             d.src = p.kv + (size_t)s.l * p.kv_layer_elems + (size_t)page * 2 * kv_stride + (size_t)it.kvh * head_stride +
@@ -1289,6 +1291,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         if (prof && p.dbg_fine == 1 && lane == 0 && d.tag == ((uint32_t)(p.dbg_kind == EPI_QKV ? MG_PH_QKV : p.dbg_kind == EPI_RESID ? MG_PH_OUT : MG_PH_FC1) | (1u << 8) | ((uint32_t)p.dbg_step << 16)) && n_fine < 32)
           p.dbg[(size_t)blockIdx.x * MG_TRACE_SLOTS + 32 + n_fine++] = mg_globaltimer();     // issue time of this fc1 stage
         if (d.src != nullptr) {
+          ZB_ASSERT(cx.stage >= 0 && cx.stage < p.n_stages && d.dst_off + d.bytes <= MG_STAGE_BYTES && (d.bytes & 15) == 0);
           const uint32_t dst = mg_smem_u32(cx.ring + (size_t)cx.stage * MG_STAGE_BYTES + d.dst_off);
           if (d.tag != 0 && p.stream_evict_first) mg_bulk_g2s_hint(dst, d.src, d.bytes, cx.full0 + 8u * cx.stage, pol_stream);   // weight tiles
           else mg_bulk_g2s(dst, d.src, d.bytes, cx.full0 + 8u * cx.stage);
@@ -1410,6 +1413,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
         const int r = tid / (MG_ROPE_BYTES / 16), c = tid % (MG_ROPE_BYTES / 16);
         *reinterpret_cast<uint4*>(cx.s_rope + r * ZB_DH + c * 4) = mg_lds128(sp + r * MG_ROW_BYTES + c * 16);
       }
+      ZB_ASSERT(pos >= 0 && pos / ZB_PAGE < p.max_pages);
       if (tid < p.R) cx.s_page[tid] = p.page_table[tid * p.max_pages + pos / ZB_PAGE];
       mg_cons_release(cx);
     }

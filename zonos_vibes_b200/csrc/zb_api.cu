@@ -128,6 +128,7 @@ struct zb_ctx {
   int opt_bt_prefill = 1;              // transformer: prefill blocks of tokens as extra rows of the batched tcgen05 path
   bf16* pf_embed = nullptr;            // block prefill of an audio prefix: embedded prefix columns [rows][P][d]
   size_t pf_embed_elems = 0;
+  size_t bt_partial_elems = 0;         // floats behind bt_partial
   int bt_vM = 0, bt_vrows = 0;         // block prefill in progress: bt_vM activation rows = tokens x bt_vrows cache rows
   bool bt_ready = false;
   int bt_mpad = 0;
@@ -386,7 +387,7 @@ cudaError_t enqueue_attn_layer(zb_ctx* c, int l, const std::vector<Pass>& passes
       memset(&a, 0, sizeof(a));
       a.q = c->q; a.kv_layer = kv_layer; a.page_table = c->page_table; a.max_pages = c->max_pages;
       a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
-      a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
+      a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f; a.total_pages = c->rows * c->max_pages;
       if ((e = launch(c, attn_kernel(H / Hkv, c->opt_attn_mma != 0), dim3(c->nsplit, Hkv, c->rows), dim3(ATT_THREADS), 0, s, a)) != cudaSuccess) return e;
     }
     for (const Pass& ps : passes) {   // out_proj + residual
@@ -700,7 +701,8 @@ int bt_setup(zb_ctx* c, int rows_pad) {
   if (c->hybrid && c->m_dinproj > maxN) maxN = c->m_dinproj;
   ZB_CUDA(c->err, cudaMalloc((void**)&c->bt_xn, (size_t)rows_pad * d * 2));
   ZB_CUDA(c->err, cudaMemset(c->bt_xn, 0, (size_t)rows_pad * d * 2));
-  ZB_CUDA(c->err, cudaMalloc((void**)&c->bt_partial, (size_t)8 * rows_pad * maxN * 4));
+  c->bt_partial_elems = (size_t)8 * rows_pad * maxN;
+  ZB_CUDA(c->err, cudaMalloc((void**)&c->bt_partial, c->bt_partial_elems * 4));
   int rc;
   if ((rc = bt_make_map(c, &c->bt_map_xn, c->bt_xn, d, rows_pad, BT_BM))) return rc;
   if ((rc = bt_make_map(c, &c->bt_map_y, c->y, q_size, rows_pad, BT_BM))) return rc;
@@ -740,7 +742,7 @@ cudaError_t bt_gemm(zb_ctx* c, const CUtensorMap& mx, const CUtensorMap& mw, int
   BtGemmParams p;
   memset(&p, 0, sizeof(p));
   p.M = Mrows; p.N = N; p.num_kb = pl.num_kb; p.kb_per_split = pl.kb_per_split; p.mode = mode;
-  p.partial = c->bt_partial; p.m_pad = c->bt_mpad; p.h = c->h; p.st = c->st;
+  p.partial = c->bt_partial; p.m_pad = c->bt_mpad; p.h = c->h; p.st = c->st; p.partial_elems = c->bt_partial_elems;
   if (splits_out) *splits_out = pl.splits;
   // the activation tile is shared by the CTAs of a cluster (multicast): the slice map that goes with the full-tile map
   const int cs = c->bt_cs;
@@ -804,7 +806,7 @@ BtFinishParams bt_finish_params(zb_ctx* c, int splits, int N) {
   f.q = c->q; f.page_table = c->page_table; f.max_pages = c->max_pages; f.Hkv = g.num_heads_kv;
   f.q_size = g.num_heads * ZB_DH; f.kv_size = g.num_heads_kv * ZB_DH; f.rope = c->rope; f.rope_pos = c->rope_pos;
   f.logits = c->logits; f.n_q = g.n_codebooks; f.V = g.vocab; f.eos = g.eos_token_id; f.B = c->rows / 2; f.st = c->st;
-  f.vrows = c->bt_vrows;
+  f.vrows = c->bt_vrows; f.total_pages = c->rows * c->max_pages;
   return f;
 }
 
@@ -882,7 +884,7 @@ cudaError_t enqueue_bt_layers(zb_ctx* c, cudaStream_t s) {
       memset(&a, 0, sizeof(a));
       a.q = c->q; a.kv_layer = kv_layer; a.page_table = c->page_table; a.max_pages = c->max_pages;
       a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
-      a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
+      a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f; a.total_pages = c->rows * c->max_pages;
       a.vrows = c->bt_vrows;
       // block prefill: one split per (token row, kv head) - no partial buffers or tickets (they are sized for the cache rows)
       if (c->opt_attn_tma >= 2 || (c->opt_attn_tma == 1 && c->rows >= 64)) {
@@ -1858,7 +1860,7 @@ int zb_bench_kernel(zb_ctx* c, const char* name, int iters, float* ms_out, void*
       memset(&a, 0, sizeof(a));
       a.q = c->q; a.kv_layer = c->kv + (size_t)l * c->kv_layer_elems; a.page_table = c->page_table; a.max_pages = c->max_pages;
       a.H = H; a.Hkv = Hkv; a.y = c->y; a.part_o = c->part_o; a.part_ml = c->part_ml; a.counters = c->counters;
-      a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f;
+      a.st = c->st; a.scale_log2 = (1.0f / sqrtf((float)ZB_DH)) * 1.4426950408889634f; a.total_pages = c->rows * c->max_pages;
       e = launch(c, attn_kernel(H / Hkv, c->opt_attn_mma != 0), dim3(c->nsplit, Hkv, c->rows), dim3(ATT_THREADS), 0, s, a);
     } else {
       c->counting = counting;

@@ -34,6 +34,21 @@ struct ZbErr {
 // ---------------------------------------------------------------------------------------------
 // device helpers
 // ---------------------------------------------------------------------------------------------
+// Checked build (-DZB_BOUNDS, scripts/build_checked.sh -> libzonos_b200_checked.so, loaded with ZB_LIB=...): index and capacity
+// assertions at the address computations of the kernels; a violation prints where and traps (the launch fails, the test fails).
+// compute-sanitizer is closed on the GPU pool this was developed on; this is the substitute.  The production build has none of it.
+#ifdef ZB_BOUNDS
+#define ZB_ASSERT(c)                                                                                                              \
+  do {                                                                                                                            \
+    if (!(c)) {                                                                                                                   \
+      printf("ZB_ASSERT failed: %s  (%s:%d, block %d,%d,%d thread %d)\n", #c, __FILE__, __LINE__, (int)blockIdx.x, (int)blockIdx.y, \
+             (int)blockIdx.z, (int)threadIdx.x);                                                                                  \
+      __trap();                                                                                                                   \
+    }                                                                                                                             \
+  } while (0)
+#else
+#define ZB_ASSERT(c) do { } while (0)
+#endif
 __device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 
 // two packed bf16 (little end = element 0) -> fp32; bf16->fp32 is a 16-bit shift.
