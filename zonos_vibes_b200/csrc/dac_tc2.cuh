@@ -202,6 +202,10 @@ __global__ void __launch_bounds__(64 + 32 * EW, 1) k_dac_conv_tc2(const __grid_c
       const int orA = __shfl_sync(0xffffffffu, out_row, lane & ~1), orB = __shfl_sync(0xffffffffu, out_row, lane | 1);
       const size_t ubase = (size_t)ub * p.T_out;
       const size_t rowA = (ubase + (size_t)(vA ? orA : 0)) * p.Cout + n0, rowB = (ubase + (size_t)(vB ? orB : 0)) * p.Cout + n0;
+      ZB_ASSERT(ub >= 0 && ub < p.nb && n0 >= 0 && n0 < p.n_tiles * p.n_tile);
+      ZB_ASSERT(!vA || (orA >= 0 && orA < p.T_out));
+      ZB_ASSERT(!vB || (orB >= 0 && orB < p.T_out));
+      ZB_ASSERT((as * p.mt + acc + 1) * p.acc_cols <= 512);
       // the warp's residual rows of the whole tile are requested before the accumulator wait
       uint4 res[NCH][4];
       if (p.residual) {

@@ -340,6 +340,7 @@ __global__ void k_embed(const bf16* __restrict__ emb /*[n_q][vocab_rows][d]*/, c
     for (int k = 0; k < n_q; ++k) {
       long long id = delayed[((size_t)b * n_q + k) * L + col];
       id = id < 0 ? 0 : (id >= emb_rows ? emb_rows - 1 : id);
+      ZB_ASSERT(id >= 0 && id < emb_rows);
       const uint4 raw = *reinterpret_cast<const uint4*>(emb + ((size_t)k * emb_rows + id) * d + e);
       const float v[8] = {bf16lo(raw.x), bf16hi(raw.x), bf16lo(raw.y), bf16hi(raw.y), bf16lo(raw.z), bf16hi(raw.z), bf16lo(raw.w), bf16hi(raw.w)};
 #pragma unroll
@@ -363,6 +364,7 @@ __global__ void k_embed_cols(const bf16* __restrict__ emb, const long long* __re
     for (int k = 0; k < n_q; ++k) {
       long long id = delayed[((size_t)b * n_q + k) * L + j];
       id = id < 0 ? 0 : (id >= emb_rows ? emb_rows - 1 : id);
+      ZB_ASSERT(id >= 0 && id < emb_rows);
       const uint4 raw = *reinterpret_cast<const uint4*>(emb + ((size_t)k * emb_rows + id) * d + e);
       const float v[8] = {bf16lo(raw.x), bf16hi(raw.x), bf16lo(raw.y), bf16hi(raw.y), bf16lo(raw.z), bf16hi(raw.z), bf16lo(raw.w), bf16hi(raw.w)};
 #pragma unroll

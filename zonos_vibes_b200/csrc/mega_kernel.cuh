@@ -1192,6 +1192,7 @@ __device__ __noinline__ void mg_embed_row(const MegaParams& p, int b, int col, i
         const int k = k0 + u;
         const int id = __shfl_sync(0xffffffffu, myid, k & 31);
         raw[u] = make_uint4(0, 0, 0, 0);
+        ZB_ASSERT(k >= p.n_q || (id >= 0 && id < p.V));
         if (k < p.n_q) raw[u] = *reinterpret_cast<const uint4*>(p.emb + ((size_t)k * p.V + id) * d + e);
       }
 #pragma unroll
@@ -1518,6 +1519,7 @@ __global__ void __launch_bounds__(MG_THREADS, 1) k_decode_mega(const __grid_cons
             // hint: pull the embedding row of the sampled token into L2 now; CTA 0 gathers it after the write-back
             long long id = p.tokens[blockIdx.x];
             id = id < 0 ? 0 : (id >= p.V ? p.V - 1 : id);
+            ZB_ASSERT(id >= 0 && id < p.V);
             const bf16* rowp = p.emb + ((size_t)(blockIdx.x % p.n_q) * p.V + id) * p.d;
             asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(rowp), "r"(p.d * 2) : "memory");
           }
