@@ -278,6 +278,20 @@ def test_library_staleness_is_by_content(tmp_path, monkeypatch):
     assert not build._stale()
 
 
+def test_library_override_by_environment(monkeypatch):
+    """ZB_LIB names another build of the library (scripts/build_checked.sh); it goes through the same symbol / ABI checks."""
+    from zonos_vibes_b200 import _lib
+    prod = _lib.load()
+    monkeypatch.setenv("ZB_LIB", _lib.LIB_PATH)
+    monkeypatch.setattr(_lib, "_lib", None)
+    other = _lib.load()
+    assert other is not prod and other.zb_abi_version() == 1
+    monkeypatch.setenv("ZB_LIB", "/nonexistent/libzonos_b200_checked.so")
+    monkeypatch.setattr(_lib, "_lib", None)
+    with pytest.raises(OSError):
+        _lib.load()
+
+
 def test_serving_shell_batches_and_wav_container():
     """Row f2 host side: the batching engine groups compatible requests (same conditioning length and sampling parameters) into
     one generate call of at most max_batch utterances, keeps arrival order, and resolves every future; the WAV container is
